@@ -1,0 +1,105 @@
+// Shared device helpers for the delay-spectrum Gibbs sampler (sm_100a).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace dg {
+
+constexpr int TILE = 128;     // block-column width and row-tile height of the factorisation
+constexpr int KC = 16;        // K chunk staged per pipeline stage
+constexpr int THREADS = 256;  // 8 warps per CTA, one CTA per SM
+constexpr int NWARP = THREADS / 32;
+constexpr int LDA_NT = KC + 4;    // smem row pitch (doubles) of a [rows][KC] tile: conflict-free fragments
+constexpr int LDB_NN = TILE + 4;  // smem row pitch of a [KC][TILE] tile
+constexpr int LDW = TILE + 4;     // smem row pitch of a full 128x128 tile
+
+// ---------------------------------------------------------------- fp64 tensor pipe
+// D(8x8) += A(8x4) * B(4x8).  Lane l: g = l>>2, q = l&3.
+//   a = A[g][q]   b = B[q][g]   c0 = C[g][2q]  c1 = C[g][2q+1]
+__device__ __forceinline__ void dmma(double& c0, double& c1, double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+               : "+d"(c0), "+d"(c1)
+               : "d"(a), "d"(b));
+}
+
+// ---------------------------------------------------------------- async copies
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src) {
+  unsigned s = (unsigned)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
+// ---------------------------------------------------------------- Philox4x32-10
+struct Philox {
+  uint32_t k0, k1;
+  __device__ __forceinline__ Philox(uint64_t key) : k0((uint32_t)key), k1((uint32_t)(key >> 32)) {}
+  __device__ __forceinline__ uint4 operator()(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3) const {
+    uint32_t a = k0, b = k1;
+#pragma unroll
+    for (int r = 0; r < 10; r++) {
+      uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+      uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+      uint32_t n0 = hi1 ^ c1 ^ a, n1 = lo1, n2 = hi0 ^ c3 ^ b, n3 = lo0;
+      c0 = n0; c1 = n1; c2 = n2; c3 = n3;
+      a += 0x9E3779B9u; b += 0xBB67AE85u;
+    }
+    return make_uint4(c0, c1, c2, c3);
+  }
+};
+
+// uniform in (0, 1], 53 bits
+__device__ __forceinline__ double u01(uint32_t lo, uint32_t hi) {
+  uint64_t v = ((uint64_t)hi << 32) | lo;
+  return ((double)(v >> 11) + 1.0) * (1.0 / 9007199254740992.0);
+}
+
+// Two independent standard normals from one Philox block (Box-Muller, fp64).
+__device__ __forceinline__ void normal_pair(const uint4& r, double& z0, double& z1) {
+  double u1 = u01(r.x, r.y), u2 = u01(r.z, r.w);
+  double rad = sqrt(-2.0 * log(u1));
+  double s, c;
+  sincospi(2.0 * u2, &s, &c);
+  z0 = rad * c;
+  z1 = rad * s;
+}
+
+// RNG stream ids inside one (baseline, iteration)
+enum { STREAM_W1 = 0, STREAM_W2 = 1, STREAM_CHI2 = 2 };
+
+__device__ __forceinline__ uint64_t mix_key(uint64_t seed, uint64_t gid) {
+  // splitmix64 of (seed, global baseline id): the Philox key of a baseline
+  uint64_t z = seed + 0x9E3779B97F4A7C15ull * (gid + 1);
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+  return z ^ (z >> 31);
+}
+
+// Standard normal number `idx` of stream `stream` of iteration `iter` (pair-wise generated:
+// element idx uses block idx>>1, lane idx&1).
+__device__ __forceinline__ double philox_normal(const Philox& ph, uint32_t iter, uint32_t stream, uint64_t idx) {
+  uint64_t blk = idx >> 1;
+  uint4 r = ph((uint32_t)blk, (uint32_t)(blk >> 32), iter, stream);
+  double z0, z1;
+  normal_pair(r, z0, z1);
+  return (idx & 1) ? z1 : z0;
+}
+
+// Entry (r, c) of FTNiF = F^T N^-1 F, which is circulant (real mode) or 2x2-block circulant
+// (complex time domain); ct = first column c[k] (cplx: cr[0..N) then ci[0..N)).
+__device__ __forceinline__ double circ_entry(const double* ct, int N, int cplx, int r, int c) {
+  if (!cplx) {
+    int k = r - c;
+    if (k < 0) k += N;
+    return ct[k];
+  }
+  int k = (r >> 1) - (c >> 1);
+  if (k < 0) k += N;
+  int pr = r & 1, pc = c & 1;
+  return (pr == pc) ? ct[k] : (pr ? ct[N + k] : -ct[N + k]);
+}
+
+}  // namespace dg

@@ -1,0 +1,470 @@
+// C ABI of libdgibbs (see include/dgibbs.h).  Host-side orchestration only: staging, workspace,
+// kernel launches and timing.  There is NO CPU fallback: every entry point that computes
+// requires a CUDA device and returns the CUDA error otherwise.
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <string>
+#include <vector>
+
+#include "../../include/dgibbs.h"
+#include "common.cuh"
+#include "internal.h"
+
+using namespace dg;
+
+struct Buf {
+  void* p = nullptr;
+  size_t cap = 0;
+};
+
+struct dgibbs_handle_s {
+  int device = 0;
+  int sm_count = 0;
+  cudaStream_t stream = nullptr;
+  bool own_stream = false;
+  std::string err;
+  dgibbs_timing timing{};
+  std::map<std::string, Buf> pool;  // grow-only device workspace, freed in destroy
+  cudaEvent_t ev[5]{};
+  // cached projection table
+  int ft_N = -1, ft_cplx = -1;
+};
+
+#define CU(call)                                                                      \
+  do {                                                                                \
+    cudaError_t e_ = (call);                                                          \
+    if (e_ != cudaSuccess) {                                                          \
+      char msg_[512];                                                                 \
+      snprintf(msg_, sizeof msg_, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+      h->err = msg_;                                                                  \
+      return (int)e_;                                                                 \
+    }                                                                                 \
+  } while (0)
+
+static int bad_arg(dgibbs_handle h, int idx, const char* what) {
+  if (h) h->err = std::string("bad argument: ") + what;
+  return -idx;
+}
+
+static cudaError_t pool_get(dgibbs_handle h, const char* name, size_t bytes, void** out) {
+  Buf& b = h->pool[name];
+  if (bytes > b.cap) {
+    if (b.p) cudaFree(b.p);
+    b.p = nullptr;
+    b.cap = 0;
+    size_t want = bytes + (bytes >> 4) + 256;
+    cudaError_t e = cudaMalloc(&b.p, want);
+    if (e != cudaSuccess) {
+      want = bytes;
+      e = cudaMalloc(&b.p, want);
+      if (e != cudaSuccess) return e;
+    }
+    b.cap = want;
+  }
+  *out = b.p;
+  return cudaSuccess;
+}
+
+extern "C" int dgibbs_version(void) { return DGIBBS_VERSION; }
+
+extern "C" int dgibbs_create(int device_id, uint64_t stream, dgibbs_handle* out) {
+  if (!out) return -3;
+  *out = nullptr;
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess) return (int)e;
+  if (device_id < 0 || device_id >= ndev) return -1;
+  e = cudaSetDevice(device_id);
+  if (e != cudaSuccess) return (int)e;
+  dgibbs_handle h = new dgibbs_handle_s();
+  h->device = device_id;
+  cudaDeviceProp prop;
+  e = cudaGetDeviceProperties(&prop, device_id);
+  if (e != cudaSuccess) { delete h; return (int)e; }
+  h->sm_count = prop.multiProcessorCount;
+  if (stream) {
+    h->stream = (cudaStream_t)(uintptr_t)stream;
+  } else {
+    e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
+    if (e != cudaSuccess) { delete h; return (int)e; }
+    h->own_stream = true;
+  }
+  for (auto& ev : h->ev) cudaEventCreate(&ev);
+  *out = h;
+  return 0;
+}
+
+extern "C" int dgibbs_destroy(dgibbs_handle h) {
+  if (!h) return -1;
+  cudaSetDevice(h->device);
+  cudaStreamSynchronize(h->stream);
+  for (auto& kv : h->pool)
+    if (kv.second.p) cudaFree(kv.second.p);
+  for (auto& ev : h->ev) cudaEventDestroy(ev);
+  if (h->own_stream) cudaStreamDestroy(h->stream);
+  delete h;
+  return 0;
+}
+
+extern "C" const char* dgibbs_last_error(dgibbs_handle h) { return h ? h->err.c_str() : "null handle"; }
+
+extern "C" int dgibbs_get_timing(dgibbs_handle h, dgibbs_timing* t) {
+  if (!h) return -1;
+  if (!t) return -2;
+  *t = h->timing;
+  return 0;
+}
+
+// ------------------------------------------------------------------------------ batch staging
+struct Staged {
+  DevBatch d{};
+  std::vector<int> T, M;
+  std::vector<long long> data_off, chan_off;
+  const double* S0 = nullptr;  // device
+  long long sumT = 0;
+  std::vector<long long> xoff;
+};
+
+static int round_up(int x, int m) { return (x + m - 1) / m * m; }
+
+template <typename Tp>
+static cudaError_t fetch(std::vector<Tp>& dst, const Tp* src, size_t n, bool on_device, cudaStream_t st) {
+  dst.resize(n);
+  if (n == 0) return cudaSuccess;
+  if (on_device) {
+    cudaError_t e = cudaMemcpyAsync(dst.data(), src, n * sizeof(Tp), cudaMemcpyDeviceToHost, st);
+    if (e != cudaSuccess) return e;
+    return cudaStreamSynchronize(st);
+  }
+  memcpy(dst.data(), src, n * sizeof(Tp));
+  return cudaSuccess;
+}
+
+// copy (or alias) an input array onto the device
+template <typename Tp>
+static cudaError_t stage_in(dgibbs_handle h, const char* name, const Tp* src, size_t n, bool on_device, const Tp** out) {
+  if (!src || n == 0) { *out = nullptr; return cudaSuccess; }
+  if (on_device) { *out = src; return cudaSuccess; }
+  void* p;
+  cudaError_t e = pool_get(h, name, n * sizeof(Tp), &p);
+  if (e != cudaSuccess) return e;
+  e = cudaMemcpyAsync(p, src, n * sizeof(Tp), cudaMemcpyHostToDevice, h->stream);
+  *out = (const Tp*)p;
+  return e;
+}
+
+static int check_problem(dgibbs_handle h, const dgibbs_problem* p) {
+  if (!h) return -1;
+  if (!p) return bad_arg(h, 2, "problem is NULL");
+  if (p->struct_size != (int32_t)sizeof(dgibbs_problem)) return bad_arg(h, 2, "problem.struct_size mismatch");
+  if (p->B <= 0) return bad_arg(h, 2, "B must be positive");
+  if (p->N < 2 || (!p->complex_timedomain && (p->N & 1))) return bad_arg(h, 2, "N must be even and >= 2");
+  if (p->niter < 0) return bad_arg(h, 2, "niter must be >= 0");
+  if (p->window_id < -1 || p->window_id > 7) return bad_arg(h, 2, "unknown window_id");
+  if (p->rng_mode < 0 || p->rng_mode > 2) return bad_arg(h, 2, "unknown rng_mode");
+  if (!p->T || !p->M || !p->data_off || !p->chan_off || !p->data || !p->Ni || !p->fsel || !p->S0)
+    return bad_arg(h, 2, "a required input pointer is NULL");
+  if (p->rng_mode == DGIBBS_RNG_INJECTED && p->niter > 0 && (!p->w1 || !p->w2 || !p->chi2 || !p->w1_off || !p->w2_off))
+    return bad_arg(h, 2, "injected rng mode needs w1, w2, chi2 and their offsets");
+  return 0;
+}
+
+// Builds the device-side batch: geometry, staged inputs, derived tables (setup kernels enqueued).
+static int stage_batch(dgibbs_handle h, const dgibbs_problem* p, Staged& s, bool wiener) {
+  DevBatch& d = s.d;
+  const bool dev = p->on_device != 0;
+  const int B = p->B;
+  CU(cudaSetDevice(h->device));
+  CU(fetch(s.T, p->T, B, dev, h->stream));
+  CU(fetch(s.M, p->M, B, dev, h->stream));
+  CU(fetch(s.data_off, (const long long*)p->data_off, (size_t)B + 1, dev, h->stream));
+  CU(fetch(s.chan_off, (const long long*)p->chan_off, (size_t)B + 1, dev, h->stream));
+
+  d.B = B;
+  d.N = p->N;
+  d.cplx = p->complex_timedomain ? 1 : 0;
+  d.nsys = d.cplx ? 2 * d.N : d.N;
+  d.npad = round_up(d.nsys, TILE);
+  d.nblk = d.npad / TILE;
+  d.nch = d.cplx ? d.N : d.N / 2 + 1;
+  d.K = 2 * d.nch;
+  d.Kpad = round_up(d.K, KC);
+  d.niter = wiener ? 1 : p->niter;
+  d.window_id = p->window_id;
+  d.rng_mode = wiener ? DGIBBS_RNG_ZERO : p->rng_mode;
+  d.seed = p->seed;
+  d.wiener = wiener ? 1 : 0;
+  int Tmax = 1;
+  s.sumT = 0;
+  s.xoff.resize(B);
+  for (int b = 0; b < B; b++) {
+    if (s.T[b] <= 0) return bad_arg(h, 2, "T[b] must be positive");
+    if (s.M[b] <= 0 || s.M[b] > d.nch) return bad_arg(h, 2, "M[b] out of range");
+    if (s.chan_off[b + 1] - s.chan_off[b] != s.M[b]) return bad_arg(h, 2, "chan_off inconsistent with M");
+    if (s.data_off[b + 1] - s.data_off[b] != (long long)s.T[b] * s.M[b])
+      return bad_arg(h, 2, "data_off inconsistent with T*M");
+    Tmax = s.T[b] > Tmax ? s.T[b] : Tmax;
+    s.xoff[b] = s.sumT;
+    s.sumT += s.T[b];
+  }
+  d.Tmax = Tmax;
+  d.RT = (Tmax + TILE - 1) / TILE;
+  d.nslots = B < h->sm_count ? B : h->sm_count;
+  d.ctab_smem = 1;
+  if (dense_smem_bytes(d) > 227 * 1024) d.ctab_smem = 0;
+
+  // --- inputs
+  const long long nchan = s.chan_off[B], ndata = s.data_off[B];
+  CU(stage_in(h, "in_T", (const int*)p->T, B, dev, &d.T));
+  CU(stage_in(h, "in_M", (const int*)p->M, B, dev, &d.M));
+  CU(stage_in(h, "in_doff", (const long long*)p->data_off, (size_t)B + 1, dev, &d.data_off));
+  CU(stage_in(h, "in_coff", (const long long*)p->chan_off, (size_t)B + 1, dev, &d.chan_off));
+  CU(stage_in(h, "in_data", (const double2*)p->data, (size_t)ndata, dev, &d.data));
+  CU(stage_in(h, "in_Ni", p->Ni, (size_t)nchan, dev, &d.Ni));
+  CU(stage_in(h, "in_fsel", (const long long*)p->fsel, (size_t)nchan, dev, &d.fsel));
+  CU(stage_in(h, "in_S0", p->S0, (size_t)B * d.N, dev, &s.S0));
+  CU(stage_in(h, "in_gid", (const long long*)p->global_id, B, dev, &d.gid));
+  if (d.rng_mode == DGIBBS_RNG_INJECTED && d.niter > 0) {
+    std::vector<long long> w1o, w2o;
+    CU(fetch(w1o, (const long long*)p->w1_off, (size_t)B + 1, dev, h->stream));
+    CU(fetch(w2o, (const long long*)p->w2_off, (size_t)B + 1, dev, h->stream));
+    CU(stage_in(h, "in_w1off", (const long long*)p->w1_off, (size_t)B + 1, dev, &d.w1_off));
+    CU(stage_in(h, "in_w2off", (const long long*)p->w2_off, (size_t)B + 1, dev, &d.w2_off));
+    CU(stage_in(h, "in_w1", p->w1, (size_t)w1o[B], dev, &d.w1));
+    CU(stage_in(h, "in_w2", p->w2, (size_t)w2o[B], dev, &d.w2));
+    CU(stage_in(h, "in_chi2", p->chi2, (size_t)B * d.niter * d.N, dev, &d.chi2));
+  }
+  if (wiener) {
+    void* px;
+    CU(pool_get(h, "xoff", sizeof(long long) * B, &px));
+    CU(cudaMemcpyAsync(px, s.xoff.data(), sizeof(long long) * B, cudaMemcpyHostToDevice, h->stream));
+    d.xoff = (const long long*)px;
+  }
+  CU(cudaEventRecord(h->ev[1], h->stream));
+
+  // --- derived tables and workspace
+  void* q;
+  CU(pool_get(h, "cidx", sizeof(int) * (size_t)B * d.nch, &q)); d.cidx = (int*)q;
+  CU(pool_get(h, "h", sizeof(double) * (size_t)B * d.Kpad, &q)); d.h = (double*)q;
+  CU(pool_get(h, "zT", sizeof(double) * (size_t)B * d.Tmax * d.Kpad, &q)); d.zT = (double*)q;
+  CU(pool_get(h, "ctab", sizeof(double) * (size_t)B * d.nsys, &q)); d.ctab = (double*)q;
+  CU(pool_get(h, "S", sizeof(double) * (size_t)B * d.N, &q)); d.S = (double*)q;
+  CU(pool_get(h, "n_done", sizeof(int) * (size_t)B, &q)); d.n_done = (int*)q;
+  CU(pool_get(h, "failed", sizeof(int) * (size_t)B, &q)); d.failed = (int*)q;
+  const size_t wrows = (size_t)d.npad + (size_t)d.RT * TILE;
+  CU(pool_get(h, "work", sizeof(double) * (size_t)d.nslots * wrows * d.npad, &q)); d.work = (double*)q;
+  CU(pool_get(h, "uT", sizeof(double) * (size_t)d.nslots * d.RT * TILE * d.Kpad, &q)); d.uT = (double*)q;
+  CU(pool_get(h, "Si", sizeof(double) * (size_t)d.nslots * d.npad, &q)); d.Si = (double*)q;
+  {
+    size_t ftbytes = sizeof(double) * (size_t)d.Kpad * d.npad;
+    bool fresh = h->pool["Ftab"].cap < ftbytes || h->ft_N != d.N || h->ft_cplx != d.cplx;
+    CU(pool_get(h, "Ftab", ftbytes, &q));
+    d.Ftab = (const double*)q;
+    if (fresh) {
+      CU(launch_build_ftab(d, (double*)q, h->stream));
+      h->timing.launches++;
+      h->ft_N = d.N;
+      h->ft_cplx = d.cplx;
+    }
+  }
+  CU(launch_setup_baselines(d, s.S0, h->stream));
+  h->timing.launches++;
+  CU(dense_configure(d));
+  return 0;
+}
+
+static double dense_flop_per_iter(const DevBatch& d, int T, int M) {
+  // W_f = n^3/3 + 2 n^2 T + 4 n M T  (n = system size)
+  double n = d.nsys;
+  return n * n * n / 3.0 + 2.0 * n * n * T + 4.0 * n * M * (double)T;
+}
+
+extern "C" int dgibbs_workspace_bytes(dgibbs_handle h, const dgibbs_problem* p, int64_t* bytes) {
+  int rc = check_problem(h, p);
+  if (rc) return rc;
+  if (!bytes) return -3;
+  if (p->on_device) return bad_arg(h, 2, "workspace query needs host-side T/M arrays");
+  int cplx = p->complex_timedomain ? 1 : 0;
+  size_t nsys = cplx ? 2 * (size_t)p->N : p->N, npad = round_up((int)nsys, TILE);
+  size_t nch = cplx ? p->N : p->N / 2 + 1, Kpad = round_up((int)(2 * nch), KC);
+  size_t Tmax = 1;
+  for (int b = 0; b < p->B; b++) Tmax = (size_t)p->T[b] > Tmax ? p->T[b] : Tmax;
+  size_t RT = (Tmax + TILE - 1) / TILE, B = p->B;
+  size_t nslots = B < (size_t)h->sm_count ? B : h->sm_count;
+  size_t tot = 8 * (B * Kpad + B * Tmax * Kpad + B * nsys + 2 * B * p->N + Kpad * npad) + 4 * B * nch +
+               8 * nslots * ((npad + RT * TILE) * npad + RT * TILE * Kpad + npad) +
+               8 * (size_t)p->niter * B * p->N + 8 * B * p->N;
+  *bytes = (int64_t)(tot + tot / 16);
+  return 0;
+}
+
+extern "C" int dgibbs_run(dgibbs_handle h, const dgibbs_problem* p, dgibbs_result* r) {
+  int rc = check_problem(h, p);
+  if (rc) return rc;
+  if (!r || r->struct_size != (int32_t)sizeof(dgibbs_result)) return bad_arg(h, 3, "result struct");
+  if (!r->spectrum || !r->n_done || !r->success) return bad_arg(h, 3, "result.spectrum/n_done/success required");
+  if ((r->on_device != 0) != (p->on_device != 0)) return bad_arg(h, 3, "problem and result must live on the same side");
+  const bool dev = p->on_device != 0;
+  h->timing = dgibbs_timing{};
+  CU(cudaSetDevice(h->device));
+  CU(cudaEventRecord(h->ev[0], h->stream));
+
+  Staged s;
+  rc = stage_batch(h, p, s, false);
+  if (rc) return rc;
+  DevBatch& d = s.d;
+  const size_t BN = (size_t)d.B * d.N;
+
+  // outputs: write straight into the caller's buffers when they are device buffers
+  void* q;
+  double* d_spec; double* d_samples; int* d_ndone; unsigned char* d_succ; double* d_final = nullptr;
+  if (dev) {
+    d_spec = r->spectrum; d_ndone = r->n_done; d_succ = r->success; d_final = r->final_S;
+  } else {
+    CU(pool_get(h, "out_spec", sizeof(double) * BN, &q)); d_spec = (double*)q;
+    CU(pool_get(h, "out_ndone", sizeof(int) * d.B, &q)); d_ndone = (int*)q;
+    CU(pool_get(h, "out_succ", d.B, &q)); d_succ = (unsigned char*)q;
+    if (r->final_S) { CU(pool_get(h, "out_final", sizeof(double) * BN, &q)); d_final = (double*)q; }
+  }
+  if (dev && r->samples) {
+    d_samples = r->samples;
+  } else {
+    CU(pool_get(h, "samples", sizeof(double) * (size_t)(d.niter > 0 ? d.niter : 1) * BN, &q));
+    d_samples = (double*)q;
+  }
+  d.samples = d_samples;
+  CU(cudaEventRecord(h->ev[2], h->stream));
+
+  // --- the chains: one persistent launch covers every iteration of every baseline
+  double flop = 0.0;
+  if (d.niter > 0) {
+    CU(launch_dense_sampler(d, 0, d.niter, h->stream));
+    h->timing.launches++;
+    h->timing.sampler_launches++;
+  }
+  CU(cudaEventRecord(h->ev[3], h->stream));
+
+  CU(launch_finish(d, s.S0, p->median_frac, d_spec, r->samples ? d_samples : nullptr, d_ndone, d_succ, d_final,
+                   h->stream));
+  h->timing.launches++;
+  if (!dev) {
+    CU(cudaMemcpyAsync(r->spectrum, d_spec, sizeof(double) * BN, cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaMemcpyAsync(r->n_done, d_ndone, sizeof(int) * d.B, cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaMemcpyAsync(r->success, d_succ, d.B, cudaMemcpyDeviceToHost, h->stream));
+    if (r->final_S) CU(cudaMemcpyAsync(r->final_S, d_final, sizeof(double) * BN, cudaMemcpyDeviceToHost, h->stream));
+    if (r->samples && d.niter > 0)
+      CU(cudaMemcpyAsync(r->samples, d_samples, sizeof(double) * (size_t)d.niter * BN, cudaMemcpyDeviceToHost, h->stream));
+  }
+  CU(cudaEventRecord(h->ev[4], h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+
+  // bookkeeping that needs n_done
+  std::vector<int> nd(d.B);
+  if (dev) CU(cudaMemcpy(nd.data(), d_ndone, sizeof(int) * d.B, cudaMemcpyDeviceToHost));
+  else memcpy(nd.data(), r->n_done, sizeof(int) * d.B);
+  for (int b = 0; b < d.B; b++) flop += (double)nd[b] * dense_flop_per_iter(d, s.T[b], s.M[b]);
+  if (r->branch) {
+    std::vector<unsigned char> br(d.B, (unsigned char)DGIBBS_BRANCH_DELAY_SPACE);
+    if (dev) CU(cudaMemcpy(r->branch, br.data(), d.B, cudaMemcpyHostToDevice));
+    else memcpy(r->branch, br.data(), d.B);
+  }
+  float ms;
+  cudaEventElapsedTime(&ms, h->ev[0], h->ev[1]); h->timing.ms_h2d = ms;
+  cudaEventElapsedTime(&ms, h->ev[1], h->ev[2]); h->timing.ms_setup = ms;
+  cudaEventElapsedTime(&ms, h->ev[2], h->ev[3]); h->timing.ms_sampler = ms;
+  cudaEventElapsedTime(&ms, h->ev[3], h->ev[4]); h->timing.ms_finish = ms;
+  h->timing.flop_sampler = flop;
+  h->timing.bytes_sampler = 0.0;
+  return 0;
+}
+
+extern "C" int dgibbs_setup_inputs(dgibbs_handle h, const dgibbs_problem* p, int32_t b, double* data_w,
+                                   double* FTNih, double* FTNiF) {
+  int rc = check_problem(h, p);
+  if (rc) return rc;
+  if (b < 0 || b >= p->B) return bad_arg(h, 3, "baseline index out of range");
+  h->timing = dgibbs_timing{};
+  CU(cudaSetDevice(h->device));
+  CU(cudaEventRecord(h->ev[0], h->stream));
+  Staged s;
+  dgibbs_problem pp = *p;
+  pp.rng_mode = DGIBBS_RNG_ZERO;  // draws are irrelevant here
+  rc = stage_batch(h, &pp, s, false);
+  if (rc) return rc;
+  DevBatch& d = s.d;
+  const bool dev = p->on_device != 0;
+  const size_t n_dw = 2 * (size_t)s.M[b] * s.T[b], n_h = (size_t)d.nsys * 2 * s.M[b], n_f = (size_t)d.nsys * d.nsys;
+  double *o_dw = data_w, *o_h = FTNih, *o_f = FTNiF;
+  void* q;
+  if (!dev) {
+    if (data_w) { CU(pool_get(h, "dbg_dw", 8 * n_dw, &q)); o_dw = (double*)q; }
+    if (FTNih) { CU(pool_get(h, "dbg_h", 8 * n_h, &q)); o_h = (double*)q; }
+    if (FTNiF) { CU(pool_get(h, "dbg_f", 8 * n_f, &q)); o_f = (double*)q; }
+  }
+  CU(launch_materialize_inputs(d, b, o_dw, o_h, o_f, h->stream));
+  if (!dev) {
+    if (data_w) CU(cudaMemcpyAsync(data_w, o_dw, 8 * n_dw, cudaMemcpyDeviceToHost, h->stream));
+    if (FTNih) CU(cudaMemcpyAsync(FTNih, o_h, 8 * n_h, cudaMemcpyDeviceToHost, h->stream));
+    if (FTNiF) CU(cudaMemcpyAsync(FTNiF, o_f, 8 * n_f, cudaMemcpyDeviceToHost, h->stream));
+  }
+  CU(cudaStreamSynchronize(h->stream));
+  return 0;
+}
+
+extern "C" int dgibbs_wiener(dgibbs_handle h, const dgibbs_problem* p, double* out, uint8_t* success) {
+  int rc = check_problem(h, p);
+  if (rc) return rc;
+  if (!out) return bad_arg(h, 3, "out is NULL");
+  h->timing = dgibbs_timing{};
+  CU(cudaSetDevice(h->device));
+  CU(cudaEventRecord(h->ev[0], h->stream));
+  Staged s;
+  rc = stage_batch(h, p, s, true);
+  if (rc) return rc;
+  DevBatch& d = s.d;
+  const bool dev = p->on_device != 0;
+  const size_t nout = (size_t)s.sumT * d.nsys;
+  void* q;
+  double* d_out = out;
+  if (!dev) { CU(pool_get(h, "wiener_out", 8 * nout, &q)); d_out = (double*)q; }
+  d.xout = d_out;
+  CU(pool_get(h, "samples", sizeof(double) * (size_t)d.B * d.N, &q));
+  d.samples = (double*)q;
+  CU(cudaEventRecord(h->ev[2], h->stream));
+  CU(launch_dense_sampler(d, 0, 1, h->stream));
+  h->timing.launches++;
+  h->timing.sampler_launches++;
+  CU(cudaEventRecord(h->ev[3], h->stream));
+  if (!dev) CU(cudaMemcpyAsync(out, d_out, 8 * nout, cudaMemcpyDeviceToHost, h->stream));
+  std::vector<int> failed(d.B);
+  CU(cudaMemcpyAsync(failed.data(), d.failed, sizeof(int) * d.B, cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaEventRecord(h->ev[4], h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  if (success) {
+    std::vector<unsigned char> ok(d.B);
+    for (int b = 0; b < d.B; b++) ok[b] = failed[b] ? 0 : 1;
+    if (dev) CU(cudaMemcpy(success, ok.data(), d.B, cudaMemcpyHostToDevice));
+    else memcpy(success, ok.data(), d.B);
+  }
+  float ms;
+  cudaEventElapsedTime(&ms, h->ev[2], h->ev[3]); h->timing.ms_sampler = ms;
+  return 0;
+}
+
+extern "C" int dgibbs_fourier_matrix(dgibbs_handle h, int32_t kind, int32_t N, const int64_t* fsel, int32_t M,
+                                     double* out) {
+  if (!h) return -1;
+  if (kind < 0 || kind > 3) return bad_arg(h, 2, "kind");
+  if (N < 1 || M < 1 || !fsel || !out) return bad_arg(h, 3, "N/M/fsel/out");
+  CU(cudaSetDevice(h->device));
+  size_t n = (kind == 2 ? 4 : 2) * (size_t)M * N;
+  void *dsel, *dout;
+  CU(pool_get(h, "fm_sel", sizeof(long long) * M, &dsel));
+  CU(pool_get(h, "fm_out", 8 * n, &dout));
+  CU(cudaMemcpyAsync(dsel, fsel, sizeof(long long) * M, cudaMemcpyHostToDevice, h->stream));
+  CU(launch_fourier_matrix(kind, N, (const long long*)dsel, M, (double*)dout, h->stream));
+  CU(cudaMemcpyAsync(out, dout, 8 * n, cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  return 0;
+}

@@ -1,0 +1,86 @@
+// Internal (non-ABI) declarations shared by the .cu files of libdgibbs.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace dg {
+
+// Device-side description of one batch.  All pointers are device pointers.
+struct DevBatch {
+  // geometry
+  int B;       // baselines
+  int N;       // delays
+  int nsys;    // system size of the delay-space branch: N (real) or 2N (complex time domain)
+  int npad;    // nsys rounded up to TILE
+  int nblk;    // npad / TILE
+  int nch;     // channels of the FULL grid: N/2+1 (real) or N (complex)
+  int K;       // 2*nch  rows of the projection table
+  int Kpad;    // K rounded up to KC
+  int Tmax;    // max_b T[b]
+  int RT;      // RHS row tiles: ceil(Tmax / TILE)
+  int niter;
+  int window_id;
+  int cplx;
+  int rng_mode;
+  unsigned long long seed;
+  int nslots;  // concurrent CTAs (= workspace slots)
+  int wiener;  // 1: stop after the solve of iteration 0 and keep x (Wiener filter)
+  int ctab_smem;  // circulant table fits in shared memory
+
+  // caller inputs
+  const int* T;
+  const int* M;
+  const long long* data_off;
+  const long long* chan_off;
+  const double2* data;
+  const double* Ni;
+  const long long* fsel;
+  const long long* gid;  // may be null
+  const double* w1;
+  const long long* w1_off;
+  const double* w2;
+  const long long* w2_off;
+  const double* chi2;
+
+  // derived per-baseline tables
+  int* cidx;     // [B][nch]   compact channel index on the full grid, -1 = masked
+  double* h;     // [B][Kpad]  window * sqrt(Ni_r) on the full grid (0 where masked)
+  double* zT;    // [B][Tmax][Kpad] whitened data, transposed (sample-major)
+  double* ctab;  // [B][nsys]  first column of the circulant FTNiF (cplx: cr[N] then ci[N])
+  double* S;     // [B][N]     chain state
+  double* samples;  // [niter][B][N]
+  int* n_done;      // [B] completed iterations
+  int* failed;      // [B] 1 once a factorisation met a non-positive pivot
+  unsigned char* branch;  // [B]
+
+  // shared tables
+  const double* Ftab;  // [Kpad][npad] projection table  F[k][col]
+
+  // per-slot workspace
+  double* work;  // [nslots][(npad + RT*TILE)][npad]  L (lower) with W=inv(L_jj) in the diagonal
+                 //                                   blocks, then the RHS rows (sample-major)
+  double* uT;    // [nslots][RT*TILE][Kpad]
+  double* Si;    // [nslots][npad]
+  double* xout;  // wiener: [sum T][nsys] output; else null
+  const long long* xoff;  // [B] row offsets into xout
+};
+
+// setup_kernels.cu
+cudaError_t launch_build_ftab(const DevBatch& d, double* Ftab, cudaStream_t st);
+cudaError_t launch_setup_baselines(const DevBatch& d, const double* S0, cudaStream_t st);
+cudaError_t launch_materialize_inputs(const DevBatch& d, int b, double* data_w, double* FTNih,
+                                      double* FTNiF, cudaStream_t st);
+cudaError_t launch_fourier_matrix(int kind, int N, const long long* fsel, int M, double* out,
+                                  cudaStream_t st);
+
+// sampler_dense.cu
+size_t dense_smem_bytes(const DevBatch& d);
+cudaError_t dense_configure(const DevBatch& d);
+cudaError_t launch_dense_sampler(const DevBatch& d, int it_begin, int it_end, cudaStream_t st);
+
+// finish_kernels.cu
+cudaError_t launch_finish(const DevBatch& d, const double* S0, double median_frac, double* spectrum,
+                          double* samples_out, int* n_done_out, unsigned char* success_out,
+                          double* final_S, cudaStream_t st);
+
+}  // namespace dg

@@ -1,0 +1,241 @@
+// Per-batch setup: projection table, window/whiten/pack, circulant first columns.
+// Reference behaviour: _compute_delay_spectrum_inputs, draco/analysis/delay.py:1657-1710,
+// fourier_matrix_* delay.py:1480-1613, window_generalised draco/util/tools.py:547-601.
+#include "common.cuh"
+#include "internal.h"
+
+namespace dg {
+
+// cosine-sum coefficients, draco/util/tools.py:584-595 (digit for digit)
+__constant__ double c_window[8][4] = {
+    {1, 0, 0, 0},
+    {0.5, -0.5, 0, 0},
+    {0.5, -0.5, 0, 0},
+    {0.53836, -0.46164, 0, 0},
+    {0.42, -0.5, 0.08, 0},
+    {0.355768, -0.487396, 0.144232, -0.012604},
+    {0.3635819, -0.4891775, 0.1365995, -0.0106411},
+    {0.35875, -0.48829, 0.14128, -0.01168},
+};
+
+__device__ __forceinline__ double window_value(int window_id, double x) {
+  if (window_id < 0) return 1.0;
+  double w = 0.0;
+#pragma unroll
+  for (int j = 0; j < 4; j++) w += c_window[window_id][j] * cos(2.0 * 3.141592653589793 * (double)j * x);
+  return (x >= 0.0 && x <= 1.0) ? w : 0.0;
+}
+
+// exact twiddle: cos/sin(2 pi m / N) with the integer phase m already reduced mod N
+__device__ __forceinline__ void twiddle(long long m, int N, double& c, double& s) {
+  sincospi(2.0 * (double)m / (double)N, &s, &c);
+}
+
+// Ftab[k][col]: the (zero padded) matrix F of the FULL channel grid, stored channel-row major
+// so that  y[t, col] = sum_k u[t, k] * Ftab[k, col]  is the masked inverse DFT.
+__global__ void build_ftab_kernel(double* __restrict__ F, int N, int nsys, int npad, int K, int Kpad, int cplx) {
+  long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  long long total = (long long)Kpad * npad;
+  if (idx >= total) return;
+  int k = (int)(idx / npad), col = (int)(idx % npad);
+  double v = 0.0;
+  if (k < K && col < nsys) {
+    int i = k >> 1, pr = k & 1;
+    double c, s;
+    if (!cplx) {
+      twiddle(((long long)i * col) % N, N, c, s);
+      v = pr ? -s : c;  // delay.py:1507-1508
+    } else {
+      int t = col >> 1, pc = col & 1;
+      twiddle(((long long)i * t) % N, N, c, s);
+      v = (pr == pc) ? c : (pr ? -s : s);  // delay.py:1580-1583
+    }
+  }
+  F[idx] = v;
+}
+
+cudaError_t launch_build_ftab(const DevBatch& d, double* Ftab, cudaStream_t st) {
+  long long total = (long long)d.Kpad * d.npad;
+  int blocks = (int)((total + 255) / 256);
+  build_ftab_kernel<<<blocks, 256, 0, st>>>(Ftab, d.N, d.nsys, d.npad, d.K, d.Kpad, d.cplx);
+  return cudaGetLastError();
+}
+
+// One CTA per baseline.
+__global__ void setup_baseline_kernel(DevBatch d, const double* __restrict__ S0) {
+  extern __shared__ double sm[];
+  const int b = blockIdx.x;
+  const int N = d.N, nch = d.nch;
+  double* tabc = sm;                          // [N]
+  double* tabs = d.cplx ? sm + N : nullptr;   // [N]
+  double* hsq = sm + (d.cplx ? 2 * N : N);    // [nch]
+  double* s_w = hsq + nch;                    // [nch] window
+  double* s_re = s_w + nch;                   // [nch] sqrt(Ni_r) of the real part
+  double* s_im = s_re + nch;                  // [nch] sqrt(Ni_r) of the imaginary part
+  const int Tb = d.T[b], Mb = d.M[b];
+  const long long coff = d.chan_off[b], doff = d.data_off[b];
+  int* cidx = d.cidx + (size_t)b * nch;
+  double* h = d.h + (size_t)b * d.Kpad;
+  double* zT = d.zT + (size_t)b * d.Tmax * d.Kpad;
+
+  for (int i = threadIdx.x; i < nch; i += blockDim.x) cidx[i] = -1;
+  for (int m = threadIdx.x; m < N; m += blockDim.x) {
+    double c, s;
+    twiddle(m, N, c, s);
+    tabc[m] = c;
+    if (tabs) tabs[m] = s;
+  }
+  __syncthreads();
+  for (int ci = threadIdx.x; ci < Mb; ci += blockDim.x) {
+    long long f = d.fsel[coff + ci];
+    if (f >= 0 && f < nch) cidx[f] = ci;
+  }
+  __syncthreads();
+
+  // window * sqrt(Ni_r) on the full grid (delay.py:1679-1703)
+  for (int i = threadIdx.x; i < d.Kpad / 2; i += blockDim.x) {
+    double hre = 0.0, him = 0.0;
+    if (i < nch) {
+      int ci = cidx[i];
+      if (ci >= 0) {
+        double w = window_value(d.window_id, (double)i / (double)nch);
+        double ni = d.Ni[coff + ci];
+        bool purely_real = !d.cplx && (i == 0 || i == N / 2);  // delay.py:1692
+        double nre = purely_real ? ni : 2.0 * ni;
+        double nim = purely_real ? 0.0 : 2.0 * ni;
+        double sre = sqrt(nre), sim = sqrt(nim);
+        hre = w * sre;
+        him = w * sim;
+        s_w[i] = w;
+        s_re[i] = sre;
+        s_im[i] = sim;
+      }
+      hsq[i] = hre * hre;
+    }
+    h[2 * i] = hre;
+    h[2 * i + 1] = him;
+  }
+  __syncthreads();
+
+  // whitened, windowed data, sample-major (delay.py:1676,1687,1707)
+  const int halfK = d.Kpad / 2;
+  for (long long e = threadIdx.x; e < (long long)d.Tmax * halfK; e += blockDim.x) {
+    int t = (int)(e / halfK), i = (int)(e % halfK);
+    double zr = 0.0, zi = 0.0;
+    if (t < Tb && i < nch) {
+      int ci = cidx[i];
+      if (ci >= 0) {
+        double2 v = d.data[doff + (long long)t * Mb + ci];
+        zr = (v.x * s_w[i]) * s_re[i];
+        zi = (v.y * s_w[i]) * s_im[i];
+      }
+    }
+    zT[(size_t)t * d.Kpad + 2 * i] = zr;
+    zT[(size_t)t * d.Kpad + 2 * i + 1] = zi;
+  }
+
+  // first column of the circulant  FTNiF[t,t'] = c[(t-t') mod N]
+  double* ct = d.ctab + (size_t)b * d.nsys;
+  for (int k = threadIdx.x; k < N; k += blockDim.x) {
+    double accr = 0.0, acci = 0.0;
+    int m = 0;
+    for (int i = 0; i < nch; i++) {
+      double g = hsq[i];
+      accr += g * tabc[m];
+      if (tabs) acci += g * tabs[m];
+      m += k;
+      if (m >= N) m -= N;
+    }
+    ct[k] = accr;
+    if (tabs) ct[N + k] = acci;
+  }
+
+  for (int k = threadIdx.x; k < N; k += blockDim.x) d.S[(size_t)b * N + k] = S0[(size_t)b * N + k];
+  if (threadIdx.x == 0) {
+    d.n_done[b] = 0;
+    d.failed[b] = 0;
+  }
+}
+
+cudaError_t launch_setup_baselines(const DevBatch& d, const double* S0, cudaStream_t st) {
+  size_t smem = sizeof(double) * ((d.cplx ? 2 : 1) * (size_t)d.N + 4 * (size_t)d.nch);
+  cudaError_t e = cudaFuncSetAttribute(setup_baseline_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  setup_baseline_kernel<<<d.B, 256, smem, st>>>(d, S0);
+  return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------ debug / parity
+__global__ void materialize_kernel(DevBatch d, int b, double* data_w, double* FTNih, double* FTNiF) {
+  const int Tb = d.T[b], Mb = d.M[b];
+  const long long coff = d.chan_off[b];
+  const double* h = d.h + (size_t)b * d.Kpad;
+  const double* zT = d.zT + (size_t)b * d.Tmax * d.Kpad;
+  const double* ct = d.ctab + (size_t)b * d.nsys;
+  long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x, nth = (long long)gridDim.x * blockDim.x;
+  if (data_w)
+    for (long long e = tid; e < 2LL * Mb * Tb; e += nth) {
+      int row = (int)(e / Tb), t = (int)(e % Tb);
+      long long f = d.fsel[coff + (row >> 1)];
+      data_w[e] = zT[(size_t)t * d.Kpad + 2 * f + (row & 1)];
+    }
+  if (FTNih)
+    for (long long e = tid; e < (long long)d.nsys * 2 * Mb; e += nth) {
+      int r = (int)(e / (2 * Mb)), col = (int)(e % (2 * Mb));
+      long long f = d.fsel[coff + (col >> 1)];
+      long long k = 2 * f + (col & 1);
+      FTNih[e] = d.Ftab[(size_t)k * d.npad + r] * h[k];
+    }
+  if (FTNiF)
+    for (long long e = tid; e < (long long)d.nsys * d.nsys; e += nth) {
+      int r = (int)(e / d.nsys), c = (int)(e % d.nsys);
+      FTNiF[e] = circ_entry(ct, d.N, d.cplx, r, c);
+    }
+}
+
+cudaError_t launch_materialize_inputs(const DevBatch& d, int b, double* data_w, double* FTNih, double* FTNiF,
+                                      cudaStream_t st) {
+  materialize_kernel<<<296, 256, 0, st>>>(d, b, data_w, FTNih, FTNiF);
+  return cudaGetLastError();
+}
+
+// kind: 0 r2c (2M,N)  1 c2r (N,2M)  2 c2c (2M,2N)  3 complex (M,N) interleaved
+__global__ void fourier_matrix_kernel(int kind, int N, const long long* fsel, int M, double* out) {
+  long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x, nth = (long long)gridDim.x * blockDim.x;
+  long long total = (kind == 2) ? 4LL * M * N : 2LL * M * N;
+  for (long long e = tid; e < total; e += nth) {
+    int row, col;
+    double c, s, v;
+    if (kind == 0) {  // delay.py:1480-1510
+      row = (int)(e / N); col = (int)(e % N);
+      long long f = fsel[row >> 1];
+      twiddle((f * col) % N, N, c, s);
+      v = (row & 1) ? -s : c;
+    } else if (kind == 1) {  // delay.py:1513-1546
+      row = (int)(e / (2 * M)); col = (int)(e % (2 * M));
+      long long f = fsel[col >> 1];
+      twiddle((f * row) % N, N, c, s);
+      double mul = ((f == 0 || f == N / 2) ? 1.0 : 2.0) / (double)N;
+      v = ((col & 1) ? -s : c) * mul;
+    } else if (kind == 2) {  // delay.py:1549-1585
+      row = (int)(e / (2 * N)); col = (int)(e % (2 * N));
+      long long f = fsel[row >> 1];
+      twiddle((f * (col >> 1)) % N, N, c, s);
+      int pr = row & 1, pc = col & 1;
+      v = (pr == pc) ? c : (pr ? -s : s);
+    } else {  // delay.py:1588-1613  exp(-2 pi i t f / N)
+      row = (int)(e / (2 * N)); col = (int)(e % (2 * N));
+      long long f = fsel[row];
+      twiddle((f * (col >> 1)) % N, N, c, s);
+      v = (col & 1) ? -s : c;
+    }
+    out[e] = v;
+  }
+}
+
+cudaError_t launch_fourier_matrix(int kind, int N, const long long* fsel, int M, double* out, cudaStream_t st) {
+  fourier_matrix_kernel<<<296, 256, 0, st>>>(kind, N, fsel, M, out);
+  return cudaGetLastError();
+}
+
+}  // namespace dg

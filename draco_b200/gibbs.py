@@ -1,0 +1,372 @@
+"""Python face of the device sampler: same names and argument meaning as the reference's
+module-level functions in ``draco/analysis/delay.py`` (cited per function), plus the
+batched entry point the task class uses.  All arithmetic happens in ``libdgibbs.so``.
+"""
+
+from __future__ import annotations
+
+import ctypes as C
+import dataclasses
+
+import numpy as np
+
+from . import _lib
+from ._lib import RNG_INJECTED, RNG_PHILOX, RNG_ZERO, WINDOW_IDS, DGibbsError, Handle  # noqa: F401
+
+_handles: dict = {}
+
+
+def get_handle(device=0) -> Handle:
+    """Per-process handle cache (one handle per device)."""
+    h = _handles.get(device)
+    if h is None:
+        h = _handles[device] = Handle(device)
+    return h
+
+
+def _ptr(a):
+    if a is None:
+        return None
+    if isinstance(a, np.ndarray):
+        return a.ctypes.data
+    return a.data_ptr()  # torch tensor
+
+
+def _is_device(a):
+    return not isinstance(a, np.ndarray) and hasattr(a, "is_cuda") and a.is_cuda
+
+
+@dataclasses.dataclass
+class PackedBatch:
+    """Ragged batch of cut baselines in the layout ``include/dgibbs.h`` describes."""
+
+    N: int
+    T: object  # int32 [B]
+    M: object  # int32 [B]
+    data_off: object  # int64 [B+1]
+    chan_off: object  # int64 [B+1]
+    data: object  # complex128 flat
+    Ni: object  # float64 flat
+    fsel: object  # int64 flat
+    S0: object  # float64 [B, N]
+    global_id: object = None  # int64 [B]
+    complex_timedomain: bool = False
+    window: str | None = "nuttall"
+
+    @property
+    def B(self):
+        return int(self.T.shape[0])
+
+    @property
+    def on_device(self):
+        return _is_device(self.data)
+
+    def to_device(self, device=0):
+        """Move every array to ``cuda:device`` (torch tensors); inputs then stay resident in HBM."""
+        import torch
+
+        dev = torch.device("cuda", device)
+        kw = {}
+        for f in dataclasses.fields(self):
+            v = getattr(self, f.name)
+            if isinstance(v, np.ndarray):
+                if v.dtype == np.complex128:
+                    v = torch.from_numpy(v.view(np.float64)).to(dev)
+                else:
+                    v = torch.from_numpy(v).to(dev)
+            kw[f.name] = v
+        return PackedBatch(**kw)
+
+
+def pack_batch(datas, Nis, fsels, N, S0, window="nuttall", complex_timedomain=False, global_id=None) -> PackedBatch:
+    """Pack per-baseline ``(data[T,M] c128, Ni[M], fsel[M])`` triples (the outputs of
+    ``_cut_data`` and ``channel_ind[nzf]``, delay.py:1156-1167) into one ragged batch."""
+    B = len(datas)
+    T = np.array([d.shape[0] for d in datas], dtype=np.int32)
+    M = np.array([d.shape[1] for d in datas], dtype=np.int32)
+    data_off = np.zeros(B + 1, dtype=np.int64)
+    np.cumsum(T.astype(np.int64) * M, out=data_off[1:])
+    chan_off = np.zeros(B + 1, dtype=np.int64)
+    np.cumsum(M, out=chan_off[1:])
+    data = np.empty(int(data_off[-1]), dtype=np.complex128)
+    Ni = np.empty(int(chan_off[-1]), dtype=np.float64)
+    fsel = np.empty(int(chan_off[-1]), dtype=np.int64)
+    for b in range(B):
+        if Nis[b].ndim != 1:
+            # same restriction as the reference sampler (delay.py:1697 assumes 1-D Ni)
+            raise ValueError("the Gibbs sampler needs time-averaged weights (use_average_weights=True)")
+        data[data_off[b] : data_off[b + 1]] = np.asarray(datas[b], dtype=np.complex128).ravel()
+        Ni[chan_off[b] : chan_off[b + 1]] = Nis[b]
+        fsel[chan_off[b] : chan_off[b + 1]] = fsels[b]
+    S0 = np.ascontiguousarray(np.broadcast_to(np.asarray(S0, dtype=np.float64), (B, N)))
+    gid = None if global_id is None else np.ascontiguousarray(global_id, dtype=np.int64)
+    return PackedBatch(N, T, M, data_off, chan_off, data, Ni, fsel, S0, gid, bool(complex_timedomain), window)
+
+
+def pack_uniform(vis, weight, fsel, N, S0, window="nuttall", complex_timedomain=False, global_id=None) -> PackedBatch:
+    """Fast path of :func:`pack_batch` when every baseline has the same (T, M):
+    ``vis[B,T,M]`` c128, ``weight[B,M]``, common ``fsel[M]``."""
+    B, T, M = vis.shape
+    data_off = np.arange(B + 1, dtype=np.int64) * (T * M)
+    chan_off = np.arange(B + 1, dtype=np.int64) * M
+    S0 = np.ascontiguousarray(np.broadcast_to(np.asarray(S0, dtype=np.float64), (B, N)))
+    gid = None if global_id is None else np.ascontiguousarray(global_id, dtype=np.int64)
+    return PackedBatch(
+        N,
+        np.full(B, T, dtype=np.int32),
+        np.full(B, M, dtype=np.int32),
+        data_off,
+        chan_off,
+        np.ascontiguousarray(vis, dtype=np.complex128).reshape(-1),
+        np.ascontiguousarray(weight, dtype=np.float64).reshape(-1),
+        np.ascontiguousarray(np.broadcast_to(np.asarray(fsel, dtype=np.int64), (B, M))).reshape(-1),
+        S0,
+        gid,
+        bool(complex_timedomain),
+        window,
+    )
+
+
+def _problem(pb: PackedBatch, niter, rng_mode, seed, median_frac, draws=None):
+    p = _lib.Problem()
+    p.struct_size = C.sizeof(_lib.Problem)
+    p.on_device = 1 if pb.on_device else 0
+    p.B, p.N, p.niter = pb.B, int(pb.N), int(niter)
+    if pb.window not in WINDOW_IDS:
+        raise ValueError(f"window {pb.window!r} is not one of {sorted(k for k in WINDOW_IDS if k)}")
+    p.window_id = WINDOW_IDS[pb.window]
+    p.complex_timedomain = 1 if pb.complex_timedomain else 0
+    p.rng_mode = rng_mode
+    p.seed = int(seed) & 0xFFFFFFFFFFFFFFFF
+    p.median_frac = float(median_frac)
+    for name in ("T", "M", "data_off", "chan_off", "data", "Ni", "fsel", "S0", "global_id"):
+        setattr(p, name, _ptr(getattr(pb, name)))
+    keep = []
+    if draws is not None:
+        w1, w1_off, w2, w2_off, chi2 = draws
+        keep = [w1, w1_off, w2, w2_off, chi2]
+        p.w1, p.w1_off, p.w2, p.w2_off, p.chi2 = map(_ptr, keep)
+    return p, keep
+
+
+def pack_draws(pb: PackedBatch, niter, w1s, w2s, chi2s):
+    """Concatenate per-baseline injected draws: ``w1s[b]`` (niter, n_sys, T), ``w2s[b]``
+    (niter, 2M, T), ``chi2s[b]`` (niter, N) -- the reference's shapes and order."""
+    B = pb.B
+    w1_off = np.zeros(B + 1, dtype=np.int64)
+    w2_off = np.zeros(B + 1, dtype=np.int64)
+    np.cumsum([int(np.asarray(w).size) for w in w1s], out=w1_off[1:])
+    np.cumsum([int(np.asarray(w).size) for w in w2s], out=w2_off[1:])
+    w1 = np.concatenate([np.asarray(w, dtype=np.float64).ravel() for w in w1s]) if niter else np.zeros(1)
+    w2 = np.concatenate([np.asarray(w, dtype=np.float64).ravel() for w in w2s]) if niter else np.zeros(1)
+    chi2 = np.ascontiguousarray(np.stack([np.asarray(c, dtype=np.float64) for c in chi2s])) if niter else np.zeros(1)
+    return w1, w1_off, w2, w2_off, chi2
+
+
+@dataclasses.dataclass
+class BatchResult:
+    spectrum: object  # [B, N] fftshifted median
+    samples: object  # [niter, B, N] or None
+    n_done: object  # [B]
+    success: object  # [B] bool
+    branch: object  # [B]
+    final_S: object
+    timing: dict
+
+
+def run_batch(
+    pb: PackedBatch,
+    niter,
+    *,
+    handle: Handle | None = None,
+    rng_mode=RNG_PHILOX,
+    seed=0,
+    median_frac=0.5,
+    draws=None,
+    save_samples=False,
+    want_final_S=False,
+) -> BatchResult:
+    """Run every chain of a packed batch on the GPU (replaces the loop delay.py:1146-1178)."""
+    device = pb.data.device.index if pb.on_device else 0
+    h = handle or get_handle(device or 0)
+    B, N = pb.B, int(pb.N)
+    if draws is not None:
+        rng_mode = RNG_INJECTED
+    if rng_mode == RNG_INJECTED and draws is None and niter > 0:
+        raise ValueError("injected rng mode needs draws")
+    if pb.on_device:
+        import torch
+
+        dev = pb.data.device
+        if draws is not None:
+            draws = tuple(torch.from_numpy(np.ascontiguousarray(a)).to(dev) for a in draws)
+        spectrum = torch.empty((B, N), dtype=torch.float64, device=dev)
+        samples = torch.empty((niter, B, N), dtype=torch.float64, device=dev) if save_samples else None
+        n_done = torch.empty(B, dtype=torch.int32, device=dev)
+        success = torch.empty(B, dtype=torch.uint8, device=dev)
+        branch = torch.empty(B, dtype=torch.uint8, device=dev)
+        final_S = torch.empty((B, N), dtype=torch.float64, device=dev) if want_final_S else None
+    else:
+        spectrum = np.empty((B, N), dtype=np.float64)
+        samples = np.empty((niter, B, N), dtype=np.float64) if save_samples else None
+        n_done = np.empty(B, dtype=np.int32)
+        success = np.empty(B, dtype=np.uint8)
+        branch = np.empty(B, dtype=np.uint8)
+        final_S = np.empty((B, N), dtype=np.float64) if want_final_S else None
+    p, keep = _problem(pb, niter, rng_mode, seed, median_frac, draws)
+    r = _lib.Result()
+    r.struct_size = C.sizeof(_lib.Result)
+    r.on_device = p.on_device
+    r.spectrum, r.samples, r.n_done = _ptr(spectrum), _ptr(samples), _ptr(n_done)
+    r.success, r.branch, r.final_S = _ptr(success), _ptr(branch), _ptr(final_S)
+    h.check(h.lib.dgibbs_run(h._h, C.byref(p), C.byref(r)), "dgibbs_run")
+    del keep
+    ok = success.bool() if pb.on_device else success.astype(bool)
+    return BatchResult(spectrum, samples, n_done, ok, branch, final_S, h.timing())
+
+
+# ---------------------------------------------------------------------------------------
+# Reference-named single-baseline functions
+# ---------------------------------------------------------------------------------------
+
+
+def _default_fsel(N, complex_timedomain):
+    return np.arange(N if complex_timedomain else N // 2 + 1)
+
+
+def _host_draws(rng, niter, n_sys, M, T, N):
+    """Draw (w1, w2, chi2) for one baseline from a numpy Generator in the reference's call
+    order (delay.py:1806-1809, 1878): per iteration normal(n_sys,T), normal(2M,T), chisquare(T,N)."""
+    w1 = np.empty((niter, n_sys, T))
+    w2 = np.empty((niter, 2 * M, T))
+    c2 = np.empty((niter, N))
+    for i in range(niter):
+        w1[i] = rng.standard_normal((n_sys, T))
+        w2[i] = rng.standard_normal((2 * M, T))
+        c2[i] = rng.chisquare(T, size=N)
+    return w1, w2, c2
+
+
+def delay_power_spectrum_gibbs(
+    data,
+    N,
+    Ni,
+    initial_S,
+    window="nuttall",
+    fsel=None,
+    niter=20,
+    rng=None,
+    complex_timedomain=False,
+    *,
+    device=0,
+    seed=None,
+):
+    """Drop-in for ``delay_power_spectrum_gibbs`` (delay.py:1713-1904): returns
+    ``(list of (N,) spectrum samples in unshifted delay order, success)``.
+
+    ``rng``: a ``numpy.random.Generator`` selects deterministic mode -- the Gaussian and
+    chi^2 variates are drawn from it on the host in the reference's order and injected, so
+    the same seed reproduces the reference's chain to rounding.  ``rng=None`` uses the
+    device Philox generator (``seed``; default taken from OS entropy).
+    """
+    data = np.asarray(data)
+    fsel = _default_fsel(N, complex_timedomain) if fsel is None else np.asarray(fsel)
+    T, M = data.shape
+    pb = pack_batch([data], [np.asarray(Ni, dtype=np.float64)], [fsel], N, np.asarray(initial_S)[None, :], window,
+                    complex_timedomain)
+    if rng is not None:
+        n_sys = 2 * N if complex_timedomain else N
+        w1, w2, c2 = _host_draws(rng, niter, n_sys, M, T, N)
+        draws = pack_draws(pb, niter, [w1], [w2], [c2])
+        res = run_batch(pb, niter, handle=get_handle(device), draws=draws, save_samples=True)
+    else:
+        if seed is None:
+            seed = int(np.random.SeedSequence().generate_state(1, dtype=np.uint64)[0])
+        res = run_batch(pb, niter, handle=get_handle(device), rng_mode=RNG_PHILOX, seed=seed, save_samples=True)
+    nd = int(res.n_done[0])
+    spec = [res.samples[niter - nd + i, 0].copy() for i in range(nd)]
+    return spec, bool(res.success[0])
+
+
+def delay_spectrum_wiener_filter(delay_PS, data, N, Ni, window="nuttall", fsel=None, complex_timedomain=False, *,
+                                 device=0):
+    """Drop-in for ``delay_spectrum_wiener_filter`` (delay.py:2132-2201): ``(T, N)`` float64,
+    or complex128 in complex_timedomain mode.  Raises ``np.linalg.LinAlgError`` when the
+    Wiener covariance is not positive definite, like ``scipy.linalg.cho_factor``."""
+    data = np.asarray(data)
+    fsel = _default_fsel(N, complex_timedomain) if fsel is None else np.asarray(fsel)
+    pb = pack_batch([data], [np.asarray(Ni, dtype=np.float64)], [fsel], N, np.asarray(delay_PS)[None, :], window,
+                    complex_timedomain)
+    out, ok = wiener_batch(pb, handle=get_handle(device))
+    if not ok[0]:
+        raise np.linalg.LinAlgError("Wiener covariance is not positive definite")
+    y = out[0]
+    return y.view(np.complex128) if complex_timedomain else y
+
+
+def wiener_batch(pb: PackedBatch, *, handle: Handle | None = None):
+    """Wiener-filter every baseline of a (host) packed batch; returns a list of (T_b, n_sys)
+    arrays and a success flag per baseline."""
+    if pb.on_device:
+        raise NotImplementedError("wiener_batch takes host batches")
+    h = handle or get_handle(0)
+    n_sys = (2 if pb.complex_timedomain else 1) * int(pb.N)
+    out = np.empty(int(pb.T.astype(np.int64).sum()) * n_sys, dtype=np.float64)
+    ok = np.empty(pb.B, dtype=np.uint8)
+    p, _ = _problem(pb, 1, RNG_ZERO, 0, 0.5)
+    h.check(h.lib.dgibbs_wiener(h._h, C.byref(p), out.ctypes.data, ok.ctypes.data), "dgibbs_wiener")
+    res, o = [], 0
+    for b in range(pb.B):
+        n = int(pb.T[b]) * n_sys
+        res.append(out[o : o + n].reshape(int(pb.T[b]), n_sys))
+        o += n
+    return res, ok.astype(bool)
+
+
+def compute_delay_spectrum_inputs(data, N, Ni, fsel, window, complex_timedomain, *, device=0):
+    """Device evaluation of ``_compute_delay_spectrum_inputs`` (delay.py:1657-1710):
+    ``(data_w (2M,T), FTNih (n_sys,2M), FTNiF (n_sys,n_sys))``."""
+    data = np.asarray(data)
+    fsel = _default_fsel(N, complex_timedomain) if fsel is None else np.asarray(fsel)
+    T, M = data.shape
+    n_sys = 2 * N if complex_timedomain else N
+    pb = pack_batch([data], [np.asarray(Ni, dtype=np.float64)], [fsel], N, np.ones((1, N)), window, complex_timedomain)
+    h = get_handle(device)
+    dw = np.empty((2 * M, T))
+    fh = np.empty((n_sys, 2 * M))
+    ff = np.empty((n_sys, n_sys))
+    p, _ = _problem(pb, 0, RNG_ZERO, 0, 0.5)
+    h.check(
+        h.lib.dgibbs_setup_inputs(h._h, C.byref(p), 0, dw.ctypes.data, fh.ctypes.data, ff.ctypes.data),
+        "dgibbs_setup_inputs",
+    )
+    return dw, fh, ff
+
+
+def _fourier(kind, N, fsel, default_count, shape_fn, device):
+    fa = np.arange(default_count, dtype=np.int64) if fsel is None else np.ascontiguousarray(fsel, dtype=np.int64)
+    M = fa.shape[0]
+    out = np.empty(shape_fn(M), dtype=np.float64)
+    h = get_handle(device)
+    h.check(h.lib.dgibbs_fourier_matrix(h._h, kind, int(N), fa.ctypes.data, M, out.ctypes.data), "dgibbs_fourier_matrix")
+    return out
+
+
+def fourier_matrix_r2c(N, fsel=None, *, device=0):
+    """delay.py:1480-1510."""
+    return _fourier(0, N, fsel, N // 2 + 1, lambda M: (2 * M, N), device)
+
+
+def fourier_matrix_c2r(N, fsel=None, *, device=0):
+    """delay.py:1513-1546."""
+    return _fourier(1, N, fsel, N // 2 + 1, lambda M: (N, 2 * M), device)
+
+
+def fourier_matrix_c2c(N, fsel=None, *, device=0):
+    """delay.py:1549-1585."""
+    return _fourier(2, N, fsel, N, lambda M: (2 * M, 2 * N), device)
+
+
+def fourier_matrix(N, fsel=None, *, device=0):
+    """delay.py:1588-1613 (complex128 (M, N))."""
+    return _fourier(3, N, fsel, N, lambda M: (M, 2 * N), device).view(np.complex128)

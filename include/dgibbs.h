@@ -1,0 +1,178 @@
+/*
+ * dgibbs.h -- C ABI of the B200-native delay power-spectrum Gibbs sampler.
+ *
+ * The reference (radiocosmology/draco) has no FFI: the path is Python calling
+ * numpy / scipy.linalg.  The entry points below are what a ctypes binding inside
+ * draco's own task would call instead of the per-baseline Python loop
+ *   DelayPowerSpectrumBase._evaluate          draco/analysis/delay.py:1117-1185
+ *     -> DelayPowerSpectrumGibbs._estimator   draco/analysis/delay.py:1242-1267
+ *        -> delay_power_spectrum_gibbs        draco/analysis/delay.py:1713-1904
+ *           -> _compute_delay_spectrum_inputs draco/analysis/delay.py:1657-1710
+ *              fourier_matrix_r2c / _c2c      draco/analysis/delay.py:1480-1585
+ *              tools.window_generalised       draco/util/tools.py:547-601
+ *   delay_spectrum_wiener_filter              draco/analysis/delay.py:2132-2201
+ * (see INTEGRATION.md for the binding a draco maintainer would add).
+ *
+ * Conventions
+ *   - plain pointers and sizes only; every buffer is allocated and owned by the caller;
+ *     nothing is retained after a call returns.  `on_device` says whether the pointers of
+ *     a problem/result are CUDA device pointers (on the handle's device) or host pointers.
+ *   - return value: 0 ok; <0 = -(index of the offending argument/field); >0 = a CUDA
+ *     error code (text via dgibbs_last_error).  A numerically non-positive-definite
+ *     system is NOT an error: it is reported per baseline through success[]/n_done[],
+ *     reproducing delay.py:1891-1896 and 1261-1265.
+ *   - one handle per process/rank, bound to one CUDA device; calls on one handle are
+ *     synchronous with respect to the handle's stream and not re-entrant.
+ */
+#ifndef DGIBBS_H
+#define DGIBBS_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DGIBBS_VERSION 100 /* 0.1.0 */
+
+/* window_id: index into the cosine-sum table of draco/util/tools.py:584-595 */
+enum {
+  DGIBBS_WINDOW_NONE = -1,
+  DGIBBS_WINDOW_UNIFORM = 0,
+  DGIBBS_WINDOW_HANN = 1,
+  DGIBBS_WINDOW_HANNING = 2,
+  DGIBBS_WINDOW_HAMMING = 3,
+  DGIBBS_WINDOW_BLACKMAN = 4,
+  DGIBBS_WINDOW_NUTTALL = 5,
+  DGIBBS_WINDOW_BLACKMAN_NUTTALL = 6,
+  DGIBBS_WINDOW_BLACKMAN_HARRIS = 7
+};
+
+/* rng_mode */
+enum {
+  DGIBBS_RNG_INJECTED = 0, /* caller supplies w1, w2, chi2 in the reference's draw order */
+  DGIBBS_RNG_PHILOX = 1,   /* device Philox4x32-10 keyed on (seed, global baseline id, iteration) */
+  DGIBBS_RNG_ZERO = 2      /* no perturbation: the signal draw becomes the Wiener mean */
+};
+
+/* branch[] values (which solver ran for a baseline) */
+enum {
+  DGIBBS_BRANCH_SKIPPED = 0,
+  DGIBBS_BRANCH_DELAY_SPACE = 1, /* _draw_signal_sample_f, n_sys x n_sys system, delay.py:1778-1819 */
+  DGIBBS_BRANCH_FREQ_SPACE = 2,  /* _draw_signal_sample_t, 2M x 2M system,     delay.py:1821-1860 */
+  DGIBBS_BRANCH_DIAGONAL = 3     /* diagonal(+rank-1) special case of the _f system */
+};
+
+typedef struct dgibbs_handle_s* dgibbs_handle;
+
+/*
+ * One batch of baselines sharing N (number of delays), window and mode.
+ * Ragged per-baseline shapes are described by offset arrays, i.e. each baseline is stored
+ * exactly as DelayTransformBase._cut_data (delay.py:516-597) returns it:
+ *   data  : complex128, baseline b occupies data[data_off[b] .. data_off[b+1]) (complex
+ *           elements), row-major (T[b], M[b])
+ *   Ni    : float64 inverse noise variance, baseline b at Ni[chan_off[b] .. chan_off[b+1])
+ *   fsel  : int64 channel indices (values in [0, N/2] real mode, [0, N) complex mode),
+ *           same offsets as Ni
+ */
+typedef struct {
+  int32_t struct_size; /* sizeof(dgibbs_problem), for forward compatibility */
+  int32_t on_device;   /* 1: array pointers below are device pointers; 0: host pointers */
+  int32_t B;           /* baselines in the batch */
+  int32_t N;           /* number of delays (even) */
+  int32_t niter;       /* Gibbs iterations (nsamp) */
+  int32_t window_id;
+  int32_t complex_timedomain;
+  int32_t rng_mode;
+  uint64_t seed;
+  double median_frac;         /* spectrum = median of the last int(niter*median_frac) samples */
+  const int32_t* T;           /* [B] samples per baseline */
+  const int32_t* M;           /* [B] retained channels per baseline */
+  const int64_t* data_off;    /* [B+1] */
+  const int64_t* chan_off;    /* [B+1] */
+  const void* data;           /* complex128 */
+  const double* Ni;
+  const int64_t* fsel;
+  const double* S0;           /* [B, N] initial power spectrum (prior) */
+  const int64_t* global_id;   /* [B] global baseline index: Philox key, makes results
+                                 independent of sharding; may be NULL (= 0..B-1) */
+  /* injected draws (rng_mode == DGIBBS_RNG_INJECTED), in the reference's order and shapes:
+   *   w1   : baseline b, iteration i at w1[w1_off[b] + i*n_sys*T[b] ...], (n_sys, T[b]) row-major
+   *   w2   : baseline b, iteration i at w2[w2_off[b] + i*2*M[b]*T[b] ...], (2*M[b], T[b])
+   *   chi2 : [B, niter, N]
+   * n_sys = N (real) or 2N (complex_timedomain). */
+  const double* w1;
+  const int64_t* w1_off; /* [B+1] offsets in doubles */
+  const double* w2;
+  const int64_t* w2_off; /* [B+1] */
+  const double* chi2;
+  int32_t force_branch;  /* 0 = choose as the reference does (delay.py:1884-1886); else a
+                            DGIBBS_BRANCH_* value to force where mathematically valid */
+  int32_t reserved;
+} dgibbs_problem;
+
+typedef struct {
+  int32_t struct_size;
+  int32_t on_device;
+  double* spectrum;   /* [B, N] fftshifted median (delay.py:1256-1260); prior if the chain is empty */
+  double* samples;    /* [niter, B, N] unshifted samples, zero where a chain stopped early
+                         (front-padded like delay.py:1175-1178); may be NULL */
+  int32_t* n_done;    /* [B] completed iterations */
+  uint8_t* success;   /* [B] 1 = full chain */
+  uint8_t* branch;    /* [B] DGIBBS_BRANCH_* ; may be NULL */
+  double* final_S;    /* [B, N] last state of the chain (to continue it); may be NULL */
+} dgibbs_result;
+
+/* timings of the last dgibbs_run on a handle, CUDA events on the handle's stream */
+typedef struct {
+  double ms_h2d;      /* host->device staging (0 when on_device) */
+  double ms_setup;    /* window/whiten/projection-table kernels */
+  double ms_sampler;  /* all Gibbs iterations */
+  double ms_finish;   /* median + fftshift (+ device->host) */
+  int64_t launches;   /* kernels launched by the call */
+  int64_t sampler_launches;
+  double flop_sampler; /* algorithmic fp64 flop of the sampler launches (SURVEY 8d W_f/W_t) */
+  double bytes_sampler; /* algorithmic HBM bytes (diagonal branch, Q_d) */
+} dgibbs_timing;
+
+int dgibbs_version(void);
+
+/* Create a handle on CUDA device `device_id`.  `stream` is a cudaStream_t passed as an
+ * integer (0 = the library creates its own non-blocking stream). */
+int dgibbs_create(int device_id, uint64_t stream, dgibbs_handle* out);
+int dgibbs_destroy(dgibbs_handle h);
+const char* dgibbs_last_error(dgibbs_handle h);
+
+/* Upper bound of device workspace (bytes) dgibbs_run would allocate for this problem. */
+int dgibbs_workspace_bytes(dgibbs_handle h, const dgibbs_problem* p, int64_t* bytes);
+
+/* Run every chain of the batch on the device (replaces delay.py:1146-1178). */
+int dgibbs_run(dgibbs_handle h, const dgibbs_problem* p, dgibbs_result* r);
+int dgibbs_get_timing(dgibbs_handle h, dgibbs_timing* t);
+
+/* Debug / parity: the three return values of _compute_delay_spectrum_inputs
+ * (delay.py:1657-1710) for baseline `b` of the problem, written to HOST or DEVICE buffers
+ * according to p->on_device:
+ *   data_w : (2M, T)      windowed + whitened data, interleaved re/im rows
+ *   FTNih  : (n_sys, 2M)
+ *   FTNiF  : (n_sys, n_sys)
+ * any of the three may be NULL. */
+int dgibbs_setup_inputs(dgibbs_handle h, const dgibbs_problem* p, int32_t b,
+                        double* data_w, double* FTNih, double* FTNiF);
+
+/* Wiener filter (delay.py:2132-2201): one deterministic solve per baseline with
+ * S = delay_PS (passed in p->S0); `out` is [sum_b T[b] * n_sys] doubles, baseline b at
+ * offset n_sys * sum_{b'<b} T[b'], row-major (T[b], n_sys) (i.e. complex128 (T, N) in
+ * complex_timedomain mode). */
+int dgibbs_wiener(dgibbs_handle h, const dgibbs_problem* p, double* out, uint8_t* success);
+
+/* Fourier matrices of delay.py:1480-1613 generated on the device (API completeness and
+ * the definition of the masked forward/inverse DFT kernels); `kind`: 0 r2c (2M,N),
+ * 1 c2r (N,2M), 2 c2c (2M,2N), 3 complex (M,N) as interleaved re/im.  Host output. */
+int dgibbs_fourier_matrix(dgibbs_handle h, int32_t kind, int32_t N, const int64_t* fsel,
+                          int32_t M, double* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DGIBBS_H */
