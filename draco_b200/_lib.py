@@ -28,6 +28,7 @@ BRANCH_SKIPPED, BRANCH_DELAY_SPACE, BRANCH_FREQ_SPACE, BRANCH_DIAGONAL = 0, 1, 2
 
 EXPORTED = [
     "dgibbs_version",
+    "dgibbs_sizeof",
     "dgibbs_create",
     "dgibbs_destroy",
     "dgibbs_last_error",
@@ -114,6 +115,7 @@ def load():
         )
     lib = C.CDLL(LIB_PATH)
     lib.dgibbs_version.restype = C.c_int
+    lib.dgibbs_sizeof.argtypes = [C.c_int]
     lib.dgibbs_create.argtypes = [C.c_int, C.c_uint64, C.POINTER(_vp)]
     lib.dgibbs_destroy.argtypes = [_vp]
     lib.dgibbs_last_error.argtypes = [_vp]
@@ -127,6 +129,10 @@ def load():
     for name in EXPORTED:
         if name not in ("dgibbs_last_error", "dgibbs_version"):
             getattr(lib, name).restype = C.c_int
+    for which, st in enumerate((Problem, Result, Timing)):
+        if lib.dgibbs_sizeof(which) != C.sizeof(st):
+            raise RuntimeError(f"ABI mismatch: {st.__name__} is {C.sizeof(st)} bytes here, "
+                               f"{lib.dgibbs_sizeof(which)} in {LIB_PATH}; rebuild the library")
     _lib = lib
     return lib
 

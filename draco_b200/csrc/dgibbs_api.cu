@@ -68,6 +68,15 @@ static cudaError_t pool_get(dgibbs_handle h, const char* name, size_t bytes, voi
 
 extern "C" int dgibbs_version(void) { return DGIBBS_VERSION; }
 
+extern "C" int dgibbs_sizeof(int which) {
+  switch (which) {
+    case 0: return (int)sizeof(dgibbs_problem);
+    case 1: return (int)sizeof(dgibbs_result);
+    case 2: return (int)sizeof(dgibbs_timing);
+    default: return -1;
+  }
+}
+
 extern "C" int dgibbs_create(int device_id, uint64_t stream, dgibbs_handle* out) {
   if (!out) return -3;
   *out = nullptr;

@@ -136,6 +136,9 @@ typedef struct {
 } dgibbs_timing;
 
 int dgibbs_version(void);
+/* sizeof of the ABI structs as compiled (0: dgibbs_problem, 1: dgibbs_result, 2: dgibbs_timing);
+ * lets a binding verify its struct layout without a GPU. */
+int dgibbs_sizeof(int which);
 
 /* Create a handle on CUDA device `device_id`.  `stream` is a cudaStream_t passed as an
  * integer (0 = the library creates its own non-blocking stream). */

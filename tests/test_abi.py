@@ -1,0 +1,66 @@
+"""The C-ABI boundary without a GPU: the library builds/loads, exports every symbol the
+header declares, struct layouts agree, and compute entry points fail loudly (no fallback)."""
+import ctypes as C
+import os
+import re
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def lib():
+    from draco_b200 import _build, _lib
+
+    _build.build()
+    return _lib.load()
+
+
+def _declared():
+    hdr = open(os.path.join(ROOT, "include", "dgibbs.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    return sorted(set(re.findall(r"\b(dgibbs_[a-z_]+)\s*\(", hdr)))
+
+
+def test_header_symbols_exported(lib):
+    names = _declared()
+    assert len(names) >= 10
+    for n in names:
+        assert hasattr(lib, n), f"{n} declared in include/dgibbs.h but not exported"
+
+
+def test_binding_lists_every_symbol():
+    from draco_b200 import _lib
+
+    assert sorted(_lib.EXPORTED) == _declared()
+
+
+def test_struct_sizes(lib):
+    from draco_b200 import _lib
+
+    assert lib.dgibbs_sizeof(0) == C.sizeof(_lib.Problem)
+    assert lib.dgibbs_sizeof(1) == C.sizeof(_lib.Result)
+    assert lib.dgibbs_sizeof(2) == C.sizeof(_lib.Timing)
+    assert lib.dgibbs_version() == 100
+
+
+def test_no_cpu_fallback(lib):
+    """Without a CUDA device the product path must raise, never compute on the CPU."""
+    import torch
+
+    from draco_b200 import _lib
+
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    with pytest.raises(_lib.DGibbsError):
+        _lib.Handle(0)
+
+
+def test_product_does_not_import_oracle():
+    pkg = os.path.join(ROOT, "draco_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                src = open(os.path.join(dirpath, f)).read()
+                assert not re.search(r"^\s*(from|import)\s+oracle", src, flags=re.M), f
