@@ -238,7 +238,7 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     nbase = args.nbase or cfg.nbase  # per rank: weak scaling
     group_size = 64
-    ngroup = max(1, world * nbase // group_size)
+    ngroup = max(1, -(-world * nbase // group_size))
 
     pb_host = make_inputs(cfg, nbase, base_offset=rank * nbase)
     pb_dev = pb_host.to_device(local)

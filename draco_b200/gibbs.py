@@ -73,7 +73,7 @@ class PackedBatch:
                 if v.dtype == np.complex128:
                     v = torch.from_numpy(v.view(np.float64)).to(dev)
                 else:
-                    v = torch.from_numpy(v).to(dev)
+                    v = torch.from_numpy(np.ascontiguousarray(v).copy() if not v.flags.writeable else v).to(dev)
             kw[f.name] = v
         return PackedBatch(**kw)
 

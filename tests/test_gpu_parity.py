@@ -173,13 +173,15 @@ def test_device_resident_equals_host_path(gibbs):
 
 
 def test_philox_posterior_statistics(gibbs):
-    """Native-RNG mode: posterior of log S agrees with the oracle chain run with numpy's RNG
-    (means within 3 sigma, two-sample KS at a Bonferroni-adjusted level)."""
+    """Native-RNG mode: 64 independent chains x 200 iterations on each side (device Philox vs the
+    oracle with numpy's generator), first half discarded.  Per delay, the posterior mean of log S
+    agrees within 3 sigma (Bonferroni-widened maximum) and two-sample KS tests pass.  Samples
+    inside one chain are strongly autocorrelated (unconstrained delays random-walk in log S), so
+    every test uses one independent number per chain: the chain mean, and the final sample."""
     from scipy import stats
 
-    N, M, T, niter, nb = 64, 29, 16, 400, 24
+    N, M, T, niter, nb = 64, 29, 16, 200, 64
     data, Ni, fsel, S0 = make_case(N, M, T, False, False, seed=42)
-    # independent chains: same data replicated, different streams
     pb = gibbs.pack_batch([data] * nb, [Ni] * nb, [fsel] * nb, N, np.full((nb, N), 10.0), global_id=np.arange(nb))
     res = gibbs.run_batch(pb, niter, seed=123, save_samples=True)
     assert res.success.all()
@@ -187,19 +189,18 @@ def test_philox_posterior_statistics(gibbs):
     ora = []
     for c in range(nb):
         s, ok = oracle.gibbs_chain(data, N, Ni, S0, "nuttall", fsel, niter, np.random.default_rng(1000 + c))
+        assert ok
         ora.append(np.log(np.array(s)[niter // 2:]))
     ora = np.stack(ora, axis=1)
-    # chain means are independent across chains -> standard error from the between-chain scatter
-    md, mo = dev.mean(axis=0), ora.mean(axis=0)  # [chain, delay]
+    md, mo = dev.mean(axis=0), ora.mean(axis=0)  # chain means [chain, delay], iid across chains
     se = np.sqrt(md.var(axis=0, ddof=1) / nb + mo.var(axis=0, ddof=1) / nb)
     zscore = (md.mean(axis=0) - mo.mean(axis=0)) / se
-    assert np.max(np.abs(zscore)) < 4.0, zscore  # 64 delays: 3 sigma per delay, Bonferroni -> ~4
-    assert np.mean(np.abs(zscore) < 3.0) > 0.95
-    # KS on thinned post-burn-in samples at 16 delays
-    alpha = 0.01 / 16
+    assert np.mean(np.abs(zscore) < 3.0) >= 0.95, zscore
+    assert np.max(np.abs(zscore)) < 4.2, zscore  # P(max of 64 |z| > 4.2) ~ 2e-3
+    alpha = 0.01 / (2 * 16)  # Bonferroni over 16 delays x 2 statistics
     for k in range(0, N, 4):
-        p = stats.ks_2samp(dev[::10, :, k].ravel(), ora[::10, :, k].ravel()).pvalue
-        assert p > alpha, (k, p)
+        assert stats.ks_2samp(md[:, k], mo[:, k]).pvalue > alpha, k
+        assert stats.ks_2samp(dev[-1, :, k], ora[-1, :, k]).pvalue > alpha, k
 
 
 def test_full_size_properties(gibbs):
