@@ -2,6 +2,7 @@
 // kernel launches and timing.  There is NO CPU fallback: every entry point that computes
 // requires a CUDA device and returns the CUDA error otherwise.
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <string>
@@ -345,6 +346,11 @@ extern "C" int dgibbs_run(dgibbs_handle h, const dgibbs_problem* p, dgibbs_resul
   d.samples = d_samples;
   CU(cudaEventRecord(h->ev[2], h->stream));
 
+  if (getenv("DGIBBS_PROFILE")) {
+    CU(pool_get(h, "prof", 16 * sizeof(long long), &q));
+    CU(cudaMemsetAsync(q, 0, 16 * sizeof(long long), h->stream));
+    d.prof = (long long*)q;
+  }
   // --- the chains: one persistent launch covers every iteration of every baseline
   double flop = 0.0;
   if (d.niter > 0) {
@@ -367,6 +373,16 @@ extern "C" int dgibbs_run(dgibbs_handle h, const dgibbs_problem* p, dgibbs_resul
   }
   CU(cudaEventRecord(h->ev[4], h->stream));
   CU(cudaStreamSynchronize(h->stream));
+  if (d.prof) {
+    long long pc[16];
+    CU(cudaMemcpy(pc, d.prof, sizeof pc, cudaMemcpyDeviceToHost));
+    static const char* names[12] = {"prepass", "phase0_gemm", "diag_gemm", "diag_potrf", "diag_trtri", "row_generate",
+                                    "row_gemm", "row_loadW", "row_trimul_store", "back_gemm", "back_trimul", "draw"};
+    double tot = 0;
+    for (int i = 0; i < 12; i++) tot += (double)pc[i];
+    for (int i = 0; i < 12; i++)
+      fprintf(stderr, "[dgibbs prof] %-18s %14lld cyc  %5.1f%%\n", names[i], pc[i], 100.0 * pc[i] / (tot > 0 ? tot : 1));
+  }
 
   // bookkeeping that needs n_done
   std::vector<int> nd(d.B);

@@ -63,6 +63,7 @@ struct DevBatch {
   double* Si;    // [nslots][npad]
   double* xout;  // wiener: [sum T][nsys] output; else null
   const long long* xoff;  // [B] row offsets into xout
+  long long* prof;        // optional [16] phase cycle counters (debug), else null
 };
 
 // setup_kernels.cu

@@ -23,6 +23,17 @@ static_assert(TILE * LDA_NT + KC * LDB_NN <= STAGE_DOUBLES, "NN stage must fit")
 
 typedef double Acc[2][16][2];
 
+// optional phase profiler (DevBatch::prof != nullptr): thread 0 accumulates clock64 deltas per phase
+#define PROF(idx)                                   \
+  do {                                              \
+    if (d.prof && threadIdx.x == 0) {               \
+      long long t_ = clock64();                     \
+      atomicAdd((unsigned long long*)&d.prof[idx], (unsigned long long)(t_ - tlast)); \
+      tlast = t_;                                   \
+    }                                               \
+  } while (0)
+
+
 struct Lane {
   int warp, g, q;
   int rf[2];  // the two 8-row fragments of this warp: {w, 15-w} (balances triangular tiles)
@@ -313,6 +324,7 @@ __global__ void __launch_bounds__(THREADS, 1) dense_sampler_kernel(DevBatch d, i
   double* uT = d.uT + (size_t)slot * RT * TILE * Kpad;
   double* Si = d.Si + (size_t)slot * npad;
 
+  long long tlast = clock64();
   for (int b = slot; b < d.B; b += gridDim.x) {
     if (d.failed[b]) continue;
     const int Tb = d.T[b], Mb = d.M[b];
@@ -393,6 +405,7 @@ __global__ void __launch_bounds__(THREADS, 1) dense_sampler_kernel(DevBatch d, i
         }
       }
       __syncthreads();
+      PROF(0);
 
       Acc acc;
       // ---------------- phase 0: Y += u F
@@ -407,6 +420,7 @@ __global__ void __launch_bounds__(THREADS, 1) dense_sampler_kernel(DevBatch d, i
         }
       }
       __syncthreads();
+      PROF(1);
 
       // ---------------- factor (+ forward solve on the RHS row tiles)
       for (int j = 0; j < nblk && alive; j++) {
@@ -414,6 +428,7 @@ __global__ void __launch_bounds__(THREADS, 1) dense_sampler_kernel(DevBatch d, i
         // diagonal tile
         tile_generate(acc, ct, Si, N, nsys, d.cplx, j, j, ln);
         gemm_nt(pipe, acc, ln, Bp, Bp, npad, j * (TILE / KC), true, true, ln.rf[0], ln.rf[1]);
+        PROF(2);
 #pragma unroll
         for (int f = 0; f < 2; f++)
 #pragma unroll
@@ -425,6 +440,7 @@ __global__ void __launch_bounds__(THREADS, 1) dense_sampler_kernel(DevBatch d, i
             }
         alive = potrf_tile(pipe, scol);
         if (!alive) break;
+        PROF(3);
         trtri_tile(pipe);
         {  // W_j = inv(L_jj) into the diagonal block, zeros above the diagonal
           double* dst = Wk + (size_t)j * TILE * npad + j * TILE;
@@ -436,6 +452,7 @@ __global__ void __launch_bounds__(THREADS, 1) dense_sampler_kernel(DevBatch d, i
           }
         }
         __syncthreads();
+        PROF(4);
         // tiles below the diagonal, then the RHS row tiles
         for (int i = j + 1; i < nblk + RT; i++) {
           bool do0 = true, do1 = true;
@@ -450,11 +467,15 @@ __global__ void __launch_bounds__(THREADS, 1) dense_sampler_kernel(DevBatch d, i
             out = Rh + (size_t)rt * TILE * npad + j * TILE;
             tile_load_global(acc, out, npad, ln);
           }
+          PROF(5);
           gemm_nt(pipe, acc, ln, Wk + (size_t)i * TILE * npad, Bp, npad, j * (TILE / KC), do0, do1, 15, 15);
+          PROF(6);
           load_tile(pipe, Wk + (size_t)j * TILE * npad + j * TILE, npad);
+          PROF(7);
           trimul_nt(acc, pipe, ln, do0, do1);
           tile_store_global(acc, out, npad, ln, do0, do1);
           __syncthreads();
+          PROF(8);
         }
       }
       if (!alive) {
@@ -475,10 +496,12 @@ __global__ void __launch_bounds__(THREADS, 1) dense_sampler_kernel(DevBatch d, i
           tile_load_global(acc, xt, npad, ln);
           gemm_nn<true>(pipe, acc, ln, rrow, npad, Wk + j * TILE, npad, (j + 1) * TILE, (nblk - 1 - j) * (TILE / KC),
                         do0, do1);
+          PROF(9);
           load_tile(pipe, Wk + (size_t)j * TILE * npad + j * TILE, npad);
           trimul_nn(acc, pipe, ln, do0, do1);
           tile_store_global(acc, xt, npad, ln, do0, do1);
           __syncthreads();
+          PROF(10);
         }
       }
 
@@ -534,6 +557,8 @@ __global__ void __launch_bounds__(THREADS, 1) dense_sampler_kernel(DevBatch d, i
         d.samples[((size_t)it * d.B + b) * N + k] = snew;
       }
       if (threadIdx.x == 0) d.n_done[b] = it + 1;
+      __syncthreads();
+      PROF(11);
     }
   }
 }
