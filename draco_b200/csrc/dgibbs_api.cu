@@ -264,6 +264,7 @@ static int stage_batch(dgibbs_handle h, const dgibbs_problem* p, Staged& s, bool
   CU(pool_get(h, "failed", sizeof(int) * (size_t)B, &q)); d.failed = (int*)q;
   const size_t wrows = (size_t)d.npad + (size_t)d.RT * TILE;
   CU(pool_get(h, "work", sizeof(double) * (size_t)d.nslots * wrows * d.npad, &q)); d.work = (double*)q;
+  CU(pool_get(h, "Wp", sizeof(double) * (size_t)d.nslots * dense_wp_doubles_per_slot(d), &q)); d.Wp = (double*)q;
   CU(pool_get(h, "uT", sizeof(double) * (size_t)d.nslots * d.RT * TILE * d.Kpad, &q)); d.uT = (double*)q;
   CU(pool_get(h, "Si", sizeof(double) * (size_t)d.nslots * d.npad, &q)); d.Si = (double*)q;
   {
@@ -376,8 +377,8 @@ extern "C" int dgibbs_run(dgibbs_handle h, const dgibbs_problem* p, dgibbs_resul
   if (d.prof) {
     long long pc[16];
     CU(cudaMemcpy(pc, d.prof, sizeof pc, cudaMemcpyDeviceToHost));
-    static const char* names[12] = {"prepass", "phase0_gemm", "diag_gemm", "diag_potrf", "diag_trtri", "row_generate",
-                                    "row_gemm", "row_loadW", "row_trimul_store", "back_gemm", "back_trimul", "draw"};
+    static const char* names[12] = {"prepass", "phase0_gemm", "diag_gemm", "diag_stage_factor", "diag_storeW", "row_stage_addG",
+                                    "row_gemm", "(unused)", "row_trimul_store", "back_gemm", "back_trimul", "draw"};
     double tot = 0;
     for (int i = 0; i < 12; i++) tot += (double)pc[i];
     for (int i = 0; i < 12; i++)

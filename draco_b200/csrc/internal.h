@@ -59,6 +59,7 @@ struct DevBatch {
   // per-slot workspace
   double* work;  // [nslots][(npad + RT*TILE)][npad]  L (lower) with W=inv(L_jj) in the diagonal
                  //                                   blocks, then the RHS rows (sample-major)
+  double* Wp;    // [nslots][nblk][8704]  packed inv(L_jj) per block column (for the backward solve)
   double* uT;    // [nslots][RT*TILE][Kpad]
   double* Si;    // [nslots][npad]
   double* xout;  // wiener: [sum T][nsys] output; else null
@@ -76,6 +77,7 @@ cudaError_t launch_fourier_matrix(int kind, int N, const long long* fsel, int M,
 
 // sampler_dense.cu
 size_t dense_smem_bytes(const DevBatch& d);
+size_t dense_wp_doubles_per_slot(const DevBatch& d);
 cudaError_t dense_configure(const DevBatch& d);
 cudaError_t launch_dense_sampler(const DevBatch& d, int it_begin, int it_end, cudaStream_t st);
 

@@ -9,30 +9,37 @@
 //             The RHS rows ride along as extra row tiles, so the forward solve is free.
 //   backward  x = L^-T z  (DMMA), sample-major
 //   draw      S = var_t(x) T / chi2
-// The diagonal blocks hold W_j = inv(L_jj) so that every triangular solve is a DMMA multiply.
+// W_j = inv(L_jj) is kept (packed by 8x8 blocks, bank-swizzled) in shared memory for the whole
+// block column, so every triangular solve is a DMMA multiply against a smem-staged tile.
+//
+// All hot loops are ROLLED or small: straight-line code larger than the instruction caches costs
+// ~140 cycles per 128 B line on this part (measured, profiles/r01a), so register-tile code that
+// touches all 64 accumulators is kept to loads/stores only.
 #include "common.cuh"
 #include "internal.h"
 
 namespace dg {
 
-constexpr int STAGES = 4;
-constexpr int STAGE_DOUBLES = 2 * TILE * LDA_NT;        // A[128][20] + B[128][20]  (NN form needs less)
-constexpr int PIPE_DOUBLES = STAGES * STAGE_DOUBLES;    // 20480 doubles = 160 KB >= one 128x132 tile
-static_assert(PIPE_DOUBLES >= TILE * LDW, "pipeline region must hold a full tile");
+constexpr int STAGES = 3;
+constexpr int STAGE_DOUBLES = 2 * TILE * LDA_NT;      // A[128][20] + B[128][20]  (NN form needs less)
+constexpr int TILE_DOUBLES = TILE * LDW;              // one staged 128x128 tile, pitch 132
+constexpr int PIPE_DOUBLES = (STAGES * STAGE_DOUBLES > TILE_DOUBLES) ? STAGES * STAGE_DOUBLES : TILE_DOUBLES;
+constexpr int WP_BLOCKS = 16 * 17 / 2;                // lower-triangular 8x8 blocks of a 128x128 tile
+constexpr int WP_DOUBLES = WP_BLOCKS * 64;            // 8704 doubles = 68 KB
+constexpr int MISC_DOUBLES = 8;                       // flag
 static_assert(TILE * LDA_NT + KC * LDB_NN <= STAGE_DOUBLES, "NN stage must fit");
 
 typedef double Acc[2][16][2];
 
 // optional phase profiler (DevBatch::prof != nullptr): thread 0 accumulates clock64 deltas per phase
-#define PROF(idx)                                   \
-  do {                                              \
-    if (d.prof && threadIdx.x == 0) {               \
-      long long t_ = clock64();                     \
-      atomicAdd((unsigned long long*)&d.prof[idx], (unsigned long long)(t_ - tlast)); \
-      tlast = t_;                                   \
-    }                                               \
+#define PROF(idx)                                                                       \
+  do {                                                                                  \
+    if (d.prof && threadIdx.x == 0) {                                                   \
+      long long t_ = clock64();                                                         \
+      atomicAdd((unsigned long long*)&d.prof[idx], (unsigned long long)(t_ - tlast));   \
+      tlast = t_;                                                                       \
+    }                                                                                   \
   } while (0)
-
 
 struct Lane {
   int warp, g, q;
@@ -46,6 +53,19 @@ struct Lane {
     rf[1] = 15 - warp;
   }
 };
+
+// which 8-column blocks each of the two row fragments of a warp computes (compile-time variants:
+// predicated-off DMMAs still occupy the fp64 tensor pipe, so skipping must be a real branch)
+enum Variant { V_FULL = 0, V_ROW0 = 1, V_ROW1 = 2, V_NONE = 3, V_DIAG_LO = 4, V_DIAG_HI = 5 };
+
+__device__ __forceinline__ int rhs_variant(bool do0, bool do1) {
+  return do0 ? (do1 ? V_FULL : V_ROW0) : (do1 ? V_ROW1 : V_NONE);
+}
+
+// packed W: block (bn, bk), bk <= bn, at ((bn*(bn+1))/2 + bk) * 64; element (r, c) of the block at
+// r*8 + (c ^ swz(r)),  swz(r) = ((r >> 1) & 1) << 2  (conflict-free fragment reads in both forms)
+__device__ __forceinline__ int wp_block(int bn, int bk) { return ((bn * (bn + 1)) / 2 + bk) * 64; }
+__device__ __forceinline__ int wp_swz(int r) { return ((r >> 1) & 1) << 2; }
 
 // ----------------------------------------------------------------------------- loaders
 // NT chunk: A rows [0,128) x k0..k0+KC of a row-major panel (ld), same for B.
@@ -73,42 +93,40 @@ __device__ __forceinline__ void load_nn(double* stage, const double* A, int lda,
     cp_async16(sB + krow * LDB_NN + c * 2, Bm + (size_t)(k0 + krow) * ldb + c * 2);
   }
 }
-// full 128x128 tile (row pitch ld in global) -> smem pitch LDW
-__device__ __forceinline__ void load_tile(double* sW, const double* src, int ld) {
-#pragma unroll 4
-  for (int r = 0; r < 32; r++) {
-    int idx = threadIdx.x + THREADS * r;  // 0..8191
-    int row = idx >> 6, c = idx & 63;
-    cp_async16(sW + row * LDW + c * 2, src + (size_t)row * ld + c * 2);
-  }
+// packed W_j (contiguous WP_DOUBLES in global) -> smem
+__device__ __forceinline__ void load_wp(double* sWp, const double* src) {
+  for (int idx = threadIdx.x; idx < WP_DOUBLES / 2; idx += THREADS) cp_async16(sWp + idx * 2, src + idx * 2);
   cp_async_commit();
   cp_async_wait<0>();
   __syncthreads();
 }
 
 // ----------------------------------------------------------------------------- chunk math
-// acc -= A * B^T over one KC chunk (A, B both [row][k]).  nbmax: last column block to touch.
-__device__ __forceinline__ void mma_nt(const double* stage, Acc& acc, const Lane& ln, bool do0, bool do1,
-                                       int nbmax0, int nbmax1) {
+// acc -= A * B^T over one KC chunk (A, B both [row][k]); NB0/NB1 = column blocks done for rf0/rf1.
+template <int NB0, int NB1>
+__device__ __forceinline__ void mma_nt(const double* stage, Acc& acc, const Lane& ln) {
   const double* sA = stage;
   const double* sB = stage + TILE * LDA_NT;
   const int r0 = (ln.rf[0] * 8 + ln.g) * LDA_NT + ln.q;
   const int r1 = (ln.rf[1] * 8 + ln.g) * LDA_NT + ln.q;
   const int rb = ln.g * LDA_NT + ln.q;
+  constexpr int NBM = NB0 > NB1 ? NB0 : NB1;
 #pragma unroll
   for (int ks = 0; ks < KC / 4; ks++) {
-    double a0 = -sA[r0 + ks * 4], a1 = -sA[r1 + ks * 4];
+    double a0 = 0, a1 = 0;
+    if (NB0 > 0) a0 = -sA[r0 + ks * 4];
+    if (NB1 > 0) a1 = -sA[r1 + ks * 4];
 #pragma unroll
-    for (int nb = 0; nb < 16; nb++) {
+    for (int nb = 0; nb < NBM; nb++) {
       double b = sB[rb + nb * 8 * LDA_NT + ks * 4];
-      if (do0 && nb <= nbmax0) dmma(acc[0][nb][0], acc[0][nb][1], a0, b);
-      if (do1 && nb <= nbmax1) dmma(acc[1][nb][0], acc[1][nb][1], a1, b);
+      if (nb < NB0) dmma(acc[0][nb][0], acc[0][nb][1], a0, b);
+      if (nb < NB1) dmma(acc[1][nb][0], acc[1][nb][1], a1, b);
     }
   }
 }
 // acc += sign * A * B over one KC chunk (A [row][k], B [k][col]).
-template <bool NEG>
-__device__ __forceinline__ void mma_nn(const double* stage, Acc& acc, const Lane& ln, bool do0, bool do1) {
+template <bool NEG, bool D0, bool D1>
+__device__ __forceinline__ void mma_nn(const double* stage, Acc& acc, const Lane& ln) {
   const double* sA = stage;
   const double* sB = stage + TILE * LDA_NT;
   const int r0 = (ln.rf[0] * 8 + ln.g) * LDA_NT + ln.q;
@@ -116,115 +134,22 @@ __device__ __forceinline__ void mma_nn(const double* stage, Acc& acc, const Lane
   const int rb = ln.q * LDB_NN + ln.g;
 #pragma unroll
   for (int ks = 0; ks < KC / 4; ks++) {
-    double a0 = sA[r0 + ks * 4], a1 = sA[r1 + ks * 4];
-    if (NEG) { a0 = -a0; a1 = -a1; }
+    double a0 = 0, a1 = 0;
+    if (D0) a0 = NEG ? -sA[r0 + ks * 4] : sA[r0 + ks * 4];
+    if (D1) a1 = NEG ? -sA[r1 + ks * 4] : sA[r1 + ks * 4];
 #pragma unroll
     for (int nb = 0; nb < 16; nb++) {
       double b = sB[rb + ks * 4 * LDB_NN + nb * 8];
-      if (do0) dmma(acc[0][nb][0], acc[0][nb][1], a0, b);
-      if (do1) dmma(acc[1][nb][0], acc[1][nb][1], a1, b);
+      if (D0) dmma(acc[0][nb][0], acc[0][nb][1], a0, b);
+      if (D1) dmma(acc[1][nb][0], acc[1][nb][1], a1, b);
     }
-  }
-}
-
-// C-fragment (8x8, cols 2q,2q+1) -> A-fragment (8x4) of its column half `half`: A[g][q] = C[g][4*half+q]
-__device__ __forceinline__ double c_to_a(double c0, double c1, int half, const Lane& ln) {
-  int src = (ln.g << 2) + half * 2 + (ln.q >> 1);
-  double v0 = __shfl_sync(0xffffffffu, c0, src);
-  double v1 = __shfl_sync(0xffffffffu, c1, src);
-  return (ln.q & 1) ? v1 : v0;
-}
-
-// In place  acc <- acc * W^T  with W lower triangular in smem (W[n][k], pitch LDW): phase 2 of a tile.
-__device__ __forceinline__ void trimul_nt(Acc& acc, const double* sW, const Lane& ln, bool do0, bool do1) {
-#pragma unroll
-  for (int nb = 15; nb >= 0; nb--) {
-    double o00 = 0, o01 = 0, o10 = 0, o11 = 0;
-#pragma unroll
-    for (int kb = 0; kb <= nb; kb++) {
-#pragma unroll
-      for (int half = 0; half < 2; half++) {
-        double b = sW[(nb * 8 + ln.g) * LDW + kb * 8 + half * 4 + ln.q];
-        double a0 = c_to_a(acc[0][kb][0], acc[0][kb][1], half, ln);
-        double a1 = c_to_a(acc[1][kb][0], acc[1][kb][1], half, ln);
-        if (do0) dmma(o00, o01, a0, b);
-        if (do1) dmma(o10, o11, a1, b);
-      }
-    }
-    acc[0][nb][0] = o00; acc[0][nb][1] = o01;
-    acc[1][nb][0] = o10; acc[1][nb][1] = o11;
-  }
-}
-// In place  acc <- acc * W  (W[k][n] lower triangular: k >= n): backward substitution step.
-__device__ __forceinline__ void trimul_nn(Acc& acc, const double* sW, const Lane& ln, bool do0, bool do1) {
-#pragma unroll
-  for (int nb = 0; nb < 16; nb++) {
-    double o00 = 0, o01 = 0, o10 = 0, o11 = 0;
-#pragma unroll
-    for (int kb = nb; kb < 16; kb++) {
-#pragma unroll
-      for (int half = 0; half < 2; half++) {
-        double b = sW[(kb * 8 + half * 4 + ln.q) * LDW + nb * 8 + ln.g];
-        double a0 = c_to_a(acc[0][kb][0], acc[0][kb][1], half, ln);
-        double a1 = c_to_a(acc[1][kb][0], acc[1][kb][1], half, ln);
-        if (do0) dmma(o00, o01, a0, b);
-        if (do1) dmma(o10, o11, a1, b);
-      }
-    }
-    acc[0][nb][0] = o00; acc[0][nb][1] = o01;
-    acc[1][nb][0] = o10; acc[1][nb][1] = o11;
-  }
-}
-
-// ----------------------------------------------------------------------------- tile I/O
-__device__ __forceinline__ void tile_load_global(Acc& acc, const double* base, int ld, const Lane& ln) {
-#pragma unroll
-  for (int f = 0; f < 2; f++)
-#pragma unroll
-    for (int nb = 0; nb < 16; nb++) {
-      double2 v = *reinterpret_cast<const double2*>(base + (size_t)(ln.rf[f] * 8 + ln.g) * ld + nb * 8 + 2 * ln.q);
-      acc[f][nb][0] = v.x;
-      acc[f][nb][1] = v.y;
-    }
-}
-__device__ __forceinline__ void tile_store_global(const Acc& acc, double* base, int ld, const Lane& ln, bool do0,
-                                                  bool do1) {
-#pragma unroll
-  for (int f = 0; f < 2; f++) {
-    if (f == 0 ? !do0 : !do1) continue;
-#pragma unroll
-    for (int nb = 0; nb < 16; nb++)
-      *reinterpret_cast<double2*>(base + (size_t)(ln.rf[f] * 8 + ln.g) * ld + nb * 8 + 2 * ln.q) =
-          make_double2(acc[f][nb][0], acc[f][nb][1]);
-  }
-}
-// Tile (ti, tj) of Ci = circ(c) + diag(Si), identity in the padding.
-__device__ __forceinline__ void tile_generate(Acc& acc, const double* ct, const double* Si, int N, int nsys, int cplx,
-                                              int ti, int tj, const Lane& ln) {
-#pragma unroll
-  for (int f = 0; f < 2; f++) {
-    int r = ti * TILE + ln.rf[f] * 8 + ln.g;
-#pragma unroll
-    for (int nb = 0; nb < 16; nb++)
-#pragma unroll
-      for (int e = 0; e < 2; e++) {
-        int c = tj * TILE + nb * 8 + 2 * ln.q + e;
-        double v;
-        if (r < nsys && c < nsys) {
-          v = circ_entry(ct, N, cplx, r, c);
-          if (r == c) v += Si[r];
-        } else {
-          v = (r == c) ? 1.0 : 0.0;
-        }
-        acc[f][nb][e] = v;
-      }
   }
 }
 
 // ----------------------------------------------------------------------------- pipelined K loops
 // acc -= A[0:128, k] * B[0:128, k]^T  for k in [0, nchunks*KC)
 __device__ __forceinline__ void gemm_nt(double* pipe, Acc& acc, const Lane& ln, const double* A, const double* Bm,
-                                        int ld, int nchunks, bool do0, bool do1, int nbmax0, int nbmax1) {
+                                        int ld, int nchunks, int variant) {
 #pragma unroll
   for (int s = 0; s < STAGES - 1; s++) {
     if (s < nchunks) load_nt(pipe + s * STAGE_DOUBLES, A, Bm, ld, s * KC);
@@ -236,15 +161,23 @@ __device__ __forceinline__ void gemm_nt(double* pipe, Acc& acc, const Lane& ln, 
     int nxt = c + STAGES - 1;
     if (nxt < nchunks) load_nt(pipe + (nxt % STAGES) * STAGE_DOUBLES, A, Bm, ld, nxt * KC);
     cp_async_commit();
-    mma_nt(pipe + (c % STAGES) * STAGE_DOUBLES, acc, ln, do0, do1, nbmax0, nbmax1);
+    const double* st = pipe + (c % STAGES) * STAGE_DOUBLES;
+    switch (variant) {  // warp-uniform
+      case V_FULL: mma_nt<16, 16>(st, acc, ln); break;
+      case V_ROW0: mma_nt<16, 0>(st, acc, ln); break;
+      case V_ROW1: mma_nt<0, 16>(st, acc, ln); break;
+      case V_DIAG_LO: mma_nt<4, 16>(st, acc, ln); break;
+      case V_DIAG_HI: mma_nt<8, 12>(st, acc, ln); break;
+      default: break;
+    }
   }
   cp_async_wait<0>();
   __syncthreads();
 }
-// acc (+/-)= A[0:128, k0 + k] * B[k0 + k, 0:128]  for k in [0, nchunks*KC)
+// acc (+/-)= A[0:128, kbase + k] * B[kbase + k, 0:128]  for k in [0, nchunks*KC)
 template <bool NEG>
 __device__ __forceinline__ void gemm_nn(double* pipe, Acc& acc, const Lane& ln, const double* A, int lda,
-                                        const double* Bm, int ldb, int kbase, int nchunks, bool do0, bool do1) {
+                                        const double* Bm, int ldb, int kbase, int nchunks, int variant) {
 #pragma unroll
   for (int s = 0; s < STAGES - 1; s++) {
     if (s < nchunks) load_nn(pipe + s * STAGE_DOUBLES, A, lda, Bm, ldb, kbase + s * KC);
@@ -256,71 +189,299 @@ __device__ __forceinline__ void gemm_nn(double* pipe, Acc& acc, const Lane& ln, 
     int nxt = c + STAGES - 1;
     if (nxt < nchunks) load_nn(pipe + (nxt % STAGES) * STAGE_DOUBLES, A, lda, Bm, ldb, kbase + nxt * KC);
     cp_async_commit();
-    mma_nn<NEG>(pipe + (c % STAGES) * STAGE_DOUBLES, acc, ln, do0, do1);
+    const double* st = pipe + (c % STAGES) * STAGE_DOUBLES;
+    switch (variant) {
+      case V_FULL: mma_nn<NEG, true, true>(st, acc, ln); break;
+      case V_ROW0: mma_nn<NEG, true, false>(st, acc, ln); break;
+      case V_ROW1: mma_nn<NEG, false, true>(st, acc, ln); break;
+      default: break;
+    }
   }
   cp_async_wait<0>();
   __syncthreads();
 }
 
+// ----------------------------------------------------------------------------- tile staging
+__device__ __forceinline__ void acc_zero(Acc& acc) {
+#pragma unroll
+  for (int f = 0; f < 2; f++)
+#pragma unroll
+    for (int nb = 0; nb < 16; nb++) acc[f][nb][0] = acc[f][nb][1] = 0.0;
+}
+// registers -> staged tile sT[128][LDW]
+__device__ __forceinline__ void stage_acc(const Acc& acc, double* sT, const Lane& ln, bool do0, bool do1) {
+#pragma unroll
+  for (int f = 0; f < 2; f++) {
+    if (f == 0 ? !do0 : !do1) continue;
+    double* row = sT + (ln.rf[f] * 8 + ln.g) * LDW + 2 * ln.q;
+#pragma unroll
+    for (int nb = 0; nb < 16; nb++) *reinterpret_cast<double2*>(row + nb * 8) = make_double2(acc[f][nb][0], acc[f][nb][1]);
+  }
+}
+__device__ __forceinline__ void tile_store_global(const Acc& acc, double* base, int ld, const Lane& ln, bool do0,
+                                                  bool do1) {
+#pragma unroll
+  for (int f = 0; f < 2; f++) {
+    if (f == 0 ? !do0 : !do1) continue;
+    double* row = base + (size_t)(ln.rf[f] * 8 + ln.g) * ld + 2 * ln.q;
+#pragma unroll
+    for (int nb = 0; nb < 16; nb++) *reinterpret_cast<double2*>(row + nb * 8) = make_double2(acc[f][nb][0], acc[f][nb][1]);
+  }
+}
+__device__ __forceinline__ void tile_load_global(Acc& acc, const double* base, int ld, const Lane& ln) {
+#pragma unroll
+  for (int f = 0; f < 2; f++) {
+    const double* row = base + (size_t)(ln.rf[f] * 8 + ln.g) * ld + 2 * ln.q;
+#pragma unroll
+    for (int nb = 0; nb < 16; nb++) {
+      double2 v = *reinterpret_cast<const double2*>(row + nb * 8);
+      acc[f][nb][0] = v.x;
+      acc[f][nb][1] = v.y;
+    }
+  }
+}
+// sT += tile (ti, tj) of Ci = circ(c) + diag(Si) (identity in the padding).  Rolled, coalesced.
+__device__ __forceinline__ void add_generated(double* sT, const double* ct, const double* Si, int N, int nsys, int cplx,
+                                              int ti, int tj, bool lower_only) {
+  const bool interior = !cplx && (ti + 1) * TILE <= nsys && (tj + 1) * TILE <= nsys;
+  const int R0 = ti * TILE, C0 = tj * TILE;
+#pragma unroll 2
+  for (int e = threadIdx.x; e < TILE * TILE; e += THREADS) {
+    int r = e >> 7, c = e & 127;
+    if (lower_only && c > r) continue;
+    int R = R0 + r, C = C0 + c;
+    double v;
+    if (interior) {
+      int k = R - C;
+      if (k < 0) k += N;
+      v = ct[k];
+      if (R == C) v += Si[R];
+    } else if (R < nsys && C < nsys) {
+      v = circ_entry(ct, N, cplx, R, C);
+      if (R == C) v += Si[R];
+    } else {
+      v = (R == C) ? 1.0 : 0.0;
+    }
+    sT[r * LDW + c] += v;
+  }
+}
+// sT[0:nrows] += src[0:nrows][0:128]  (row pitch ld in global)
+__device__ __forceinline__ void add_global(double* sT, const double* src, int ld, int nrows) {
+  for (int e = threadIdx.x; e < nrows * (TILE / 2); e += THREADS) {
+    int r = e >> 6, c = (e & 63) * 2;
+    double2 v = *reinterpret_cast<const double2*>(src + (size_t)r * ld + c);
+    double2* p = reinterpret_cast<double2*>(sT + r * LDW + c);
+    double2 o = *p;
+    o.x += v.x;
+    o.y += v.y;
+    *p = o;
+  }
+}
+
+// In place  sT <- sT * inv(L_jj)^T  by blocked forward substitution over the 16 column blocks:
+//   X_p = (C_p - sum_{k<p} X_k L(p,k)^T) W8_p^T ,  W8_p = inv(L(p,p))  (8x8, well conditioned)
+// sWp holds L_jj packed by 8x8 blocks with W8_p in the diagonal block slots.  Each warp owns its 16
+// rows, so only __syncwarp is needed.  Same accuracy class as LAPACK's dtrsm (explicit inverses only
+// at the 8x8 level): a full 128x128 inverse costs 20x in accuracy at cond(Ci) ~ 4e8.
+template <bool D0, bool D1>
+__device__ __forceinline__ void trisolve_nt_body(double* sT, const double* sWp, const Lane& ln) {
+  double* r0 = sT + (ln.rf[0] * 8 + ln.g) * LDW;
+  double* r1 = sT + (ln.rf[1] * 8 + ln.g) * LDW;
+  const int q = ln.q, sw = wp_swz(ln.g);
+  const int bo0 = ln.g * 8 + (q ^ sw), bo1 = ln.g * 8 + ((4 + q) ^ sw);
+#pragma unroll 1
+  for (int p = 0; p < 16; p++) {
+    double c00 = 0, c01 = 0, c10 = 0, c11 = 0, e00 = 0, e01 = 0, e10 = 0, e11 = 0;
+    if (D0) { c00 = r0[8 * p + 2 * q]; c01 = r0[8 * p + 2 * q + 1]; }
+    if (D1) { c10 = r1[8 * p + 2 * q]; c11 = r1[8 * p + 2 * q + 1]; }
+    const double* wb = sWp + wp_block(p, 0);
+#pragma unroll 1
+    for (int k = 0; k < p; k++) {
+      double b0 = wb[k * 64 + bo0], b1 = wb[k * 64 + bo1];
+      if (D0) { dmma(c00, c01, -r0[8 * k + q], b0); dmma(e00, e01, -r0[8 * k + 4 + q], b1); }
+      if (D1) { dmma(c10, c11, -r1[8 * k + q], b0); dmma(e10, e11, -r1[8 * k + 4 + q], b1); }
+    }
+    __syncwarp();
+    if (D0) { r0[8 * p + 2 * q] = c00 + e00; r0[8 * p + 2 * q + 1] = c01 + e01; }
+    if (D1) { r1[8 * p + 2 * q] = c10 + e10; r1[8 * p + 2 * q + 1] = c11 + e11; }
+    __syncwarp();
+    const double* w8 = sWp + wp_block(p, p);
+    double b0 = w8[bo0], b1 = w8[bo1];
+    double o00 = 0, o01 = 0, o10 = 0, o11 = 0;
+    if (D0) { dmma(o00, o01, r0[8 * p + q], b0); dmma(o00, o01, r0[8 * p + 4 + q], b1); }
+    if (D1) { dmma(o10, o11, r1[8 * p + q], b0); dmma(o10, o11, r1[8 * p + 4 + q], b1); }
+    __syncwarp();
+    if (D0) { r0[8 * p + 2 * q] = o00; r0[8 * p + 2 * q + 1] = o01; }
+    if (D1) { r1[8 * p + 2 * q] = o10; r1[8 * p + 2 * q + 1] = o11; }
+    __syncwarp();
+  }
+}
+// In place  sT <- sT * inv(L_jj)  by blocked backward substitution:
+//   X_p = (Z_p - sum_{k>p} X_k L(k,p)) W8_p
+template <bool D0, bool D1>
+__device__ __forceinline__ void trisolve_nn_body(double* sT, const double* sWp, const Lane& ln) {
+  double* r0 = sT + (ln.rf[0] * 8 + ln.g) * LDW;
+  double* r1 = sT + (ln.rf[1] * 8 + ln.g) * LDW;
+  const int q = ln.q;
+  const int bo0 = q * 8 + (ln.g ^ wp_swz(q)), bo1 = (4 + q) * 8 + (ln.g ^ wp_swz(4 + q));
+#pragma unroll 1
+  for (int p = 15; p >= 0; p--) {
+    double c00 = 0, c01 = 0, c10 = 0, c11 = 0, e00 = 0, e01 = 0, e10 = 0, e11 = 0;
+    if (D0) { c00 = r0[8 * p + 2 * q]; c01 = r0[8 * p + 2 * q + 1]; }
+    if (D1) { c10 = r1[8 * p + 2 * q]; c11 = r1[8 * p + 2 * q + 1]; }
+#pragma unroll 1
+    for (int k = p + 1; k < 16; k++) {
+      const double* wb = sWp + wp_block(k, p);
+      double b0 = wb[bo0], b1 = wb[bo1];
+      if (D0) { dmma(c00, c01, -r0[8 * k + q], b0); dmma(e00, e01, -r0[8 * k + 4 + q], b1); }
+      if (D1) { dmma(c10, c11, -r1[8 * k + q], b0); dmma(e10, e11, -r1[8 * k + 4 + q], b1); }
+    }
+    __syncwarp();
+    if (D0) { r0[8 * p + 2 * q] = c00 + e00; r0[8 * p + 2 * q + 1] = c01 + e01; }
+    if (D1) { r1[8 * p + 2 * q] = c10 + e10; r1[8 * p + 2 * q + 1] = c11 + e11; }
+    __syncwarp();
+    const double* w8 = sWp + wp_block(p, p);
+    double b0 = w8[bo0], b1 = w8[bo1];
+    double o00 = 0, o01 = 0, o10 = 0, o11 = 0;
+    if (D0) { dmma(o00, o01, r0[8 * p + q], b0); dmma(o00, o01, r0[8 * p + 4 + q], b1); }
+    if (D1) { dmma(o10, o11, r1[8 * p + q], b0); dmma(o10, o11, r1[8 * p + 4 + q], b1); }
+    __syncwarp();
+    if (D0) { r0[8 * p + 2 * q] = o00; r0[8 * p + 2 * q + 1] = o01; }
+    if (D1) { r1[8 * p + 2 * q] = o10; r1[8 * p + 2 * q + 1] = o11; }
+    __syncwarp();
+  }
+}
+template <bool NN>
+__device__ __forceinline__ void trisolve(double* sT, const double* sWp, const Lane& ln, int variant) {
+  switch (variant) {
+    case V_FULL: NN ? trisolve_nn_body<true, true>(sT, sWp, ln) : trisolve_nt_body<true, true>(sT, sWp, ln); break;
+    case V_ROW0: NN ? trisolve_nn_body<true, false>(sT, sWp, ln) : trisolve_nt_body<true, false>(sT, sWp, ln); break;
+    case V_ROW1: NN ? trisolve_nn_body<false, true>(sT, sWp, ln) : trisolve_nt_body<false, true>(sT, sWp, ln); break;
+    default: break;
+  }
+}
+// staged tile rows [0, nrows) -> global (row pitch ld), coalesced
+__device__ __forceinline__ void copy_tile_out(const double* sT, double* dst, int ld, int nrows) {
+  for (int e = threadIdx.x; e < nrows * (TILE / 2); e += THREADS) {
+    int r = e >> 6, c = (e & 63) * 2;
+    *reinterpret_cast<double2*>(dst + (size_t)r * ld + c) = *reinterpret_cast<const double2*>(sT + r * LDW + c);
+  }
+}
+
 // ----------------------------------------------------------------------------- diagonal tile
-// In-place Cholesky of the 128x128 tile in smem (lower).  Returns false on a non-positive pivot
-// (same test as LAPACK dpotrf: ajj <= 0 or NaN).  scol: 128 doubles of scratch.
-__device__ bool potrf_tile(double* sD, double* scol) {
-  const int t = threadIdx.x;
-  for (int k = 0; k < TILE; k++) {
-    __syncthreads();
-    double d = sD[k * LDW + k];
-    if (!(d > 0.0)) return false;  // uniform across the CTA
-    double ajj = sqrt(d);
-    double rinv = 1.0 / ajj;
-    int i = k + 1 + (t >> 1);
-    double lik = 0.0;
-    if (i < TILE) {
-      lik = sD[i * LDW + k] * rinv;
-      if ((t & 1) == 0) scol[i] = lik;
+// In-place blocked Cholesky of the staged 128x128 tile (lower) by 8-column panels.  Per panel p:
+//   S1  all warps : panel blocks  C(rb,p) -= L(rb,0:p) L(p,0:p)^T                      (DMMA)
+//   S2  warp 0    : 8x8 Cholesky of C(p,p) and its inverse W8_p, in registers
+//   S3  all warps : L(rb,p) = C(rb,p) W8_p^T  (rb > p)                                 (DMMA)
+// On exit sWp holds L_jj packed by 8x8 blocks (bank-swizzled) with W8_p in the diagonal slots.
+// Returns false on a non-positive pivot (same test as LAPACK dpotrf: ajj <= 0 or NaN).
+__device__ bool factor_diag(double* sT, double* sWp, double* misc, const Lane& ln) {
+  int* flag = reinterpret_cast<int*>(misc);
+  const int g = ln.g, q = ln.q;
+  const int bo0 = g * 8 + (q ^ wp_swz(g)), bo1 = g * 8 + ((4 + q) ^ wp_swz(g));
+  if (threadIdx.x == 0) *flag = 0;
+  for (int p = 0; p < 16; p++) {
+    // ---- S1
+    for (int rb = p + ln.warp; rb < 16; rb += NWARP) {
+      double* cp = sT + (rb * 8 + g) * LDW + 8 * p + 2 * q;
+      double c0 = cp[0], c1 = cp[1], e0 = 0.0, e1 = 0.0;
+      const double* ap = sT + (rb * 8 + g) * LDW + q;
+      const double* bp = sT + (8 * p + g) * LDW + q;
+#pragma unroll 1
+      for (int k = 0; k < p; k++) {
+        dmma(c0, c1, -ap[8 * k], bp[8 * k]);
+        dmma(e0, e1, -ap[8 * k + 4], bp[8 * k + 4]);
+      }
+      cp[0] = c0 + e0;
+      cp[1] = c1 + e1;
     }
     __syncthreads();
-    if (t == 0) sD[k * LDW + k] = ajj;
-    if (i < TILE) {
-      if ((t & 1) == 0) sD[i * LDW + k] = lik;
-      for (int c = k + 1 + (t & 1); c <= i; c += 2) sD[i * LDW + c] -= lik * scol[c];
+    // ---- S2 (every lane of warp 0 computes the same 8x8 factor; identical-value stores)
+    if (ln.warp == 0) {
+      double a[8][8], w[8][8], rinv[8];
+      bool ok = true;
+#pragma unroll
+      for (int i = 0; i < 8; i++)
+#pragma unroll
+        for (int c = 0; c <= i; c++) a[i][c] = sT[(8 * p + i) * LDW + 8 * p + c];
+#pragma unroll
+      for (int k = 0; k < 8; k++) {
+        double dk = a[k][k];
+        if (!(dk > 0.0)) ok = false;
+        double piv = sqrt(dk);
+        double r = 1.0 / piv;
+        rinv[k] = r;
+        a[k][k] = piv;
+#pragma unroll
+        for (int i = k + 1; i < 8; i++) a[i][k] *= r;
+#pragma unroll
+        for (int c = k + 1; c < 8; c++)
+#pragma unroll
+          for (int i = c; i < 8; i++) a[i][c] -= a[i][k] * a[c][k];
+      }
+#pragma unroll
+      for (int c = 0; c < 8; c++) {
+        w[c][c] = rinv[c];
+#pragma unroll
+        for (int i = c + 1; i < 8; i++) {
+          double s = 0.0;
+#pragma unroll
+          for (int k = c; k < i; k++) s += a[i][k] * w[k][c];
+          w[i][c] = -s * rinv[i];
+        }
+      }
+      double* wpp = sWp + wp_block(p, p);
+#pragma unroll
+      for (int i = 0; i < 8; i++)
+#pragma unroll
+        for (int c = 0; c < 8; c++) wpp[i * 8 + (c ^ wp_swz(i))] = (c <= i) ? w[i][c] : 0.0;
+      if (!ok) *flag = 1;
     }
+    __syncthreads();
+    if (*flag) return false;
+    // ---- S3
+    {
+      const double* w8 = sWp + wp_block(p, p);
+      const double b0 = w8[bo0], b1 = w8[bo1];
+      for (int rb = p + 1 + ln.warp; rb < 16; rb += NWARP) {
+        double* cp = sT + (rb * 8 + g) * LDW + 8 * p;
+        double a0 = cp[q], a1 = cp[4 + q];
+        double o0 = 0.0, o1 = 0.0;
+        dmma(o0, o1, a0, b0);
+        dmma(o0, o1, a1, b1);
+        __syncwarp();
+        cp[2 * q] = o0;
+        cp[2 * q + 1] = o1;
+      }
+    }
+    __syncthreads();
+  }
+  // pack the strictly-lower 8x8 blocks of L_jj next to the W8 diagonal blocks
+  for (int e = threadIdx.x; e < TILE * TILE; e += THREADS) {
+    int n = e >> 7, k = e & 127;
+    int bn = n >> 3, bk = k >> 3;
+    if (bk < bn) sWp[wp_block(bn, bk) + (n & 7) * 8 + ((k & 7) ^ wp_swz(n & 7))] = sT[n * LDW + k];
   }
   __syncthreads();
   return true;
 }
-// In-place inverse of the lower-triangular tile (dtrti2, 'L', 'N').
-__device__ void trtri_tile(double* sD) {
-  const int t = threadIdx.x;
-  for (int j = TILE - 1; j >= 0; j--) {
-    __syncthreads();
-    double ajj = 1.0 / sD[j * LDW + j];
-    int i = j + 1 + (t >> 1);
-    double sum = 0.0;
-    if (i < TILE)
-      for (int k = j + 1 + (t & 1); k <= i; k += 2) sum += sD[i * LDW + k] * sD[k * LDW + j];
-    sum += __shfl_xor_sync(0xffffffffu, sum, 1);
-    __syncthreads();
-    if (i < TILE && (t & 1) == 0) sD[i * LDW + j] = -ajj * sum;
-    if (t == 0) sD[j * LDW + j] = ajj;
-  }
-  __syncthreads();
-}
 
 // ----------------------------------------------------------------------------- the sampler
-// Shared memory:  [ctab: nsys (optional)] [pipe: PIPE_DOUBLES] [scol: TILE] [flag]
+// Shared memory:  [ctab: nsys (optional)] [sWp: WP_DOUBLES] [pipe/tile: PIPE_DOUBLES] [misc]
 __global__ void __launch_bounds__(THREADS, 1) dense_sampler_kernel(DevBatch d, int it_begin, int it_end) {
   extern __shared__ __align__(16) double smem[];
   const Lane ln;
   const int slot = blockIdx.x;
   const int N = d.N, nsys = d.nsys, npad = d.npad, nblk = d.nblk, Kpad = d.Kpad, RT = d.RT;
   double* s_ct = smem;
-  double* pipe = smem + (d.ctab_smem ? nsys : 0);
-  double* scol = pipe + PIPE_DOUBLES;
+  double* sWp = smem + (d.ctab_smem ? nsys : 0);
+  double* pipe = sWp + WP_DOUBLES;
+  double* misc = pipe + PIPE_DOUBLES;
 
   const size_t wrows = (size_t)npad + (size_t)RT * TILE;
   double* Wk = d.work + (size_t)slot * wrows * npad;   // L rows then RHS rows, pitch npad
   double* Rh = Wk + (size_t)npad * npad;               // RHS rows (sample-major)
+  double* Wpg = d.Wp + (size_t)slot * nblk * WP_DOUBLES;  // packed inv(L_jj), one per block column
   double* uT = d.uT + (size_t)slot * RT * TILE * Kpad;
   double* Si = d.Si + (size_t)slot * npad;
 
@@ -411,11 +572,11 @@ __global__ void __launch_bounds__(THREADS, 1) dense_sampler_kernel(DevBatch d, i
       // ---------------- phase 0: Y += u F
       for (int rt = 0; rt < RT; rt++) {
         const bool do0 = rt * 16 + ln.rf[0] < rhs_frags, do1 = rt * 16 + ln.rf[1] < rhs_frags;
+        const int var = rhs_variant(do0, do1);
         for (int cb = 0; cb < nblk; cb++) {
           double* ytile = Rh + (size_t)rt * TILE * npad + cb * TILE;
           tile_load_global(acc, ytile, npad, ln);
-          gemm_nn<false>(pipe, acc, ln, uT + (size_t)rt * TILE * Kpad, Kpad, d.Ftab + cb * TILE, npad, 0, Kpad / KC,
-                         do0, do1);
+          gemm_nn<false>(pipe, acc, ln, uT + (size_t)rt * TILE * Kpad, Kpad, d.Ftab + cb * TILE, npad, 0, Kpad / KC, var);
           tile_store_global(acc, ytile, npad, ln, do0, do1);
         }
       }
@@ -426,54 +587,47 @@ __global__ void __launch_bounds__(THREADS, 1) dense_sampler_kernel(DevBatch d, i
       for (int j = 0; j < nblk && alive; j++) {
         const double* Bp = Wk + (size_t)j * TILE * npad;
         // diagonal tile
-        tile_generate(acc, ct, Si, N, nsys, d.cplx, j, j, ln);
-        gemm_nt(pipe, acc, ln, Bp, Bp, npad, j * (TILE / KC), true, true, ln.rf[0], ln.rf[1]);
+        acc_zero(acc);
+        gemm_nt(pipe, acc, ln, Bp, Bp, npad, j * (TILE / KC), ln.warp < 4 ? V_DIAG_LO : V_DIAG_HI);
         PROF(2);
-#pragma unroll
-        for (int f = 0; f < 2; f++)
-#pragma unroll
-          for (int nb = 0; nb < 16; nb++)
-            if (nb <= ln.rf[f]) {
-              double* p = pipe + (ln.rf[f] * 8 + ln.g) * LDW + nb * 8 + 2 * ln.q;
-              p[0] = acc[f][nb][0];
-              p[1] = acc[f][nb][1];
-            }
-        alive = potrf_tile(pipe, scol);
+        stage_acc(acc, pipe, ln, true, true);
+        __syncthreads();
+        add_generated(pipe, ct, Si, N, nsys, d.cplx, j, j, true);
+        __syncthreads();
+        alive = factor_diag(pipe, sWp, misc, ln);
         if (!alive) break;
         PROF(3);
-        trtri_tile(pipe);
-        {  // W_j = inv(L_jj) into the diagonal block, zeros above the diagonal
-          double* dst = Wk + (size_t)j * TILE * npad + j * TILE;
-          for (int idx = threadIdx.x; idx < TILE * TILE / 2; idx += THREADS) {
-            int r = idx >> 6, c = (idx & 63) * 2;
-            double v0 = (c <= r) ? pipe[r * LDW + c] : 0.0;
-            double v1 = (c + 1 <= r) ? pipe[r * LDW + c + 1] : 0.0;
-            *reinterpret_cast<double2*>(dst + (size_t)r * npad + c) = make_double2(v0, v1);
-          }
-        }
+        for (int idx = threadIdx.x; idx < WP_DOUBLES / 2; idx += THREADS)
+          reinterpret_cast<double2*>(Wpg + (size_t)j * WP_DOUBLES)[idx] = reinterpret_cast<const double2*>(sWp)[idx];
         __syncthreads();
         PROF(4);
         // tiles below the diagonal, then the RHS row tiles
         for (int i = j + 1; i < nblk + RT; i++) {
           bool do0 = true, do1 = true;
+          int nrows = TILE;
           double* out;
           if (i < nblk) {
-            tile_generate(acc, ct, Si, N, nsys, d.cplx, i, j, ln);
             out = Wk + (size_t)i * TILE * npad + j * TILE;
           } else {
             int rt = i - nblk;
             do0 = rt * 16 + ln.rf[0] < rhs_frags;
             do1 = rt * 16 + ln.rf[1] < rhs_frags;
+            nrows = min(TILE, max(0, rhs_frags * 8 - rt * TILE));
             out = Rh + (size_t)rt * TILE * npad + j * TILE;
-            tile_load_global(acc, out, npad, ln);
           }
-          PROF(5);
-          gemm_nt(pipe, acc, ln, Wk + (size_t)i * TILE * npad, Bp, npad, j * (TILE / KC), do0, do1, 15, 15);
+          const int var = rhs_variant(do0, do1);
+          acc_zero(acc);
+          gemm_nt(pipe, acc, ln, Wk + (size_t)i * TILE * npad, Bp, npad, j * (TILE / KC), var);
           PROF(6);
-          load_tile(pipe, Wk + (size_t)j * TILE * npad + j * TILE, npad);
-          PROF(7);
-          trimul_nt(acc, pipe, ln, do0, do1);
-          tile_store_global(acc, out, npad, ln, do0, do1);
+          stage_acc(acc, pipe, ln, do0, do1);
+          __syncthreads();
+          if (i < nblk) add_generated(pipe, ct, Si, N, nsys, d.cplx, i, j, false);
+          else add_global(pipe, out, npad, nrows);
+          __syncthreads();
+          PROF(5);
+          trisolve<false>(pipe, sWp, ln, var);
+          __syncthreads();
+          copy_tile_out(pipe, out, npad, nrows);
           __syncthreads();
           PROF(8);
         }
@@ -490,16 +644,25 @@ __global__ void __launch_bounds__(THREADS, 1) dense_sampler_kernel(DevBatch d, i
       // ---------------- backward solve  x^T = z^T L^-1
       for (int rt = 0; rt < RT; rt++) {
         const bool do0 = rt * 16 + ln.rf[0] < rhs_frags, do1 = rt * 16 + ln.rf[1] < rhs_frags;
+        const int var = rhs_variant(do0, do1);
+        const int nrows = min(TILE, max(0, rhs_frags * 8 - rt * TILE));
         double* rrow = Rh + (size_t)rt * TILE * npad;
         for (int j = nblk - 1; j >= 0; j--) {
           double* xt = rrow + j * TILE;
-          tile_load_global(acc, xt, npad, ln);
-          gemm_nn<true>(pipe, acc, ln, rrow, npad, Wk + j * TILE, npad, (j + 1) * TILE, (nblk - 1 - j) * (TILE / KC),
-                        do0, do1);
+          // W_j streams into sWp underneath the GEMM (its copy group is older than the pipeline's)
+          for (int idx = threadIdx.x; idx < WP_DOUBLES / 2; idx += THREADS)
+            cp_async16(sWp + idx * 2, Wpg + (size_t)j * WP_DOUBLES + idx * 2);
+          cp_async_commit();
+          acc_zero(acc);
+          gemm_nn<true>(pipe, acc, ln, rrow, npad, Wk + j * TILE, npad, (j + 1) * TILE, (nblk - 1 - j) * (TILE / KC), var);
           PROF(9);
-          load_tile(pipe, Wk + (size_t)j * TILE * npad + j * TILE, npad);
-          trimul_nn(acc, pipe, ln, do0, do1);
-          tile_store_global(acc, xt, npad, ln, do0, do1);
+          stage_acc(acc, pipe, ln, do0, do1);
+          __syncthreads();
+          add_global(pipe, xt, npad, nrows);
+          __syncthreads();
+          trisolve<true>(pipe, sWp, ln, var);
+          __syncthreads();
+          copy_tile_out(pipe, xt, npad, nrows);
           __syncthreads();
           PROF(10);
         }
@@ -564,8 +727,9 @@ __global__ void __launch_bounds__(THREADS, 1) dense_sampler_kernel(DevBatch d, i
 }
 
 size_t dense_smem_bytes(const DevBatch& d) {
-  return sizeof(double) * ((d.ctab_smem ? (size_t)d.nsys : 0) + PIPE_DOUBLES + TILE) + 16;
+  return sizeof(double) * ((d.ctab_smem ? (size_t)d.nsys : 0) + WP_DOUBLES + PIPE_DOUBLES + MISC_DOUBLES);
 }
+size_t dense_wp_doubles_per_slot(const DevBatch& d) { return (size_t)d.nblk * WP_DOUBLES; }
 
 cudaError_t dense_configure(const DevBatch& d) {
   return cudaFuncSetAttribute(dense_sampler_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
