@@ -77,3 +77,13 @@ def allreduce_count(n):
     t = torch.tensor([int(n)], dtype=torch.int64, device=dev)
     dist.all_reduce(t)
     return int(t.item())
+
+
+def broadcast_int(value, src=0):
+    """Make one Python int identical on every rank (rank ``src`` wins)."""
+    dist = _dist()
+    if dist is None or dist.get_world_size() == 1:
+        return int(value)
+    box = [int(value)]
+    dist.broadcast_object_list(box, src=src)
+    return int(box[0])
