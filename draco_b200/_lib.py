@@ -97,6 +97,10 @@ class Timing(C.Structure):
         ("sampler_launches", C.c_int64),
         ("flop_sampler", C.c_double),
         ("bytes_sampler", C.c_double),
+        ("ms_diag_project", C.c_double),
+        ("ms_sampler_diag", C.c_double),
+        ("n_dense", C.c_int64),
+        ("n_diag", C.c_int64),
     ]
 
 

@@ -27,7 +27,7 @@ struct dgibbs_handle_s {
   std::string err;
   dgibbs_timing timing{};
   std::map<std::string, Buf> pool;  // grow-only device workspace, freed in destroy
-  cudaEvent_t ev[5]{};
+  cudaEvent_t ev[8]{};
   // cached projection table
   int ft_N = -1, ft_cplx = -1;
 };
@@ -262,6 +262,9 @@ static int stage_batch(dgibbs_handle h, const dgibbs_problem* p, Staged& s, bool
   CU(pool_get(h, "S", sizeof(double) * (size_t)B * d.N, &q)); d.S = (double*)q;
   CU(pool_get(h, "n_done", sizeof(int) * (size_t)B, &q)); d.n_done = (int*)q;
   CU(pool_get(h, "failed", sizeof(int) * (size_t)B, &q)); d.failed = (int*)q;
+  CU(pool_get(h, "branch", (size_t)B, &q)); d.branch = (unsigned char*)q;
+  CU(pool_get(h, "diag_ab", sizeof(double) * 2 * (size_t)B, &q)); d.diag_ab = (double*)q;
+  d.force_branch = p->force_branch;
   const size_t wrows = (size_t)d.npad + (size_t)d.RT * TILE;
   CU(pool_get(h, "work", sizeof(double) * (size_t)d.nslots * wrows * d.npad, &q)); d.work = (double*)q;
   CU(pool_get(h, "Wp", sizeof(double) * (size_t)d.nslots * dense_wp_doubles_per_slot(d), &q)); d.Wp = (double*)q;
@@ -352,10 +355,68 @@ extern "C" int dgibbs_run(dgibbs_handle h, const dgibbs_problem* p, dgibbs_resul
     CU(cudaMemsetAsync(q, 0, 16 * sizeof(long long), h->stream));
     d.prof = (long long*)q;
   }
-  // --- the chains: one persistent launch covers every iteration of every baseline
+  // --- classify: which baselines have a diagonal(+rank-1) system (decided by the setup kernel)
+  std::vector<unsigned char> br(d.B);
+  CU(cudaMemcpyAsync(br.data(), d.branch, d.B, cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  const bool fast_diag = d.rng_mode == DGIBBS_RNG_PHILOX && d.nsys <= 4096 && d.niter > 0;
+  std::vector<int> dense_list, diag_list, ycompact(d.B, -1);
+  for (int b = 0; b < d.B; b++) {
+    if (br[b] == DGIBBS_BRANCH_DIAGONAL && fast_diag) {
+      ycompact[b] = (int)diag_list.size();
+      diag_list.push_back(b);
+    } else {
+      dense_list.push_back(b);
+    }
+  }
+  int *d_dense = nullptr, *d_diag = nullptr, *d_yc = nullptr;
+  if (!diag_list.empty()) {
+    CU(pool_get(h, "list_dense", sizeof(int) * (dense_list.size() + 1), &q)); d_dense = (int*)q;
+    CU(pool_get(h, "list_diag", sizeof(int) * diag_list.size(), &q)); d_diag = (int*)q;
+    CU(pool_get(h, "ycompact", sizeof(int) * d.B, &q)); d_yc = (int*)q;
+    if (!dense_list.empty())
+      CU(cudaMemcpyAsync(d_dense, dense_list.data(), sizeof(int) * dense_list.size(), cudaMemcpyHostToDevice, h->stream));
+    CU(cudaMemcpyAsync(d_diag, diag_list.data(), sizeof(int) * diag_list.size(), cudaMemcpyHostToDevice, h->stream));
+    CU(cudaMemcpyAsync(d_yc, ycompact.data(), sizeof(int) * d.B, cudaMemcpyHostToDevice, h->stream));
+    CU(pool_get(h, "yhat", sizeof(double) * diag_list.size() * (size_t)d.Tmax * d.npad, &q));
+    d.yhat = (double*)q;
+    d.ycompact = d_yc;
+  }
+  h->timing.n_dense = (int64_t)dense_list.size();
+  h->timing.n_diag = (int64_t)diag_list.size();
+  CU(cudaEventRecord(h->ev[5], h->stream));
+  if (!diag_list.empty()) {
+    // projection yhat = F^T N^-1/2 z with the dense kernel's phase 0 (zero draws), then the streaming chains
+    DevBatch dp = d;
+    dp.blist = d_diag;
+    dp.nlist = (int)diag_list.size();
+    dp.project_only = 1;
+    dp.rng_mode = DGIBBS_RNG_ZERO;
+    dp.nslots = dp.nlist < d.nslots ? dp.nlist : d.nslots;
+    CU(launch_dense_sampler(dp, 0, 1, h->stream));
+    h->timing.launches++;
+    CU(cudaEventRecord(h->ev[6], h->stream));
+    DevBatch dd = d;
+    dd.blist = d_diag;
+    dd.nlist = (int)diag_list.size();
+    CU(launch_diag_sampler(dd, 0, d.niter, h->sm_count, h->stream));
+    h->timing.launches++;
+    h->timing.sampler_launches++;
+  } else {
+    CU(cudaEventRecord(h->ev[6], h->stream));
+  }
+  CU(cudaEventRecord(h->ev[7], h->stream));
+
+  // --- the dense chains: one persistent launch covers every iteration of every baseline
   double flop = 0.0;
-  if (d.niter > 0) {
-    CU(launch_dense_sampler(d, 0, d.niter, h->stream));
+  if (d.niter > 0 && !dense_list.empty()) {
+    DevBatch dn = d;
+    if (!diag_list.empty()) {
+      dn.blist = d_dense;
+      dn.nlist = (int)dense_list.size();
+      dn.nslots = dn.nlist < d.nslots ? dn.nlist : d.nslots;
+    }
+    CU(launch_dense_sampler(dn, 0, d.niter, h->stream));
     h->timing.launches++;
     h->timing.sampler_launches++;
   }
@@ -389,19 +450,26 @@ extern "C" int dgibbs_run(dgibbs_handle h, const dgibbs_problem* p, dgibbs_resul
   std::vector<int> nd(d.B);
   if (dev) CU(cudaMemcpy(nd.data(), d_ndone, sizeof(int) * d.B, cudaMemcpyDeviceToHost));
   else memcpy(nd.data(), r->n_done, sizeof(int) * d.B);
-  for (int b = 0; b < d.B; b++) flop += (double)nd[b] * dense_flop_per_iter(d, s.T[b], s.M[b]);
+  double bytes = 0.0;
+  for (int b = 0; b < d.B; b++) {
+    if (ycompact[b] >= 0) bytes += (double)nd[b] * (8.0 * d.nsys * s.T[b] + 16.0 * d.N);  // Q_d
+    else flop += (double)nd[b] * dense_flop_per_iter(d, s.T[b], s.M[b]);
+  }
   if (r->branch) {
-    std::vector<unsigned char> br(d.B, (unsigned char)DGIBBS_BRANCH_DELAY_SPACE);
+    for (int b = 0; b < d.B; b++)
+      if (br[b] != DGIBBS_BRANCH_DIAGONAL) br[b] = DGIBBS_BRANCH_DELAY_SPACE;
     if (dev) CU(cudaMemcpy(r->branch, br.data(), d.B, cudaMemcpyHostToDevice));
     else memcpy(r->branch, br.data(), d.B);
   }
   float ms;
   cudaEventElapsedTime(&ms, h->ev[0], h->ev[1]); h->timing.ms_h2d = ms;
-  cudaEventElapsedTime(&ms, h->ev[1], h->ev[2]); h->timing.ms_setup = ms;
-  cudaEventElapsedTime(&ms, h->ev[2], h->ev[3]); h->timing.ms_sampler = ms;
+  cudaEventElapsedTime(&ms, h->ev[1], h->ev[5]); h->timing.ms_setup = ms;
+  cudaEventElapsedTime(&ms, h->ev[5], h->ev[6]); h->timing.ms_diag_project = ms;
+  cudaEventElapsedTime(&ms, h->ev[6], h->ev[7]); h->timing.ms_sampler_diag = ms;
+  cudaEventElapsedTime(&ms, h->ev[7], h->ev[3]); h->timing.ms_sampler = ms;
   cudaEventElapsedTime(&ms, h->ev[3], h->ev[4]); h->timing.ms_finish = ms;
   h->timing.flop_sampler = flop;
-  h->timing.bytes_sampler = 0.0;
+  h->timing.bytes_sampler = bytes;
   return 0;
 }
 

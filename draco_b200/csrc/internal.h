@@ -26,6 +26,8 @@ struct DevBatch {
   int nslots;  // concurrent CTAs (= workspace slots)
   int wiener;  // 1: stop after the solve of iteration 0 and keep x (Wiener filter)
   int ctab_smem;  // circulant table fits in shared memory
+  int force_branch;  // 0 auto; DGIBBS_BRANCH_DELAY_SPACE (1) = never take the diagonal shortcut
+  int project_only;  // dense kernel: stop after phase 0 and export y^T = (F^T h z)^T to yhat
 
   // caller inputs
   const int* T;
@@ -51,7 +53,12 @@ struct DevBatch {
   double* samples;  // [niter][B][N]
   int* n_done;      // [B] completed iterations
   int* failed;      // [B] 1 once a factorisation met a non-positive pivot
-  unsigned char* branch;  // [B]
+  unsigned char* branch;  // [B] 1 = dense delay-space system, 3 = diagonal(+rank-1) system
+  double* diag_ab;        // [B][2]  FTNiF = a I + b u u^T (u = (-1)^t) when branch == 3
+  const int* blist;       // baselines this launch works on (null = all B)
+  int nlist;
+  double* yhat;           // [ndiag][Tmax][npad] projected data of the diagonal-branch baselines
+  const int* ycompact;    // [B] row block of a baseline in yhat, or -1
 
   // shared tables
   const double* Ftab;  // [Kpad][npad] projection table  F[k][col]
@@ -80,6 +87,9 @@ size_t dense_smem_bytes(const DevBatch& d);
 size_t dense_wp_doubles_per_slot(const DevBatch& d);
 cudaError_t dense_configure(const DevBatch& d);
 cudaError_t launch_dense_sampler(const DevBatch& d, int it_begin, int it_end, cudaStream_t st);
+
+// sampler_diag.cu
+cudaError_t launch_diag_sampler(const DevBatch& d, int it_begin, int it_end, int sm_count, cudaStream_t st);
 
 // finish_kernels.cu
 cudaError_t launch_finish(const DevBatch& d, const double* S0, double median_frac, double* spectrum,

@@ -26,7 +26,7 @@ constexpr int TILE_DOUBLES = TILE * LDW;              // one staged 128x128 tile
 constexpr int PIPE_DOUBLES = (STAGES * STAGE_DOUBLES > TILE_DOUBLES) ? STAGES * STAGE_DOUBLES : TILE_DOUBLES;
 constexpr int WP_BLOCKS = 16 * 17 / 2;                // lower-triangular 8x8 blocks of a 128x128 tile
 constexpr int WP_DOUBLES = WP_BLOCKS * 64;            // 8704 doubles = 68 KB
-constexpr int MISC_DOUBLES = 8;                       // flag
+constexpr int MISC_DOUBLES = 16;                      // flag + reduction scratch
 static_assert(TILE * LDA_NT + KC * LDB_NN <= STAGE_DOUBLES, "NN stage must fit");
 
 typedef double Acc[2][16][2];
@@ -466,6 +466,46 @@ __device__ bool factor_diag(double* sT, double* sWp, double* misc, const Lane& l
   return true;
 }
 
+// ----------------------------------------------------------------------------- diagonal branch
+// Ci = D + b u u^T with D = diag(a + Si), u_k = (-1)^k: solve every RHS row in place by
+// Sherman-Morrison.  Returns false when the system is not positive definite (some D_k <= 0 or
+// 1 + b u^T D^-1 u <= 0), which is when the reference's Cholesky would fail.
+__device__ bool diag_solve_rows(double* Rh, const double* Si, double a, double bc, int nsys, int npad, int Tb,
+                                double* misc) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  double ql = 0.0;
+  bool pos = true;
+  for (int k = threadIdx.x; k < nsys; k += THREADS) {
+    double D = a + Si[k];
+    if (!(D > 0.0)) pos = false;
+    ql += 1.0 / D;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) ql += __shfl_xor_sync(0xffffffffu, ql, o);
+  __syncthreads();
+  if (lane == 0) misc[2 + warp] = ql;
+  int allpos = __syncthreads_and(pos ? 1 : 0);
+  double q = 0.0;
+#pragma unroll
+  for (int w = 0; w < NWARP; w++) q += misc[2 + w];
+  const double den = 1.0 + bc * q;
+  if (!allpos || !(den > 0.0)) return false;
+  const double beta = bc / den;
+  for (int t = warp; t < Tb; t += NWARP) {
+    double* row = Rh + (size_t)t * npad;
+    double s = 0.0;
+    if (bc != 0.0) {
+      for (int k = lane; k < nsys; k += 32) s += ((k & 1) ? -row[k] : row[k]) / (a + Si[k]);
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    }
+    const double bs = beta * s;
+    for (int k = lane; k < nsys; k += 32) row[k] = (row[k] - ((k & 1) ? -bs : bs)) / (a + Si[k]);
+  }
+  __syncthreads();
+  return true;
+}
+
 // ----------------------------------------------------------------------------- the sampler
 // Shared memory:  [ctab: nsys (optional)] [sWp: WP_DOUBLES] [pipe/tile: PIPE_DOUBLES] [misc]
 __global__ void __launch_bounds__(THREADS, 1) dense_sampler_kernel(DevBatch d, int it_begin, int it_end) {
@@ -486,8 +526,12 @@ __global__ void __launch_bounds__(THREADS, 1) dense_sampler_kernel(DevBatch d, i
   double* Si = d.Si + (size_t)slot * npad;
 
   long long tlast = clock64();
-  for (int b = slot; b < d.B; b += gridDim.x) {
+  const int nl = d.blist ? d.nlist : d.B;
+  for (int li = slot; li < nl; li += gridDim.x) {
+    const int b = d.blist ? d.blist[li] : li;
     if (d.failed[b]) continue;
+    const bool isdiag = d.branch[b] == 3;
+    const double dg_a = d.diag_ab[2 * b], dg_b = d.diag_ab[2 * b + 1];
     const int Tb = d.T[b], Mb = d.M[b];
     const double* ctg = d.ctab + (size_t)b * nsys;
     const double* ct = ctg;
@@ -583,8 +627,19 @@ __global__ void __launch_bounds__(THREADS, 1) dense_sampler_kernel(DevBatch d, i
       __syncthreads();
       PROF(1);
 
+      if (d.project_only) {  // export y^T = (F^T h z)^T for the streaming diagonal kernel
+        double* yo = d.yhat + (size_t)d.ycompact[b] * d.Tmax * npad;
+        for (long long e = threadIdx.x; e < (long long)Tb * (npad / 2); e += THREADS) {
+          int t = (int)(e / (npad / 2)), k = (int)(e % (npad / 2)) * 2;
+          *reinterpret_cast<double2*>(yo + (size_t)t * npad + k) = *reinterpret_cast<const double2*>(Rh + (size_t)t * npad + k);
+        }
+        break;
+      }
+
+      if (isdiag) alive = diag_solve_rows(Rh, Si, dg_a, dg_b, nsys, npad, Tb, misc);
+
       // ---------------- factor (+ forward solve on the RHS row tiles)
-      for (int j = 0; j < nblk && alive; j++) {
+      for (int j = 0; j < nblk && alive && !isdiag; j++) {
         const double* Bp = Wk + (size_t)j * TILE * npad;
         // diagonal tile
         acc_zero(acc);
@@ -642,7 +697,7 @@ __global__ void __launch_bounds__(THREADS, 1) dense_sampler_kernel(DevBatch d, i
       }
 
       // ---------------- backward solve  x^T = z^T L^-1
-      for (int rt = 0; rt < RT; rt++) {
+      for (int rt = 0; rt < RT && !isdiag; rt++) {
         const bool do0 = rt * 16 + ln.rf[0] < rhs_frags, do1 = rt * 16 + ln.rf[1] < rhs_frags;
         const int var = rhs_variant(do0, do1);
         const int nrows = min(TILE, max(0, rhs_frags * 8 - rt * TILE));

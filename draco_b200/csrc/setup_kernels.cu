@@ -150,6 +150,33 @@ __global__ void setup_baseline_kernel(DevBatch d, const double* __restrict__ S0)
     if (tabs) ct[N + k] = acci;
   }
 
+  // Is FTNiF = a I + b u u^T (u_t = (-1)^t)?  True for uniform weights, no window and a complete
+  // channel set (b = 0), or with only the Nyquist channel missing (b = -Ni): SURVEY 8d.  Gate on
+  // the computed first column, not on configuration flags.
+  __syncthreads();
+  {
+    const double tol = 1e-12;
+    const double c0 = ct[0];
+    double bc = 0.0;
+    bool ok = c0 > 0.0;
+    if (!d.cplx) {
+      bc = (N > 1) ? -ct[1] : 0.0;
+      if (fabs(bc) <= tol * c0) bc = 0.0;
+      for (int k = 1 + threadIdx.x; k < N; k += blockDim.x)
+        if (fabs(ct[k] - ((k & 1) ? -bc : bc)) > tol * c0) ok = false;
+    } else {
+      for (int k = threadIdx.x; k < N; k += blockDim.x)
+        if ((k > 0 && fabs(ct[k]) > tol * c0) || fabs(ct[N + k]) > tol * c0) ok = false;
+    }
+    int all = __syncthreads_and(ok ? 1 : 0);
+    if (threadIdx.x == 0) {
+      bool isdiag = all && d.force_branch != 1 && (c0 - bc) > 0.0;
+      d.branch[b] = isdiag ? 3 : 1;
+      d.diag_ab[2 * b] = c0 - bc;
+      d.diag_ab[2 * b + 1] = bc;
+    }
+  }
+
   for (int k = threadIdx.x; k < N; k += blockDim.x) d.S[(size_t)b * N + k] = S0[(size_t)b * N + k];
   if (threadIdx.x == 0) {
     d.n_done[b] = 0;

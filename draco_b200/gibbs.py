@@ -12,6 +12,7 @@ import numpy as np
 
 from . import _lib
 from ._lib import RNG_INJECTED, RNG_PHILOX, RNG_ZERO, WINDOW_IDS, DGibbsError, Handle  # noqa: F401
+from ._lib import BRANCH_DELAY_SPACE, BRANCH_DIAGONAL, BRANCH_FREQ_SPACE  # noqa: F401
 
 _handles: dict = {}
 
@@ -127,7 +128,7 @@ def pack_uniform(vis, weight, fsel, N, S0, window="nuttall", complex_timedomain=
     )
 
 
-def _problem(pb: PackedBatch, niter, rng_mode, seed, median_frac, draws=None):
+def _problem(pb: PackedBatch, niter, rng_mode, seed, median_frac, draws=None, force_branch=0):
     p = _lib.Problem()
     p.struct_size = C.sizeof(_lib.Problem)
     p.on_device = 1 if pb.on_device else 0
@@ -139,6 +140,7 @@ def _problem(pb: PackedBatch, niter, rng_mode, seed, median_frac, draws=None):
     p.rng_mode = rng_mode
     p.seed = int(seed) & 0xFFFFFFFFFFFFFFFF
     p.median_frac = float(median_frac)
+    p.force_branch = int(force_branch)
     for name in ("T", "M", "data_off", "chan_off", "data", "Ni", "fsel", "S0", "global_id"):
         setattr(p, name, _ptr(getattr(pb, name)))
     keep = []
@@ -185,6 +187,7 @@ def run_batch(
     draws=None,
     save_samples=False,
     want_final_S=False,
+    force_branch=0,
 ) -> BatchResult:
     """Run every chain of a packed batch on the GPU (replaces the loop delay.py:1146-1178)."""
     device = pb.data.device.index if pb.on_device else 0
@@ -213,7 +216,7 @@ def run_batch(
         success = np.empty(B, dtype=np.uint8)
         branch = np.empty(B, dtype=np.uint8)
         final_S = np.empty((B, N), dtype=np.float64) if want_final_S else None
-    p, keep = _problem(pb, niter, rng_mode, seed, median_frac, draws)
+    p, keep = _problem(pb, niter, rng_mode, seed, median_frac, draws, force_branch)
     r = _lib.Result()
     r.struct_size = C.sizeof(_lib.Result)
     r.on_device = p.on_device

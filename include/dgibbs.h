@@ -127,12 +127,16 @@ typedef struct {
 typedef struct {
   double ms_h2d;      /* host->device staging (0 when on_device) */
   double ms_setup;    /* window/whiten/projection-table kernels */
-  double ms_sampler;  /* all Gibbs iterations */
+  double ms_sampler;  /* all Gibbs iterations of the dense-branch baselines */
   double ms_finish;   /* median + fftshift (+ device->host) */
   int64_t launches;   /* kernels launched by the call */
   int64_t sampler_launches;
   double flop_sampler; /* algorithmic fp64 flop of the sampler launches (SURVEY 8d W_f/W_t) */
-  double bytes_sampler; /* algorithmic HBM bytes (diagonal branch, Q_d) */
+  double bytes_sampler; /* algorithmic HBM bytes of the diagonal-branch launch (SURVEY 8d Q_d = 8nT + 16N per baseline-iteration) */
+  double ms_diag_project; /* one-off projection yhat = F^T N^-1/2 z of the diagonal-branch baselines */
+  double ms_sampler_diag; /* all Gibbs iterations of the diagonal-branch baselines (streaming kernel) */
+  int64_t n_dense;        /* baselines that ran the dense system */
+  int64_t n_diag;         /* baselines that ran the diagonal(+rank-1) system */
 } dgibbs_timing;
 
 int dgibbs_version(void);

@@ -1,0 +1,148 @@
+"""The diagonal(+rank-1) branch: uniform weights, no window, complete channel set
+(optionally without the Nyquist channel).  Injected-draw parity of the Sherman-Morrison solve with
+the reference's dense Cholesky, and statistical parity of the streaming kernel's native draws."""
+import numpy as np
+import pytest
+
+import oracle
+from _cases import recorded_chain
+
+pytestmark = pytest.mark.gpu
+
+RTOL = 1e-6
+DIAG, DENSE = 3, 1
+
+
+@pytest.fixture(scope="module")
+def gibbs():
+    from draco_b200 import gibbs as g
+
+    g.get_handle(0)
+    return g
+
+
+def uniform_case(N, T, cplx, nyquist, seed, Ni=3.0):
+    r = np.random.default_rng(seed)
+    fsel = np.arange(N) if cplx else np.arange(N // 2 + (1 if nyquist else 0))
+    M = len(fsel)
+    data = r.standard_normal((T, M)) + 1j * r.standard_normal((T, M))
+    # a band-limited signal on top so that the posterior is not pure prior
+    data[:, : M // 4] *= 6.0
+    return data, np.full(M, Ni), fsel, np.full(N, 10.0)
+
+
+@pytest.mark.parametrize("N,T,cplx,nyquist", [(64, 8, False, False), (64, 6, False, True), (32, 5, True, True),
+                                              (256, 16, False, False), (100, 4, False, False)])
+def test_injected_parity_and_branch_detection(gibbs, N, T, cplx, nyquist):
+    niter = 6
+    data, Ni, fsel, S0 = uniform_case(N, T, cplx, nyquist, seed=N + T)
+    ref, ok, (w1, w2, c2) = recorded_chain(data, N, Ni, S0, None, fsel, niter, cplx)
+    assert ok
+    pb = gibbs.pack_batch([data], [Ni], [fsel], N, S0[None], window=None, complex_timedomain=cplx)
+    draws = gibbs.pack_draws(pb, niter, [w1], [w2], [c2])
+    res = gibbs.run_batch(pb, niter, draws=draws, save_samples=True)
+    assert int(res.branch[0]) == DIAG and res.success[0]
+    np.testing.assert_allclose(res.samples[:, 0], ref, rtol=RTOL)
+    forced = gibbs.run_batch(pb, niter, draws=draws, save_samples=True, force_branch=DENSE)
+    assert int(forced.branch[0]) == DENSE
+    np.testing.assert_allclose(forced.samples[:, 0], ref, rtol=RTOL)
+    # the Wiener filter takes the same shortcut
+    wf = gibbs.delay_spectrum_wiener_filter(S0, data, N, Ni, None, fsel, cplx)
+    rf = oracle.wiener_filter(S0, data, N, Ni, None, fsel, cplx)
+    assert np.max(np.abs(wf - rf)) < 1e-9 * np.max(np.abs(rf))
+
+
+def test_not_diagonal_when_windowed_masked_or_weighted(gibbs):
+    N, T = 64, 4
+    data, Ni, fsel, S0 = uniform_case(N, T, False, False, seed=1)
+    cases = [
+        dict(window="nuttall"),                                  # any window
+        dict(drop=5),                                            # a masked channel
+        dict(weights=np.linspace(1.0, 2.0, len(fsel))),          # non-uniform weights
+    ]
+    for c in cases:
+        d, w, f = data, Ni, fsel
+        if "drop" in c:
+            keep = np.arange(len(fsel)) != c["drop"]
+            d, w, f = data[:, keep], Ni[keep], fsel[keep]
+        if "weights" in c:
+            w = c["weights"]
+        pb = gibbs.pack_batch([d], [w], [f], N, S0[None], window=c.get("window"))
+        res = gibbs.run_batch(pb, 2, seed=1)
+        assert int(res.branch[0]) == DENSE, c
+
+
+def test_failure_semantics_diag(gibbs):
+    N, T, niter = 64, 8, 6
+    data, Ni, fsel, S0 = uniform_case(N, T, False, False, seed=3)
+    _, _, (w1, w2, c2) = recorded_chain(data, N, Ni, S0, None, fsel, niter, False)
+    c2 = c2.copy()
+    c2[1] = -c2[1]
+
+    class Bad(oracle.InjectedDraws):
+        pass
+
+    ref, ok = oracle.gibbs_chain(data, N, Ni, S0, None, fsel, niter, oracle.InjectedDraws(w1, w2, c2), False)
+    assert not ok and len(ref) == 2
+    pb = gibbs.pack_batch([data], [Ni], [fsel], N, S0[None], window=None)
+    res = gibbs.run_batch(pb, niter, draws=gibbs.pack_draws(pb, niter, [w1], [w2], [c2]), save_samples=True)
+    assert int(res.branch[0]) == DIAG and int(res.n_done[0]) == 2 and not res.success[0]
+    np.testing.assert_allclose(res.samples[-2:, 0], np.array(ref), rtol=RTOL)
+
+
+def test_streaming_kernel_statistics_vs_oracle(gibbs):
+    """Native RNG: the streaming kernel draws the same posterior as the reference (64 chains x 200
+    iterations each side, first half dropped; per-chain means and final samples, see
+    test_gpu_parity.test_philox_posterior_statistics for the rationale)."""
+    from scipy import stats
+
+    N, T, niter, nb = 64, 16, 200, 64
+    data, Ni, fsel, S0 = uniform_case(N, T, False, False, seed=9)
+    pb = gibbs.pack_batch([data] * nb, [Ni] * nb, [fsel] * nb, N, np.full((nb, N), 10.0), window=None,
+                          global_id=np.arange(nb))
+    res = gibbs.run_batch(pb, niter, seed=77, save_samples=True)
+    assert res.success.all() and np.all(res.branch == DIAG) and res.timing["n_diag"] == nb
+    assert res.timing["bytes_sampler"] == nb * niter * (8 * N * T + 16 * N)
+    dev = np.log(res.samples[niter // 2:])
+    ora = []
+    for c in range(nb):
+        s, ok = oracle.gibbs_chain(data, N, Ni, S0, None, fsel, niter, np.random.default_rng(5000 + c))
+        assert ok
+        ora.append(np.log(np.array(s)[niter // 2:]))
+    ora = np.stack(ora, axis=1)
+    md, mo = dev.mean(axis=0), ora.mean(axis=0)
+    se = np.sqrt(md.var(axis=0, ddof=1) / nb + mo.var(axis=0, ddof=1) / nb)
+    z = (md.mean(axis=0) - mo.mean(axis=0)) / se
+    assert np.mean(np.abs(z) < 3.0) >= 0.95 and np.max(np.abs(z)) < 4.2, z
+    alpha = 0.01 / 32
+    for k in range(0, N, 4):
+        assert stats.ks_2samp(md[:, k], mo[:, k]).pvalue > alpha, k
+        assert stats.ks_2samp(dev[-1, :, k], ora[-1, :, k]).pvalue > alpha, k
+
+
+def test_streaming_kernel_vs_dense_kernel_cfg3_geometry(gibbs):
+    """BASELINE config 3 geometry (N=2048, 1024 channels, uniform weights, no window, T=64): the
+    streaming kernel and the dense DMMA kernel sample the same posterior (device RNG both sides)."""
+    from scipy import stats
+
+    from draco_b200 import synth
+
+    cfg = synth.CONFIGS["cfg3"]
+    nb, niter = 48, 40
+    freq, vis, wgt = synth.make_stack(cfg, nbase=1)
+    delays, chan = oracle.calculate_delays(freq)
+    N = len(delays)
+    d, w, nzf, _ = oracle.cut_data(vis[0], wgt[0])
+    pb = gibbs.pack_batch([d] * nb, [w] * nb, [chan[nzf]] * nb, N, np.full((nb, N), 10.0), window=None,
+                          global_id=np.arange(nb)).to_device(0)
+    a = gibbs.run_batch(pb, niter, seed=5, save_samples=True)
+    b = gibbs.run_batch(pb, niter, seed=6, save_samples=True, force_branch=DENSE)
+    assert bool((a.branch == DIAG).all()) and bool((b.branch == DENSE).all())
+    sa = np.log(a.samples[niter // 2:].cpu().numpy())
+    sb = np.log(b.samples[niter // 2:].cpu().numpy())
+    ma, mb = sa.mean(axis=0), sb.mean(axis=0)
+    se = np.sqrt(ma.var(axis=0, ddof=1) / nb + mb.var(axis=0, ddof=1) / nb)
+    z = (ma.mean(axis=0) - mb.mean(axis=0)) / se
+    assert np.mean(np.abs(z) < 3.0) >= 0.98 and np.max(np.abs(z)) < 5.0, (np.abs(z).max(), np.mean(np.abs(z) < 3))
+    for k in range(0, N, 128):
+        assert stats.ks_2samp(sa[-1, :, k], sb[-1, :, k]).pvalue > 0.01 / 16, k
