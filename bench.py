@@ -192,6 +192,26 @@ def fp64_peak_tflops():
     return 2.0 * n**3 / best / 1e9
 
 
+# dram__bytes_read.sum + dram__bytes_write.sum of one dense_sampler_kernel launch from the committed
+# `ncu --set full` capture (profiles/), or None while no capture of the current kernel exists
+DENSE_TRAFFIC_PER_LAUNCH = None
+
+
+def hbm_roofline(nbytes, ms):
+    peaks = {}
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            peaks = json.load(f)
+    except OSError:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    src = "MEASURED_PEAKS.json hbm_gbs (of measured)" if "hbm_gbs" in peaks else "6650 GB/s (of fallback)"
+    ach = nbytes / (ms / 1e3) / 1e9 if ms > 0 else 0.0
+    return {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
+            "peak_source": src, "kernel": "diag_sampler_kernel",
+            "byte_model": "Q_d = 8 n T + 16 N bytes per baseline-iteration (read projected data once, read+write S)"}
+
+
 def run_reference(args, cfg, nsamp):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -263,13 +283,16 @@ def main():
     sync()
     clocks = ClockSampler(local)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    flop = ms_sampler = 0.0
-    launches = 0
+    flop = ms_sampler = nbytes = ms_diag = 0.0
+    launches = n_diag = 0
     e0.record()
     for i in range(args.steps):
         res, avg = step_device(args.warmup + i)
         flop += res.timing["flop_sampler"]
         ms_sampler += res.timing["ms_sampler"]
+        nbytes += res.timing["bytes_sampler"]
+        ms_diag += res.timing["ms_sampler_diag"]
+        n_diag = int(res.timing["n_diag"])
         launches += int(res.timing["launches"])
     e1.record()
     sync()
@@ -306,7 +329,18 @@ def main():
     e2e_value = world * nbase * nsamp * args.steps / (float(ms2.item()) / 1e3)
 
     if rank == 0:
-        ach = flop / (ms_sampler / 1e3) / 1e12
+        ach = flop / (max(ms_sampler, 1e-9) / 1e3) / 1e12
+        if n_diag > 0:
+            # diagonal(+rank-1) branch: streaming kernel, HBM-bound (SURVEY 8d Q_d = 8 n T + 16 N per baseline-iteration)
+            roof = hbm_roofline(nbytes, ms_diag)
+            branch = f"diagonal(+rank-1) streaming sampler ({n_diag} of {nbase} baselines)"
+        else:
+            roof = {"bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
+                    "traffic": DENSE_TRAFFIC_PER_LAUNCH,
+                    "peak_source": "fp64: cuBLAS DGEMM 8192^3 measured in this run (MEASURED_PEAKS.json has no fp64 entry; "
+                                   "tcgen05 has no fp64 kind, DMMA pipe probe = 37.0 TFLOP/s, profiles/r01_fp64_pipe_probe.log)",
+                    "kernel": "dense_sampler_kernel", "flop_model": "W_f = n^3/3 + 2 n^2 T + 4 n M T per baseline-iteration"}
+            branch = "dense (_f), fp64 DMMA Cholesky"
         out = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -314,7 +348,7 @@ def main():
             "config": {
                 "workload": f"{cfg.name}: {nbase} baselines/GPU x {cfg.nfreq} freq (N={cfg.ndelay}), T={cfg.ntime}, "
                             f"nsamp={nsamp}, window={cfg.window}, weights={cfg.weights}, mask={cfg.mask}",
-                "branch": "dense (_f), fp64 DMMA Cholesky", "rng": "device Philox4x32-10",
+                "branch": branch, "rng": "device Philox4x32-10",
                 "parallelism": f"baseline-sharded x{world}, group-average allreduce ({ngroup} groups of {group_size})",
                 "l2": "inputs (1 GiB visibilities + 5 GiB factor workspace) larger than L2; no flush needed",
                 "chains_ok": n_ok,
@@ -322,11 +356,7 @@ def main():
             "clocks": clk,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
             "gpu_launches": launches,
-            "roofline": {"bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
-                         "traffic": None,
-                         "peak_source": "fp64: cuBLAS DGEMM 8192^3 measured in this run (MEASURED_PEAKS.json has no fp64 entry; "
-                                        "tcgen05 has no fp64 kind, DMMA pipe probe = 37.0 TFLOP/s, profiles/r01_fp64_pipe_probe.log)",
-                         "kernel": "dense_sampler_kernel", "flop_model": "W_f = n^3/3 + 2 n^2 T + 4 n M T per baseline-iteration"},
+            "roofline": roof,
         }
         if not args.no_cpu_baseline and world == 1:
             out["cpu_baseline"] = cpu_baseline(cfg, nsamp)

@@ -29,7 +29,7 @@ struct dgibbs_handle_s {
   std::map<std::string, Buf> pool;  // grow-only device workspace, freed in destroy
   cudaEvent_t ev[8]{};
   // cached projection table
-  int ft_N = -1, ft_cplx = -1;
+  int ft_N = -1, ft_cplx = -1, tw_N = -1;
 };
 
 #define CU(call)                                                                      \
@@ -280,6 +280,19 @@ static int stage_batch(dgibbs_handle h, const dgibbs_problem* p, Staged& s, bool
       h->timing.launches++;
       h->ft_N = d.N;
       h->ft_cplx = d.cplx;
+    }
+  }
+  // in-smem FFT for the masked inverse DFT when N is a power of two that fits the pipeline buffers
+  d.use_fft = (d.N >= 8 && (d.N & (d.N - 1)) == 0 && d.N <= 4096 && !getenv("DGIBBS_NO_FFT")) ? 1 : 0;
+  d.twtab = nullptr;
+  if (d.use_fft) {
+    bool fresh = h->tw_N != d.N;
+    CU(pool_get(h, "twtab", sizeof(double2) * (size_t)(d.N / 2), &q));
+    d.twtab = (const double2*)q;
+    if (fresh) {
+      CU(launch_build_twtab(d.N, (double2*)q, h->stream));
+      h->timing.launches++;
+      h->tw_N = d.N;
     }
   }
   CU(launch_setup_baselines(d, s.S0, h->stream));

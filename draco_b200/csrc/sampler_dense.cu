@@ -368,6 +368,169 @@ __device__ __forceinline__ void copy_tile_out(const double* sT, double* dst, int
   }
 }
 
+
+// ----------------------------------------------------------------------------- masked inverse DFT as an FFT
+// y[t, n] = sum_i u[t, 2i] cos(2 pi i n / N) - u[t, 2i+1] sin(2 pi i n / N) = Re sum_i U_i e^{+2 pi i (i n) / N}
+// (the rows of fourier_matrix_r2c / _c2c, delay.py:1480-1510, 1549-1585, applied transposed) is an
+// unnormalised inverse DFT of the zero-filled channel grid: O(N log N) per sample instead of the
+// 4 n M flop of the dense projection, and it needs no projection table.  Stockham autosort, radix 4
+// (+ one radix-2 stage), ping-pong between two shared-memory buffers, exact twiddles from a table.
+__device__ __forceinline__ double2 tw_get(const double2* tw, int m, int N) {  // e^{2 pi i m / N}, 0 <= m < N
+  const int half = N >> 1;
+  double2 w = tw[m & (half - 1)];
+  if (m & half) { w.x = -w.x; w.y = -w.y; }
+  return w;
+}
+__device__ __forceinline__ double2 cmul(double2 a, double2 b) {
+  return make_double2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x);
+}
+// Inverse (sign +) DFT of x[0:N) (N = 2^m >= 8); returns the buffer that holds the result (x or y).
+// All threads of the CTA must call it; the inputs must be visible (caller synchronises before).
+__device__ double2* fft_inverse_smem(double2* x, double2* y, const double2* tw, int N) {
+  int Ns = 1;
+  const int quarter = N >> 2;
+  while (Ns * 4 <= N) {
+    const int s = N / (4 * Ns);
+    for (int j = threadIdx.x; j < quarter; j += THREADS) {
+      const int k = j & (Ns - 1);
+      double2 v0 = x[j], v1 = x[j + quarter], v2 = x[j + 2 * quarter], v3 = x[j + 3 * quarter];
+      if (Ns > 1) {
+        v1 = cmul(v1, tw_get(tw, k * s, N));
+        v2 = cmul(v2, tw_get(tw, 2 * k * s, N));
+        v3 = cmul(v3, tw_get(tw, 3 * k * s, N));
+      }
+      const double2 a = make_double2(v0.x + v2.x, v0.y + v2.y), b = make_double2(v0.x - v2.x, v0.y - v2.y);
+      const double2 c = make_double2(v1.x + v3.x, v1.y + v3.y), e = make_double2(v1.x - v3.x, v1.y - v3.y);
+      const int j0 = ((j - k) << 2) + k;
+      y[j0] = make_double2(a.x + c.x, a.y + c.y);
+      y[j0 + Ns] = make_double2(b.x - e.y, b.y + e.x);      // b + i e
+      y[j0 + 2 * Ns] = make_double2(a.x - c.x, a.y - c.y);
+      y[j0 + 3 * Ns] = make_double2(b.x + e.y, b.y - e.x);  // b - i e
+    }
+    __syncthreads();
+    double2* tmp = x; x = y; y = tmp;
+    Ns <<= 2;
+  }
+  if (Ns < N) {  // Ns == N/2: one radix-2 stage, twiddle stride 1
+    const int half = N >> 1;
+    for (int j = threadIdx.x; j < half; j += THREADS) {
+      const double2 v0 = x[j], v1 = cmul(x[j + half], tw[j]);
+      y[j] = make_double2(v0.x + v1.x, v0.y + v1.y);
+      y[j + half] = make_double2(v0.x - v1.x, v0.y - v1.y);
+    }
+    __syncthreads();
+    double2* tmp = x; x = y; y = tmp;
+  }
+  return x;
+}
+
+// u_i = h_i (z_i + w2_i) of sample t, channel i of the full grid (delay.py:1814,1817); 0 where masked
+struct DrawCtx {
+  const DevBatch* d;
+  const Philox* ph;
+  const int* cidx;
+  const double* h;
+  const double* zT;
+  const double* w1;  // injected draws of this iteration (or null)
+  const double* w2;
+  int Tb, it, half;
+};
+__device__ __forceinline__ double2 u_value(const DrawCtx& c, int t, int i) {
+  if (t >= c.Tb) return make_double2(0.0, 0.0);
+  const int ci = c.cidx[i];
+  if (ci < 0) return make_double2(0.0, 0.0);
+  double n0 = 0.0, n1 = 0.0;
+  if (c.d->rng_mode == 1) {
+    unsigned long long blk = (unsigned long long)t * c.half + i;
+    normal_pair((*c.ph)((unsigned)blk, (unsigned)(blk >> 32), (unsigned)c.it, STREAM_W2), n0, n1);
+  } else if (c.d->rng_mode == 0) {
+    n0 = c.w2[(long long)(2 * ci) * c.Tb + t];
+    n1 = c.w2[(long long)(2 * ci + 1) * c.Tb + t];
+  }
+  const double2 z = *reinterpret_cast<const double2*>(c.zT + (size_t)t * c.d->Kpad + 2 * i);
+  return make_double2(c.h[2 * i] * (z.x + n0), c.h[2 * i + 1] * (z.y + n1));
+}
+// the two standard normals w1[t, k], w1[t, k+1] (k even) of this iteration
+__device__ __forceinline__ void w1_pair(const DrawCtx& c, int t, int k, int nsys, double& n0, double& n1) {
+  n0 = n1 = 0.0;
+  if (c.d->rng_mode == 1) {
+    unsigned long long blk = ((unsigned long long)t * nsys + k) >> 1;
+    normal_pair((*c.ph)((unsigned)blk, (unsigned)(blk >> 32), (unsigned)c.it, STREAM_W1), n0, n1);
+  } else if (c.d->rng_mode == 0) {
+    n0 = c.w1[(long long)k * c.Tb + t];
+    n1 = c.w1[(long long)(k + 1) * c.Tb + t];
+  }
+}
+
+// Fused prepass + phase 0:  Rh[t, :] = sqrt(Si) w1[t] + F^T (h (z[t] + w2[t]))   for every sample row,
+// zero in the padding rows / columns the factorisation sweeps over.
+//   real mode    : two samples per complex FFT (their spectra are Hermitian-extended and combined as A + iB)
+//   complex mode : one sample per FFT, output interleaved re/im
+__device__ void project_rows_fft(const DevBatch& d, const DrawCtx& c, double* Rh, const double* Si, double2* bufA,
+                                 double2* bufB, double2* tw_s, int rows) {
+  const int N = d.N, nsys = d.nsys, npad = d.npad, nch = d.nch;
+  for (int m = threadIdx.x; m < N / 2; m += THREADS) tw_s[m] = d.twtab[m];
+  const int step = d.cplx ? 1 : 2;
+  for (int t0 = 0; t0 < rows; t0 += step) {
+    __syncthreads();  // previous epilogue finished with the buffers (and tw_s is loaded)
+    if (t0 >= c.Tb) {  // padding rows: zeros (CTA-uniform branch)
+      for (int e = threadIdx.x; e < step * (npad / 2); e += THREADS) {
+        int r = e / (npad / 2), k = (e % (npad / 2)) * 2;
+        if (t0 + r < rows) *reinterpret_cast<double2*>(Rh + (size_t)(t0 + r) * npad + k) = make_double2(0.0, 0.0);
+      }
+      continue;
+    }
+    if (!d.cplx) {
+      for (int i = threadIdx.x; i < nch; i += THREADS) {
+        const double2 U0 = u_value(c, t0, i), U1 = u_value(c, t0 + 1, i);
+        if (i == 0 || i == N / 2) {
+          bufA[i] = make_double2(U0.x, U1.x);
+        } else {
+          bufA[i] = make_double2(0.5 * (U0.x - U1.y), 0.5 * (U0.y + U1.x));       // (U0 + i U1) / 2
+          bufA[N - i] = make_double2(0.5 * (U0.x + U1.y), 0.5 * (U1.x - U0.y));   // (conj U0 + i conj U1) / 2
+        }
+      }
+    } else {
+      for (int i = threadIdx.x; i < N; i += THREADS) bufA[i] = u_value(c, t0, i);
+    }
+    __syncthreads();
+    const double2* res = fft_inverse_smem(bufA, bufB, tw_s, N);
+    if (!d.cplx) {
+      const bool two = t0 + 1 < rows;
+      for (int p = threadIdx.x; p < npad / 2; p += THREADS) {
+        const int k = 2 * p;
+        double2 ya = make_double2(0.0, 0.0), yb = make_double2(0.0, 0.0);
+        if (k < nsys) {
+          const double2 r0 = res[k], r1 = res[k + 1];
+          const double s0 = sqrt(Si[k]), s1 = sqrt(Si[k + 1]);
+          double n0, n1;
+          w1_pair(c, t0, k, nsys, n0, n1);
+          ya = make_double2(s0 * n0 + r0.x, s1 * n1 + r1.x);   // delay.py:1815-1817
+          if (t0 + 1 < c.Tb) {
+            w1_pair(c, t0 + 1, k, nsys, n0, n1);
+            yb = make_double2(s0 * n0 + r0.y, s1 * n1 + r1.y);
+          }
+        }
+        *reinterpret_cast<double2*>(Rh + (size_t)t0 * npad + k) = ya;
+        if (two) *reinterpret_cast<double2*>(Rh + (size_t)(t0 + 1) * npad + k) = yb;
+      }
+    } else {
+      for (int p = threadIdx.x; p < npad / 2; p += THREADS) {
+        const int k = 2 * p;
+        double2 ya = make_double2(0.0, 0.0);
+        if (k < nsys) {
+          const double2 r0 = res[p];
+          double n0, n1;
+          w1_pair(c, t0, k, nsys, n0, n1);
+          ya = make_double2(sqrt(Si[k]) * n0 + r0.x, sqrt(Si[k + 1]) * n1 + r0.y);
+        }
+        *reinterpret_cast<double2*>(Rh + (size_t)t0 * npad + k) = ya;
+      }
+    }
+  }
+  __syncthreads();
+}
+
 // ----------------------------------------------------------------------------- diagonal tile
 // In-place blocked Cholesky of the staged 128x128 tile (lower) by 8-column panels.  Per panel p:
 //   S1  all warps : panel blocks  C(rb,p) -= L(rb,0:p) L(p,0:p)^T                      (DMMA)
@@ -547,6 +710,10 @@ __global__ void __launch_bounds__(THREADS, 1) dense_sampler_kernel(DevBatch d, i
     const Philox ph(mix_key(d.seed, d.gid ? (unsigned long long)d.gid[b] : (unsigned long long)b));
     const int rhs_frags = (Tb + 7) >> 3;  // valid 8-row fragments of the RHS
 
+    if (d.use_fft) {  // RHS rows the FFT projection never writes (skipped by every tile variant): keep them finite
+      const long long r0 = (long long)rhs_frags * 8 * (npad / 2), r1 = (long long)RT * TILE * (npad / 2);
+      for (long long e = r0 + threadIdx.x; e < r1; e += THREADS) reinterpret_cast<double2*>(Rh)[e] = make_double2(0.0, 0.0);
+    }
     bool alive = true;
     for (int it = it_begin; it < it_end && alive; it++) {
       // ---------------- prepass
@@ -561,6 +728,18 @@ __global__ void __launch_bounds__(THREADS, 1) dense_sampler_kernel(DevBatch d, i
         Si[k] = si;
       }
       __syncthreads();
+      Acc acc;
+      if (d.use_fft) {
+        // ---------------- fused prepass + phase 0: draws, u, masked inverse DFT (FFT), Y
+        DrawCtx dc;
+        dc.d = &d; dc.ph = &ph; dc.cidx = cidx; dc.h = h; dc.zT = zT;
+        dc.w1 = (d.rng_mode == 0) ? d.w1 + d.w1_off[b] + (long long)it * nsys * Tb : nullptr;
+        dc.w2 = (d.rng_mode == 0) ? d.w2 + d.w2_off[b] + (long long)it * 2 * Mb * Tb : nullptr;
+        dc.Tb = Tb; dc.it = it; dc.half = Kpad >> 1;
+        double2* fbuf = reinterpret_cast<double2*>(pipe);
+        project_rows_fft(d, dc, Rh, Si, fbuf, fbuf + N, reinterpret_cast<double2*>(sWp), rhs_frags * 8);
+        PROF(0);
+      } else {
       {  // Y = sqrt(Si) * w1  (two adjacent delays per thread), zero in the padding
         const int half = npad >> 1;
         const long long tot = (long long)RT * TILE * half;
@@ -612,7 +791,6 @@ __global__ void __launch_bounds__(THREADS, 1) dense_sampler_kernel(DevBatch d, i
       __syncthreads();
       PROF(0);
 
-      Acc acc;
       // ---------------- phase 0: Y += u F
       for (int rt = 0; rt < RT; rt++) {
         const bool do0 = rt * 16 + ln.rf[0] < rhs_frags, do1 = rt * 16 + ln.rf[1] < rhs_frags;
@@ -626,6 +804,7 @@ __global__ void __launch_bounds__(THREADS, 1) dense_sampler_kernel(DevBatch d, i
       }
       __syncthreads();
       PROF(1);
+      }
 
       if (d.project_only) {  // export y^T = (F^T h z)^T for the streaming diagonal kernel
         double* yo = d.yhat + (size_t)d.ycompact[b] * d.Tmax * npad;

@@ -61,6 +61,20 @@ cudaError_t launch_build_ftab(const DevBatch& d, double* Ftab, cudaStream_t st) 
   return cudaGetLastError();
 }
 
+// tw[m] = e^{2 pi i m / N}, m < N/2: the twiddles of the in-smem inverse FFT (sampler_dense.cu)
+__global__ void build_twtab_kernel(double2* __restrict__ tw, int N) {
+  int m = blockIdx.x * blockDim.x + threadIdx.x;
+  if (m >= N / 2) return;
+  double c, s;
+  twiddle(m, N, c, s);
+  tw[m] = make_double2(c, s);
+}
+
+cudaError_t launch_build_twtab(int N, double2* tw, cudaStream_t st) {
+  build_twtab_kernel<<<(N / 2 + 255) / 256, 256, 0, st>>>(tw, N);
+  return cudaGetLastError();
+}
+
 // One CTA per baseline.
 __global__ void setup_baseline_kernel(DevBatch d, const double* __restrict__ S0) {
   extern __shared__ double sm[];

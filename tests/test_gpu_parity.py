@@ -61,6 +61,18 @@ def test_golden_setup_wiener_chain(gibbs, golden, name):
     np.testing.assert_allclose(np.array(samples), ref, rtol=RTOL_SAMPLES)
 
 
+@pytest.mark.parametrize("name", ["f_real_cfg1", "f_cplx_n64", "t_real_n64"])
+def test_dense_projection_fallback_matches_golden(gibbs, golden, name, monkeypatch):
+    """The masked inverse DFT has two implementations: an in-smem FFT (N a power of two) and the
+    dense DMMA projection against the shared table (any N).  Pin the second on power-of-two cases too."""
+    monkeypatch.setenv("DGIBBS_NO_FFT", "1")
+    _, N, M, T, cplx, window, niter, nyq = CASES[name]
+    data, Ni, fsel, S0 = make_case(N, M, T, cplx, nyq, seed=11)
+    samples, ok = gibbs.delay_power_spectrum_gibbs(data, N, Ni, S0, window, fsel, niter, np.random.default_rng(7), cplx)
+    assert ok == bool(golden[f"{name}_success"])
+    np.testing.assert_allclose(np.array(samples), golden[f"{name}_samples"], rtol=RTOL_SAMPLES)
+
+
 def test_failure_semantics(gibbs, golden):
     """A non-PD system ends that chain at the same iteration as LAPACK does (delay.py:1891-1896)."""
     data, Ni, fsel, S0 = make_case(64, 29, 8, False, False, seed=11)
