@@ -356,6 +356,7 @@ def main():
             "clocks": clk,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
             "gpu_launches": launches,
+            "timing_last_step_ms": {k: round(float(v), 3) for k, v in res.timing.items() if k.startswith("ms_")},
             "roofline": roof,
         }
         if not args.no_cpu_baseline and world == 1:

@@ -412,7 +412,13 @@ extern "C" int dgibbs_run(dgibbs_handle h, const dgibbs_problem* p, dgibbs_resul
     DevBatch dd = d;
     dd.blist = d_diag;
     dd.nlist = (int)diag_list.size();
-    CU(launch_diag_sampler(dd, 0, d.niter, h->sm_count, h->stream));
+    // b > 0 never comes out of the reference's Fourier matrices; if it does, use the streaming kernel
+    std::vector<double> ab(2 * (size_t)d.B);
+    CU(cudaMemcpyAsync(ab.data(), d.diag_ab, sizeof(double) * ab.size(), cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    bool resident_ok = !getenv("DGIBBS_DIAG_STREAMING");
+    for (int b : diag_list) resident_ok = resident_ok && !(ab[2 * (size_t)b + 1] > 0.0);
+    CU(launch_diag_sampler(dd, 0, d.niter, h->sm_count, h->stream, resident_ok));
     h->timing.launches++;
     h->timing.sampler_launches++;
   } else {

@@ -92,7 +92,9 @@ cudaError_t dense_configure(const DevBatch& d);
 cudaError_t launch_dense_sampler(const DevBatch& d, int it_begin, int it_end, cudaStream_t st);
 
 // sampler_diag.cu
-cudaError_t launch_diag_sampler(const DevBatch& d, int it_begin, int it_end, int sm_count, cudaStream_t st);
+// allow_resident: every listed baseline has b <= 0, so the cluster-resident kernel may be used
+cudaError_t launch_diag_sampler(const DevBatch& d, int it_begin, int it_end, int sm_count, cudaStream_t st,
+                                bool allow_resident);
 
 // finish_kernels.cu
 cudaError_t launch_finish(const DevBatch& d, const double* S0, double median_frac, double* spectrum,

@@ -15,8 +15,15 @@
 //
 // Per baseline-iteration the kernel reads yhat (8 n T bytes) once and reads/writes S (16 N): the
 // algorithmic traffic Q_d of SURVEY 8d.  One CTA per baseline chain, all iterations on the device.
+#include <cooperative_groups.h>
+
+#include <cstdio>
+#include <cstdlib>
+
 #include "common.cuh"
 #include "internal.h"
+
+namespace cg = cooperative_groups;
 
 namespace dg {
 
@@ -216,8 +223,389 @@ __global__ void __launch_bounds__(DTHREADS, 1) diag_sampler_kernel(DevBatch d, i
   }
 }
 
-cudaError_t launch_diag_sampler(const DevBatch& d, int it_begin, int it_end, int sm_count, cudaStream_t st) {
+
+// ============================================================================ cluster-resident variant
+// Two observations make the diagonal branch far cheaper than streaming yhat once per iteration:
+//
+// 1. Residency.  The projected data yhat of one baseline (8 n T bytes: 1 MiB at cfg3) does not fit one
+//    SM's shared memory, but it fits the distributed shared memory of a thread-block cluster: C CTAs
+//    each keep a column slice [T][n / C] resident for ALL iterations of the chain, so HBM is read once
+//    per baseline instead of once per baseline-iteration.  Per iteration the only cross-CTA traffic is
+//    an all-gather of the partial sums of P_t and q through DSMEM and one cluster barrier.
+//
+// 2. Collapsed moments.  The chain only uses x through  ssq_k = sum_t (x_tk - mean_t x_k)^2  (delay.py:1867).
+//    For b <= 0 (the only values the reference's Fourier matrices produce: b = 0 with the Nyquist channel,
+//    b = -Ni without it) the posterior covariance is  D^-1 + |beta| v v^T,  v = D^-1 u,  so
+//        x_tk = m_tk + e_tk / sqrt(D_k),   m_tk = (y_tk + u_k corr_t) / D_k,
+//        corr_t = -beta P_t + sqrt(|beta|) xi_t,   e_tk, xi_t ~ N(0, 1) independent,
+//    and, with m~ = m - mean_t m (orthogonal to the ones vector),
+//        ssq_k = |m~_k|^2 + 2 |m~_k| g_k / sqrt(D_k) + (g_k^2 + c_k) / D_k,   g_k ~ N(0,1), c_k ~ chi^2_{T-2}
+//    EXACTLY in distribution (split e along 1, m~ and the rest).  One normal and one chi^2 per delay
+//    replace T normals, and |m~_k|^2 follows from per-baseline constants (sum_t y, sum_t y^2) plus one
+//    matrix-vector product  r_k = sum_t y_tk corr_t  with the resident slice.
+//
+// b > 0 falls back to the streaming kernel above.
+constexpr int RMAXC = 16;      // cluster sizes tried: 1, 2, 4, 8 (portable) and 16 (opt-in)
+constexpr int RBATCH = 4;      // iterations whose scalar draws are generated together (ILP)
+enum { STREAM_DIAG_XI = 6, STREAM_DIAG_G = 7, STREAM_DIAG_C2 = 8 };
+
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, int count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned parity) {
+  unsigned ok = 0;
+  while (!ok) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+  }
+}
+// TMA bulk copy global -> this CTA's shared memory, completion counted in bytes on an mbarrier
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned bytes, unsigned long long* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
+               "l"(src), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+
+// one fp32 standard normal (Box-Muller, fast intrinsics) from two 32-bit words
+__device__ __forceinline__ float normal1_f32(unsigned a, unsigned b) {
+  float u1 = ((float)(a >> 8) + 0.5f) * 5.9604644775390625e-8f;
+  float s, c;
+  __sincosf(6.2831853071795865f * ((float)b * 2.3283064365386963e-10f), &s, &c);
+  return sqrtf(-2.0f * __logf(u1)) * c;
+}
+// chi^2 with `dof` degrees of freedom (Marsaglia-Tsang on 2 Gamma(dof/2)); the proposal normal and the
+// acceptance test run in fp32, the variate itself is formed in fp64.  dof <= 0 gives 0.
+__device__ __forceinline__ double chi2_fast(const Philox& ph, unsigned it, unsigned key, unsigned stream, int dof) {
+  if (dof <= 0) return 0.0;
+  if (dof == 1) {
+    uint4 r = ph(key, 0u, it, stream);
+    double z = (double)normal1_f32(r.x, r.y);
+    return z * z;
+  }
+  const float dd = 0.5f * (float)dof - (1.0f / 3.0f), cc = rsqrtf(9.0f * dd);
+  for (unsigned attempt = 0; attempt < 64; attempt++) {
+    uint4 r = ph(key, attempt, it, stream);
+    const float x = normal1_f32(r.x, r.y);
+    const float v1 = 1.0f + cc * x;
+    if (v1 <= 0.0f) continue;
+    const float v = v1 * v1 * v1;
+    const float u = ((float)(r.z >> 8) + 0.5f) * 5.9604644775390625e-8f;
+    const float x2 = x * x;
+    if (u < 1.0f - 0.0331f * x2 * x2 || __logf(u) < 0.5f * x2 + dd * (1.0f - v + __logf(v))) {
+      const double w = 1.0 + (double)cc * (double)x;
+      return 2.0 * (double)dd * w * w * w;
+    }
+  }
+  return 2.0 * (double)dd;  // unreachable in practice (acceptance > 95 % per attempt)
+}
+
+struct ResidentGeom {
+  int C;        // cluster size (0: does not fit)
+  int ncol;     // system columns per CTA
+  int threads;  // ncol rounded up to a warp
+  int XQp;      // padded width of one exchange vector: P_t[Tmax], then q and bad partials per warp
+  size_t smem;
+};
+
+// shared memory: [ysm: Tmax*ncol][wsm: ncol][corr: Tmax][xi: RBATCH*Tmax][qw: 64][xch: 2*C*XQp][mbar]
+static ResidentGeom resident_geom(const DevBatch& d, size_t smem_cap, int maxC) {
+  ResidentGeom g{};
+  for (int C = 1; C <= maxC; C *= 2) {
+    if (d.npad % (2 * C)) continue;
+    const int ncol = d.npad / C;
+    if (ncol > 1024 || ncol % 2) continue;
+    const int threads = (ncol + 31) / 32 * 32;
+    const int XQp = (d.Tmax + 2 + 1) & ~1;  // P_t[Tmax], q, bad
+    size_t doubles = (size_t)d.Tmax * ncol + (size_t)ncol + (size_t)((d.Tmax + 1) & ~1) + (size_t)RBATCH * d.Tmax + 64 +
+                     2 * (size_t)C * XQp + 2;
+    if (doubles * 8 <= smem_cap) {
+      g.C = C; g.ncol = ncol; g.threads = threads; g.XQp = XQp; g.smem = doubles * 8;
+      return g;
+    }
+  }
+  return g;
+}
+
+template <int MAXT>
+__global__ void __launch_bounds__(MAXT, 1) diag_resident_kernel(DevBatch d, int it_begin, int it_end, int C, int ncol,
+                                                                 int XQp) {
+  extern __shared__ __align__(16) double dsm[];
+  cg::cluster_group cluster = cg::this_cluster();
+  const int rank = (int)cluster.block_rank();
+  const int cid = blockIdx.x / C, ncl = gridDim.x / C;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, W = blockDim.x >> 5;
+  const int N = d.N, nsys = d.nsys, npad = d.npad, Tm = d.Tmax;
+  double* ysm = dsm;                                   // resident slice [Tb][ncol]
+  double* wsm = ysm + (size_t)Tm * ncol;               // u_k / D_k of the local columns
+  double* corr = wsm + ncol;                           // corr_t
+  double* xi = corr + ((Tm + 1) & ~1);                 // [RBATCH][Tm] xi_t of the current batch of iterations
+  double* qw = xi + RBATCH * Tm;                       // [64] per-warp partials of q and of the non-positive count
+  double* xch = qw + 64;                               // [2][C][XQp] gathered partial vectors
+  unsigned long long* mbar = reinterpret_cast<unsigned long long*>(xch + 2 * (size_t)C * XQp);
+  const int col0 = rank * ncol;                        // first system column of this CTA (even)
+  const int k = col0 + tid;                            // this thread's system column
+  const bool owner = tid < ncol && k < nsys;
+  const double sg = (tid & 1) ? -1.0 : 1.0;            // u_k = (-1)^k  (col0 is even)
+
+  if (tid == 0) {
+    mbar_init(mbar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  unsigned phase = 0;
+  int par = 0;
+
+  for (int li = cid; li < d.nlist; li += ncl) {
+    const int b = d.blist[li];
+    if (d.failed[b]) continue;  // uniform across the cluster (set by an earlier launch only)
+    const int Tb = d.T[b];
+    const double a = d.diag_ab[2 * b], bc = d.diag_ab[2 * b + 1];
+    const double* yh = d.yhat + (size_t)d.ycompact[b] * Tm * npad + col0;
+    double* S = d.S + (size_t)b * N;
+    const Philox ph(mix_key(d.seed, d.gid ? (unsigned long long)d.gid[b] : (unsigned long long)b));
+    const unsigned dkey = (unsigned)(d.cplx ? (k >> 1) : k);  // delay index: key of the chi^2_T draw
+
+    // ---- the column slice of yhat becomes resident (TMA bulk copies, one per sample row)
+    if (tid == 0) {
+      mbar_expect_tx(mbar, (unsigned)(Tb * ncol * 8));
+      for (int t = 0; t < Tb; t++) bulk_g2s(ysm + (size_t)t * ncol, yh + (size_t)t * npad, (unsigned)(ncol * 8), mbar);
+    }
+    double Sk = owner ? S[dkey] : 0.0;
+    mbar_wait(mbar, phase);
+    phase ^= 1;
+    // per-baseline constants of the owned column: sum_t y, sum_t y^2
+    double sy = 0.0, syy = 0.0;
+    if (owner)
+      for (int t = 0; t < Tb; t++) {
+        const double v = ysm[(size_t)t * ncol + tid];
+        sy += v;
+        syy += v * v;
+      }
+    double iv = 0.0, rd = 0.0;
+    // A: D = a + 1/S on the owned column; per-warp partials of q = sum 1/D and of the non-positive count
+    auto stage_A = [&]() {
+      double ql = 0.0, badl = 0.0;
+      iv = 0.0;
+      if (owner) {
+        double si = (Sk != 0.0) ? 1.0 / Sk : 0.0;  // invert_no_zero, delay.py:1785
+        if (d.cplx) si *= 2.0;                      // delay.py:1794
+        const double D = a + si;
+        if (!(D > 0.0)) badl = 1.0;
+        iv = 1.0 / D;
+        ql = iv;
+      }
+      rd = sqrt(iv);
+      if (tid < ncol) wsm[tid] = sg * iv;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        ql += __shfl_xor_sync(0xffffffffu, ql, o);
+        badl += __shfl_xor_sync(0xffffffffu, badl, o);
+      }
+      if (lane == 0) {
+        qw[warp] = ql;
+        qw[32 + warp] = badl;
+      }
+    };
+    stage_A();
+    __syncthreads();
+
+    double dg[RBATCH], dc2[RBATCH], idct[RBATCH];
+    for (int it = it_begin; it < it_end; it++) {
+      // ---- scalar draws of this and the next RBATCH-1 iterations (independent chains: ILP)
+      const int bi = (it - it_begin) % RBATCH;
+      if (bi == 0) {
+        if (owner) {
+#pragma unroll
+          for (int j = 0; j < RBATCH; j++) {
+            uint4 r = ph((unsigned)k, 0u, (unsigned)(it + j), STREAM_DIAG_G);
+            dg[j] = (double)normal1_f32(r.x, r.y);
+            dc2[j] = chi2_fast(ph, (unsigned)(it + j), (unsigned)k, STREAM_DIAG_C2, Tb - 2);
+            idct[j] = 1.0 / chi2_fast(ph, (unsigned)(it + j), dkey, STREAM_DIAG_CHI2, Tb);
+          }
+        }
+        if (bc != 0.0)
+          for (int e = tid; e < RBATCH * Tb; e += blockDim.x) {  // xi_t of the batch
+            const int j = e / Tb, t = e - j * Tb;
+            uint4 r = ph((unsigned)t, 0u, (unsigned)(it + j), STREAM_DIAG_XI);
+            xi[j * Tm + t] = (double)normal1_f32(r.x, r.y);
+          }
+      }
+      // ---- B: partial P_t = sum_k u_k y_tk / D_k over the local columns; a warp takes 8 sample rows at a
+      // time (independent accumulators) and sends the sums straight to every CTA of the cluster
+      double* xmine = xch + (size_t)(par * C + rank) * XQp;
+      if (warp == 0 && lane < C) {
+        double qs = 0.0, bs = 0.0;
+        for (int w = 0; w < W; w++) {
+          qs += qw[w];
+          bs += qw[32 + w];
+        }
+        double* dst = cluster.map_shared_rank(xmine + Tm, lane);
+        dst[0] = qs;
+        dst[1] = bs;
+      }
+      if (bc != 0.0) {
+        for (int t0 = warp; t0 < Tb; t0 += 8 * W) {
+          double acc[8];
+#pragma unroll
+          for (int j = 0; j < 8; j++) acc[j] = 0.0;
+          for (int c = lane; c < ncol; c += 32) {
+            const double wv = wsm[c];
+#pragma unroll
+            for (int j = 0; j < 8; j++) {
+              const int t = t0 + j * W;
+              if (t < Tb) acc[j] += wv * ysm[(size_t)t * ncol + c];
+            }
+          }
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+            for (int j = 0; j < 8; j++) acc[j] += __shfl_xor_sync(0xffffffffu, acc[j], o);
+          }
+          if (lane < C) {
+            double* dst = cluster.map_shared_rank(xmine, lane);
+#pragma unroll
+            for (int j = 0; j < 8; j++) {
+              const int t = t0 + j * W;
+              if (t < Tb) dst[t] = acc[j];
+            }
+          }
+        }
+      }
+      cluster.sync();
+      // ---- D: every thread forms q, the failure flag and beta; thread t forms corr_t
+      const double* xb = xch + (size_t)par * C * XQp;
+      double q = 0.0, bad = 0.0;
+      for (int r = 0; r < C; r++) {
+        q += xb[(size_t)r * XQp + Tm];
+        bad += xb[(size_t)r * XQp + Tm + 1];
+      }
+      par ^= 1;
+      const double den = 1.0 + bc * q;
+      if (bad > 0.0 || !(den > 0.0)) {  // not positive definite: the chain stops here (delay.py:1891-1896); cluster-uniform
+        if (rank == 0 && tid == 0) {
+          d.failed[b] = 1;
+          d.n_done[b] = it;
+        }
+        break;
+      }
+      if (bc != 0.0) {
+        const double beta = bc / den, sb = sqrt(-beta);
+        for (int t = tid; t < Tb; t += blockDim.x) {
+          double P = 0.0;
+          for (int r = 0; r < C; r++) P += xb[(size_t)r * XQp + t];
+          corr[t] = -beta * P + sb * xi[bi * Tm + t];
+        }
+        __syncthreads();
+      }
+      // ---- E + F: moments of the owned column, power-spectrum draw (delay.py:1862-1880), next D
+      double ssq = 0.0;
+      if (owner) {
+        double r0 = 0.0, r1 = 0.0, sc = 0.0, scc = 0.0;
+        if (bc != 0.0) {
+          int t = 0;
+          for (; t + 1 < Tb; t += 2) {
+            const double c0 = corr[t], c1 = corr[t + 1];
+            r0 += ysm[(size_t)t * ncol + tid] * c0;
+            r1 += ysm[(size_t)(t + 1) * ncol + tid] * c1;
+            sc += c0 + c1;
+            scc += c0 * c0 + c1 * c1;
+          }
+          if (t < Tb) {
+            const double c0 = corr[t];
+            r0 += ysm[(size_t)t * ncol + tid] * c0;
+            sc += c0;
+            scc += c0 * c0;
+          }
+        }
+        const double sm1 = iv * (sy + sg * sc);                              // sum_t m
+        const double sm2 = iv * iv * (syy + 2.0 * sg * (r0 + r1) + scc);     // sum_t m^2
+        const double mm = fmax(sm2 - sm1 * sm1 / (double)Tb, 0.0);           // |m~|^2
+        if (Tb > 1) ssq = mm + 2.0 * rd * sqrt(mm) * dg[0] + rd * rd * (dg[0] * dg[0] + dc2[0]);
+      }
+      if (d.cplx) ssq += __shfl_xor_sync(0xffffffffu, ssq, 1);  // re + im columns of one delay (delay.py:1869-1875)
+      if (owner) {
+        Sk = ssq * idct[0];
+        if (!d.cplx || !(tid & 1)) {
+          S[dkey] = Sk;
+          d.samples[((size_t)it * d.B + b) * N + dkey] = Sk;
+        }
+      }
+#pragma unroll
+      for (int j = 0; j + 1 < RBATCH; j++) {  // rotate the batched draws (keeps them in registers)
+        dg[j] = dg[j + 1];
+        dc2[j] = dc2[j + 1];
+        idct[j] = idct[j + 1];
+      }
+      if (rank == 0 && tid == 0) d.n_done[b] = it + 1;
+      stage_A();
+      __syncthreads();
+    }
+    __syncthreads();  // every reader of ysm is done before the next baseline's copies land
+  }
+  cluster.sync();  // no CTA exits while a peer may still write its shared memory
+}
+
+static cudaError_t launch_resident(const DevBatch& d, int it_begin, int it_end, cudaStream_t st, bool* launched) {
+  *launched = false;
+  for (int maxC = 8; maxC <= RMAXC; maxC *= 2) {
+    ResidentGeom g = resident_geom(d, 227 * 1024, maxC);
+    if (g.C == 0) continue;
+    auto kern = g.threads <= 256 ? diag_resident_kernel<256> : diag_resident_kernel<1024>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g.smem);
+    if (e != cudaSuccess) return e;
+    if (g.C > 8) {
+      e = cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+      if (e != cudaSuccess) { (void)cudaGetLastError(); return cudaSuccess; }
+    }
+    cudaLaunchConfig_t cfg{};
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = g.C;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    cfg.blockDim = dim3(g.threads);
+    cfg.dynamicSmemBytes = g.smem;
+    cfg.stream = st;
+    cfg.gridDim = dim3(g.C);
+    int ncl = 0;
+    e = cudaOccupancyMaxActiveClusters(&ncl, kern, &cfg);
+    if (e != cudaSuccess || ncl <= 0) {
+      (void)cudaGetLastError();
+      return cudaSuccess;  // not launchable on this device: the caller falls back to the streaming kernel
+    }
+    if (ncl > d.nlist) ncl = d.nlist;
+    cfg.gridDim = dim3(ncl * g.C);
+    if (getenv("DGIBBS_VERBOSE"))
+      fprintf(stderr, "[dgibbs] resident diagonal sampler: cluster %d x %d threads, %d clusters, %zu B smem\n", g.C, g.threads,
+              ncl, g.smem);
+    e = cudaLaunchKernelEx(&cfg, kern, d, it_begin, it_end, g.C, g.ncol, g.XQp);
+    if (e == cudaSuccess) *launched = true;
+    return e;
+  }
+  return cudaSuccess;
+}
+
+cudaError_t launch_diag_sampler(const DevBatch& d, int it_begin, int it_end, int sm_count, cudaStream_t st,
+                                bool allow_resident) {
   if (d.nlist <= 0) return cudaSuccess;
+  if (allow_resident) {
+    bool launched = false;
+    cudaError_t e = launch_resident(d, it_begin, it_end, st, &launched);
+    if (e != cudaSuccess || launched) return e;
+  }
   int grid = d.nlist < sm_count ? d.nlist : sm_count;
   if (d.nsys <= 2048)
     diag_sampler_kernel<1, 4><<<grid, DTHREADS, 0, st>>>(d, it_begin, it_end);

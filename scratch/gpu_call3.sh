@@ -1,0 +1,5 @@
+set -x
+timeout 600 python -m pytest tests -m gpu -x -q > gpurun_out/c3_pytest.log 2>&1; echo "pytest rc=$?" >> gpurun_out/c3_pytest.log
+timeout 300 python bench.py --config cfg3 --nbase 2048 --steps 2 --warmup 2 --no-cpu-baseline > gpurun_out/c3_bench_cfg3.log 2>&1; echo "rc=$?" >> gpurun_out/c3_bench_cfg3.log
+DGIBBS_DIAG_STREAMING=1 timeout 300 python bench.py --config cfg3 --nbase 2048 --steps 2 --warmup 2 --no-cpu-baseline > gpurun_out/c3_bench_cfg3_streaming.log 2>&1; echo "rc=$?" >> gpurun_out/c3_bench_cfg3_streaming.log
+echo done
