@@ -13,8 +13,8 @@ import subprocess
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libdgibbs.so")
-SOURCES = ["dgibbs_api.cu", "setup_kernels.cu", "sampler_dense.cu", "sampler_diag.cu", "finish_kernels.cu"]
-HEADERS = ["common.cuh", "internal.h", os.path.join("..", "..", "include", "dgibbs.h")]
+SOURCES = ["dgibbs_api.cu", "setup_kernels.cu", "sampler_dense.cu", "sampler_diag.cu", "sampler_cross.cu", "finish_kernels.cu"]
+HEADERS = ["common.cuh", "internal.h", "dense_core.cuh", os.path.join("..", "..", "include", "dgibbs.h")]
 NVCC_FLAGS = [
     "-gencode",
     "arch=compute_100a,code=sm_100a",

@@ -38,7 +38,9 @@ EXPORTED = [
     "dgibbs_setup_inputs",
     "dgibbs_wiener",
     "dgibbs_fourier_matrix",
+    "dgibbs_cross_run",
 ]
+CROSS_MAX_DATASETS = 4
 
 _vp = C.c_void_p
 
@@ -87,6 +89,31 @@ class Result(C.Structure):
     ]
 
 
+class CrossProblem(C.Structure):
+    _fields_ = [
+        ("struct_size", C.c_int32),
+        ("B", C.c_int32),
+        ("nd", C.c_int32),
+        ("N", C.c_int32),
+        ("T", C.c_int32),
+        ("M", C.c_int32),
+        ("niter", C.c_int32),
+        ("window_id", C.c_int32),
+        ("rng_mode", C.c_int32),
+        ("reserved", C.c_int32),
+        ("seed", C.c_uint64),
+        ("data", _vp),
+        ("Ni", _vp),
+        ("fsel", _vp),
+        ("S0", _vp),
+        ("global_id", _vp),
+        ("w1", _vp),
+        ("w2", _vp),
+        ("wn", _vp),
+        ("wg", _vp),
+    ]
+
+
 class Timing(C.Structure):
     _fields_ = [
         ("ms_h2d", C.c_double),
@@ -130,10 +157,11 @@ def load():
     lib.dgibbs_setup_inputs.argtypes = [_vp, C.POINTER(Problem), C.c_int32, _vp, _vp, _vp]
     lib.dgibbs_wiener.argtypes = [_vp, C.POINTER(Problem), _vp, _vp]
     lib.dgibbs_fourier_matrix.argtypes = [_vp, C.c_int32, C.c_int32, _vp, C.c_int32, _vp]
+    lib.dgibbs_cross_run.argtypes = [_vp, C.POINTER(CrossProblem), _vp, _vp, _vp]
     for name in EXPORTED:
         if name not in ("dgibbs_last_error", "dgibbs_version"):
             getattr(lib, name).restype = C.c_int
-    for which, st in enumerate((Problem, Result, Timing)):
+    for which, st in enumerate((Problem, Result, Timing, CrossProblem)):
         if lib.dgibbs_sizeof(which) != C.sizeof(st):
             raise RuntimeError(f"ABI mismatch: {st.__name__} is {C.sizeof(st)} bytes here, "
                                f"{lib.dgibbs_sizeof(which)} in {LIB_PATH}; rebuild the library")

@@ -67,6 +67,12 @@ static cudaError_t pool_get(dgibbs_handle h, const char* name, size_t bytes, voi
   return cudaSuccess;
 }
 
+cudaError_t dg_pool_get(dgibbs_handle h, const char* name, size_t bytes, void** out) { return pool_get(h, name, bytes, out); }
+cudaStream_t dg_stream(dgibbs_handle h) { return h->stream; }
+int dg_device(dgibbs_handle h) { return h->device; }
+int dg_sm_count(dgibbs_handle h) { return h->sm_count; }
+void dg_set_error(dgibbs_handle h, const char* msg) { h->err = msg; }
+
 extern "C" int dgibbs_version(void) { return DGIBBS_VERSION; }
 
 extern "C" int dgibbs_sizeof(int which) {
@@ -74,6 +80,7 @@ extern "C" int dgibbs_sizeof(int which) {
     case 0: return (int)sizeof(dgibbs_problem);
     case 1: return (int)sizeof(dgibbs_result);
     case 2: return (int)sizeof(dgibbs_timing);
+    case 3: return (int)sizeof(dgibbs_cross_problem);
     default: return -1;
   }
 }

@@ -76,6 +76,16 @@ struct DevBatch {
   long long* prof;        // optional [16] phase cycle counters (debug), else null
 };
 
+// handle services for entry points implemented outside dgibbs_api.cu (sampler_cross.cu)
+}  // namespace dg
+struct dgibbs_handle_s;
+cudaError_t dg_pool_get(dgibbs_handle_s* h, const char* name, size_t bytes, void** out);
+cudaStream_t dg_stream(dgibbs_handle_s* h);
+int dg_device(dgibbs_handle_s* h);
+int dg_sm_count(dgibbs_handle_s* h);
+void dg_set_error(dgibbs_handle_s* h, const char* msg);
+namespace dg {
+
 // setup_kernels.cu
 cudaError_t launch_build_ftab(const DevBatch& d, double* Ftab, cudaStream_t st);
 cudaError_t launch_build_twtab(int N, double2* tw, cudaStream_t st);

@@ -15,659 +15,9 @@
 // All hot loops are ROLLED or small: straight-line code larger than the instruction caches costs
 // ~140 cycles per 128 B line on this part (measured, profiles/r01a), so register-tile code that
 // touches all 64 accumulators is kept to loads/stores only.
-#include "common.cuh"
-#include "internal.h"
+#include "dense_core.cuh"
 
 namespace dg {
-
-constexpr int STAGES = 3;
-constexpr int STAGE_DOUBLES = 2 * TILE * LDA_NT;      // A[128][20] + B[128][20]  (NN form needs less)
-constexpr int TILE_DOUBLES = TILE * LDW;              // one staged 128x128 tile, pitch 132
-constexpr int PIPE_DOUBLES = (STAGES * STAGE_DOUBLES > TILE_DOUBLES) ? STAGES * STAGE_DOUBLES : TILE_DOUBLES;
-constexpr int WP_BLOCKS = 16 * 17 / 2;                // lower-triangular 8x8 blocks of a 128x128 tile
-constexpr int WP_DOUBLES = WP_BLOCKS * 64;            // 8704 doubles = 68 KB
-constexpr int MISC_DOUBLES = 16;                      // flag + reduction scratch
-static_assert(TILE * LDA_NT + KC * LDB_NN <= STAGE_DOUBLES, "NN stage must fit");
-
-typedef double Acc[2][16][2];
-
-// optional phase profiler (DevBatch::prof != nullptr): thread 0 accumulates clock64 deltas per phase
-#define PROF(idx)                                                                       \
-  do {                                                                                  \
-    if (d.prof && threadIdx.x == 0) {                                                   \
-      long long t_ = clock64();                                                         \
-      atomicAdd((unsigned long long*)&d.prof[idx], (unsigned long long)(t_ - tlast));   \
-      tlast = t_;                                                                       \
-    }                                                                                   \
-  } while (0)
-
-struct Lane {
-  int warp, g, q;
-  int rf[2];  // the two 8-row fragments of this warp: {w, 15-w} (balances triangular tiles)
-  __device__ Lane() {
-    warp = threadIdx.x >> 5;
-    int l = threadIdx.x & 31;
-    g = l >> 2;
-    q = l & 3;
-    rf[0] = warp;
-    rf[1] = 15 - warp;
-  }
-};
-
-// which 8-column blocks each of the two row fragments of a warp computes (compile-time variants:
-// predicated-off DMMAs still occupy the fp64 tensor pipe, so skipping must be a real branch)
-enum Variant { V_FULL = 0, V_ROW0 = 1, V_ROW1 = 2, V_NONE = 3, V_DIAG_LO = 4, V_DIAG_HI = 5 };
-
-__device__ __forceinline__ int rhs_variant(bool do0, bool do1) {
-  return do0 ? (do1 ? V_FULL : V_ROW0) : (do1 ? V_ROW1 : V_NONE);
-}
-
-// packed W: block (bn, bk), bk <= bn, at ((bn*(bn+1))/2 + bk) * 64; element (r, c) of the block at
-// r*8 + (c ^ swz(r)),  swz(r) = ((r >> 1) & 1) << 2  (conflict-free fragment reads in both forms)
-__device__ __forceinline__ int wp_block(int bn, int bk) { return ((bn * (bn + 1)) / 2 + bk) * 64; }
-__device__ __forceinline__ int wp_swz(int r) { return ((r >> 1) & 1) << 2; }
-
-// ----------------------------------------------------------------------------- loaders
-// NT chunk: A rows [0,128) x k0..k0+KC of a row-major panel (ld), same for B.
-__device__ __forceinline__ void load_nt(double* stage, const double* A, const double* Bm, int ld, int k0) {
-  double* sA = stage;
-  double* sB = stage + TILE * LDA_NT;
-#pragma unroll
-  for (int r = 0; r < 4; r++) {
-    int idx = threadIdx.x + THREADS * r;  // 0..1023
-    int row = idx >> 3, c16 = idx & 7;
-    cp_async16(sA + row * LDA_NT + c16 * 2, A + (size_t)row * ld + k0 + c16 * 2);
-    cp_async16(sB + row * LDA_NT + c16 * 2, Bm + (size_t)row * ld + k0 + c16 * 2);
-  }
-}
-// NN chunk: A rows [0,128) x k0..k0+KC (lda);  B rows k0..k0+KC x 128 columns (ldb).
-__device__ __forceinline__ void load_nn(double* stage, const double* A, int lda, const double* Bm, int ldb, int k0) {
-  double* sA = stage;
-  double* sB = stage + TILE * LDA_NT;
-#pragma unroll
-  for (int r = 0; r < 4; r++) {
-    int idx = threadIdx.x + THREADS * r;
-    int row = idx >> 3, c16 = idx & 7;
-    cp_async16(sA + row * LDA_NT + c16 * 2, A + (size_t)row * lda + k0 + c16 * 2);
-    int krow = idx >> 6, c = idx & 63;
-    cp_async16(sB + krow * LDB_NN + c * 2, Bm + (size_t)(k0 + krow) * ldb + c * 2);
-  }
-}
-// packed W_j (contiguous WP_DOUBLES in global) -> smem
-__device__ __forceinline__ void load_wp(double* sWp, const double* src) {
-  for (int idx = threadIdx.x; idx < WP_DOUBLES / 2; idx += THREADS) cp_async16(sWp + idx * 2, src + idx * 2);
-  cp_async_commit();
-  cp_async_wait<0>();
-  __syncthreads();
-}
-
-// ----------------------------------------------------------------------------- chunk math
-// acc -= A * B^T over one KC chunk (A, B both [row][k]); NB0/NB1 = column blocks done for rf0/rf1.
-template <int NB0, int NB1>
-__device__ __forceinline__ void mma_nt(const double* stage, Acc& acc, const Lane& ln) {
-  const double* sA = stage;
-  const double* sB = stage + TILE * LDA_NT;
-  const int r0 = (ln.rf[0] * 8 + ln.g) * LDA_NT + ln.q;
-  const int r1 = (ln.rf[1] * 8 + ln.g) * LDA_NT + ln.q;
-  const int rb = ln.g * LDA_NT + ln.q;
-  constexpr int NBM = NB0 > NB1 ? NB0 : NB1;
-#pragma unroll
-  for (int ks = 0; ks < KC / 4; ks++) {
-    double a0 = 0, a1 = 0;
-    if (NB0 > 0) a0 = -sA[r0 + ks * 4];
-    if (NB1 > 0) a1 = -sA[r1 + ks * 4];
-#pragma unroll
-    for (int nb = 0; nb < NBM; nb++) {
-      double b = sB[rb + nb * 8 * LDA_NT + ks * 4];
-      if (nb < NB0) dmma(acc[0][nb][0], acc[0][nb][1], a0, b);
-      if (nb < NB1) dmma(acc[1][nb][0], acc[1][nb][1], a1, b);
-    }
-  }
-}
-// acc += sign * A * B over one KC chunk (A [row][k], B [k][col]).
-template <bool NEG, bool D0, bool D1>
-__device__ __forceinline__ void mma_nn(const double* stage, Acc& acc, const Lane& ln) {
-  const double* sA = stage;
-  const double* sB = stage + TILE * LDA_NT;
-  const int r0 = (ln.rf[0] * 8 + ln.g) * LDA_NT + ln.q;
-  const int r1 = (ln.rf[1] * 8 + ln.g) * LDA_NT + ln.q;
-  const int rb = ln.q * LDB_NN + ln.g;
-#pragma unroll
-  for (int ks = 0; ks < KC / 4; ks++) {
-    double a0 = 0, a1 = 0;
-    if (D0) a0 = NEG ? -sA[r0 + ks * 4] : sA[r0 + ks * 4];
-    if (D1) a1 = NEG ? -sA[r1 + ks * 4] : sA[r1 + ks * 4];
-#pragma unroll
-    for (int nb = 0; nb < 16; nb++) {
-      double b = sB[rb + ks * 4 * LDB_NN + nb * 8];
-      if (D0) dmma(acc[0][nb][0], acc[0][nb][1], a0, b);
-      if (D1) dmma(acc[1][nb][0], acc[1][nb][1], a1, b);
-    }
-  }
-}
-
-// ----------------------------------------------------------------------------- pipelined K loops
-// acc -= A[0:128, k] * B[0:128, k]^T  for k in [0, nchunks*KC)
-__device__ __forceinline__ void gemm_nt(double* pipe, Acc& acc, const Lane& ln, const double* A, const double* Bm,
-                                        int ld, int nchunks, int variant) {
-#pragma unroll
-  for (int s = 0; s < STAGES - 1; s++) {
-    if (s < nchunks) load_nt(pipe + s * STAGE_DOUBLES, A, Bm, ld, s * KC);
-    cp_async_commit();
-  }
-  for (int c = 0; c < nchunks; c++) {
-    cp_async_wait<STAGES - 2>();
-    __syncthreads();
-    int nxt = c + STAGES - 1;
-    if (nxt < nchunks) load_nt(pipe + (nxt % STAGES) * STAGE_DOUBLES, A, Bm, ld, nxt * KC);
-    cp_async_commit();
-    const double* st = pipe + (c % STAGES) * STAGE_DOUBLES;
-    switch (variant) {  // warp-uniform
-      case V_FULL: mma_nt<16, 16>(st, acc, ln); break;
-      case V_ROW0: mma_nt<16, 0>(st, acc, ln); break;
-      case V_ROW1: mma_nt<0, 16>(st, acc, ln); break;
-      case V_DIAG_LO: mma_nt<4, 16>(st, acc, ln); break;
-      case V_DIAG_HI: mma_nt<8, 12>(st, acc, ln); break;
-      default: break;
-    }
-  }
-  cp_async_wait<0>();
-  __syncthreads();
-}
-// acc (+/-)= A[0:128, kbase + k] * B[kbase + k, 0:128]  for k in [0, nchunks*KC)
-template <bool NEG>
-__device__ __forceinline__ void gemm_nn(double* pipe, Acc& acc, const Lane& ln, const double* A, int lda,
-                                        const double* Bm, int ldb, int kbase, int nchunks, int variant) {
-#pragma unroll
-  for (int s = 0; s < STAGES - 1; s++) {
-    if (s < nchunks) load_nn(pipe + s * STAGE_DOUBLES, A, lda, Bm, ldb, kbase + s * KC);
-    cp_async_commit();
-  }
-  for (int c = 0; c < nchunks; c++) {
-    cp_async_wait<STAGES - 2>();
-    __syncthreads();
-    int nxt = c + STAGES - 1;
-    if (nxt < nchunks) load_nn(pipe + (nxt % STAGES) * STAGE_DOUBLES, A, lda, Bm, ldb, kbase + nxt * KC);
-    cp_async_commit();
-    const double* st = pipe + (c % STAGES) * STAGE_DOUBLES;
-    switch (variant) {
-      case V_FULL: mma_nn<NEG, true, true>(st, acc, ln); break;
-      case V_ROW0: mma_nn<NEG, true, false>(st, acc, ln); break;
-      case V_ROW1: mma_nn<NEG, false, true>(st, acc, ln); break;
-      default: break;
-    }
-  }
-  cp_async_wait<0>();
-  __syncthreads();
-}
-
-// ----------------------------------------------------------------------------- tile staging
-__device__ __forceinline__ void acc_zero(Acc& acc) {
-#pragma unroll
-  for (int f = 0; f < 2; f++)
-#pragma unroll
-    for (int nb = 0; nb < 16; nb++) acc[f][nb][0] = acc[f][nb][1] = 0.0;
-}
-// registers -> staged tile sT[128][LDW]
-__device__ __forceinline__ void stage_acc(const Acc& acc, double* sT, const Lane& ln, bool do0, bool do1) {
-#pragma unroll
-  for (int f = 0; f < 2; f++) {
-    if (f == 0 ? !do0 : !do1) continue;
-    double* row = sT + (ln.rf[f] * 8 + ln.g) * LDW + 2 * ln.q;
-#pragma unroll
-    for (int nb = 0; nb < 16; nb++) *reinterpret_cast<double2*>(row + nb * 8) = make_double2(acc[f][nb][0], acc[f][nb][1]);
-  }
-}
-__device__ __forceinline__ void tile_store_global(const Acc& acc, double* base, int ld, const Lane& ln, bool do0,
-                                                  bool do1) {
-#pragma unroll
-  for (int f = 0; f < 2; f++) {
-    if (f == 0 ? !do0 : !do1) continue;
-    double* row = base + (size_t)(ln.rf[f] * 8 + ln.g) * ld + 2 * ln.q;
-#pragma unroll
-    for (int nb = 0; nb < 16; nb++) *reinterpret_cast<double2*>(row + nb * 8) = make_double2(acc[f][nb][0], acc[f][nb][1]);
-  }
-}
-__device__ __forceinline__ void tile_load_global(Acc& acc, const double* base, int ld, const Lane& ln) {
-#pragma unroll
-  for (int f = 0; f < 2; f++) {
-    const double* row = base + (size_t)(ln.rf[f] * 8 + ln.g) * ld + 2 * ln.q;
-#pragma unroll
-    for (int nb = 0; nb < 16; nb++) {
-      double2 v = *reinterpret_cast<const double2*>(row + nb * 8);
-      acc[f][nb][0] = v.x;
-      acc[f][nb][1] = v.y;
-    }
-  }
-}
-// sT += tile (ti, tj) of Ci = circ(c) + diag(Si) (identity in the padding).  Rolled, coalesced.
-__device__ __forceinline__ void add_generated(double* sT, const double* ct, const double* Si, int N, int nsys, int cplx,
-                                              int ti, int tj, bool lower_only) {
-  const bool interior = !cplx && (ti + 1) * TILE <= nsys && (tj + 1) * TILE <= nsys;
-  const int R0 = ti * TILE, C0 = tj * TILE;
-#pragma unroll 2
-  for (int e = threadIdx.x; e < TILE * TILE; e += THREADS) {
-    int r = e >> 7, c = e & 127;
-    if (lower_only && c > r) continue;
-    int R = R0 + r, C = C0 + c;
-    double v;
-    if (interior) {
-      int k = R - C;
-      if (k < 0) k += N;
-      v = ct[k];
-      if (R == C) v += Si[R];
-    } else if (R < nsys && C < nsys) {
-      v = circ_entry(ct, N, cplx, R, C);
-      if (R == C) v += Si[R];
-    } else {
-      v = (R == C) ? 1.0 : 0.0;
-    }
-    sT[r * LDW + c] += v;
-  }
-}
-// sT[0:nrows] += src[0:nrows][0:128]  (row pitch ld in global)
-__device__ __forceinline__ void add_global(double* sT, const double* src, int ld, int nrows) {
-  for (int e = threadIdx.x; e < nrows * (TILE / 2); e += THREADS) {
-    int r = e >> 6, c = (e & 63) * 2;
-    double2 v = *reinterpret_cast<const double2*>(src + (size_t)r * ld + c);
-    double2* p = reinterpret_cast<double2*>(sT + r * LDW + c);
-    double2 o = *p;
-    o.x += v.x;
-    o.y += v.y;
-    *p = o;
-  }
-}
-
-// In place  sT <- sT * inv(L_jj)^T  by blocked forward substitution over the 16 column blocks:
-//   X_p = (C_p - sum_{k<p} X_k L(p,k)^T) W8_p^T ,  W8_p = inv(L(p,p))  (8x8, well conditioned)
-// sWp holds L_jj packed by 8x8 blocks with W8_p in the diagonal block slots.  Each warp owns its 16
-// rows, so only __syncwarp is needed.  Same accuracy class as LAPACK's dtrsm (explicit inverses only
-// at the 8x8 level): a full 128x128 inverse costs 20x in accuracy at cond(Ci) ~ 4e8.
-template <bool D0, bool D1>
-__device__ __forceinline__ void trisolve_nt_body(double* sT, const double* sWp, const Lane& ln) {
-  double* r0 = sT + (ln.rf[0] * 8 + ln.g) * LDW;
-  double* r1 = sT + (ln.rf[1] * 8 + ln.g) * LDW;
-  const int q = ln.q, sw = wp_swz(ln.g);
-  const int bo0 = ln.g * 8 + (q ^ sw), bo1 = ln.g * 8 + ((4 + q) ^ sw);
-#pragma unroll 1
-  for (int p = 0; p < 16; p++) {
-    double c00 = 0, c01 = 0, c10 = 0, c11 = 0, e00 = 0, e01 = 0, e10 = 0, e11 = 0;
-    if (D0) { c00 = r0[8 * p + 2 * q]; c01 = r0[8 * p + 2 * q + 1]; }
-    if (D1) { c10 = r1[8 * p + 2 * q]; c11 = r1[8 * p + 2 * q + 1]; }
-    const double* wb = sWp + wp_block(p, 0);
-#pragma unroll 1
-    for (int k = 0; k < p; k++) {
-      double b0 = wb[k * 64 + bo0], b1 = wb[k * 64 + bo1];
-      if (D0) { dmma(c00, c01, -r0[8 * k + q], b0); dmma(e00, e01, -r0[8 * k + 4 + q], b1); }
-      if (D1) { dmma(c10, c11, -r1[8 * k + q], b0); dmma(e10, e11, -r1[8 * k + 4 + q], b1); }
-    }
-    __syncwarp();
-    if (D0) { r0[8 * p + 2 * q] = c00 + e00; r0[8 * p + 2 * q + 1] = c01 + e01; }
-    if (D1) { r1[8 * p + 2 * q] = c10 + e10; r1[8 * p + 2 * q + 1] = c11 + e11; }
-    __syncwarp();
-    const double* w8 = sWp + wp_block(p, p);
-    double b0 = w8[bo0], b1 = w8[bo1];
-    double o00 = 0, o01 = 0, o10 = 0, o11 = 0;
-    if (D0) { dmma(o00, o01, r0[8 * p + q], b0); dmma(o00, o01, r0[8 * p + 4 + q], b1); }
-    if (D1) { dmma(o10, o11, r1[8 * p + q], b0); dmma(o10, o11, r1[8 * p + 4 + q], b1); }
-    __syncwarp();
-    if (D0) { r0[8 * p + 2 * q] = o00; r0[8 * p + 2 * q + 1] = o01; }
-    if (D1) { r1[8 * p + 2 * q] = o10; r1[8 * p + 2 * q + 1] = o11; }
-    __syncwarp();
-  }
-}
-// In place  sT <- sT * inv(L_jj)  by blocked backward substitution:
-//   X_p = (Z_p - sum_{k>p} X_k L(k,p)) W8_p
-template <bool D0, bool D1>
-__device__ __forceinline__ void trisolve_nn_body(double* sT, const double* sWp, const Lane& ln) {
-  double* r0 = sT + (ln.rf[0] * 8 + ln.g) * LDW;
-  double* r1 = sT + (ln.rf[1] * 8 + ln.g) * LDW;
-  const int q = ln.q;
-  const int bo0 = q * 8 + (ln.g ^ wp_swz(q)), bo1 = (4 + q) * 8 + (ln.g ^ wp_swz(4 + q));
-#pragma unroll 1
-  for (int p = 15; p >= 0; p--) {
-    double c00 = 0, c01 = 0, c10 = 0, c11 = 0, e00 = 0, e01 = 0, e10 = 0, e11 = 0;
-    if (D0) { c00 = r0[8 * p + 2 * q]; c01 = r0[8 * p + 2 * q + 1]; }
-    if (D1) { c10 = r1[8 * p + 2 * q]; c11 = r1[8 * p + 2 * q + 1]; }
-#pragma unroll 1
-    for (int k = p + 1; k < 16; k++) {
-      const double* wb = sWp + wp_block(k, p);
-      double b0 = wb[bo0], b1 = wb[bo1];
-      if (D0) { dmma(c00, c01, -r0[8 * k + q], b0); dmma(e00, e01, -r0[8 * k + 4 + q], b1); }
-      if (D1) { dmma(c10, c11, -r1[8 * k + q], b0); dmma(e10, e11, -r1[8 * k + 4 + q], b1); }
-    }
-    __syncwarp();
-    if (D0) { r0[8 * p + 2 * q] = c00 + e00; r0[8 * p + 2 * q + 1] = c01 + e01; }
-    if (D1) { r1[8 * p + 2 * q] = c10 + e10; r1[8 * p + 2 * q + 1] = c11 + e11; }
-    __syncwarp();
-    const double* w8 = sWp + wp_block(p, p);
-    double b0 = w8[bo0], b1 = w8[bo1];
-    double o00 = 0, o01 = 0, o10 = 0, o11 = 0;
-    if (D0) { dmma(o00, o01, r0[8 * p + q], b0); dmma(o00, o01, r0[8 * p + 4 + q], b1); }
-    if (D1) { dmma(o10, o11, r1[8 * p + q], b0); dmma(o10, o11, r1[8 * p + 4 + q], b1); }
-    __syncwarp();
-    if (D0) { r0[8 * p + 2 * q] = o00; r0[8 * p + 2 * q + 1] = o01; }
-    if (D1) { r1[8 * p + 2 * q] = o10; r1[8 * p + 2 * q + 1] = o11; }
-    __syncwarp();
-  }
-}
-template <bool NN>
-__device__ __forceinline__ void trisolve(double* sT, const double* sWp, const Lane& ln, int variant) {
-  switch (variant) {
-    case V_FULL: NN ? trisolve_nn_body<true, true>(sT, sWp, ln) : trisolve_nt_body<true, true>(sT, sWp, ln); break;
-    case V_ROW0: NN ? trisolve_nn_body<true, false>(sT, sWp, ln) : trisolve_nt_body<true, false>(sT, sWp, ln); break;
-    case V_ROW1: NN ? trisolve_nn_body<false, true>(sT, sWp, ln) : trisolve_nt_body<false, true>(sT, sWp, ln); break;
-    default: break;
-  }
-}
-// staged tile rows [0, nrows) -> global (row pitch ld), coalesced
-__device__ __forceinline__ void copy_tile_out(const double* sT, double* dst, int ld, int nrows) {
-  for (int e = threadIdx.x; e < nrows * (TILE / 2); e += THREADS) {
-    int r = e >> 6, c = (e & 63) * 2;
-    *reinterpret_cast<double2*>(dst + (size_t)r * ld + c) = *reinterpret_cast<const double2*>(sT + r * LDW + c);
-  }
-}
-
-
-// ----------------------------------------------------------------------------- masked inverse DFT as an FFT
-// y[t, n] = sum_i u[t, 2i] cos(2 pi i n / N) - u[t, 2i+1] sin(2 pi i n / N) = Re sum_i U_i e^{+2 pi i (i n) / N}
-// (the rows of fourier_matrix_r2c / _c2c, delay.py:1480-1510, 1549-1585, applied transposed) is an
-// unnormalised inverse DFT of the zero-filled channel grid: O(N log N) per sample instead of the
-// 4 n M flop of the dense projection, and it needs no projection table.  Stockham autosort, radix 4
-// (+ one radix-2 stage), ping-pong between two shared-memory buffers, exact twiddles from a table.
-__device__ __forceinline__ double2 tw_get(const double2* tw, int m, int N) {  // e^{2 pi i m / N}, 0 <= m < N
-  const int half = N >> 1;
-  double2 w = tw[m & (half - 1)];
-  if (m & half) { w.x = -w.x; w.y = -w.y; }
-  return w;
-}
-__device__ __forceinline__ double2 cmul(double2 a, double2 b) {
-  return make_double2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x);
-}
-// Inverse (sign +) DFT of x[0:N) (N = 2^m >= 8); returns the buffer that holds the result (x or y).
-// All threads of the CTA must call it; the inputs must be visible (caller synchronises before).
-__device__ double2* fft_inverse_smem(double2* x, double2* y, const double2* tw, int N) {
-  int Ns = 1;
-  const int quarter = N >> 2;
-  while (Ns * 4 <= N) {
-    const int s = N / (4 * Ns);
-    for (int j = threadIdx.x; j < quarter; j += THREADS) {
-      const int k = j & (Ns - 1);
-      double2 v0 = x[j], v1 = x[j + quarter], v2 = x[j + 2 * quarter], v3 = x[j + 3 * quarter];
-      if (Ns > 1) {
-        v1 = cmul(v1, tw_get(tw, k * s, N));
-        v2 = cmul(v2, tw_get(tw, 2 * k * s, N));
-        v3 = cmul(v3, tw_get(tw, 3 * k * s, N));
-      }
-      const double2 a = make_double2(v0.x + v2.x, v0.y + v2.y), b = make_double2(v0.x - v2.x, v0.y - v2.y);
-      const double2 c = make_double2(v1.x + v3.x, v1.y + v3.y), e = make_double2(v1.x - v3.x, v1.y - v3.y);
-      const int j0 = ((j - k) << 2) + k;
-      y[j0] = make_double2(a.x + c.x, a.y + c.y);
-      y[j0 + Ns] = make_double2(b.x - e.y, b.y + e.x);      // b + i e
-      y[j0 + 2 * Ns] = make_double2(a.x - c.x, a.y - c.y);
-      y[j0 + 3 * Ns] = make_double2(b.x + e.y, b.y - e.x);  // b - i e
-    }
-    __syncthreads();
-    double2* tmp = x; x = y; y = tmp;
-    Ns <<= 2;
-  }
-  if (Ns < N) {  // Ns == N/2: one radix-2 stage, twiddle stride 1
-    const int half = N >> 1;
-    for (int j = threadIdx.x; j < half; j += THREADS) {
-      const double2 v0 = x[j], v1 = cmul(x[j + half], tw[j]);
-      y[j] = make_double2(v0.x + v1.x, v0.y + v1.y);
-      y[j + half] = make_double2(v0.x - v1.x, v0.y - v1.y);
-    }
-    __syncthreads();
-    double2* tmp = x; x = y; y = tmp;
-  }
-  return x;
-}
-
-// u_i = h_i (z_i + w2_i) of sample t, channel i of the full grid (delay.py:1814,1817); 0 where masked
-struct DrawCtx {
-  const DevBatch* d;
-  const Philox* ph;
-  const int* cidx;
-  const double* h;
-  const double* zT;
-  const double* w1;  // injected draws of this iteration (or null)
-  const double* w2;
-  int Tb, it, half;
-};
-__device__ __forceinline__ double2 u_value(const DrawCtx& c, int t, int i) {
-  if (t >= c.Tb) return make_double2(0.0, 0.0);
-  const int ci = c.cidx[i];
-  if (ci < 0) return make_double2(0.0, 0.0);
-  double n0 = 0.0, n1 = 0.0;
-  if (c.d->rng_mode == 1) {
-    unsigned long long blk = (unsigned long long)t * c.half + i;
-    normal_pair((*c.ph)((unsigned)blk, (unsigned)(blk >> 32), (unsigned)c.it, STREAM_W2), n0, n1);
-  } else if (c.d->rng_mode == 0) {
-    n0 = c.w2[(long long)(2 * ci) * c.Tb + t];
-    n1 = c.w2[(long long)(2 * ci + 1) * c.Tb + t];
-  }
-  const double2 z = *reinterpret_cast<const double2*>(c.zT + (size_t)t * c.d->Kpad + 2 * i);
-  return make_double2(c.h[2 * i] * (z.x + n0), c.h[2 * i + 1] * (z.y + n1));
-}
-// the two standard normals w1[t, k], w1[t, k+1] (k even) of this iteration
-__device__ __forceinline__ void w1_pair(const DrawCtx& c, int t, int k, int nsys, double& n0, double& n1) {
-  n0 = n1 = 0.0;
-  if (c.d->rng_mode == 1) {
-    unsigned long long blk = ((unsigned long long)t * nsys + k) >> 1;
-    normal_pair((*c.ph)((unsigned)blk, (unsigned)(blk >> 32), (unsigned)c.it, STREAM_W1), n0, n1);
-  } else if (c.d->rng_mode == 0) {
-    n0 = c.w1[(long long)k * c.Tb + t];
-    n1 = c.w1[(long long)(k + 1) * c.Tb + t];
-  }
-}
-
-// Fused prepass + phase 0:  Rh[t, :] = sqrt(Si) w1[t] + F^T (h (z[t] + w2[t]))   for every sample row,
-// zero in the padding rows / columns the factorisation sweeps over.
-//   real mode    : two samples per complex FFT (their spectra are Hermitian-extended and combined as A + iB)
-//   complex mode : one sample per FFT, output interleaved re/im
-__device__ void project_rows_fft(const DevBatch& d, const DrawCtx& c, double* Rh, const double* Si, double2* bufA,
-                                 double2* bufB, double2* tw_s, int rows) {
-  const int N = d.N, nsys = d.nsys, npad = d.npad, nch = d.nch;
-  for (int m = threadIdx.x; m < N / 2; m += THREADS) tw_s[m] = d.twtab[m];
-  const int step = d.cplx ? 1 : 2;
-  for (int t0 = 0; t0 < rows; t0 += step) {
-    __syncthreads();  // previous epilogue finished with the buffers (and tw_s is loaded)
-    if (t0 >= c.Tb) {  // padding rows: zeros (CTA-uniform branch)
-      for (int e = threadIdx.x; e < step * (npad / 2); e += THREADS) {
-        int r = e / (npad / 2), k = (e % (npad / 2)) * 2;
-        if (t0 + r < rows) *reinterpret_cast<double2*>(Rh + (size_t)(t0 + r) * npad + k) = make_double2(0.0, 0.0);
-      }
-      continue;
-    }
-    if (!d.cplx) {
-      for (int i = threadIdx.x; i < nch; i += THREADS) {
-        const double2 U0 = u_value(c, t0, i), U1 = u_value(c, t0 + 1, i);
-        if (i == 0 || i == N / 2) {
-          bufA[i] = make_double2(U0.x, U1.x);
-        } else {
-          bufA[i] = make_double2(0.5 * (U0.x - U1.y), 0.5 * (U0.y + U1.x));       // (U0 + i U1) / 2
-          bufA[N - i] = make_double2(0.5 * (U0.x + U1.y), 0.5 * (U1.x - U0.y));   // (conj U0 + i conj U1) / 2
-        }
-      }
-    } else {
-      for (int i = threadIdx.x; i < N; i += THREADS) bufA[i] = u_value(c, t0, i);
-    }
-    __syncthreads();
-    const double2* res = fft_inverse_smem(bufA, bufB, tw_s, N);
-    if (!d.cplx) {
-      const bool two = t0 + 1 < rows;
-      for (int p = threadIdx.x; p < npad / 2; p += THREADS) {
-        const int k = 2 * p;
-        double2 ya = make_double2(0.0, 0.0), yb = make_double2(0.0, 0.0);
-        if (k < nsys) {
-          const double2 r0 = res[k], r1 = res[k + 1];
-          const double s0 = sqrt(Si[k]), s1 = sqrt(Si[k + 1]);
-          double n0, n1;
-          w1_pair(c, t0, k, nsys, n0, n1);
-          ya = make_double2(s0 * n0 + r0.x, s1 * n1 + r1.x);   // delay.py:1815-1817
-          if (t0 + 1 < c.Tb) {
-            w1_pair(c, t0 + 1, k, nsys, n0, n1);
-            yb = make_double2(s0 * n0 + r0.y, s1 * n1 + r1.y);
-          }
-        }
-        *reinterpret_cast<double2*>(Rh + (size_t)t0 * npad + k) = ya;
-        if (two) *reinterpret_cast<double2*>(Rh + (size_t)(t0 + 1) * npad + k) = yb;
-      }
-    } else {
-      for (int p = threadIdx.x; p < npad / 2; p += THREADS) {
-        const int k = 2 * p;
-        double2 ya = make_double2(0.0, 0.0);
-        if (k < nsys) {
-          const double2 r0 = res[p];
-          double n0, n1;
-          w1_pair(c, t0, k, nsys, n0, n1);
-          ya = make_double2(sqrt(Si[k]) * n0 + r0.x, sqrt(Si[k + 1]) * n1 + r0.y);
-        }
-        *reinterpret_cast<double2*>(Rh + (size_t)t0 * npad + k) = ya;
-      }
-    }
-  }
-  __syncthreads();
-}
-
-// ----------------------------------------------------------------------------- diagonal tile
-// In-place blocked Cholesky of the staged 128x128 tile (lower) by 8-column panels.  Per panel p:
-//   S1  all warps : panel blocks  C(rb,p) -= L(rb,0:p) L(p,0:p)^T                      (DMMA)
-//   S2  warp 0    : 8x8 Cholesky of C(p,p) and its inverse W8_p, in registers
-//   S3  all warps : L(rb,p) = C(rb,p) W8_p^T  (rb > p)                                 (DMMA)
-// On exit sWp holds L_jj packed by 8x8 blocks (bank-swizzled) with W8_p in the diagonal slots.
-// Returns false on a non-positive pivot (same test as LAPACK dpotrf: ajj <= 0 or NaN).
-__device__ bool factor_diag(double* sT, double* sWp, double* misc, const Lane& ln) {
-  int* flag = reinterpret_cast<int*>(misc);
-  const int g = ln.g, q = ln.q;
-  const int bo0 = g * 8 + (q ^ wp_swz(g)), bo1 = g * 8 + ((4 + q) ^ wp_swz(g));
-  if (threadIdx.x == 0) *flag = 0;
-  for (int p = 0; p < 16; p++) {
-    // ---- S1
-    for (int rb = p + ln.warp; rb < 16; rb += NWARP) {
-      double* cp = sT + (rb * 8 + g) * LDW + 8 * p + 2 * q;
-      double c0 = cp[0], c1 = cp[1], e0 = 0.0, e1 = 0.0;
-      const double* ap = sT + (rb * 8 + g) * LDW + q;
-      const double* bp = sT + (8 * p + g) * LDW + q;
-#pragma unroll 1
-      for (int k = 0; k < p; k++) {
-        dmma(c0, c1, -ap[8 * k], bp[8 * k]);
-        dmma(e0, e1, -ap[8 * k + 4], bp[8 * k + 4]);
-      }
-      cp[0] = c0 + e0;
-      cp[1] = c1 + e1;
-    }
-    __syncthreads();
-    // ---- S2 (every lane of warp 0 computes the same 8x8 factor; identical-value stores)
-    if (ln.warp == 0) {
-      double a[8][8], w[8][8], rinv[8];
-      bool ok = true;
-#pragma unroll
-      for (int i = 0; i < 8; i++)
-#pragma unroll
-        for (int c = 0; c <= i; c++) a[i][c] = sT[(8 * p + i) * LDW + 8 * p + c];
-#pragma unroll
-      for (int k = 0; k < 8; k++) {
-        double dk = a[k][k];
-        if (!(dk > 0.0)) ok = false;
-        double piv = sqrt(dk);
-        double r = 1.0 / piv;
-        rinv[k] = r;
-        a[k][k] = piv;
-#pragma unroll
-        for (int i = k + 1; i < 8; i++) a[i][k] *= r;
-#pragma unroll
-        for (int c = k + 1; c < 8; c++)
-#pragma unroll
-          for (int i = c; i < 8; i++) a[i][c] -= a[i][k] * a[c][k];
-      }
-#pragma unroll
-      for (int c = 0; c < 8; c++) {
-        w[c][c] = rinv[c];
-#pragma unroll
-        for (int i = c + 1; i < 8; i++) {
-          double s = 0.0;
-#pragma unroll
-          for (int k = c; k < i; k++) s += a[i][k] * w[k][c];
-          w[i][c] = -s * rinv[i];
-        }
-      }
-      double* wpp = sWp + wp_block(p, p);
-#pragma unroll
-      for (int i = 0; i < 8; i++)
-#pragma unroll
-        for (int c = 0; c < 8; c++) wpp[i * 8 + (c ^ wp_swz(i))] = (c <= i) ? w[i][c] : 0.0;
-      if (!ok) *flag = 1;
-    }
-    __syncthreads();
-    if (*flag) return false;
-    // ---- S3
-    {
-      const double* w8 = sWp + wp_block(p, p);
-      const double b0 = w8[bo0], b1 = w8[bo1];
-      for (int rb = p + 1 + ln.warp; rb < 16; rb += NWARP) {
-        double* cp = sT + (rb * 8 + g) * LDW + 8 * p;
-        double a0 = cp[q], a1 = cp[4 + q];
-        double o0 = 0.0, o1 = 0.0;
-        dmma(o0, o1, a0, b0);
-        dmma(o0, o1, a1, b1);
-        __syncwarp();
-        cp[2 * q] = o0;
-        cp[2 * q + 1] = o1;
-      }
-    }
-    __syncthreads();
-  }
-  // pack the strictly-lower 8x8 blocks of L_jj next to the W8 diagonal blocks
-  for (int e = threadIdx.x; e < TILE * TILE; e += THREADS) {
-    int n = e >> 7, k = e & 127;
-    int bn = n >> 3, bk = k >> 3;
-    if (bk < bn) sWp[wp_block(bn, bk) + (n & 7) * 8 + ((k & 7) ^ wp_swz(n & 7))] = sT[n * LDW + k];
-  }
-  __syncthreads();
-  return true;
-}
-
-// ----------------------------------------------------------------------------- diagonal branch
-// Ci = D + b u u^T with D = diag(a + Si), u_k = (-1)^k: solve every RHS row in place by
-// Sherman-Morrison.  Returns false when the system is not positive definite (some D_k <= 0 or
-// 1 + b u^T D^-1 u <= 0), which is when the reference's Cholesky would fail.
-__device__ bool diag_solve_rows(double* Rh, const double* Si, double a, double bc, int nsys, int npad, int Tb,
-                                double* misc) {
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  double ql = 0.0;
-  bool pos = true;
-  for (int k = threadIdx.x; k < nsys; k += THREADS) {
-    double D = a + Si[k];
-    if (!(D > 0.0)) pos = false;
-    ql += 1.0 / D;
-  }
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) ql += __shfl_xor_sync(0xffffffffu, ql, o);
-  __syncthreads();
-  if (lane == 0) misc[2 + warp] = ql;
-  int allpos = __syncthreads_and(pos ? 1 : 0);
-  double q = 0.0;
-#pragma unroll
-  for (int w = 0; w < NWARP; w++) q += misc[2 + w];
-  const double den = 1.0 + bc * q;
-  if (!allpos || !(den > 0.0)) return false;
-  const double beta = bc / den;
-  for (int t = warp; t < Tb; t += NWARP) {
-    double* row = Rh + (size_t)t * npad;
-    double s = 0.0;
-    if (bc != 0.0) {
-      for (int k = lane; k < nsys; k += 32) s += ((k & 1) ? -row[k] : row[k]) / (a + Si[k]);
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-    }
-    const double bs = beta * s;
-    for (int k = lane; k < nsys; k += 32) row[k] = (row[k] - ((k & 1) ? -bs : bs)) / (a + Si[k]);
-  }
-  __syncthreads();
-  return true;
-}
 
 // ----------------------------------------------------------------------------- the sampler
 // Shared memory:  [ctab: nsys (optional)] [sWp: WP_DOUBLES] [pipe/tile: PIPE_DOUBLES] [misc]

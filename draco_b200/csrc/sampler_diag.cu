@@ -270,6 +270,19 @@ __device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned pari
         : "memory");
   }
 }
+// shared::cluster address of `saddr` (a shared::cta address) in CTA `rank` of the cluster
+__device__ __forceinline__ unsigned mapa_u32(unsigned saddr, unsigned rank) {
+  unsigned r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(saddr), "r"(rank));
+  return r;
+}
+// remote 8-byte store whose completion is counted (in bytes) on the DESTINATION CTA's mbarrier: the
+// consumer waits on its own barrier, no cluster-wide fence or barrier is involved
+__device__ __forceinline__ void st_async_f64(unsigned raddr, double v, unsigned rmbar) {
+  asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.b64 [%0], %1, [%2];" ::"r"(raddr),
+               "l"(__double_as_longlong(v)), "r"(rmbar)
+               : "memory");
+}
 // TMA bulk copy global -> this CTA's shared memory, completion counted in bytes on an mbarrier
 __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned bytes, unsigned long long* bar) {
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
@@ -286,7 +299,8 @@ __device__ __forceinline__ float normal1_f32(unsigned a, unsigned b) {
 }
 // chi^2 with `dof` degrees of freedom (Marsaglia-Tsang on 2 Gamma(dof/2)); the proposal normal and the
 // acceptance test run in fp32, the variate itself is formed in fp64.  dof <= 0 gives 0.
-__device__ __forceinline__ double chi2_fast(const Philox& ph, unsigned it, unsigned key, unsigned stream, int dof) {
+__device__ __forceinline__ double chi2_fast(const Philox& ph, unsigned it, unsigned key, unsigned stream, int dof,
+                                            bool have_first = false, unsigned fa = 0, unsigned fb = 0, unsigned fu = 0) {
   if (dof <= 0) return 0.0;
   if (dof == 1) {
     uint4 r = ph(key, 0u, it, stream);
@@ -295,12 +309,16 @@ __device__ __forceinline__ double chi2_fast(const Philox& ph, unsigned it, unsig
   }
   const float dd = 0.5f * (float)dof - (1.0f / 3.0f), cc = rsqrtf(9.0f * dd);
   for (unsigned attempt = 0; attempt < 64; attempt++) {
-    uint4 r = ph(key, attempt, it, stream);
-    const float x = normal1_f32(r.x, r.y);
+    unsigned a = fa, b = fb, uu = fu;
+    if (attempt > 0 || !have_first) {
+      uint4 r = ph(key, attempt, it, stream);
+      a = r.x; b = r.y; uu = r.z;
+    }
+    const float x = normal1_f32(a, b);
     const float v1 = 1.0f + cc * x;
     if (v1 <= 0.0f) continue;
     const float v = v1 * v1 * v1;
-    const float u = ((float)(r.z >> 8) + 0.5f) * 5.9604644775390625e-8f;
+    const float u = ((float)(uu >> 8) + 0.5f) * 5.9604644775390625e-8f;
     const float x2 = x * x;
     if (u < 1.0f - 0.0331f * x2 * x2 || __logf(u) < 0.5f * x2 + dd * (1.0f - v + __logf(v))) {
       const double w = 1.0 + (double)cc * (double)x;
@@ -318,7 +336,7 @@ struct ResidentGeom {
   size_t smem;
 };
 
-// shared memory: [ysm: Tmax*ncol][wsm: ncol][corr: Tmax][xi: RBATCH*Tmax][qw: 64][xch: 2*C*XQp][mbar]
+// shared memory: [ysm: Tmax*ncol][wsm: ncol][corr: Tmax][xi: RBATCH*Tmax][qw: 64][scw: 64][xch: 2*C*XQp][mbar: 3]
 static ResidentGeom resident_geom(const DevBatch& d, size_t smem_cap, int maxC) {
   ResidentGeom g{};
   for (int C = 1; C <= maxC; C *= 2) {
@@ -327,8 +345,8 @@ static ResidentGeom resident_geom(const DevBatch& d, size_t smem_cap, int maxC) 
     if (ncol > 1024 || ncol % 2) continue;
     const int threads = (ncol + 31) / 32 * 32;
     const int XQp = (d.Tmax + 2 + 1) & ~1;  // P_t[Tmax], q, bad
-    size_t doubles = (size_t)d.Tmax * ncol + (size_t)ncol + (size_t)((d.Tmax + 1) & ~1) + (size_t)RBATCH * d.Tmax + 64 +
-                     2 * (size_t)C * XQp + 2;
+    size_t doubles = (size_t)d.Tmax * ncol + (size_t)ncol + (size_t)((d.Tmax + 1) & ~1) + (size_t)RBATCH * d.Tmax + 128 +
+                     2 * (size_t)C * XQp + 4;
     if (doubles * 8 <= smem_cap) {
       g.C = C; g.ncol = ncol; g.threads = threads; g.XQp = XQp; g.smem = doubles * 8;
       return g;
@@ -351,19 +369,23 @@ __global__ void __launch_bounds__(MAXT, 1) diag_resident_kernel(DevBatch d, int 
   double* corr = wsm + ncol;                           // corr_t
   double* xi = corr + ((Tm + 1) & ~1);                 // [RBATCH][Tm] xi_t of the current batch of iterations
   double* qw = xi + RBATCH * Tm;                       // [64] per-warp partials of q and of the non-positive count
-  double* xch = qw + 64;                               // [2][C][XQp] gathered partial vectors
+  double* scw = qw + 64;                               // [64] per-warp partials of sum corr, sum corr^2
+  double* xch = scw + 64;                               // [2][C][XQp] gathered partial vectors
   unsigned long long* mbar = reinterpret_cast<unsigned long long*>(xch + 2 * (size_t)C * XQp);
   const int col0 = rank * ncol;                        // first system column of this CTA (even)
   const int k = col0 + tid;                            // this thread's system column
   const bool owner = tid < ncol && k < nsys;
   const double sg = (tid & 1) ? -1.0 : 1.0;            // u_k = (-1)^k  (col0 is even)
 
+  unsigned long long* xbar = mbar + 1;  // [2] exchange barriers, one per parity
   if (tid == 0) {
     mbar_init(mbar, 1);
+    mbar_init(xbar, 1);
+    mbar_init(xbar + 1, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  __syncthreads();
-  unsigned phase = 0;
+  cluster.sync();  // every CTA's barriers exist before a peer signals them
+  unsigned phase = 0, xphase = 0;  // xphase bit p: phase parity of xbar[p]
   int par = 0;
 
   for (int li = cid; li < d.nlist; li += ncl) {
@@ -428,10 +450,13 @@ __global__ void __launch_bounds__(MAXT, 1) diag_resident_kernel(DevBatch d, int 
         if (owner) {
 #pragma unroll
           for (int j = 0; j < RBATCH; j++) {
-            uint4 r = ph((unsigned)k, 0u, (unsigned)(it + j), STREAM_DIAG_G);
+            // two Philox blocks feed g and the first attempts of both chi^2 draws (real mode; in complex
+            // mode the chi^2_T draw is shared by the re/im columns of a delay and keyed on the delay)
+            const uint4 r = ph((unsigned)k, 0u, (unsigned)(it + j), STREAM_DIAG_G);
+            const uint4 r2 = ph((unsigned)k, 1u, (unsigned)(it + j), STREAM_DIAG_G);
             dg[j] = (double)normal1_f32(r.x, r.y);
-            dc2[j] = chi2_fast(ph, (unsigned)(it + j), (unsigned)k, STREAM_DIAG_C2, Tb - 2);
-            idct[j] = 1.0 / chi2_fast(ph, (unsigned)(it + j), dkey, STREAM_DIAG_CHI2, Tb);
+            dc2[j] = chi2_fast(ph, (unsigned)(it + j), (unsigned)k, STREAM_DIAG_C2, Tb - 2, true, r.z, r.w, r2.z);
+            idct[j] = 1.0 / chi2_fast(ph, (unsigned)(it + j), dkey, STREAM_DIAG_CHI2, Tb, !d.cplx, r2.x, r2.y, r2.w);
           }
         }
         if (bc != 0.0)
@@ -450,39 +475,64 @@ __global__ void __launch_bounds__(MAXT, 1) diag_resident_kernel(DevBatch d, int 
           qs += qw[w];
           bs += qw[32 + w];
         }
-        double* dst = cluster.map_shared_rank(xmine + Tm, lane);
-        dst[0] = qs;
-        dst[1] = bs;
+        const unsigned rb = mapa_u32(smem_u32(xbar + par), lane), ra = mapa_u32(smem_u32(xmine + Tm), lane);
+        st_async_f64(ra, qs, rb);
+        st_async_f64(ra + 8, bs, rb);
       }
+      if (tid == 32 % blockDim.x)  // arm this phase: q and bad from every CTA, plus T partial sums each if b != 0
+        mbar_expect_tx(xbar + par, (unsigned)(C * ((bc != 0.0 ? Tb : 0) + 2) * 8));
       if (bc != 0.0) {
+        // rows t0 + j W, j < 8, of this warp; each lane takes column pairs (LDS.128), rows past Tb read row
+        // Tb-1 and are dropped at the store
+        const double2* w2 = reinterpret_cast<const double2*>(wsm);
         for (int t0 = warp; t0 < Tb; t0 += 8 * W) {
+          const double2* yr[8];
           double acc[8];
 #pragma unroll
-          for (int j = 0; j < 8; j++) acc[j] = 0.0;
-          for (int c = lane; c < ncol; c += 32) {
-            const double wv = wsm[c];
+          for (int j = 0; j < 8; j++) {
+            acc[j] = 0.0;
+            yr[j] = reinterpret_cast<const double2*>(ysm + (size_t)min(t0 + j * W, Tb - 1) * ncol);
+          }
+          for (int c = lane; c < (ncol >> 1); c += 32) {
+            const double2 wv = w2[c];
 #pragma unroll
             for (int j = 0; j < 8; j++) {
-              const int t = t0 + j * W;
-              if (t < Tb) acc[j] += wv * ysm[(size_t)t * ncol + c];
+              const double2 yv = yr[j][c];
+              acc[j] = fma(wv.x, yv.x, fma(wv.y, yv.y, acc[j]));
             }
           }
+          // transposing butterfly: 8 sums x 32 lanes -> lane l holds the total of row j = l >> 2 (9 exchanges)
+          {
+            const bool hi = lane & 16;
 #pragma unroll
-          for (int o = 16; o > 0; o >>= 1) {
-#pragma unroll
-            for (int j = 0; j < 8; j++) acc[j] += __shfl_xor_sync(0xffffffffu, acc[j], o);
-          }
-          if (lane < C) {
-            double* dst = cluster.map_shared_rank(xmine, lane);
-#pragma unroll
-            for (int j = 0; j < 8; j++) {
-              const int t = t0 + j * W;
-              if (t < Tb) dst[t] = acc[j];
+            for (int j = 0; j < 4; j++) {
+              const double send = hi ? acc[j] : acc[j + 4], keep = hi ? acc[j + 4] : acc[j];
+              acc[j] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
             }
           }
+          {
+            const bool hi = lane & 8;
+#pragma unroll
+            for (int j = 0; j < 2; j++) {
+              const double send = hi ? acc[j] : acc[j + 2], keep = hi ? acc[j + 2] : acc[j];
+              acc[j] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+            }
+          }
+          {
+            const bool hi = lane & 4;
+            const double send = hi ? acc[0] : acc[1], keep = hi ? acc[1] : acc[0];
+            acc[0] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+          }
+          acc[0] += __shfl_xor_sync(0xffffffffu, acc[0], 2);
+          acc[0] += __shfl_xor_sync(0xffffffffu, acc[0], 1);
+          const int t = t0 + (lane >> 2) * W;
+          if (t < Tb)
+            for (int dst = lane & 3; dst < C; dst += 4)
+              st_async_f64(mapa_u32(smem_u32(xmine + t), dst), acc[0], mapa_u32(smem_u32(xbar + par), dst));
         }
       }
-      cluster.sync();
+      mbar_wait(xbar + par, (xphase >> par) & 1u);
+      xphase ^= 1u << par;
       // ---- D: every thread forms q, the failure flag and beta; thread t forms corr_t
       const double* xb = xch + (size_t)par * C * XQp;
       double q = 0.0, bad = 0.0;
@@ -501,10 +551,23 @@ __global__ void __launch_bounds__(MAXT, 1) diag_resident_kernel(DevBatch d, int 
       }
       if (bc != 0.0) {
         const double beta = bc / den, sb = sqrt(-beta);
+        double scl = 0.0, sccl = 0.0;
         for (int t = tid; t < Tb; t += blockDim.x) {
           double P = 0.0;
           for (int r = 0; r < C; r++) P += xb[(size_t)r * XQp + t];
-          corr[t] = -beta * P + sb * xi[bi * Tm + t];
+          const double cv = -beta * P + sb * xi[bi * Tm + t];
+          corr[t] = cv;
+          scl += cv;
+          sccl += cv * cv;
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+          scl += __shfl_xor_sync(0xffffffffu, scl, o);
+          sccl += __shfl_xor_sync(0xffffffffu, sccl, o);
+        }
+        if (lane == 0) {
+          scw[warp] = scl;
+          scw[32 + warp] = sccl;
         }
         __syncthreads();
       }
@@ -513,20 +576,22 @@ __global__ void __launch_bounds__(MAXT, 1) diag_resident_kernel(DevBatch d, int 
       if (owner) {
         double r0 = 0.0, r1 = 0.0, sc = 0.0, scc = 0.0;
         if (bc != 0.0) {
+          for (int w = 0; w < W; w++) {
+            sc += scw[w];
+            scc += scw[32 + w];
+          }
+          const double* yc = ysm + tid;
+          const double2* cp = reinterpret_cast<const double2*>(corr);
+          const int ncol2 = 2 * ncol;
           int t = 0;
+#pragma unroll 4
           for (; t + 1 < Tb; t += 2) {
-            const double c0 = corr[t], c1 = corr[t + 1];
-            r0 += ysm[(size_t)t * ncol + tid] * c0;
-            r1 += ysm[(size_t)(t + 1) * ncol + tid] * c1;
-            sc += c0 + c1;
-            scc += c0 * c0 + c1 * c1;
+            const double2 c2 = *cp++;
+            r0 = fma(yc[0], c2.x, r0);
+            r1 = fma(yc[ncol], c2.y, r1);
+            yc += ncol2;
           }
-          if (t < Tb) {
-            const double c0 = corr[t];
-            r0 += ysm[(size_t)t * ncol + tid] * c0;
-            sc += c0;
-            scc += c0 * c0;
-          }
+          if (t < Tb) r0 = fma(yc[0], corr[t], r0);
         }
         const double sm1 = iv * (sy + sg * sc);                              // sum_t m
         const double sm2 = iv * iv * (syy + 2.0 * sg * (r0 + r1) + scc);     // sum_t m^2

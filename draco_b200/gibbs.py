@@ -373,3 +373,106 @@ def fourier_matrix_c2c(N, fsel=None, *, device=0):
 def fourier_matrix(N, fsel=None, *, device=0):
     """delay.py:1588-1613 (complex128 (M, N))."""
     return _fourier(3, N, fsel, N, lambda M: (M, 2 * N), device).view(np.complex128)
+
+
+# ---------------------------------------------------------------------------------------
+# Cross-power-spectrum sampler (delay.py:1907-2099)
+# ---------------------------------------------------------------------------------------
+
+
+def _host_cross_draws(rng, niter, N, nd, M, T):
+    """Draw one problem's variates from a numpy Generator in the reference's call order
+    (delay.py:2029-2030 and, per delay, draco/util/random.py:121-130)."""
+    L = nd * (nd - 1) // 2
+    w1 = np.empty((niter, N, nd, T), dtype=np.complex128)
+    w2 = np.empty((niter, nd, M, T), dtype=np.complex128)
+    wn = np.empty((niter, N, 2, L))
+    wg = np.empty((niter, N, nd))
+    for i in range(niter):
+        rng.standard_normal((N, nd, 2 * T), out=w1[i].view(np.float64))
+        w1[i] *= 1.0 / 2**0.5
+        rng.standard_normal((nd, M, 2 * T), out=w2[i].view(np.float64))
+        w2[i] *= 1.0 / 2**0.5
+        for t in range(N):
+            wn[i, t, 0] = rng.standard_normal(L)
+            wn[i, t, 1] = rng.standard_normal(L)
+            for j in range(nd):
+                wg[i, t, j] = rng.gamma(T - j)
+    return w1, w2, wn, wg
+
+
+def cross_batch(data, N, Ni, initial_S, window="nuttall", fsel=None, niter=20, *, draws=None, seed=0, global_id=None,
+                handle: Handle | None = None, rng_mode=None):
+    """Run ``B`` independent cross-spectrum chains on the GPU.
+
+    ``data`` [B, nd, T, M] c128, ``Ni`` [B, nd, M], ``initial_S`` [B, nd, nd, N] c128, common ``fsel`` [M].
+    ``draws = (w1, w2, wn, wg)`` (shapes in ``include/dgibbs.h``) selects the injected mode.
+    Returns ``(samples [B, niter, nd, nd, N] c128, n_done [B], success [B])``."""
+    data = np.ascontiguousarray(data, dtype=np.complex128)
+    B, nd, T, M = data.shape
+    if nd > _lib.CROSS_MAX_DATASETS:
+        raise ValueError(f"at most {_lib.CROSS_MAX_DATASETS} datasets are supported")
+    Ni = np.ascontiguousarray(np.broadcast_to(np.asarray(Ni, dtype=np.float64), (B, nd, M)))
+    fsel = np.arange(M, dtype=np.int64) if fsel is None else np.ascontiguousarray(fsel, dtype=np.int64)
+    if len(fsel) != M:  # delay.py:1962-1966
+        raise ValueError(f"Length of frequency selection must match frequencies passed. {len(fsel)} != {M}")
+    S0 = np.ascontiguousarray(np.broadcast_to(np.asarray(initial_S, dtype=np.complex128), (B, nd, nd, N)))
+    if window not in WINDOW_IDS:
+        raise ValueError(f"window {window!r} is not one of {sorted(k for k in WINDOW_IDS if k)}")
+    h = handle or get_handle(0)
+    p = _lib.CrossProblem()
+    p.struct_size = C.sizeof(_lib.CrossProblem)
+    p.B, p.nd, p.N, p.T, p.M, p.niter = B, nd, int(N), T, M, int(niter)
+    p.window_id = WINDOW_IDS[window]
+    p.seed = int(seed) & 0xFFFFFFFFFFFFFFFF
+    keep = [data, Ni, fsel, S0]
+    p.data, p.Ni, p.fsel, p.S0 = (a.ctypes.data for a in keep)
+    if global_id is not None:
+        gid = np.ascontiguousarray(global_id, dtype=np.int64)
+        keep.append(gid)
+        p.global_id = gid.ctypes.data
+    if draws is not None:
+        w1, w2, wn, wg = draws
+        L = nd * (nd - 1) // 2
+        w1 = np.ascontiguousarray(w1, dtype=np.complex128).reshape(B, niter, N, nd, T)
+        w2 = np.ascontiguousarray(w2, dtype=np.complex128).reshape(B, niter, nd, M, T)
+        wn = np.ascontiguousarray(wn, dtype=np.float64).reshape(B, niter, N, 2, L)
+        wg = np.ascontiguousarray(wg, dtype=np.float64).reshape(B, niter, N, nd)
+        if wn.size == 0:
+            wn = np.zeros(1)
+        keep += [w1, w2, wn, wg]
+        p.w1, p.w2, p.wn, p.wg = w1.ctypes.data, w2.ctypes.data, wn.ctypes.data, wg.ctypes.data
+        p.rng_mode = RNG_INJECTED
+    else:
+        p.rng_mode = RNG_PHILOX if rng_mode is None else rng_mode
+    samples = np.empty((B, niter, nd, nd, N), dtype=np.complex128)
+    n_done = np.empty(B, dtype=np.int32)
+    ok = np.empty(B, dtype=np.uint8)
+    h.check(h.lib.dgibbs_cross_run(h._h, C.byref(p), samples.ctypes.data, n_done.ctypes.data, ok.ctypes.data),
+            "dgibbs_cross_run")
+    del keep
+    return samples, n_done, ok.astype(bool)
+
+
+def delay_spectrum_gibbs_cross(data, N, Ni, initial_S, window="nuttall", fsel=None, niter=20, rng=None, *, device=0,
+                               seed=None):
+    """Drop-in for ``delay_spectrum_gibbs_cross`` (delay.py:1907-2099): ``data`` [nd, T, M] c128,
+    ``Ni`` [nd, M], ``initial_S`` [nd, nd, N]; returns the list of ``[nd, nd, N]`` complex samples and raises
+    ``RuntimeError("Exiting earlier as singular")`` where the reference does (delay.py:2096-2097).
+
+    ``rng``: a ``numpy.random.Generator`` selects deterministic mode (its variates are drawn on the host in the
+    reference's order and injected); ``rng=None`` uses the device Philox generator."""
+    data = np.asarray(data)
+    nd, T, M = data.shape
+    if nd == 0:
+        raise ValueError("Need at least one set of data")
+    draws = None
+    if rng is not None:
+        draws = tuple(a[None] for a in _host_cross_draws(rng, niter, N, nd, M, T))
+    elif seed is None:
+        seed = int(np.random.SeedSequence().generate_state(1, dtype=np.uint64)[0])
+    samples, n_done, ok = cross_batch(data[None], N, np.asarray(Ni)[None], np.asarray(initial_S)[None], window, fsel, niter,
+                                      draws=draws, seed=seed or 0, handle=get_handle(device))
+    if not ok[0]:
+        raise RuntimeError("Exiting earlier as singular")
+    return [samples[0, i].copy() for i in range(niter)]

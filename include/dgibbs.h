@@ -140,7 +140,7 @@ typedef struct {
 } dgibbs_timing;
 
 int dgibbs_version(void);
-/* sizeof of the ABI structs as compiled (0: dgibbs_problem, 1: dgibbs_result, 2: dgibbs_timing);
+/* sizeof of the ABI structs as compiled (0: dgibbs_problem, 1: dgibbs_result, 2: dgibbs_timing, 3: dgibbs_cross_problem);
  * lets a binding verify its struct layout without a GPU. */
 int dgibbs_sizeof(int which);
 
@@ -178,6 +178,54 @@ int dgibbs_wiener(dgibbs_handle h, const dgibbs_problem* p, double* out, uint8_t
  * 1 c2r (N,2M), 2 c2c (2M,2N), 3 complex (M,N) as interleaved re/im.  Host output. */
 int dgibbs_fourier_matrix(dgibbs_handle h, int32_t kind, int32_t N, const int64_t* fsel,
                           int32_t M, double* out);
+
+/* ------------------------------------------------------------------------------------------
+ * Cross-power-spectrum Gibbs sampler: replaces delay_spectrum_gibbs_cross
+ * (draco/analysis/delay.py:1907-2099) as called per baseline by
+ * DelayCrossPowerSpectrumEstimator._evaluate (delay.py:1395-1447).
+ *
+ * A batch of B independent problems (baselines) sharing nd datasets, N delays, T samples and
+ * one channel selection fsel[M] (values in [0, N); the sampler uses the complex Fourier matrix
+ * fourier_matrix, delay.py:1588-1613).  HOST pointers only.
+ *   data : complex128 [B, nd, T, M]      (what _cut_data returns for the stacked datasets)
+ *   Ni   : float64    [B, nd, M]
+ *   S0   : complex128 [B, nd, nd, N]     initial cross spectrum (Hermitian positive definite per delay)
+ * Injected draws (rng_mode == DGIBBS_RNG_INJECTED), the reference's call order per iteration
+ * (standard_complex_normal x2, then per delay the Bartlett factor of complex_wishart,
+ * draco/util/random.py:103-166):
+ *   w1 : complex128 [B, niter, N, nd, T]     w2 : complex128 [B, niter, nd, M, T]
+ *   wn : float64    [B, niter, N, 2, L]      L = nd(nd-1)/2; [..,0,:] real, [..,1,:] imaginary parts
+ *                                            of the strict lower triangle in numpy.tril_indices order
+ *                                            (unit-variance normals, the 1/sqrt(2) is applied here)
+ *   wg : float64    [B, niter, N, nd]        gamma(T - i) variates of the diagonal
+ * Output
+ *   samples : complex128 [B, niter, nd, nd, N]  (unshifted delay order, every iteration)
+ *   n_done  : [B] completed iterations; success[b] = 0 when a factorisation / inverse failed, which
+ *             is where the reference raises RuntimeError("Exiting earlier as singular") (delay.py:2096).
+ */
+#define DGIBBS_CROSS_MAX_DATASETS 4
+
+typedef struct {
+  int32_t struct_size;
+  int32_t B, nd, N, T, M;
+  int32_t niter;
+  int32_t window_id;
+  int32_t rng_mode;
+  int32_t reserved;
+  uint64_t seed;
+  const void* data;
+  const double* Ni;
+  const int64_t* fsel;
+  const void* S0;
+  const int64_t* global_id; /* [B] Philox key per problem; may be NULL */
+  const void* w1;
+  const void* w2;
+  const double* wn;
+  const double* wg;
+} dgibbs_cross_problem;
+
+int dgibbs_cross_run(dgibbs_handle h, const dgibbs_cross_problem* p, void* samples, int32_t* n_done,
+                     uint8_t* success);
 
 #ifdef __cplusplus
 }

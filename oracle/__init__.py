@@ -27,3 +27,12 @@ from .gibbs_oracle import (  # noqa: F401
     whiten_inputs,
     wiener_filter,
 )
+from .cross_oracle import (  # noqa: F401,E402
+    CrossInjectedDraws,
+    CrossRecordingDraws,
+    complex_wishart,
+    cross_gibbs_chain,
+    cross_whiten_inputs,
+    standard_complex_normal,
+    standard_complex_wishart,
+)

@@ -25,6 +25,7 @@ import scipy.linalg as la
 REFERENCE_ROOT = os.environ.get("DRACO_REFERENCE_ROOT", "/root/reference")
 _DELAY = "draco/analysis/delay.py"
 _TOOLS = "draco/util/tools.py"
+_RANDOM = "draco/util/random.py"
 
 
 def available() -> bool:
@@ -57,7 +58,17 @@ def load():
         window_generalised=tools_ns["window_generalised"],
         invert_no_zero=_invert_no_zero,
     )
-    random = types.SimpleNamespace(default_rng=np.random.default_rng)
+    # caput.algorithms.random is external; its in-tree twin draco/util/random.py:7-166 supplies the
+    # complex normal / complex Wishart helpers the cross-spectrum sampler calls (delay.py:2029-2030, 2079)
+    rand_ns = {"np": np, "default_rng": np.random.default_rng}
+    exec(compile(_lines(_RANDOM, 7, 166), _RANDOM, "exec"), rand_ns)
+    random = types.SimpleNamespace(
+        default_rng=np.random.default_rng,
+        standard_complex_normal=rand_ns["standard_complex_normal"],
+        complex_normal=rand_ns["complex_normal"],
+        standard_complex_wishart=rand_ns["standard_complex_wishart"],
+        complex_wishart=rand_ns["complex_wishart"],
+    )
 
     class FreqContainer:  # stand-in for draco.core.containers.FreqContainer
         def __init__(self, freq):
@@ -92,4 +103,5 @@ def load():
     out.cut_data = cut_data
     out.calculate_delays = calculate_delays
     out.window_generalised = tools.window_generalised
+    out.random = random
     return out
