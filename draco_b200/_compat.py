@@ -186,8 +186,9 @@ class DistArray:
 
     def enumerate(self, axis=0):
         """(local index, global index) pairs along ``axis`` (``MPIArray.enumerate``)."""
+        axis = axis % self.local_array.ndim
         n = self.local_array.shape[axis]
-        off = self.local_offset if axis == self.axis else 0
+        off = self.local_offset if axis == self.axis % self.local_array.ndim else 0
         return [(i, off + i) for i in range(n)]
 
     def __getitem__(self, key):
@@ -346,6 +347,23 @@ class DelaySpectrum(Container):
     @property
     def freq(self):
         return self.attrs["freq"]
+
+
+class DelayCrossSpectrum(DelaySpectrum):
+    """Delay cross power spectrum container (draco/core/containers.py:2488-2513).  NB the reference
+    declares the datasets float64: only the real part of the complex cross spectra is kept on assignment."""
+
+    _dataset_spec = {
+        "spectrum": {"axes": ["dataset", "dataset", "baseline", "delay"], "dtype": np.float64,
+                     "distributed_axis": "baseline"},
+        "spectrum_samples": {"axes": ["sample", "dataset", "dataset", "baseline", "delay"], "dtype": np.float64,
+                             "distributed_axis": "baseline"},
+    }
+
+    def __init__(self, baseline, dataset, delay, sample=1, attrs_from=None, weight_boost=1.0):
+        Container.__init__(self, attrs_from=attrs_from, baseline=baseline, dataset=dataset, sample=sample, delay=delay)
+        self.attrs["weight_boost"] = weight_boost
+        self.add_dataset("spectrum")
 
 
 class DelayTransform(Container):

@@ -583,14 +583,36 @@ __global__ void __launch_bounds__(MAXT, 1) diag_resident_kernel(DevBatch d, int 
           const double* yc = ysm + tid;
           const double2* cp = reinterpret_cast<const double2*>(corr);
           const int ncol2 = 2 * ncol;
+          double r2 = 0.0, r3 = 0.0;
           int t = 0;
-#pragma unroll 4
+          for (; t + 7 < Tb; t += 8) {  // 8 rows per trip: all loads issued before the first FMA needs them
+            double yv[8];
+            double2 cv[4];
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+              cv[j] = cp[j];
+              yv[2 * j] = yc[(size_t)j * ncol2];
+              yv[2 * j + 1] = yc[(size_t)j * ncol2 + ncol];
+            }
+            r0 = fma(yv[0], cv[0].x, r0);
+            r1 = fma(yv[1], cv[0].y, r1);
+            r2 = fma(yv[2], cv[1].x, r2);
+            r3 = fma(yv[3], cv[1].y, r3);
+            r0 = fma(yv[4], cv[2].x, r0);
+            r1 = fma(yv[5], cv[2].y, r1);
+            r2 = fma(yv[6], cv[3].x, r2);
+            r3 = fma(yv[7], cv[3].y, r3);
+            cp += 4;
+            yc += 4 * (size_t)ncol2;
+          }
           for (; t + 1 < Tb; t += 2) {
             const double2 c2 = *cp++;
             r0 = fma(yc[0], c2.x, r0);
             r1 = fma(yc[ncol], c2.y, r1);
             yc += ncol2;
           }
+          r0 += r2;
+          r1 += r3;
           if (t < Tb) r0 = fma(yc[0], corr[t], r0);
         }
         const double sm1 = iv * (sy + sg * sc);                              // sum_t m

@@ -255,6 +255,10 @@ class DelaySpectrumContainerMixin(GeneralInputContainerMixin):
         return out
 
 
+def _local_array(view):
+    return getattr(view, "local_array", view)
+
+
 def _local(dset):
     """The local numpy slab of a (caput or stand-in) distributed dataset."""
     arr = dset[:]
@@ -378,6 +382,103 @@ class DelayPowerSpectrumGibbs(DelayPowerSpectrumBase, _RandomTask):
         if self.save_spectrum_mask:
             n_conv = nbase - ddist.allreduce_count(int(mask_out.sum()))  # delay.py:1182
             self.log.debug(f"{n_conv}/{nbase} unflagged baselines.")
+        return out_cont
+
+
+class DelayCrossPowerSpectrumEstimator(DelayPowerSpectrumGibbs):
+    """Delay cross power spectrum of several compatible ``FreqContainer`` inputs (delay.py:1304-1447):
+    ``process(sslist)`` returns a ``DelayCrossSpectrum`` with the pair-wise cross spectra.  Every local
+    baseline's chain (``delay_spectrum_gibbs_cross``, delay.py:1907-2099) runs on the GPU in one batch
+    per group of baselines that share a channel selection.
+
+    Two defects of the reference wrapper that stop it from running are not reproduced: the frequency
+    check ``(ss.freq != freq_ref).all()`` (delay.py:1328; any mismatch must raise) and the call
+    ``super()._prepare_inputs(self, ss)`` (delay.py:1330; ``self`` passed twice).  Like the reference, the
+    output datasets are float64 (containers.py:2493-2506): the real part of the median is stored; and like
+    the reference the median is passed through ``np.fft.fftshift`` with no ``axes`` argument (delay.py:1442),
+    which also rolls the two dataset axes.
+    """
+
+    def _prepare_inputs(self, sslist):
+        if len(sslist) == 0:
+            raise ValueError("No datasets passed.")
+        freq_ref = np.asarray(sslist[0].freq)
+        data_views, weight_views, coord_axes = [], [], None
+        for ss in sslist:
+            ss.redistribute("freq")
+            f = np.asarray(ss.freq)
+            if f.shape != freq_ref.shape or (f != freq_ref).any():
+                raise ValueError("Input containers must have the same frequencies.")
+            dv, wv, ca = GeneralInputContainerMixin._prepare_inputs(self, ss)
+            if coord_axes is not None and not coord_axes == ca:
+                raise ValueError("Different axes found for the input containers.")
+            data_views.append(dv)
+            weight_views.append(wv)
+            coord_axes = ca
+        return data_views, weight_views, coord_axes
+
+    def _create_output(self, ss, delays, coord_axes):
+        ssref, ndata = ss[0], len(ss)
+        if len(coord_axes) == 1:
+            bl = ssref.index_map[coord_axes[0]]
+        else:
+            bl = int(np.prod([len(ssref.index_map[ax]) for ax in coord_axes]))
+        out = containers.DelayCrossSpectrum(baseline=bl, dataset=ndata, delay=delays, sample=self.nsamp, attrs_from=ssref)
+        out.redistribute("baseline")
+        out.spectrum[:] = 0.0
+        if isinstance(coord_axes, list):
+            for ax in coord_axes:
+                out.create_index_map(ax, ssref.index_map[ax])
+            out.attrs["baseline_axes"] = coord_axes
+        if self.save_samples:
+            out.add_dataset("spectrum_samples")
+        out.attrs["freq"] = ssref.freq
+        return out
+
+    def _evaluate(self, data_view, weight_view, out_cont, delays, channel_ind):
+        """Batched replacement of the loop delay.py:1421-1445."""
+        ndata, ndelay = len(data_view), len(delays)
+        nbase = out_cont.spectrum.global_shape[-2]
+        initial_S = self._get_prior(nbase, ndelay, delays.dtype)
+        if initial_S.ndim == 2:  # delay.py:1402-1407
+            initial_S = np.identity(ndata)[np.newaxis, ..., np.newaxis] * initial_S[:, np.newaxis, np.newaxis]
+        elif initial_S.ndim != 4 or initial_S.shape[1] != ndata:
+            raise ValueError(f"Expected an initial sample with dimension 4 and {ndata} datasets. "
+                             f"Got sample with dimension {initial_S.ndim} and shape {initial_S.shape}.")
+        spec_out = _local(out_cont.spectrum)
+        samp_out = _local(out_cont.datasets["spectrum_samples"]) if self.save_samples else None
+        # cut every local baseline, group by (channel selection, sample count): one device batch per group
+        groups = {}
+        for lbi, bi in out_cont.spectrum[:].enumerate(axis=-2):
+            data = np.array([_local_array(d)[lbi] for d in data_view])
+            weight = np.array([_local_array(w)[lbi] for w in weight_view])
+            t = self._cut_data(data, weight)
+            if t is None:
+                continue
+            data, weight, nzf, _ = t
+            key = (nzf.tobytes(), data.shape[1])
+            groups.setdefault(key, []).append((lbi, bi, data, weight, channel_ind[nzf]))
+        handle = gibbs.get_handle(self._device())
+        seed = self._device_seed()
+        for jobs in groups.values():
+            data = np.stack([j[2] for j in jobs])
+            T, M = data.shape[2], data.shape[3]
+            draws = None
+            if self.rng_mode == "injected":  # one generator shared by the local baselines in loop order (delay.py:1418)
+                per = [gibbs._host_cross_draws(self.rng, self.nsamp, ndelay, ndata, M, T) for _ in jobs]
+                draws = tuple(np.stack([p[i] for p in per]) for i in range(4))
+            samples, n_done, ok = gibbs.cross_batch(
+                data, ndelay, np.stack([j[3] for j in jobs]), initial_S[[j[0] for j in jobs]],
+                window=self._window(), fsel=jobs[0][4], niter=self.nsamp, draws=draws, seed=seed,
+                global_id=np.array([j[1] for j in jobs], dtype=np.int64), handle=handle)
+            if not ok.all():  # delay.py:2096-2097
+                raise RuntimeError("Exiting earlier as singular")
+            for n, (lbi, bi, *_r) in enumerate(jobs):
+                spec = samples[n]
+                spec_av = np.median(spec[-(self.nsamp // 2):], axis=0)  # delay.py:1438-1441
+                spec_out[..., lbi, :] = np.fft.fftshift(spec_av).real  # all axes, as delay.py:1442
+                if samp_out is not None:
+                    samp_out[..., lbi, :] = spec.real
         return out_cont
 
 
