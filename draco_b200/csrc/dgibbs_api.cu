@@ -273,7 +273,8 @@ static int stage_batch(dgibbs_handle h, const dgibbs_problem* p, Staged& s, bool
   CU(pool_get(h, "diag_ab", sizeof(double) * 2 * (size_t)B, &q)); d.diag_ab = (double*)q;
   d.force_branch = p->force_branch;
   const size_t wrows = (size_t)d.npad + (size_t)d.RT * TILE;
-  CU(pool_get(h, "work", sizeof(double) * (size_t)d.nslots * wrows * d.npad, &q)); d.work = (double*)q;
+  d.work_stride = wrows * d.npad + (size_t)d.N * d.Tmax;
+  CU(pool_get(h, "work", sizeof(double) * (size_t)d.nslots * d.work_stride, &q)); d.work = (double*)q;
   CU(pool_get(h, "Wp", sizeof(double) * (size_t)d.nslots * dense_wp_doubles_per_slot(d), &q)); d.Wp = (double*)q;
   CU(pool_get(h, "uT", sizeof(double) * (size_t)d.nslots * d.RT * TILE * d.Kpad, &q)); d.uT = (double*)q;
   CU(pool_get(h, "Si", sizeof(double) * (size_t)d.nslots * d.npad, &q)); d.Si = (double*)q;
@@ -314,6 +315,13 @@ static double dense_flop_per_iter(const DevBatch& d, int T, int M) {
   return n * n * n / 3.0 + 2.0 * n * n * T + 4.0 * n * M * (double)T;
 }
 
+static double freq_flop_per_iter(const DevBatch& d, int T, int M) {
+  // W_t = (2M)^3/3 + 2 (2M)^2 T + 2 (2M)^2 N + 8 N M T  (the reference's arithmetic for this branch;
+  // the device generates R Rt + I from one FFT of S instead of the 2 (2M)^2 N GEMM)
+  double m2 = 2.0 * M, n = d.N;
+  return m2 * m2 * m2 / 3.0 + 2.0 * m2 * m2 * T + 2.0 * m2 * m2 * n + 8.0 * n * M * (double)T;
+}
+
 extern "C" int dgibbs_workspace_bytes(dgibbs_handle h, const dgibbs_problem* p, int64_t* bytes) {
   int rc = check_problem(h, p);
   if (rc) return rc;
@@ -327,7 +335,7 @@ extern "C" int dgibbs_workspace_bytes(dgibbs_handle h, const dgibbs_problem* p, 
   size_t RT = (Tmax + TILE - 1) / TILE, B = p->B;
   size_t nslots = B < (size_t)h->sm_count ? B : h->sm_count;
   size_t tot = 8 * (B * Kpad + B * Tmax * Kpad + B * nsys + 2 * B * p->N + Kpad * npad) + 4 * B * nch +
-               8 * nslots * ((npad + RT * TILE) * npad + RT * TILE * Kpad + npad) +
+               8 * nslots * ((npad + RT * TILE) * npad + (size_t)p->N * Tmax + RT * TILE * Kpad + npad) +
                8 * (size_t)p->niter * B * p->N + 8 * B * p->N;
   *bytes = (int64_t)(tot + tot / 16);
   return 0;
@@ -380,22 +388,36 @@ extern "C" int dgibbs_run(dgibbs_handle h, const dgibbs_problem* p, dgibbs_resul
   CU(cudaMemcpyAsync(br.data(), d.branch, d.B, cudaMemcpyDeviceToHost, h->stream));
   CU(cudaStreamSynchronize(h->stream));
   const bool fast_diag = d.rng_mode == DGIBBS_RNG_PHILOX && d.nsys <= 4096 && d.niter > 0;
-  std::vector<int> dense_list, diag_list, ycompact(d.B, -1);
+  // frequency-space branch (_draw_signal_sample_t): the reference's rule len(fsel) <= 0.25 N (delay.py:1884-1886)
+  std::vector<int> dense_list, diag_list, freq_list, ycompact(d.B, -1);
   for (int b = 0; b < d.B; b++) {
+    const bool few = (double)s.M[b] <= 0.25 * (double)d.N;
+    const bool want_t = p->force_branch == DGIBBS_BRANCH_FREQ_SPACE || (p->force_branch == 0 && few);
     if (br[b] == DGIBBS_BRANCH_DIAGONAL && fast_diag) {
       ycompact[b] = (int)diag_list.size();
       diag_list.push_back(b);
+    } else if (br[b] != DGIBBS_BRANCH_DIAGONAL && want_t && d.niter > 0 && freq_branch_fits(d, s.M[b], s.T[b]) &&
+               !getenv("DGIBBS_NO_FREQ_BRANCH")) {
+      br[b] = DGIBBS_BRANCH_FREQ_SPACE;
+      freq_list.push_back(b);
     } else {
       dense_list.push_back(b);
     }
   }
-  int *d_dense = nullptr, *d_diag = nullptr, *d_yc = nullptr;
-  if (!diag_list.empty()) {
+  int *d_dense = nullptr, *d_diag = nullptr, *d_freq = nullptr, *d_yc = nullptr;
+  const bool split = !diag_list.empty() || !freq_list.empty();
+  if (split) {
     CU(pool_get(h, "list_dense", sizeof(int) * (dense_list.size() + 1), &q)); d_dense = (int*)q;
-    CU(pool_get(h, "list_diag", sizeof(int) * diag_list.size(), &q)); d_diag = (int*)q;
-    CU(pool_get(h, "ycompact", sizeof(int) * d.B, &q)); d_yc = (int*)q;
     if (!dense_list.empty())
       CU(cudaMemcpyAsync(d_dense, dense_list.data(), sizeof(int) * dense_list.size(), cudaMemcpyHostToDevice, h->stream));
+  }
+  if (!freq_list.empty()) {
+    CU(pool_get(h, "list_freq", sizeof(int) * freq_list.size(), &q)); d_freq = (int*)q;
+    CU(cudaMemcpyAsync(d_freq, freq_list.data(), sizeof(int) * freq_list.size(), cudaMemcpyHostToDevice, h->stream));
+  }
+  if (!diag_list.empty()) {
+    CU(pool_get(h, "list_diag", sizeof(int) * diag_list.size(), &q)); d_diag = (int*)q;
+    CU(pool_get(h, "ycompact", sizeof(int) * d.B, &q)); d_yc = (int*)q;
     CU(cudaMemcpyAsync(d_diag, diag_list.data(), sizeof(int) * diag_list.size(), cudaMemcpyHostToDevice, h->stream));
     CU(cudaMemcpyAsync(d_yc, ycompact.data(), sizeof(int) * d.B, cudaMemcpyHostToDevice, h->stream));
     CU(pool_get(h, "yhat", sizeof(double) * diag_list.size() * (size_t)d.Tmax * d.npad, &q));
@@ -437,12 +459,20 @@ extern "C" int dgibbs_run(dgibbs_handle h, const dgibbs_problem* p, dgibbs_resul
   double flop = 0.0;
   if (d.niter > 0 && !dense_list.empty()) {
     DevBatch dn = d;
-    if (!diag_list.empty()) {
+    if (split) {
       dn.blist = d_dense;
       dn.nlist = (int)dense_list.size();
       dn.nslots = dn.nlist < d.nslots ? dn.nlist : d.nslots;
     }
     CU(launch_dense_sampler(dn, 0, d.niter, h->stream));
+    h->timing.launches++;
+    h->timing.sampler_launches++;
+  }
+  if (d.niter > 0 && !freq_list.empty()) {
+    DevBatch df = d;
+    df.blist = d_freq;
+    df.nlist = (int)freq_list.size();
+    CU(launch_freq_sampler(df, 0, d.niter, h->stream));
     h->timing.launches++;
     h->timing.sampler_launches++;
   }
@@ -479,11 +509,12 @@ extern "C" int dgibbs_run(dgibbs_handle h, const dgibbs_problem* p, dgibbs_resul
   double bytes = 0.0;
   for (int b = 0; b < d.B; b++) {
     if (ycompact[b] >= 0) bytes += (double)nd[b] * (8.0 * d.nsys * s.T[b] + 16.0 * d.N);  // Q_d
+    else if (br[b] == DGIBBS_BRANCH_FREQ_SPACE) flop += (double)nd[b] * freq_flop_per_iter(d, s.T[b], s.M[b]);
     else flop += (double)nd[b] * dense_flop_per_iter(d, s.T[b], s.M[b]);
   }
   if (r->branch) {
     for (int b = 0; b < d.B; b++)
-      if (br[b] != DGIBBS_BRANCH_DIAGONAL) br[b] = DGIBBS_BRANCH_DELAY_SPACE;
+      if (br[b] != DGIBBS_BRANCH_DIAGONAL && br[b] != DGIBBS_BRANCH_FREQ_SPACE) br[b] = DGIBBS_BRANCH_DELAY_SPACE;
     if (dev) CU(cudaMemcpy(r->branch, br.data(), d.B, cudaMemcpyHostToDevice));
     else memcpy(r->branch, br.data(), d.B);
   }

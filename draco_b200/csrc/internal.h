@@ -66,6 +66,7 @@ struct DevBatch {
   int use_fft;           // 1: masked inverse DFT of phase 0 runs as an in-smem FFT (N = 2^m <= 4096)
 
   // per-slot workspace
+  size_t work_stride;  // doubles per slot of `work`: (npad + RT*TILE) * npad for L + RHS, then N * Tmax (Sh w1, _t branch)
   double* work;  // [nslots][(npad + RT*TILE)][npad]  L (lower) with W=inv(L_jj) in the diagonal
                  //                                   blocks, then the RHS rows (sample-major)
   double* Wp;    // [nslots][nblk][8704]  packed inv(L_jj) per block column (for the backward solve)
@@ -105,6 +106,10 @@ cudaError_t launch_dense_sampler(const DevBatch& d, int it_begin, int it_end, cu
 // allow_resident: every listed baseline has b <= 0, so the cluster-resident kernel may be used
 cudaError_t launch_diag_sampler(const DevBatch& d, int it_begin, int it_end, int sm_count, cudaStream_t st,
                                 bool allow_resident);
+
+// sampler_freq.cu
+bool freq_branch_fits(const DevBatch& d, int M, int T);
+cudaError_t launch_freq_sampler(const DevBatch& d, int it_begin, int it_end, cudaStream_t st);
 
 // finish_kernels.cu
 cudaError_t launch_finish(const DevBatch& d, const double* S0, double median_frac, double* spectrum,

@@ -32,7 +32,7 @@ __global__ void __launch_bounds__(THREADS, 1) dense_sampler_kernel(DevBatch d, i
   double* misc = pipe + PIPE_DOUBLES;
 
   const size_t wrows = (size_t)npad + (size_t)RT * TILE;
-  double* Wk = d.work + (size_t)slot * wrows * npad;   // L rows then RHS rows, pitch npad
+  double* Wk = d.work + (size_t)slot * d.work_stride;   // L rows then RHS rows, pitch npad
   double* Rh = Wk + (size_t)npad * npad;               // RHS rows (sample-major)
   double* Wpg = d.Wp + (size_t)slot * nblk * WP_DOUBLES;  // packed inv(L_jj), one per block column
   double* uT = d.uT + (size_t)slot * RT * TILE * Kpad;
