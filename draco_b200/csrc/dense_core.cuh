@@ -422,30 +422,55 @@ struct DrawCtx {
   const double* w2;
   int Tb, it, half;
 };
-__device__ __forceinline__ double2 u_value(const DrawCtx& c, int t, int i) {
-  if (t >= c.Tb) return make_double2(0.0, 0.0);
+// Device-RNG layout of the FFT path: one Philox block serves the sample pair (t & ~1, t | 1): words (x, y) give
+// the two normals of the even sample, (z, w) those of the odd one (fp32 Box-Muller, see normal_pair_fast).
+__device__ __forceinline__ void u_value2(const DrawCtx& c, int t0, int i, bool pair, double2& U0, double2& U1) {
+  U0 = U1 = make_double2(0.0, 0.0);
   const int ci = c.cidx[i];
-  if (ci < 0) return make_double2(0.0, 0.0);
-  double n0 = 0.0, n1 = 0.0;
+  if (ci < 0) return;
+  double a0 = 0.0, a1 = 0.0, b0 = 0.0, b1 = 0.0;
+  const bool has1 = pair && t0 + 1 < c.Tb;
   if (c.d->rng_mode == 1) {
-    unsigned long long blk = (unsigned long long)t * c.half + i;
-    normal_pair((*c.ph)((unsigned)blk, (unsigned)(blk >> 32), (unsigned)c.it, STREAM_W2), n0, n1);
+    unsigned long long blk = (unsigned long long)(t0 >> 1) * c.half + i;
+    uint4 r = (*c.ph)((unsigned)blk, (unsigned)(blk >> 32), (unsigned)c.it, STREAM_W2);
+    double e0, e1, e2, e3;
+    normal_pair_fast(r, e0, e1, e2, e3);
+    if (pair || !(t0 & 1)) { a0 = e0; a1 = e1; b0 = e2; b1 = e3; }
+    else { a0 = e2; a1 = e3; }
   } else if (c.d->rng_mode == 0) {
-    n0 = c.w2[(long long)(2 * ci) * c.Tb + t];
-    n1 = c.w2[(long long)(2 * ci + 1) * c.Tb + t];
+    a0 = c.w2[(long long)(2 * ci) * c.Tb + t0];
+    a1 = c.w2[(long long)(2 * ci + 1) * c.Tb + t0];
+    if (has1) {
+      b0 = c.w2[(long long)(2 * ci) * c.Tb + t0 + 1];
+      b1 = c.w2[(long long)(2 * ci + 1) * c.Tb + t0 + 1];
+    }
   }
-  const double2 z = *reinterpret_cast<const double2*>(c.zT + (size_t)t * c.d->Kpad + 2 * i);
-  return make_double2(c.h[2 * i] * (z.x + n0), c.h[2 * i + 1] * (z.y + n1));
+  const double h0 = c.h[2 * i], h1 = c.h[2 * i + 1];
+  const double2 z = *reinterpret_cast<const double2*>(c.zT + (size_t)t0 * c.d->Kpad + 2 * i);
+  U0 = make_double2(h0 * (z.x + a0), h1 * (z.y + a1));
+  if (has1) {
+    const double2 y = *reinterpret_cast<const double2*>(c.zT + (size_t)(t0 + 1) * c.d->Kpad + 2 * i);
+    U1 = make_double2(h0 * (y.x + b0), h1 * (y.y + b1));
+  }
 }
-// the two standard normals w1[t, k], w1[t, k+1] (k even) of this iteration
-__device__ __forceinline__ void w1_pair(const DrawCtx& c, int t, int k, int nsys, double& n0, double& n1) {
-  n0 = n1 = 0.0;
+// the standard normals w1[t0, k], w1[t0, k+1] (k even) and, if `pair`, w1[t0+1, k], w1[t0+1, k+1]
+__device__ __forceinline__ void w1_pair2(const DrawCtx& c, int t0, int k, int nsys, bool pair, double& a0, double& a1,
+                                         double& b0, double& b1) {
+  a0 = a1 = b0 = b1 = 0.0;
   if (c.d->rng_mode == 1) {
-    unsigned long long blk = ((unsigned long long)t * nsys + k) >> 1;
-    normal_pair((*c.ph)((unsigned)blk, (unsigned)(blk >> 32), (unsigned)c.it, STREAM_W1), n0, n1);
+    unsigned long long blk = ((unsigned long long)(t0 >> 1) * nsys + k) >> 1;
+    uint4 r = (*c.ph)((unsigned)blk, (unsigned)(blk >> 32), (unsigned)c.it, STREAM_W1);
+    double e0, e1, e2, e3;
+    normal_pair_fast(r, e0, e1, e2, e3);
+    if (pair || !(t0 & 1)) { a0 = e0; a1 = e1; b0 = e2; b1 = e3; }
+    else { a0 = e2; a1 = e3; }
   } else if (c.d->rng_mode == 0) {
-    n0 = c.w1[(long long)k * c.Tb + t];
-    n1 = c.w1[(long long)(k + 1) * c.Tb + t];
+    a0 = c.w1[(long long)k * c.Tb + t0];
+    a1 = c.w1[(long long)(k + 1) * c.Tb + t0];
+    if (pair && t0 + 1 < c.Tb) {
+      b0 = c.w1[(long long)k * c.Tb + t0 + 1];
+      b1 = c.w1[(long long)(k + 1) * c.Tb + t0 + 1];
+    }
   }
 }
 
@@ -458,8 +483,18 @@ static __device__ void project_rows_fft(const DevBatch& d, const DrawCtx& c, dou
   const int N = d.N, nsys = d.nsys, npad = d.npad, nch = d.nch;
   for (int m = threadIdx.x; m < N / 2; m += THREADS) tw_s[m] = d.twtab[m];
   const int step = d.cplx ? 1 : 2;
+  long long tp = clock64();
+#define PROFX(idx)                                                                       \
+  do {                                                                                   \
+    if (d.prof && threadIdx.x == 0) {                                                    \
+      long long t_ = clock64();                                                          \
+      atomicAdd((unsigned long long*)&d.prof[idx], (unsigned long long)(t_ - tp));       \
+      tp = t_;                                                                           \
+    }                                                                                    \
+  } while (0)
   for (int t0 = 0; t0 < rows; t0 += step) {
     __syncthreads();  // previous epilogue finished with the buffers (and tw_s is loaded)
+    PROFX(14);
     if (t0 >= c.Tb) {  // padding rows: zeros (CTA-uniform branch)
       for (int e = threadIdx.x; e < step * (npad / 2); e += THREADS) {
         int r = e / (npad / 2), k = (e % (npad / 2)) * 2;
@@ -469,7 +504,8 @@ static __device__ void project_rows_fft(const DevBatch& d, const DrawCtx& c, dou
     }
     if (!d.cplx) {
       for (int i = threadIdx.x; i < nch; i += THREADS) {
-        const double2 U0 = u_value(c, t0, i), U1 = u_value(c, t0 + 1, i);
+        double2 U0, U1;
+        u_value2(c, t0, i, true, U0, U1);
         if (i == 0 || i == N / 2) {
           bufA[i] = make_double2(U0.x, U1.x);
         } else {
@@ -478,10 +514,16 @@ static __device__ void project_rows_fft(const DevBatch& d, const DrawCtx& c, dou
         }
       }
     } else {
-      for (int i = threadIdx.x; i < N; i += THREADS) bufA[i] = u_value(c, t0, i);
+      for (int i = threadIdx.x; i < N; i += THREADS) {
+        double2 U0, U1;
+        u_value2(c, t0, i, false, U0, U1);
+        bufA[i] = U0;
+      }
     }
     __syncthreads();
+    PROFX(12);
     const double2* res = fft_inverse_smem(bufA, bufB, tw_s, N);
+    PROFX(13);
     if (!d.cplx) {
       const bool two = t0 + 1 < rows;
       for (int p = threadIdx.x; p < npad / 2; p += THREADS) {
@@ -490,13 +532,10 @@ static __device__ void project_rows_fft(const DevBatch& d, const DrawCtx& c, dou
         if (k < nsys) {
           const double2 r0 = res[k], r1 = res[k + 1];
           const double s0 = sqrt(Si[k]), s1 = sqrt(Si[k + 1]);
-          double n0, n1;
-          w1_pair(c, t0, k, nsys, n0, n1);
-          ya = make_double2(s0 * n0 + r0.x, s1 * n1 + r1.x);   // delay.py:1815-1817
-          if (t0 + 1 < c.Tb) {
-            w1_pair(c, t0 + 1, k, nsys, n0, n1);
-            yb = make_double2(s0 * n0 + r0.y, s1 * n1 + r1.y);
-          }
+          double a0, a1, b0, b1;
+          w1_pair2(c, t0, k, nsys, true, a0, a1, b0, b1);
+          ya = make_double2(s0 * a0 + r0.x, s1 * a1 + r1.x);   // delay.py:1815-1817
+          if (t0 + 1 < c.Tb) yb = make_double2(s0 * b0 + r0.y, s1 * b1 + r1.y);
         }
         *reinterpret_cast<double2*>(Rh + (size_t)t0 * npad + k) = ya;
         if (two) *reinterpret_cast<double2*>(Rh + (size_t)(t0 + 1) * npad + k) = yb;
@@ -507,8 +546,8 @@ static __device__ void project_rows_fft(const DevBatch& d, const DrawCtx& c, dou
         double2 ya = make_double2(0.0, 0.0);
         if (k < nsys) {
           const double2 r0 = res[p];
-          double n0, n1;
-          w1_pair(c, t0, k, nsys, n0, n1);
+          double n0, n1, b0, b1;
+          w1_pair2(c, t0, k, nsys, false, n0, n1, b0, b1);
           ya = make_double2(sqrt(Si[k]) * n0 + r0.x, sqrt(Si[k + 1]) * n1 + r0.y);
         }
         *reinterpret_cast<double2*>(Rh + (size_t)t0 * npad + k) = ya;

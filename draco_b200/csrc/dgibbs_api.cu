@@ -500,6 +500,8 @@ extern "C" int dgibbs_run(dgibbs_handle h, const dgibbs_problem* p, dgibbs_resul
     for (int i = 0; i < 12; i++) tot += (double)pc[i];
     for (int i = 0; i < 12; i++)
       fprintf(stderr, "[dgibbs prof] %-18s %14lld cyc  %5.1f%%\n", names[i], pc[i], 100.0 * pc[i] / (tot > 0 ? tot : 1));
+    fprintf(stderr, "[dgibbs prof] inside prepass (fused FFT projection): load %lld  fft %lld  epilogue %lld cyc\n", pc[12], pc[13],
+            pc[14]);
   }
 
   // bookkeeping that needs n_done

@@ -106,15 +106,19 @@ __global__ void __launch_bounds__(THREADS, 1) freq_sampler_kernel(DevBatch d, in
     for (int it = it_begin; it < it_end && alive; it++) {
       const double* w1 = (d.rng_mode == 0) ? d.w1 + d.w1_off[b] + (long long)it * N * Tb : nullptr;
       const double* w2 = (d.rng_mode == 0) ? d.w2 + d.w2_off[b] + (long long)it * 2 * Mb * Tb : nullptr;
-      // (w1[2p, s], w1[2p+1, s]): one Philox block per pair, same counters as the delay-space kernel
-      auto w1_pair_at = [&](int p, int s, double& n0, double& n1) {
-        n0 = n1 = 0.0;
+      // w1[2p, s], w1[2p+1, s] for the sample pair (s0, s0+1): one Philox block, fp32 Box-Muller (native mode)
+      auto w1_quad_at = [&](int p, int s0, bool two, double& a0, double& a1, double& b0, double& b1) {
+        a0 = a1 = b0 = b1 = 0.0;
         if (d.rng_mode == 0) {
-          n0 = w1[(long long)(2 * p) * Tb + s];
-          n1 = w1[(long long)(2 * p + 1) * Tb + s];
+          a0 = w1[(long long)(2 * p) * Tb + s0];
+          a1 = w1[(long long)(2 * p + 1) * Tb + s0];
+          if (two) {
+            b0 = w1[(long long)(2 * p) * Tb + s0 + 1];
+            b1 = w1[(long long)(2 * p + 1) * Tb + s0 + 1];
+          }
         } else if (d.rng_mode == 1) {
-          const unsigned long long blk = ((unsigned long long)s * N >> 1) + p;
-          normal_pair(ph((unsigned)blk, (unsigned)(blk >> 32), (unsigned)it, STREAM_W1), n0, n1);
+          const unsigned long long blk = (unsigned long long)(s0 >> 1) * (N >> 1) + p;
+          normal_pair_fast(ph((unsigned)blk, (unsigned)(blk >> 32), (unsigned)it, STREAM_W1), a0, a1, b0, b1);
         }
       };
       __syncthreads();
@@ -136,10 +140,10 @@ __global__ void __launch_bounds__(THREADS, 1) freq_sampler_kernel(DevBatch d, in
         const bool two = s0 + 1 < Tb;
         for (int p = threadIdx.x; p < N / 2; p += THREADS) {
           const double sh0 = Sig[2 * p], sh1 = Sig[2 * p + 1];
-          double a0, a1, b0 = 0.0, b1 = 0.0;
-          w1_pair_at(p, s0, a0, a1);
-          if (two) w1_pair_at(p, s0 + 1, b0, b1);
+          double a0, a1, b0, b1;
+          w1_quad_at(p, s0, two, a0, a1, b0, b1);
           a0 *= sh0; a1 *= sh1; b0 *= sh0; b1 *= sh1;
+          if (!two) b0 = b1 = 0.0;
           bufA[2 * p] = make_double2(a0, b0);
           bufA[2 * p + 1] = make_double2(a1, b1);
           // Sh w1 is needed again for d = S idft(h x) + Sh w1: keep it (sample-major) instead of redrawing
@@ -156,17 +160,19 @@ __global__ void __launch_bounds__(THREADS, 1) freq_sampler_kernel(DevBatch d, in
           const double var_ = 0.5 * (pf.x + pn.x), vai = 0.5 * (pf.y - pn.y);
           const double vbr = 0.5 * (pf.y + pn.y), vbi = -0.5 * (pf.x - pn.x);
           const double hre = h[2 * f], him = h[2 * f + 1];
+          double e[4] = {0.0, 0.0, 0.0, 0.0};  // w2 of (s0: re, im), (s0+1: re, im)
+          if (d.rng_mode == 1) {
+            const unsigned long long blk = (unsigned long long)(s0 >> 1) * (Kpad >> 1) + f;
+            normal_pair_fast(ph((unsigned)blk, (unsigned)(blk >> 32), (unsigned)it, STREAM_W2), e[0], e[1], e[2], e[3]);
+          }
 #pragma unroll
           for (int k = 0; k < 2; k++) {
             const int s = s0 + k;
             if (s >= Tb) break;
-            double n0 = 0.0, n1 = 0.0;
+            double n0 = e[2 * k], n1 = e[2 * k + 1];
             if (d.rng_mode == 0) {
               n0 = w2[(long long)(2 * ci) * Tb + s];
               n1 = w2[(long long)(2 * ci + 1) * Tb + s];
-            } else if (d.rng_mode == 1) {
-              unsigned long long blk = (unsigned long long)s * (Kpad >> 1) + f;
-              normal_pair(ph((unsigned)blk, (unsigned)(blk >> 32), (unsigned)it, STREAM_W2), n0, n1);
             }
             const double2 z = *reinterpret_cast<const double2*>(zT + (size_t)s * Kpad + 2 * f);
             const double vr = k ? vbr : var_, vi = k ? vbi : vai;
