@@ -494,6 +494,11 @@ extern "C" int dgibbs_run(dgibbs_handle h, const dgibbs_problem* p, dgibbs_resul
   if (d.prof) {
     long long pc[16];
     CU(cudaMemcpy(pc, d.prof, sizeof pc, cudaMemcpyDeviceToHost));
+    if (!diag_list.empty() && dense_list.empty() && freq_list.empty() && pc[8] > 0) {
+      static const char* dn[8] = {"P_partial+send", "draws", "wait_allgather", "corr+sync", "moments+draw_S", "stage_D", "sync", "loop_head"};
+      for (int i = 0; i < 8; i++) fprintf(stderr, "[dgibbs prof diag] %-16s %8.0f cyc/iteration\n", dn[i], (double)pc[i] / (double)pc[8]);
+      for (int i = 0; i < 16; i++) pc[i] = 0;
+    }
     static const char* names[12] = {"prepass", "phase0_gemm", "diag_gemm", "diag_stage_factor", "diag_storeW", "row_stage_addG",
                                     "row_gemm", "(unused)", "row_trimul_store", "back_gemm", "back_trimul", "draw"};
     double tot = 0;

@@ -328,6 +328,9 @@ __device__ __forceinline__ double chi2_fast(const Philox& ph, unsigned it, unsig
   return 2.0 * (double)dd;  // unreachable in practice (acceptance > 95 % per attempt)
 }
 
+// corr_t: even length, and at least the register-resident row count (rows past Tb are read as zeros there)
+__host__ __device__ inline int corr_len(int Tm) { return Tm < 64 ? 64 : ((Tm + 1) & ~1); }
+
 struct ResidentGeom {
   int C;        // cluster size (0: does not fit)
   int ncol;     // system columns per CTA
@@ -343,9 +346,10 @@ static ResidentGeom resident_geom(const DevBatch& d, size_t smem_cap, int maxC) 
     if (d.npad % (2 * C)) continue;
     const int ncol = d.npad / C;
     if (ncol > 1024 || ncol % 2) continue;
-    const int threads = (ncol + 31) / 32 * 32;
+    const int nmain = (ncol + 31) / 32 * 32;
+    const int threads = nmain;
     const int XQp = (d.Tmax + 2 + 1) & ~1;  // P_t[Tmax], q, bad
-    size_t doubles = (size_t)d.Tmax * ncol + (size_t)ncol + (size_t)((d.Tmax + 1) & ~1) + (size_t)RBATCH * d.Tmax + 128 +
+    size_t doubles = (size_t)d.Tmax * ncol + (size_t)ncol + (size_t)corr_len(d.Tmax) + (size_t)RBATCH * d.Tmax + 128 +
                      2 * (size_t)C * XQp + 4;
     if (doubles * 8 <= smem_cap) {
       g.C = C; g.ncol = ncol; g.threads = threads; g.XQp = XQp; g.smem = doubles * 8;
@@ -355,7 +359,69 @@ static ResidentGeom resident_geom(const DevBatch& d, size_t smem_cap, int maxC) 
   return g;
 }
 
-template <int MAXT>
+// Partial P_t = sum_k u_k y_tk / D_k over the resident columns.  A warp takes NR sample rows t0 + j W at a time
+// (independent accumulators); each lane takes column pairs (LDS.128); rows past Tb read row Tb-1 and are dropped at
+// the store.  A transposing butterfly leaves the total of row j in lanes [j 32/NR, (j+1) 32/NR), which send it
+// straight to every CTA of the cluster (st.async completes bytes on the destination's exchange barrier).
+// phase profiler of the resident kernel (build with -DDGIBBS_DIAG_PROF, run with DGIBBS_PROFILE=1): thread 0 of
+// CTA 0 accumulates clock64 deltas.  Compiled out by default: the clock reads pin the instruction schedule (7% slower).
+#ifndef DGIBBS_DIAG_PROF
+#define DPROF(idx) do { } while (0)
+#else
+#define DPROF(idx)                                                                       \
+  do {                                                                                   \
+    if (d.prof && blockIdx.x == 0 && threadIdx.x == 0) {                                 \
+      long long t_ = clock64();                                                          \
+      d.prof[idx] += t_ - tlast;                                                         \
+      tlast = t_;                                                                        \
+    }                                                                                    \
+  } while (0)
+#endif
+
+template <int NR>
+__device__ __forceinline__ void partial_P(const double* ysm, const double* wsm, double* xmine, unsigned long long* xb,
+                                          int Tb, int ncol, int C, int warp, int lane, int W) {
+  static_assert(NR == 4 || NR == 8, "rows per pass");
+  const double2* w2 = reinterpret_cast<const double2*>(wsm);
+  for (int t0 = warp; t0 < Tb; t0 += NR * W) {
+    const double2* yr[NR];
+    double acc[NR];
+#pragma unroll
+    for (int j = 0; j < NR; j++) {
+      acc[j] = 0.0;
+      yr[j] = reinterpret_cast<const double2*>(ysm + (size_t)min(t0 + j * W, Tb - 1) * ncol);
+    }
+    for (int c = lane; c < (ncol >> 1); c += 32) {
+      const double2 wv = w2[c];
+#pragma unroll
+      for (int j = 0; j < NR; j++) {
+        const double2 yv = yr[j][c];
+        acc[j] = fma(wv.x, yv.x, fma(wv.y, yv.y, acc[j]));
+      }
+    }
+    int bit = 16;
+#pragma unroll
+    for (int n = NR / 2; n >= 1; n >>= 1, bit >>= 1) {
+      const bool hi = lane & bit;
+#pragma unroll
+      for (int j = 0; j < n; j++) {
+        const double send = hi ? acc[j] : acc[j + n], keep = hi ? acc[j + n] : acc[j];
+        acc[j] = keep + __shfl_xor_sync(0xffffffffu, send, bit);
+      }
+    }
+#pragma unroll
+    for (int o = 16 / NR; o > 0; o >>= 1) acc[0] += __shfl_xor_sync(0xffffffffu, acc[0], o);
+    constexpr int G = 32 / NR;  // lanes holding the same row total
+    const int t = t0 + (lane / G) * W;
+    if (t < Tb)
+      for (int dst = lane % G; dst < C; dst += G)
+        st_async_f64(mapa_u32(smem_u32(xmine + t), dst), acc[0], mapa_u32(smem_u32(xb), dst));
+  }
+}
+
+// YREG > 0: every thread also keeps its own column of yhat (YREG >= Tb samples) in registers, so the moment pass reads
+// no shared memory but the broadcast corr_t.
+template <int MAXT, int YREG>
 __global__ void __launch_bounds__(MAXT, 1) diag_resident_kernel(DevBatch d, int it_begin, int it_end, int C, int ncol,
                                                                  int XQp) {
   extern __shared__ __align__(16) double dsm[];
@@ -367,7 +433,7 @@ __global__ void __launch_bounds__(MAXT, 1) diag_resident_kernel(DevBatch d, int 
   double* ysm = dsm;                                   // resident slice [Tb][ncol]
   double* wsm = ysm + (size_t)Tm * ncol;               // u_k / D_k of the local columns
   double* corr = wsm + ncol;                           // corr_t
-  double* xi = corr + ((Tm + 1) & ~1);                 // [RBATCH][Tm] xi_t of the current batch of iterations
+  double* xi = corr + corr_len(Tm);                 // [RBATCH][Tm] xi_t of the current batch of iterations
   double* qw = xi + RBATCH * Tm;                       // [64] per-warp partials of q and of the non-positive count
   double* scw = qw + 64;                               // [64] per-warp partials of sum corr, sum corr^2
   double* xch = scw + 64;                               // [2][C][XQp] gathered partial vectors
@@ -408,26 +474,37 @@ __global__ void __launch_bounds__(MAXT, 1) diag_resident_kernel(DevBatch d, int 
     phase ^= 1;
     // per-baseline constants of the owned column: sum_t y, sum_t y^2
     double sy = 0.0, syy = 0.0;
-    if (owner)
+    [[maybe_unused]] double ycol[YREG > 0 ? YREG : 1];
+    if constexpr (YREG > 0) {
+#pragma unroll
+      for (int t = 0; t < YREG; t++) {
+        const double v = (owner && t < Tb) ? ysm[(size_t)t * ncol + tid] : 0.0;
+        ycol[t] = v;
+        sy += v;
+        syy += v * v;
+      }
+      for (int t = Tb + tid; t < YREG; t += blockDim.x) corr[t] = 0.0;  // rows past Tb: finite, times ycol = 0
+    } else if (owner) {
       for (int t = 0; t < Tb; t++) {
         const double v = ysm[(size_t)t * ncol + tid];
         sy += v;
         syy += v * v;
       }
-    double iv = 0.0, rd = 0.0;
+    }
+    const double sfac = d.cplx ? 2.0 : 1.0, inv_a = 1.0 / a, inv_T = 1.0 / (double)Tb;  // delay.py:1794
+    double iv = 0.0;
     // A: D = a + 1/S on the owned column; per-warp partials of q = sum 1/D and of the non-positive count
     auto stage_A = [&]() {
       double ql = 0.0, badl = 0.0;
       iv = 0.0;
       if (owner) {
-        double si = (Sk != 0.0) ? 1.0 / Sk : 0.0;  // invert_no_zero, delay.py:1785
-        if (d.cplx) si *= 2.0;                      // delay.py:1794
-        const double D = a + si;
-        if (!(D > 0.0)) badl = 1.0;
-        iv = 1.0 / D;
+        // D = a + s / S_k (invert_no_zero: 1/0 -> 0, delay.py:1785) and 1/D from one division: 1/D = S_k / (a S_k + s)
+        const double den = fma(a, Sk, sfac);
+        const bool zero = Sk == 0.0 || fabs(Sk) == INFINITY;  // s / S_k = 0 either way
+        iv = zero ? inv_a : Sk / den;
+        if (!(iv > 0.0) || !(a > 0.0 || !zero)) badl = 1.0;  // D > 0 <=> 1/D > 0
         ql = iv;
       }
-      rd = sqrt(iv);
       if (tid < ncol) wsm[tid] = sg * iv;
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) {
@@ -442,30 +519,30 @@ __global__ void __launch_bounds__(MAXT, 1) diag_resident_kernel(DevBatch d, int 
     stage_A();
     __syncthreads();
 
-    double dg[RBATCH], dc2[RBATCH], idct[RBATCH];
-    for (int it = it_begin; it < it_end; it++) {
-      // ---- scalar draws of this and the next RBATCH-1 iterations (independent chains: ILP)
-      const int bi = (it - it_begin) % RBATCH;
-      if (bi == 0) {
-        if (owner) {
-#pragma unroll
-          for (int j = 0; j < RBATCH; j++) {
-            // two Philox blocks feed g and the first attempts of both chi^2 draws (real mode; in complex
-            // mode the chi^2_T draw is shared by the re/im columns of a delay and keyed on the delay)
-            const uint4 r = ph((unsigned)k, 0u, (unsigned)(it + j), STREAM_DIAG_G);
-            const uint4 r2 = ph((unsigned)k, 1u, (unsigned)(it + j), STREAM_DIAG_G);
-            dg[j] = (double)normal1_f32(r.x, r.y);
-            dc2[j] = chi2_fast(ph, (unsigned)(it + j), (unsigned)k, STREAM_DIAG_C2, Tb - 2, true, r.z, r.w, r2.z);
-            idct[j] = 1.0 / chi2_fast(ph, (unsigned)(it + j), dkey, STREAM_DIAG_CHI2, Tb, !d.cplx, r2.x, r2.y, r2.w);
-          }
-        }
-        if (bc != 0.0)
-          for (int e = tid; e < RBATCH * Tb; e += blockDim.x) {  // xi_t of the batch
-            const int j = e / Tb, t = e - j * Tb;
-            uint4 r = ph((unsigned)t, 0u, (unsigned)(it + j), STREAM_DIAG_XI);
-            xi[j * Tm + t] = (double)normal1_f32(r.x, r.y);
-          }
+    // scalar draws of one iteration: g ~ N(0,1), c2 ~ chi^2_{T-2}, 1 / chi^2_T of the owned column, and xi_t (thread t).
+    // Two Philox blocks feed g and the first attempts of both chi^2 draws (real mode; in complex mode the
+    // chi^2_T draw is shared by the re/im columns of a delay and keyed on the delay).
+    double g_cur = 0.0, c2_cur = 0.0, ict_cur = 0.0, g_nxt = 0.0, c2_nxt = 0.0, ict_nxt = 0.0;
+    auto draw_scalars = [&](int itx, double& g, double& c2, double& ict) {
+      if (owner) {
+        const uint4 r = ph((unsigned)k, 0u, (unsigned)itx, STREAM_DIAG_G);
+        const uint4 r2 = ph((unsigned)k, 1u, (unsigned)itx, STREAM_DIAG_G);
+        g = (double)normal1_f32(r.x, r.y);
+        c2 = chi2_fast(ph, (unsigned)itx, (unsigned)k, STREAM_DIAG_C2, Tb - 2, true, r.z, r.w, r2.z);
+        ict = 1.0 / chi2_fast(ph, (unsigned)itx, dkey, STREAM_DIAG_CHI2, Tb, !d.cplx, r2.x, r2.y, r2.w);
       }
+      if (bc != 0.0)
+        for (int t = tid; t < Tb; t += blockDim.x) {
+          uint4 r = ph((unsigned)t, 0u, (unsigned)itx, STREAM_DIAG_XI);
+          xi[(itx & 1) * Tm + t] = (double)normal1_f32(r.x, r.y);
+        }
+    };
+    draw_scalars(it_begin, g_cur, c2_cur, ict_cur);
+#ifdef DGIBBS_DIAG_PROF
+    long long tlast = clock64();
+#endif
+    for (int it = it_begin; it < it_end; it++) {
+      DPROF(7);
       // ---- B: partial P_t = sum_k u_k y_tk / D_k over the local columns; a warp takes 8 sample rows at a
       // time (independent accumulators) and sends the sums straight to every CTA of the cluster
       double* xmine = xch + (size_t)(par * C + rank) * XQp;
@@ -482,56 +559,17 @@ __global__ void __launch_bounds__(MAXT, 1) diag_resident_kernel(DevBatch d, int 
       if (tid == 32 % blockDim.x)  // arm this phase: q and bad from every CTA, plus T partial sums each if b != 0
         mbar_expect_tx(xbar + par, (unsigned)(C * ((bc != 0.0 ? Tb : 0) + 2) * 8));
       if (bc != 0.0) {
-        // rows t0 + j W, j < 8, of this warp; each lane takes column pairs (LDS.128), rows past Tb read row
-        // Tb-1 and are dropped at the store
-        const double2* w2 = reinterpret_cast<const double2*>(wsm);
-        for (int t0 = warp; t0 < Tb; t0 += 8 * W) {
-          const double2* yr[8];
-          double acc[8];
-#pragma unroll
-          for (int j = 0; j < 8; j++) {
-            acc[j] = 0.0;
-            yr[j] = reinterpret_cast<const double2*>(ysm + (size_t)min(t0 + j * W, Tb - 1) * ncol);
-          }
-          for (int c = lane; c < (ncol >> 1); c += 32) {
-            const double2 wv = w2[c];
-#pragma unroll
-            for (int j = 0; j < 8; j++) {
-              const double2 yv = yr[j][c];
-              acc[j] = fma(wv.x, yv.x, fma(wv.y, yv.y, acc[j]));
-            }
-          }
-          // transposing butterfly: 8 sums x 32 lanes -> lane l holds the total of row j = l >> 2 (9 exchanges)
-          {
-            const bool hi = lane & 16;
-#pragma unroll
-            for (int j = 0; j < 4; j++) {
-              const double send = hi ? acc[j] : acc[j + 4], keep = hi ? acc[j + 4] : acc[j];
-              acc[j] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
-            }
-          }
-          {
-            const bool hi = lane & 8;
-#pragma unroll
-            for (int j = 0; j < 2; j++) {
-              const double send = hi ? acc[j] : acc[j + 2], keep = hi ? acc[j + 2] : acc[j];
-              acc[j] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
-            }
-          }
-          {
-            const bool hi = lane & 4;
-            const double send = hi ? acc[0] : acc[1], keep = hi ? acc[1] : acc[0];
-            acc[0] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
-          }
-          acc[0] += __shfl_xor_sync(0xffffffffu, acc[0], 2);
-          acc[0] += __shfl_xor_sync(0xffffffffu, acc[0], 1);
-          const int t = t0 + (lane >> 2) * W;
-          if (t < Tb)
-            for (int dst = lane & 3; dst < C; dst += 4)
-              st_async_f64(mapa_u32(smem_u32(xmine + t), dst), acc[0], mapa_u32(smem_u32(xbar + par), dst));
-        }
+        if (4 * W >= Tb)
+          partial_P<4>(ysm, wsm, xmine, xbar + par, Tb, ncol, C, warp, lane, W);
+        else
+          partial_P<8>(ysm, wsm, xmine, xbar + par, Tb, ncol, C, warp, lane, W);
       }
+      DPROF(0);
+      // the next iteration's scalar draws overlap the all-gather latency
+      draw_scalars(it + 1, g_nxt, c2_nxt, ict_nxt);
+      DPROF(1);
       mbar_wait(xbar + par, (xphase >> par) & 1u);
+      DPROF(2);
       xphase ^= 1u << par;
       // ---- D: every thread forms q, the failure flag and beta; thread t forms corr_t
       const double* xb = xch + (size_t)par * C * XQp;
@@ -555,7 +593,7 @@ __global__ void __launch_bounds__(MAXT, 1) diag_resident_kernel(DevBatch d, int 
         for (int t = tid; t < Tb; t += blockDim.x) {
           double P = 0.0;
           for (int r = 0; r < C; r++) P += xb[(size_t)r * XQp + t];
-          const double cv = -beta * P + sb * xi[bi * Tm + t];
+          const double cv = -beta * P + sb * xi[(it & 1) * Tm + t];
           corr[t] = cv;
           scl += cv;
           sccl += cv * cv;
@@ -571,6 +609,7 @@ __global__ void __launch_bounds__(MAXT, 1) diag_resident_kernel(DevBatch d, int 
         }
         __syncthreads();
       }
+      DPROF(3);
       // ---- E + F: moments of the owned column, power-spectrum draw (delay.py:1862-1880), next D
       double ssq = 0.0;
       if (owner) {
@@ -580,63 +619,81 @@ __global__ void __launch_bounds__(MAXT, 1) diag_resident_kernel(DevBatch d, int 
             sc += scw[w];
             scc += scw[32 + w];
           }
-          const double* yc = ysm + tid;
-          const double2* cp = reinterpret_cast<const double2*>(corr);
-          const int ncol2 = 2 * ncol;
-          double r2 = 0.0, r3 = 0.0;
-          int t = 0;
-          for (; t + 7 < Tb; t += 8) {  // 8 rows per trip: all loads issued before the first FMA needs them
-            double yv[8];
-            double2 cv[4];
+          if constexpr (YREG > 0) {
+            const double2* cp = reinterpret_cast<const double2*>(corr);
+            double r2 = 0.0, r3 = 0.0;
 #pragma unroll
-            for (int j = 0; j < 4; j++) {
-              cv[j] = cp[j];
-              yv[2 * j] = yc[(size_t)j * ncol2];
-              yv[2 * j + 1] = yc[(size_t)j * ncol2 + ncol];
+            for (int t = 0; t < YREG; t += 4) {
+              const double2 c0 = cp[t >> 1], c1 = cp[(t >> 1) + 1];
+              r0 = fma(ycol[t], c0.x, r0);
+              r1 = fma(ycol[t + 1], c0.y, r1);
+              r2 = fma(ycol[t + 2], c1.x, r2);
+              r3 = fma(ycol[t + 3], c1.y, r3);
             }
-            r0 = fma(yv[0], cv[0].x, r0);
-            r1 = fma(yv[1], cv[0].y, r1);
-            r2 = fma(yv[2], cv[1].x, r2);
-            r3 = fma(yv[3], cv[1].y, r3);
-            r0 = fma(yv[4], cv[2].x, r0);
-            r1 = fma(yv[5], cv[2].y, r1);
-            r2 = fma(yv[6], cv[3].x, r2);
-            r3 = fma(yv[7], cv[3].y, r3);
-            cp += 4;
-            yc += 4 * (size_t)ncol2;
+            r0 += r2;
+            r1 += r3;
+          } else {
+            const double* yc = ysm + tid;
+            const double2* cp = reinterpret_cast<const double2*>(corr);
+            const int ncol2 = 2 * ncol;
+            double r2 = 0.0, r3 = 0.0;
+            int t = 0;
+            for (; t + 7 < Tb; t += 8) {  // 8 rows per trip: all loads issued before the first FMA needs them
+              double yv[8];
+              double2 cv[4];
+#pragma unroll
+              for (int j = 0; j < 4; j++) {
+                cv[j] = cp[j];
+                yv[2 * j] = yc[(size_t)j * ncol2];
+                yv[2 * j + 1] = yc[(size_t)j * ncol2 + ncol];
+              }
+              r0 = fma(yv[0], cv[0].x, r0);
+              r1 = fma(yv[1], cv[0].y, r1);
+              r2 = fma(yv[2], cv[1].x, r2);
+              r3 = fma(yv[3], cv[1].y, r3);
+              r0 = fma(yv[4], cv[2].x, r0);
+              r1 = fma(yv[5], cv[2].y, r1);
+              r2 = fma(yv[6], cv[3].x, r2);
+              r3 = fma(yv[7], cv[3].y, r3);
+              cp += 4;
+              yc += 4 * (size_t)ncol2;
+            }
+            for (; t + 1 < Tb; t += 2) {
+              const double2 c2 = *cp++;
+              r0 = fma(yc[0], c2.x, r0);
+              r1 = fma(yc[ncol], c2.y, r1);
+              yc += ncol2;
+            }
+            r0 += r2;
+            r1 += r3;
+            if (t < Tb) r0 = fma(yc[0], corr[t], r0);
           }
-          for (; t + 1 < Tb; t += 2) {
-            const double2 c2 = *cp++;
-            r0 = fma(yc[0], c2.x, r0);
-            r1 = fma(yc[ncol], c2.y, r1);
-            yc += ncol2;
-          }
-          r0 += r2;
-          r1 += r3;
-          if (t < Tb) r0 = fma(yc[0], corr[t], r0);
         }
         const double sm1 = iv * (sy + sg * sc);                              // sum_t m
         const double sm2 = iv * iv * (syy + 2.0 * sg * (r0 + r1) + scc);     // sum_t m^2
-        const double mm = fmax(sm2 - sm1 * sm1 / (double)Tb, 0.0);           // |m~|^2
-        if (Tb > 1) ssq = mm + 2.0 * rd * sqrt(mm) * dg[0] + rd * rd * (dg[0] * dg[0] + dc2[0]);
+        const double mm = fmax(sm2 - sm1 * sm1 * inv_T, 0.0);             // |m~|^2
+        if (Tb > 1) ssq = mm + 2.0 * sqrt(iv * mm) * g_cur + iv * (g_cur * g_cur + c2_cur);
       }
       if (d.cplx) ssq += __shfl_xor_sync(0xffffffffu, ssq, 1);  // re + im columns of one delay (delay.py:1869-1875)
       if (owner) {
-        Sk = ssq * idct[0];
+        Sk = ssq * ict_cur;
         if (!d.cplx || !(tid & 1)) {
           S[dkey] = Sk;
           d.samples[((size_t)it * d.B + b) * N + dkey] = Sk;
         }
       }
-#pragma unroll
-      for (int j = 0; j + 1 < RBATCH; j++) {  // rotate the batched draws (keeps them in registers)
-        dg[j] = dg[j + 1];
-        dc2[j] = dc2[j + 1];
-        idct[j] = idct[j + 1];
-      }
+      g_cur = g_nxt;
+      c2_cur = c2_nxt;
+      ict_cur = ict_nxt;
       if (rank == 0 && tid == 0) d.n_done[b] = it + 1;
+      DPROF(4);
       stage_A();
+      DPROF(5);
       __syncthreads();
+      DPROF(6);
+#ifdef DGIBBS_DIAG_PROF
+      if (d.prof && blockIdx.x == 0 && tid == 0) d.prof[8] += 1;
+#endif
     }
     __syncthreads();  // every reader of ysm is done before the next baseline's copies land
   }
@@ -648,7 +705,9 @@ static cudaError_t launch_resident(const DevBatch& d, int it_begin, int it_end, 
   for (int maxC = 8; maxC <= RMAXC; maxC *= 2) {
     ResidentGeom g = resident_geom(d, 227 * 1024, maxC);
     if (g.C == 0) continue;
-    auto kern = g.threads <= 256 ? diag_resident_kernel<256> : diag_resident_kernel<1024>;
+    static const bool no_yreg = getenv("DGIBBS_DIAG_NO_YREG") != nullptr;
+    auto kern = g.threads <= 256 ? ((d.Tmax <= 64 && !no_yreg) ? diag_resident_kernel<256, 64> : diag_resident_kernel<256, 0>)
+                                 : diag_resident_kernel<1024, 0>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g.smem);
     if (e != cudaSuccess) return e;
     if (g.C > 8) {

@@ -1,0 +1,4 @@
+set -x
+timeout 600 python -m pytest tests/test_gpu_diag.py -m gpu -x -q > gpurun_out/c22_pytest.log 2>&1; echo "pytest rc=$?" >> gpurun_out/c22_pytest.log
+timeout 300 python bench.py --config cfg3 --nbase 2048 --steps 2 --warmup 2 --no-cpu-baseline > gpurun_out/c22_bench_cfg3.log 2>&1; echo "rc=$?" >> gpurun_out/c22_bench_cfg3.log
+echo done
