@@ -435,7 +435,9 @@ extern "C" int dgibbs_run(dgibbs_handle h, const dgibbs_problem* p, dgibbs_resul
     dp.project_only = 1;
     dp.rng_mode = DGIBBS_RNG_ZERO;
     dp.nslots = dp.nlist < d.nslots ? dp.nlist : d.nslots;
-    CU(launch_dense_sampler(dp, 0, 1, h->stream));
+    static const bool no_pk = getenv("DGIBBS_NO_PROJECT_KERNEL") != nullptr;
+    if (!no_pk && diag_project_fft_fits(dp)) CU(launch_diag_project_fft(dp, h->sm_count, h->stream));
+    else CU(launch_dense_sampler(dp, 0, 1, h->stream));
     h->timing.launches++;
     CU(cudaEventRecord(h->ev[6], h->stream));
     DevBatch dd = d;

@@ -108,6 +108,8 @@ cudaError_t launch_diag_sampler(const DevBatch& d, int it_begin, int it_end, int
                                 bool allow_resident);
 
 // sampler_freq.cu
+bool diag_project_fft_fits(const DevBatch& d);
+cudaError_t launch_diag_project_fft(const DevBatch& d, int sm_count, cudaStream_t st);
 bool freq_branch_fits(const DevBatch& d, int M, int T);
 cudaError_t launch_freq_sampler(const DevBatch& d, int it_begin, int it_end, cudaStream_t st);
 

@@ -1,8 +1,7 @@
 // Per-batch setup: projection table, window/whiten/pack, circulant first columns.
 // Reference behaviour: _compute_delay_spectrum_inputs, draco/analysis/delay.py:1657-1710,
 // fourier_matrix_* delay.py:1480-1613, window_generalised draco/util/tools.py:547-601.
-#include "common.cuh"
-#include "internal.h"
+#include "dense_core.cuh"
 
 namespace dg {
 
@@ -75,14 +74,17 @@ cudaError_t launch_build_twtab(int N, double2* tw, cudaStream_t st) {
   return cudaGetLastError();
 }
 
-// One CTA per baseline.
-__global__ void setup_baseline_kernel(DevBatch d, const double* __restrict__ S0) {
-  extern __shared__ double sm[];
+// One CTA (THREADS threads) per baseline.  FFT: the first column of the circulant comes from one in-smem inverse FFT
+// of the squared channel weights (N log N) instead of the N * nch direct sum.
+template <bool FFT>
+__global__ void __launch_bounds__(THREADS) setup_baseline_kernel(DevBatch d, const double* __restrict__ S0) {
+  extern __shared__ __align__(16) double sm[];
   const int b = blockIdx.x;
   const int N = d.N, nch = d.nch;
-  double* tabc = sm;                          // [N]
-  double* tabs = d.cplx ? sm + N : nullptr;   // [N]
-  double* hsq = sm + (d.cplx ? 2 * N : N);    // [nch]
+  // FFT: [bufA: N double2][bufB: N double2]; direct: [tabc: N][tabs: N if complex]
+  double* tabc = sm;
+  double* tabs = d.cplx ? sm + N : nullptr;
+  double* hsq = sm + (FFT ? 4 * N : (d.cplx ? 2 * N : N));  // [nch]
   double* s_w = hsq + nch;                    // [nch] window
   double* s_re = s_w + nch;                   // [nch] sqrt(Ni_r) of the real part
   double* s_im = s_re + nch;                  // [nch] sqrt(Ni_r) of the imaginary part
@@ -93,12 +95,13 @@ __global__ void setup_baseline_kernel(DevBatch d, const double* __restrict__ S0)
   double* zT = d.zT + (size_t)b * d.Tmax * d.Kpad;
 
   for (int i = threadIdx.x; i < nch; i += blockDim.x) cidx[i] = -1;
-  for (int m = threadIdx.x; m < N; m += blockDim.x) {
-    double c, s;
-    twiddle(m, N, c, s);
-    tabc[m] = c;
-    if (tabs) tabs[m] = s;
-  }
+  if (!FFT)
+    for (int m = threadIdx.x; m < N; m += blockDim.x) {
+      double c, s;
+      twiddle(m, N, c, s);
+      tabc[m] = c;
+      if (tabs) tabs[m] = s;
+    }
   __syncthreads();
   for (int ci = threadIdx.x; ci < Mb; ci += blockDim.x) {
     long long f = d.fsel[coff + ci];
@@ -131,37 +134,49 @@ __global__ void setup_baseline_kernel(DevBatch d, const double* __restrict__ S0)
   }
   __syncthreads();
 
-  // whitened, windowed data, sample-major (delay.py:1676,1687,1707)
+  // whitened, windowed data, sample-major (delay.py:1676,1687,1707); a thread keeps its channels' factors
   const int halfK = d.Kpad / 2;
-  for (long long e = threadIdx.x; e < (long long)d.Tmax * halfK; e += blockDim.x) {
-    int t = (int)(e / halfK), i = (int)(e % halfK);
-    double zr = 0.0, zi = 0.0;
-    if (t < Tb && i < nch) {
-      int ci = cidx[i];
-      if (ci >= 0) {
-        double2 v = d.data[doff + (long long)t * Mb + ci];
-        zr = (v.x * s_w[i]) * s_re[i];
-        zi = (v.y * s_w[i]) * s_im[i];
+  for (int i = threadIdx.x; i < halfK; i += blockDim.x) {
+    const int ci = i < nch ? cidx[i] : -1;
+    const double w = ci >= 0 ? s_w[i] : 0.0, fre = ci >= 0 ? s_re[i] : 0.0, fim = ci >= 0 ? s_im[i] : 0.0;
+    const double2* src = d.data + doff + (ci >= 0 ? ci : 0);
+    double* dst = zT + 2 * i;
+    for (int t = 0; t < d.Tmax; t++) {
+      double2 z = make_double2(0.0, 0.0);
+      if (t < Tb && ci >= 0) {
+        const double2 v = src[(long long)t * Mb];
+        z = make_double2((v.x * w) * fre, (v.y * w) * fim);
       }
+      *reinterpret_cast<double2*>(dst + (size_t)t * d.Kpad) = z;
     }
-    zT[(size_t)t * d.Kpad + 2 * i] = zr;
-    zT[(size_t)t * d.Kpad + 2 * i + 1] = zi;
   }
 
-  // first column of the circulant  FTNiF[t,t'] = c[(t-t') mod N]
+  // first column of the circulant  FTNiF[t,t'] = c[(t-t') mod N] = sum_i hsq_i e^{2 pi i (i k) / N}  (real part in
+  // real mode)
   double* ct = d.ctab + (size_t)b * d.nsys;
-  for (int k = threadIdx.x; k < N; k += blockDim.x) {
-    double accr = 0.0, acci = 0.0;
-    int m = 0;
-    for (int i = 0; i < nch; i++) {
-      double g = hsq[i];
-      accr += g * tabc[m];
-      if (tabs) acci += g * tabs[m];
-      m += k;
-      if (m >= N) m -= N;
+  if (FFT) {
+    double2* bufA = reinterpret_cast<double2*>(sm);
+    for (int i = threadIdx.x; i < N; i += blockDim.x) bufA[i] = make_double2(i < nch ? hsq[i] : 0.0, 0.0);
+    __syncthreads();
+    const double2* res = fft_inverse_smem(bufA, bufA + N, d.twtab, N);
+    for (int k = threadIdx.x; k < N; k += blockDim.x) {
+      ct[k] = res[k].x;
+      if (d.cplx) ct[N + k] = res[k].y;
     }
-    ct[k] = accr;
-    if (tabs) ct[N + k] = acci;
+  } else {
+    for (int k = threadIdx.x; k < N; k += blockDim.x) {
+      double accr = 0.0, acci = 0.0;
+      int m = 0;
+      for (int i = 0; i < nch; i++) {
+        double g = hsq[i];
+        accr += g * tabc[m];
+        if (tabs) acci += g * tabs[m];
+        m += k;
+        if (m >= N) m -= N;
+      }
+      ct[k] = accr;
+      if (tabs) ct[N + k] = acci;
+    }
   }
 
   // Is FTNiF = a I + b u u^T (u_t = (-1)^t)?  True for uniform weights, no window and a complete
@@ -199,10 +214,13 @@ __global__ void setup_baseline_kernel(DevBatch d, const double* __restrict__ S0)
 }
 
 cudaError_t launch_setup_baselines(const DevBatch& d, const double* S0, cudaStream_t st) {
-  size_t smem = sizeof(double) * ((d.cplx ? 2 : 1) * (size_t)d.N + 4 * (size_t)d.nch);
-  cudaError_t e = cudaFuncSetAttribute(setup_baseline_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  bool fft = d.use_fft && d.twtab != nullptr;
+  if (fft && sizeof(double) * (4 * (size_t)d.N + 4 * (size_t)d.nch) > 200 * 1024) fft = false;
+  size_t smem = sizeof(double) * ((fft ? 4 : (d.cplx ? 2 : 1)) * (size_t)d.N + 4 * (size_t)d.nch);
+  auto kern = fft ? setup_baseline_kernel<true> : setup_baseline_kernel<false>;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
-  setup_baseline_kernel<<<d.B, 256, smem, st>>>(d, S0);
+  kern<<<d.B, THREADS, smem, st>>>(d, S0);
   return cudaGetLastError();
 }
 
