@@ -13,7 +13,7 @@ import subprocess
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libdgibbs.so")
-SOURCES = ["dgibbs_api.cu", "setup_kernels.cu", "sampler_dense.cu", "sampler_diag.cu", "sampler_cross.cu", "sampler_freq.cu", "project_fft.cu", "finish_kernels.cu"]
+SOURCES = ["dgibbs_api.cu", "setup_kernels.cu", "sampler_dense.cu", "sampler_diag.cu", "sampler_cross.cu", "sampler_freq.cu", "project_fft.cu", "cut_kernels.cu", "finish_kernels.cu"]
 HEADERS = ["common.cuh", "internal.h", "dense_core.cuh", os.path.join("..", "..", "include", "dgibbs.h")]
 NVCC_FLAGS = [
     "-gencode",

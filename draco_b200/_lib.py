@@ -39,6 +39,7 @@ EXPORTED = [
     "dgibbs_wiener",
     "dgibbs_fourier_matrix",
     "dgibbs_cross_run",
+    "dgibbs_cut_data",
 ]
 CROSS_MAX_DATASETS = 4
 
@@ -114,6 +115,35 @@ class CrossProblem(C.Structure):
     ]
 
 
+class Cut(C.Structure):
+    """``dgibbs_cut`` of include/dgibbs.h (device-side ``_cut_data``)."""
+
+    _fields_ = [
+        ("struct_size", C.c_int32),
+        ("on_device", C.c_int32),
+        ("B", C.c_int32),
+        ("T", C.c_int32),
+        ("nfreq", C.c_int32),
+        ("weight_f32", C.c_int32),
+        ("remove_mean", C.c_int32),
+        ("scale_freq", C.c_int32),
+        ("time_frac", C.c_double),
+        ("freq_frac", C.c_double),
+        ("weight_boost", C.c_double),
+        ("data", _vp),
+        ("weight", _vp),
+        ("channel_ind", _vp),
+        ("data_out", _vp),
+        ("Ni_out", _vp),
+        ("fsel_out", _vp),
+        ("T_out", _vp),
+        ("M_out", _vp),
+        ("alive", _vp),
+        ("keep_t", _vp),
+        ("keep_f", _vp),
+    ]
+
+
 class Timing(C.Structure):
     _fields_ = [
         ("ms_h2d", C.c_double),
@@ -158,10 +188,11 @@ def load():
     lib.dgibbs_wiener.argtypes = [_vp, C.POINTER(Problem), _vp, _vp]
     lib.dgibbs_fourier_matrix.argtypes = [_vp, C.c_int32, C.c_int32, _vp, C.c_int32, _vp]
     lib.dgibbs_cross_run.argtypes = [_vp, C.POINTER(CrossProblem), _vp, _vp, _vp]
+    lib.dgibbs_cut_data.argtypes = [_vp, C.POINTER(Cut)]
     for name in EXPORTED:
         if name not in ("dgibbs_last_error", "dgibbs_version"):
             getattr(lib, name).restype = C.c_int
-    for which, st in enumerate((Problem, Result, Timing, CrossProblem)):
+    for which, st in enumerate((Problem, Result, Timing, CrossProblem, Cut)):
         if lib.dgibbs_sizeof(which) != C.sizeof(st):
             raise RuntimeError(f"ABI mismatch: {st.__name__} is {C.sizeof(st)} bytes here, "
                                f"{lib.dgibbs_sizeof(which)} in {LIB_PATH}; rebuild the library")

@@ -81,6 +81,7 @@ extern "C" int dgibbs_sizeof(int which) {
     case 1: return (int)sizeof(dgibbs_result);
     case 2: return (int)sizeof(dgibbs_timing);
     case 3: return (int)sizeof(dgibbs_cross_problem);
+    case 4: return (int)sizeof(dgibbs_cut);
     default: return -1;
   }
 }
@@ -218,8 +219,9 @@ static int stage_batch(dgibbs_handle h, const dgibbs_problem* p, Staged& s, bool
   for (int b = 0; b < B; b++) {
     if (s.T[b] <= 0) return bad_arg(h, 2, "T[b] must be positive");
     if (s.M[b] <= 0 || s.M[b] > d.nch) return bad_arg(h, 2, "M[b] out of range");
-    if (s.chan_off[b + 1] - s.chan_off[b] != s.M[b]) return bad_arg(h, 2, "chan_off inconsistent with M");
-    if (s.data_off[b + 1] - s.data_off[b] != (long long)s.T[b] * s.M[b])
+    // blocks may leave gaps (the device-side cut writes into fixed slots) but must not overlap
+    if (s.chan_off[b] < 0 || s.chan_off[b + 1] - s.chan_off[b] < s.M[b]) return bad_arg(h, 2, "chan_off inconsistent with M");
+    if (s.data_off[b] < 0 || s.data_off[b + 1] - s.data_off[b] < (long long)s.T[b] * s.M[b])
       return bad_arg(h, 2, "data_off inconsistent with T*M");
     Tmax = s.T[b] > Tmax ? s.T[b] : Tmax;
     s.xoff[b] = s.sumT;

@@ -311,6 +311,7 @@ class DelayPowerSpectrumGibbs(DelayPowerSpectrumBase, _RandomTask):
     initial_amplitude = config.Property(proptype=float, default=10.0)
     median_frac = config.Property(proptype=float, default=0.5)
     rng_mode = config.enum(["philox", "injected"], default="philox")
+    device_cut = config.Property(proptype=bool, default=True)
 
     _ncalls = 0
 
@@ -356,9 +357,11 @@ class DelayPowerSpectrumGibbs(DelayPowerSpectrumBase, _RandomTask):
         spec_out = _local(out_cont.spectrum)
         mask_out = _local(out_cont.datasets["spectrum_mask"]) if self.save_spectrum_mask else None
         samp_out = _local(out_cont.datasets["spectrum_samples"]) if self.save_samples else None
-        jobs = self._cut_all(data_view, weight_view, out_cont, channel_ind)
         handle = gibbs.get_handle(self._device())
         seed = self._device_seed()
+        if self.device_cut and self.rng_mode == "philox":
+            return self._evaluate_device_cut(data_view, weight_view, out_cont, channel_ind, ndelay, prior, handle, seed)
+        jobs = self._cut_all(data_view, weight_view, out_cont, channel_ind)
         nsys = (2 if self.complex_timedomain else 1) * ndelay
         for chunk in self._chunks(jobs):
             lbis = [j[0] for j in chunk]
@@ -380,6 +383,46 @@ class DelayPowerSpectrumGibbs(DelayPowerSpectrumBase, _RandomTask):
                     samp_out[:, lbi] = res.samples[:, n]  # already front-padded with zeros (delay.py:1177-1178)
             self.log.debug(f"device batch of {len(chunk)} baselines: {res.timing['ms_sampler']:.1f} ms in the sampler")
         if self.save_spectrum_mask:
+            n_conv = nbase - ddist.allreduce_count(int(mask_out.sum()))  # delay.py:1182
+            self.log.debug(f"{n_conv}/{nbase} unflagged baselines.")
+        return out_cont
+
+
+    def _evaluate_device_cut(self, data_view, weight_view, out_cont, channel_ind, ndelay, prior, handle, seed):
+        """Same as the loop above with ``_cut_data`` done on the device for the whole local slab
+        (``dgibbs_cut_data``, delay.py:516-597): the raw [B, T, nfreq] slab goes up once, the cut / mean-subtracted /
+        compacted batch stays in HBM and feeds the sampler in place."""
+        from . import dist as ddist
+
+        vis = np.ascontiguousarray(_local_array(data_view))
+        wgt = np.ascontiguousarray(_local_array(weight_view))
+        spec_out = _local(out_cont.spectrum)
+        mask_out = _local(out_cont.datasets["spectrum_mask"]) if self.save_spectrum_mask else None
+        samp_out = _local(out_cont.datasets["spectrum_samples"]) if self.save_samples else None
+        gids = np.array([bi for _, bi in out_cont.spectrum[:].enumerate(axis=0)], dtype=np.int64)
+        nloc = vis.shape[0]
+        step = self.batch_baselines if self.batch_baselines and self.batch_baselines > 0 else max(1, nloc)
+        for s0 in range(0, nloc, step):
+            s1 = min(nloc, s0 + step)
+            cr = gibbs.cut_batch(vis[s0:s1], wgt[s0:s1], channel_ind, ndelay, prior[s0:s1], time_frac=self.time_frac,
+                                 freq_frac=self.freq_frac, remove_mean=self.remove_mean, scale_freq=self.scale_freq,
+                                 weight_boost=self.weight_boost, window=self._window(),
+                                 complex_timedomain=self.complex_timedomain, global_id=gids[s0:s1], handle=handle)
+            if mask_out is not None:
+                mask_out[s0:s1][~cr.alive] = 1
+            if cr.batch is None:
+                continue
+            res = gibbs.run_batch(cr.batch, self.nsamp, handle=handle, seed=seed, median_frac=self.median_frac,
+                                  save_samples=self.save_samples)
+            lbis = s0 + cr.index
+            spec_out[lbis] = res.spectrum.cpu().numpy()
+            if mask_out is not None:
+                mask_out[lbis[~res.success.cpu().numpy()]] = 1
+            if samp_out is not None:
+                samp_out[:, lbis] = res.samples.cpu().numpy()
+            self.log.debug(f"device batch of {len(lbis)} baselines: {res.timing['ms_sampler']:.1f} ms in the sampler")
+        if self.save_spectrum_mask:
+            nbase = out_cont.spectrum.global_shape[0]
             n_conv = nbase - ddist.allreduce_count(int(mask_out.sum()))  # delay.py:1182
             self.log.debug(f"{n_conv}/{nbase} unflagged baselines.")
         return out_cont

@@ -128,6 +128,97 @@ def pack_uniform(vis, weight, fsel, N, S0, window="nuttall", complex_timedomain=
     )
 
 
+@dataclasses.dataclass
+class CutResult:
+    """Outcome of :func:`cut_batch`: ``batch`` holds the surviving baselines (device resident), ``index`` their
+    positions in the raw slab; ``alive``/``keep_t``/``keep_f`` are host arrays over the whole slab."""
+
+    batch: PackedBatch | None
+    index: np.ndarray  # int64 [B_alive]
+    alive: np.ndarray  # bool [B]
+    keep_t: np.ndarray  # bool [B, T]
+    keep_f: np.ndarray  # bool [B, nfreq]
+
+
+def cut_batch(vis, weight, channel_ind, N, S0, *, time_frac=-1.0, freq_frac=-1.0, remove_mean=False, scale_freq=False,
+              weight_boost=1.0, window="nuttall", complex_timedomain=False, global_id=None, handle: Handle | None = None,
+              device=0) -> CutResult:
+    """``DelayTransformBase._cut_data`` (delay.py:516-597) for a whole raw slab on the GPU, packed in place as
+    the ragged batch :func:`run_batch` / :func:`wiener_batch` consume (replaces the loop delay.py:1146-1167).
+
+    ``vis`` [B, T, nfreq] complex128 and ``weight`` [B, T, nfreq] float32/float64 (numpy, or CUDA torch tensors with
+    ``vis`` viewed as float64 [..., 2]); ``channel_ind`` [nfreq]; ``S0`` broadcastable to [B, N].  Weights are
+    always averaged over the kept samples (``use_average_weights=True``)."""
+    import torch
+
+    h = handle or get_handle(device)
+    dev = torch.device("cuda", h.device if hasattr(h, "device") else device)
+
+    def to_dev(a, dtype=None):
+        if isinstance(a, np.ndarray):
+            if a.dtype == np.complex128:
+                a = np.ascontiguousarray(a).view(np.float64)
+            elif dtype is not None:
+                a = np.ascontiguousarray(a, dtype=dtype)
+            else:
+                a = np.ascontiguousarray(a)
+            return torch.from_numpy(a).to(dev, non_blocking=True)
+        return a.contiguous()
+
+    if isinstance(vis, np.ndarray):
+        vis = np.asarray(vis, dtype=np.complex128)
+        B, T, F = vis.shape
+    else:
+        B, T, F = vis.shape[:3]
+    if isinstance(weight, np.ndarray) and weight.dtype not in (np.float32, np.float64):
+        weight = weight.astype(np.float64)
+    d_vis, d_w = to_dev(vis), to_dev(weight)
+    if tuple(d_w.shape) != (B, T, F):
+        raise ValueError(f"weight shape {tuple(d_w.shape)} does not match the data {(B, T, F)}")
+    w32 = d_w.dtype == torch.float32
+    if not w32 and d_w.dtype != torch.float64:
+        raise ValueError("weight must be float32 or float64")
+    d_cind = to_dev(np.asarray(channel_ind, dtype=np.int64))
+    d_out = torch.empty((B, T * F, 2), dtype=torch.float64, device=dev)
+    d_Ni = torch.empty((B, F), dtype=torch.float64, device=dev)
+    d_fsel = torch.empty((B, F), dtype=torch.int64, device=dev)
+    d_T = torch.empty(B, dtype=torch.int32, device=dev)
+    d_M = torch.empty(B, dtype=torch.int32, device=dev)
+    d_alive = torch.empty(B, dtype=torch.uint8, device=dev)
+    d_kt = torch.zeros((B, T), dtype=torch.uint8, device=dev)
+    d_kf = torch.zeros((B, F), dtype=torch.uint8, device=dev)
+    c = _lib.Cut()
+    c.struct_size = C.sizeof(_lib.Cut)
+    c.on_device = 1
+    c.B, c.T, c.nfreq = B, T, F
+    c.weight_f32 = 1 if w32 else 0
+    c.remove_mean, c.scale_freq = int(bool(remove_mean)), int(bool(scale_freq))
+    c.time_frac, c.freq_frac, c.weight_boost = float(time_frac), float(freq_frac), float(weight_boost)
+    c.data, c.weight, c.channel_ind = _ptr(d_vis), _ptr(d_w), _ptr(d_cind)
+    c.data_out, c.Ni_out, c.fsel_out = _ptr(d_out), _ptr(d_Ni), _ptr(d_fsel)
+    c.T_out, c.M_out, c.alive, c.keep_t, c.keep_f = _ptr(d_T), _ptr(d_M), _ptr(d_alive), _ptr(d_kt), _ptr(d_kf)
+    torch.cuda.current_stream(dev).synchronize()  # the uploads above ran on torch's stream
+    h.check(h.lib.dgibbs_cut_data(h._h, C.byref(c)), "dgibbs_cut_data")
+    alive = d_alive.cpu().numpy().astype(bool)
+    Tk, Mk = d_T.cpu().numpy(), d_M.cpu().numpy()
+    keep_t, keep_f = d_kt.cpu().numpy().astype(bool), d_kf.cpu().numpy().astype(bool)
+    index = np.flatnonzero(alive).astype(np.int64)
+    if index.size == 0:
+        return CutResult(None, index, alive, keep_t, keep_f)
+    data_off = np.concatenate([index * (T * F), [B * T * F]]).astype(np.int64)
+    chan_off = np.concatenate([index * F, [B * F]]).astype(np.int64)
+    S0 = np.ascontiguousarray(np.broadcast_to(np.asarray(S0, dtype=np.float64), (B, N))[index])
+    gid = index if global_id is None else np.ascontiguousarray(np.asarray(global_id, dtype=np.int64)[index])
+
+    def up(a):
+        return torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+
+    pb = PackedBatch(int(N), up(Tk[index]), up(Mk[index]), up(data_off), up(chan_off), d_out.view(-1), d_Ni.view(-1),
+                     d_fsel.view(-1), up(S0), up(gid), bool(complex_timedomain), window)
+    return CutResult(pb, index, alive, keep_t, keep_f)
+
+
+
 def _problem(pb: PackedBatch, niter, rng_mode, seed, median_frac, draws=None, force_branch=0):
     p = _lib.Problem()
     p.struct_size = C.sizeof(_lib.Problem)

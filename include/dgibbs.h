@@ -88,7 +88,7 @@ typedef struct {
   double median_frac;         /* spectrum = median of the last int(niter*median_frac) samples */
   const int32_t* T;           /* [B] samples per baseline */
   const int32_t* M;           /* [B] retained channels per baseline */
-  const int64_t* data_off;    /* [B+1] */
+  const int64_t* data_off;    /* [B+1] start of each (T[b], M[b]) block; gaps allowed, no overlap */
   const int64_t* chan_off;    /* [B+1] */
   const void* data;           /* complex128 */
   const double* Ni;
@@ -226,6 +226,46 @@ typedef struct {
 
 int dgibbs_cross_run(dgibbs_handle h, const dgibbs_cross_problem* p, void* samples, int32_t* n_done,
                      uint8_t* success);
+
+/* ---------------------------------------------------------------------------------------------
+ * Device-side time / frequency cuts.  Replaces the per-baseline Python loop around
+ * DelayTransformBase._cut_data (draco/analysis/delay.py:516-597, called from delay.py:1146-1167) for a whole
+ * raw slab [B, T, nfreq]: non_zero_time / non_zero_freq masks from the fraction of positive weights
+ * (time_frac, freq_frac), compaction, mean removal over the kept samples, the optional scale_freq
+ * normalisation, the time-averaged weights (use_average_weights=True, the only mode the samplers accept,
+ * delay.py:1697) times weight_boost, and the three "skip this baseline" exits (alive[b] = 0).
+ *
+ * Output layout = the ragged batch of dgibbs_problem in fixed slots: baseline b's kept block (T_out[b],
+ * M_out[b]) row-major starts at data_out + b*T*nfreq; its averaged weights and channel indices
+ * (channel_ind of the kept frequencies) start at Ni_out / fsel_out + b*nfreq.  With on_device = 1 the outputs
+ * feed dgibbs_run in place: data_off[i] = b_i*T*nfreq, chan_off[i] = b_i*nfreq over the alive baselines b_i
+ * (offsets may leave gaps, they must not overlap).
+ * Masks, counts and channel lists are exact; data and weights are bit-identical to numpy's (sequential sums
+ * over the time axis) except under scale_freq, whose all-element std is equal to rounding. */
+typedef struct {
+  int32_t struct_size;
+  int32_t on_device;   /* 1: every pointer below is a device pointer; 0: host pointers */
+  int32_t B, T, nfreq; /* raw slab shape */
+  int32_t weight_f32;  /* element type of weight: 1 = float32, 0 = float64 */
+  int32_t remove_mean; /* delay.py:570-574 */
+  int32_t scale_freq;  /* delay.py:580-587 */
+  double time_frac;    /* delay.py:552 */
+  double freq_frac;    /* delay.py:560 */
+  double weight_boost; /* delay.py:593 */
+  const void* data;           /* [B, T, nfreq] complex128 */
+  const void* weight;         /* [B, T, nfreq] */
+  const int64_t* channel_ind; /* [nfreq] channel of each input frequency on the padded grid (delay.py:461-512) */
+  void* data_out;    /* [B, T*nfreq] complex128 */
+  double* Ni_out;    /* [B, nfreq] */
+  int64_t* fsel_out; /* [B, nfreq] */
+  int32_t* T_out;    /* [B] kept samples (0 for a skipped baseline) */
+  int32_t* M_out;    /* [B] kept frequencies */
+  uint8_t* alive;    /* [B] 0 = _cut_data returned None */
+  uint8_t* keep_t;   /* [B, T] non_zero_time; may be NULL */
+  uint8_t* keep_f;   /* [B, nfreq] non_zero_freq; may be NULL */
+} dgibbs_cut;
+
+int dgibbs_cut_data(dgibbs_handle h, const dgibbs_cut* c);
 
 #ifdef __cplusplus
 }

@@ -1,0 +1,128 @@
+"""Device-side ``_cut_data`` (``dgibbs_cut_data``) against the reference's golden vectors and
+the numpy oracle (``oracle.cut_data`` = delay.py:516-597, itself pinned on the same golden vectors)."""
+
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+HERE = os.path.dirname(__file__)
+TAGS = [("default", {}), ("timefrac", dict(time_frac=0.3)), ("freqfrac", dict(freq_frac=0.85)),
+        ("nomean", dict(remove_mean=False)), ("scale", dict(scale_freq=True, weight_boost=2.5))]
+
+
+@pytest.fixture(scope="module")
+def golden():
+    return np.load(os.path.join(HERE, "golden", "reference_delay.npz"))
+
+
+def _unpack(cr, n, T, F):
+    """Host copies of the n-th surviving baseline of a CutResult: (data[Tb, Mb], Ni[Mb], fsel[Mb])."""
+    pb = cr.batch
+    Tb, Mb = int(pb.T[n]), int(pb.M[n])
+    do, co = int(pb.data_off[n]), int(pb.chan_off[n])
+    d = pb.data.view(-1, 2)[do : do + Tb * Mb].cpu().numpy().view(np.complex128).reshape(Tb, Mb)
+    return d, pb.Ni[co : co + Mb].cpu().numpy(), pb.fsel[co : co + Mb].cpu().numpy()
+
+
+def test_cut_matches_reference_golden(golden):
+    from draco_b200 import gibbs
+
+    vis, wgt = golden["cut_vis"], golden["cut_wgt"]
+    T, F = vis.shape
+    cind = np.arange(F) * 2 + 1  # any injective channel map
+    for tag, kw in TAGS:
+        full = dict(time_frac=0.0, freq_frac=0.0, remove_mean=True, scale_freq=False, weight_boost=1.0)
+        full.update(kw)
+        cr = gibbs.cut_batch(vis[None], wgt[None], cind, 2 * F, 1.0, **full)
+        assert cr.alive.tolist() == [True]
+        assert np.array_equal(cr.keep_t[0], golden[f"cut_{tag}_nzt"])
+        assert np.array_equal(cr.keep_f[0], golden[f"cut_{tag}_nzf"])
+        d, ni, fs = _unpack(cr, 0, T, F)
+        assert np.array_equal(fs, cind[golden[f"cut_{tag}_nzf"]])
+        if tag == "scale":  # numpy's all-element std is a pairwise sum: equal to rounding
+            np.testing.assert_allclose(d, golden[f"cut_{tag}_data"], rtol=1e-13, atol=0)
+        else:
+            assert np.array_equal(d, golden[f"cut_{tag}_data"])
+        assert np.array_equal(ni, golden[f"cut_{tag}_weight"])
+    # the three "return None" exits (delay.py:545, 564, 577)
+    assert not gibbs.cut_batch(vis[None], np.zeros_like(wgt)[None], cind, 2 * F, 1.0, time_frac=0.0, freq_frac=0.0).alive[0]
+    assert not gibbs.cut_batch(np.zeros_like(vis)[None], wgt[None], cind, 2 * F, 1.0, time_frac=0.0, freq_frac=0.0).alive[0]
+    assert not gibbs.cut_batch(vis[None], wgt[None], cind, 2 * F, 1.0, time_frac=0.0, freq_frac=1.0).alive[0]
+
+
+@pytest.mark.parametrize("wdtype", [np.float64, np.float32])
+@pytest.mark.parametrize("kw", [dict(remove_mean=True), dict(remove_mean=False, time_frac=0.4, freq_frac=0.3),
+                                dict(remove_mean=True, scale_freq=True, weight_boost=1e3, time_frac=0.2)])
+def test_cut_matches_oracle_ragged(wdtype, kw):
+    import oracle
+    from draco_b200 import gibbs
+
+    rng = np.random.default_rng(5)
+    B, T, F = 41, 19, 300
+    vis = rng.standard_normal((B, T, F)) + 1j * rng.standard_normal((B, T, F))
+    wgt = rng.uniform(0.5, 2.0, (B, T, F)).astype(wdtype)
+    wgt[rng.random((B, T, F)) < 0.15] = 0.0
+    for b in range(B):  # whole channels / samples flagged, differently per baseline
+        wgt[b, :, rng.choice(F, size=rng.integers(0, F // 2), replace=False)] = 0.0
+        wgt[b, rng.choice(T, size=rng.integers(0, T // 2), replace=False), :] = 0.0
+    wgt[3] = 0.0  # dead: no weight
+    vis[7] = 0.0  # dead with remove_mean=False: all-zero data (constant data dies with remove_mean=True)
+    vis[8] = 2.5 - 1j
+    wgt[9] = -1.0  # negative weights count as flagged
+    vis[wgt <= 0] = 0.0
+    cind = np.sort(rng.choice(2 * F, size=F, replace=False))
+    full = dict(time_frac=0.0, freq_frac=0.0, scale_freq=False, weight_boost=1.0)
+    full.update(kw)
+    cr = gibbs.cut_batch(vis, wgt, cind, 4 * F, 1.0, **full)
+    n = 0
+    for b in range(B):
+        t = oracle.cut_data(vis[b].copy(), wgt[b].copy(), use_average_weights=True, **full)
+        assert (t is not None) == bool(cr.alive[b]), b
+        if t is None:
+            continue
+        d, w, nzf, nzt = t
+        assert cr.index[n] == b
+        assert np.array_equal(cr.keep_t[b], nzt) and np.array_equal(cr.keep_f[b], nzf)
+        dd, ni, fs = _unpack(cr, n, T, F)
+        assert dd.shape == d.shape
+        assert np.array_equal(fs, cind[nzf])
+        if full["scale_freq"]:
+            np.testing.assert_allclose(dd, d, rtol=1e-12, atol=0)
+        else:  # numpy reduces the (time-contiguous) columns pairwise; the kernel implements the same algorithm
+            assert np.array_equal(dd, d), b
+        assert np.array_equal(ni, np.asarray(w, dtype=np.float64)), b
+        n += 1
+    assert n == len(cr.index) and n >= B - 6
+
+
+def test_cut_feeds_sampler_in_place():
+    """dgibbs_cut_data -> dgibbs_run without a host round trip gives the chains of the host-cut batch bit for bit."""
+    import oracle
+    from draco_b200 import gibbs
+
+    rng = np.random.default_rng(11)
+    B, T, F, N = 9, 12, 33, 64
+    vis = rng.standard_normal((B, T, F)) + 1j * rng.standard_normal((B, T, F))
+    wgt = rng.uniform(0.5, 2.0, (B, T, F))
+    wgt[:, :, [4, 5, 20]] = 0.0
+    wgt[2] = 0.0
+    wgt[5, 3:7] = 0.0
+    vis[wgt == 0] = 0.0
+    cind = np.arange(F)
+    cr = gibbs.cut_batch(vis, wgt, cind, N, 10.0, time_frac=0.0, freq_frac=0.0, remove_mean=True)
+    assert cr.alive.sum() == B - 1
+    res = gibbs.run_batch(cr.batch, 12, seed=77, save_samples=True)
+    datas, Nis, fsels = [], [], []
+    for b in cr.index:
+        d, w, nzf, _ = oracle.cut_data(vis[b].copy(), wgt[b].copy())
+        datas.append(d)
+        Nis.append(np.asarray(w, dtype=np.float64))
+        fsels.append(cind[nzf])
+    pb = gibbs.pack_batch(datas, Nis, fsels, N, 10.0, global_id=cr.index)
+    ref = gibbs.run_batch(pb, 12, seed=77, save_samples=True)
+    assert np.array_equal(res.samples.cpu().numpy(), ref.samples)
+    assert np.array_equal(res.spectrum.cpu().numpy(), ref.spectrum)
+    assert bool(res.success.all())

@@ -123,3 +123,20 @@ def test_wiener_filter_task():
     it = delay.DelaySpectrumWienerFilterIteratePS.from_config(dict(sample_axis="ra"))
     out2 = it.process(ss, dps)
     np.testing.assert_allclose(out2.spectrum[:].local_array[0], out.spectrum[:].local_array[0], rtol=1e-12)
+
+
+def test_gibbs_task_device_cut_matches_host_cut():
+    """``device_cut`` (dgibbs_cut_data) changes where ``_cut_data`` runs, not one bit of the result."""
+    from draco_b200 import delay
+
+    ss, _, _ = _stream()
+    cfg = dict(sample_axis="ra", nsamp=8, seed=5, save_samples=True, save_spectrum_mask=True, time_frac=0.01,
+               weight_boost=3.0)
+    a = delay.DelayPowerSpectrumGibbs.from_config({**cfg, "device_cut": True}).process(ss)
+    b = delay.DelayPowerSpectrumGibbs.from_config({**cfg, "device_cut": False}).process(ss)
+    c = delay.DelayPowerSpectrumGibbs.from_config({**cfg, "device_cut": True, "batch_baselines": 4}).process(ss)
+    for x in (b, c):
+        assert np.array_equal(a.spectrum[:].local_array, x.spectrum[:].local_array)
+        assert np.array_equal(a.datasets["spectrum_samples"][:].local_array, x.datasets["spectrum_samples"][:].local_array)
+        assert np.array_equal(a.datasets["spectrum_mask"][:].local_array, x.datasets["spectrum_mask"][:].local_array)
+    assert a.datasets["spectrum_mask"][:].local_array[4] and np.all(a.spectrum[:].local_array[0] > 0)
