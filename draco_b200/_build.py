@@ -13,6 +13,10 @@ import subprocess
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libdgibbs.so")
+# NRML likelihood object: separate library because it links cuBLAS / cuSOLVER
+NRML_LIB = os.path.join(HERE, "libdgnrml.so")
+NRML_SOURCES = ["nrml.cu"]
+NRML_HEADERS = [os.path.join("..", "..", "include", "dgnrml.h")]
 SOURCES = ["dgibbs_api.cu", "setup_kernels.cu", "sampler_dense.cu", "sampler_diag.cu", "sampler_cross.cu", "sampler_freq.cu", "project_fft.cu", "cut_kernels.cu", "finish_kernels.cu"]
 HEADERS = ["common.cuh", "internal.h", "dense_core.cuh", os.path.join("..", "..", "include", "dgibbs.h")]
 NVCC_FLAGS = [
@@ -61,8 +65,25 @@ def build(force=False, verbose=False):
         out, _ = p.communicate()
         if p.returncode != 0:
             raise RuntimeError("nvcc failed: " + " ".join(cmd) + "\n" + out.decode())
+    nobjs = []
+    for src in NRML_SOURCES:
+        s = os.path.join(CSRC, src)
+        o = os.path.join(objdir, src.replace(".cu", ".o"))
+        nobjs.append(o)
+        if force or _stale(o, [s, *[os.path.join(CSRC, h) for h in NRML_HEADERS]]):
+            cmd = [nvcc, *NVCC_FLAGS, "-c", s, "-o", o]
+            if verbose:
+                print(" ".join(cmd))
+            procs.append((cmd, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT)))
+    for cmd, p in procs:
+        out, _ = p.communicate()
+        if p.returncode != 0:
+            raise RuntimeError("nvcc failed: " + " ".join(cmd) + "\n" + out.decode())
     if force or procs or _stale(LIB, objs):
         cmd = [nvcc, "-shared", "-o", LIB, *objs]
+        subprocess.run(cmd, check=True)
+    if force or procs or _stale(NRML_LIB, nobjs):
+        cmd = [nvcc, "-shared", "-o", NRML_LIB, *nobjs, "-lcublas", "-lcusolver"]
         subprocess.run(cmd, check=True)
     return LIB
 

@@ -428,6 +428,51 @@ class DelayPowerSpectrumGibbs(DelayPowerSpectrumBase, _RandomTask):
         return out_cont
 
 
+class DelayPowerSpectrumNRML(DelayPowerSpectrumBase):
+    """NRML / maximum-posterior estimate of the delay power spectrum (delay.py:1270-1301): the spectrum is the last
+    iterate of ``delay_power_spectrum_maxpost`` (delayopt.py:424-561).  The per-baseline loop and scipy's Newton-CG
+    stay on the host as in the reference (delay.py:1146-1178); every likelihood / gradient / Hessian evaluation runs
+    on the GPU (``draco_b200.delayopt.LogLikePS`` -> ``libdgnrml.so``)."""
+
+    maxpost_tol = config.Property(proptype=float, default=1e-3)
+
+    def _get_prior(self, nbase, ndelay, dtype):
+        return [None] * nbase
+
+    def _estimator(self, data, weight, S, ndelay, channel_ind):
+        from . import delayopt
+
+        samples, success = delayopt.delay_power_spectrum_maxpost(
+            data, ndelay, weight, S, window=self.window if self.apply_window else None, fsel=channel_ind,
+            maxiter=self.nsamp, tol=self.maxpost_tol, device=self._device())
+        return np.fft.fftshift(samples[-1]), samples, success
+
+    def _evaluate(self, data_view, weight_view, out_cont, delays, channel_ind):
+        from . import dist as ddist
+
+        nbase = out_cont.spectrum.global_shape[0]
+        ndelay = len(delays)
+        prior = self._get_prior(nbase, ndelay, delays.dtype)
+        spec_out = _local(out_cont.spectrum)
+        mask_out = _local(out_cont.datasets["spectrum_mask"]) if self.save_spectrum_mask else None
+        samp_out = _local(out_cont.datasets["spectrum_samples"]) if self.save_samples else None
+        for lbi, bi, data, weight, fsel, _nzt in self._cut_all(data_view, weight_view, out_cont, channel_ind):
+            spec, samples, success = self._estimator(data, np.asarray(weight, dtype=np.float64), prior[lbi], ndelay, fsel)
+            spec_out[lbi] = spec
+            if mask_out is not None and not success:
+                mask_out[lbi] = 1
+            if samp_out is not None:
+                # delay.py:1175-1178; a run that uses all `nsamp` iterations returns nsamp + 1 iterates (the start
+                # included), which the reference cannot store (broadcast error): keep the last `nsamp` of them
+                arr = np.array(samples)[-samp_out.shape[0]:]
+                samp_out[:, lbi] = 0.0
+                samp_out[-len(arr):, lbi] = arr
+        if self.save_spectrum_mask:
+            n_conv = nbase - ddist.allreduce_count(int(mask_out.sum()))  # delay.py:1182
+            self.log.debug(f"{n_conv}/{nbase} unflagged baselines.")
+        return out_cont
+
+
 class DelayCrossPowerSpectrumEstimator(DelayPowerSpectrumGibbs):
     """Delay cross power spectrum of several compatible ``FreqContainer`` inputs (delay.py:1304-1447):
     ``process(sslist)`` returns a ``DelayCrossSpectrum`` with the pair-wise cross spectra.  Every local

@@ -99,7 +99,27 @@ def load():
     def calculate_delays(params, freq):
         return ns["_calculate_delays"](types.SimpleNamespace(**params), FreqContainer(freq))
 
+    # draco/analysis/delayopt.py (the NRML / maximum-posterior estimator) with draco/util/kernels.py: both pure
+    # numpy/scipy.  `from ..util import kernels, tools` and the late `from .delay import fourier_matrix`
+    # (delayopt.py:472) are resolved through stand-in modules holding the objects loaded above.
+    import sys
+
+    kern_ns = {"__name__": "draco_reference_kernels"}
+    exec(compile(_lines("draco/util/kernels.py", 1, 10**6), "draco/util/kernels.py", "exec"), kern_ns)
+    kernels = types.SimpleNamespace(**{k: v for k, v in kern_ns.items() if callable(v)})
+    pkg, util, ana = (types.ModuleType(n) for n in ("_dref", "_dref.util", "_dref.analysis"))
+    dmod = types.ModuleType("_dref.analysis.delay")
+    dmod.fourier_matrix = ns["fourier_matrix"]
+    util.kernels, util.tools = kernels, tools
+    pkg.util, pkg.analysis, ana.delay = util, ana, dmod
+    saved = {k: sys.modules.get(k) for k in ("_dref", "_dref.util", "_dref.analysis", "_dref.analysis.delay")}
+    sys.modules.update({"_dref": pkg, "_dref.util": util, "_dref.analysis": ana, "_dref.analysis.delay": dmod})
+    opt_ns = {"__name__": "_dref.analysis.delayopt", "__package__": "_dref.analysis"}
+    exec(compile(_lines("draco/analysis/delayopt.py", 1, 10**6), "draco/analysis/delayopt.py", "exec"), opt_ns)
+
     out = types.SimpleNamespace(**{k: v for k, v in ns.items() if callable(v)})
+    out.delayopt = types.SimpleNamespace(**{k: v for k, v in opt_ns.items() if callable(v)})
+    out.kernels = kernels
     out.cut_data = cut_data
     out.calculate_delays = calculate_delays
     out.window_generalised = tools.window_generalised

@@ -64,3 +64,23 @@ def test_product_does_not_import_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h")):
                 src = open(os.path.join(dirpath, f)).read()
                 assert not re.search(r"^\s*(from|import)\s+oracle", src, flags=re.M), f
+
+
+def test_nrml_library_exports_header_symbols(lib):
+    """libdgnrml.so exports everything include/dgnrml.h declares and fails loudly without a GPU."""
+    import numpy as np
+    import torch
+
+    from draco_b200 import _lib, delayopt
+
+    hdr = open(os.path.join(ROOT, "include", "dgnrml.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    names = sorted(set(re.findall(r"\b(dgnrml_[a-z_]+)\s*\(", hdr)))
+    nl = delayopt.load_nrml()
+    assert names == sorted(delayopt.NRML_EXPORTED)
+    for n in names:
+        assert hasattr(nl, n), f"{n} declared in include/dgnrml.h but not exported"
+    assert lib.dgibbs_sizeof(4) == C.sizeof(_lib.Cut)
+    if not torch.cuda.is_available():
+        with pytest.raises(_lib.DGibbsError):
+            delayopt.LogLikePS(np.eye(3, dtype=complex), np.ones((3, 4), dtype=complex), np.ones(3), 5)
