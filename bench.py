@@ -210,7 +210,7 @@ def hbm_roofline(nbytes, ms):
     src = "MEASURED_PEAKS.json hbm_gbs (of measured)" if "hbm_gbs" in peaks else "6650 GB/s (of fallback)"
     ach = nbytes / (ms / 1e3) / 1e9 if ms > 0 else 0.0
     return {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
-            "peak_source": src, "kernel": "diag_sampler_kernel",
+            "peak_source": src, "kernel": "diag_resident_kernel (cluster-resident; diag_sampler_kernel when a slice does not fit)",
             "byte_model": "Q_d = 8 n T + 16 N bytes per baseline-iteration (read projected data once, read+write S)"}
 
 
@@ -333,9 +333,9 @@ def main():
     if rank == 0:
         ach = flop / (max(ms_sampler, 1e-9) / 1e3) / 1e12
         if n_diag > 0:
-            # diagonal(+rank-1) branch: streaming kernel, HBM-bound (SURVEY 8d Q_d = 8 n T + 16 N per baseline-iteration)
+            # diagonal(+rank-1) branch: cluster-resident kernel, judged against the HBM stream of its algorithmic bytes (SURVEY 8d Q_d = 8 n T + 16 N per baseline-iteration)
             roof = hbm_roofline(nbytes, ms_diag)
-            branch = f"diagonal(+rank-1) streaming sampler ({n_diag} of {nbase} baselines)"
+            branch = f"diagonal(+rank-1) cluster-resident sampler ({n_diag} of {nbase} baselines)"
         else:
             roof = {"bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
                     "traffic": (DENSE_TRAFFIC_PER_UNIT * nbase * nsamp) if cfg.ndelay == 2048 else None,

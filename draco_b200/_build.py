@@ -61,10 +61,6 @@ def build(force=False, verbose=False):
             if verbose:
                 print(" ".join(cmd))
             procs.append((cmd, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT)))
-    for cmd, p in procs:
-        out, _ = p.communicate()
-        if p.returncode != 0:
-            raise RuntimeError("nvcc failed: " + " ".join(cmd) + "\n" + out.decode())
     nobjs = []
     for src in NRML_SOURCES:
         s = os.path.join(CSRC, src)

@@ -372,13 +372,14 @@ __device__ __forceinline__ double2 cmul(double2 a, double2 b) {
   return make_double2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x);
 }
 // Inverse (sign +) DFT of x[0:N) (N = 2^m >= 8); returns the buffer that holds the result (x or y).
-// All threads of the CTA must call it; the inputs must be visible (caller synchronises before).
+// All NT threads of the CTA must call it; the inputs must be visible (caller synchronises before).
+template <int NT = THREADS>
 static __device__ double2* fft_inverse_smem(double2* x, double2* y, const double2* tw, int N) {
   int Ns = 1;
   const int quarter = N >> 2;
   while (Ns * 4 <= N) {
     const int s = N / (4 * Ns);
-    for (int j = threadIdx.x; j < quarter; j += THREADS) {
+    for (int j = threadIdx.x; j < quarter; j += NT) {
       const int k = j & (Ns - 1);
       double2 v0 = x[j], v1 = x[j + quarter], v2 = x[j + 2 * quarter], v3 = x[j + 3 * quarter];
       if (Ns > 1) {
@@ -400,7 +401,7 @@ static __device__ double2* fft_inverse_smem(double2* x, double2* y, const double
   }
   if (Ns < N) {  // Ns == N/2: one radix-2 stage, twiddle stride 1
     const int half = N >> 1;
-    for (int j = threadIdx.x; j < half; j += THREADS) {
+    for (int j = threadIdx.x; j < half; j += NT) {
       const double2 v0 = x[j], v1 = cmul(x[j + half], tw[j]);
       y[j] = make_double2(v0.x + v1.x, v0.y + v1.y);
       y[j + half] = make_double2(v0.x - v1.x, v0.y - v1.y);

@@ -141,6 +141,7 @@ __global__ void __launch_bounds__(THREADS) setup_baseline_kernel(DevBatch d, con
     const double w = ci >= 0 ? s_w[i] : 0.0, fre = ci >= 0 ? s_re[i] : 0.0, fim = ci >= 0 ? s_im[i] : 0.0;
     const double2* src = d.data + doff + (ci >= 0 ? ci : 0);
     double* dst = zT + 2 * i;
+#pragma unroll 4
     for (int t = 0; t < d.Tmax; t++) {
       double2 z = make_double2(0.0, 0.0);
       if (t < Tb && ci >= 0) {
