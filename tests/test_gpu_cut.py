@@ -126,3 +126,43 @@ def test_cut_feeds_sampler_in_place():
     assert np.array_equal(res.samples.cpu().numpy(), ref.samples)
     assert np.array_equal(res.spectrum.cpu().numpy(), ref.spectrum)
     assert bool(res.success.all())
+
+
+def test_cut_host_pointers_through_the_c_abi():
+    """``on_device = 0``: the library stages the raw slab itself and copies every output back (plain C callers)."""
+    import ctypes as C
+
+    import oracle
+    from draco_b200 import _lib, gibbs
+
+    rng = np.random.default_rng(2)
+    B, T, F = 5, 9, 40
+    vis = np.ascontiguousarray(rng.standard_normal((B, T, F)) + 1j * rng.standard_normal((B, T, F)))
+    wgt = rng.uniform(0.5, 2.0, (B, T, F)).astype(np.float32)
+    wgt[:, :, 7] = 0.0
+    wgt[1, 4] = 0.0
+    wgt[3] = 0.0
+    cind = np.arange(F, dtype=np.int64) + 3
+    out = np.zeros((B, T * F), dtype=np.complex128)
+    Ni, fsel = np.zeros((B, F)), np.zeros((B, F), dtype=np.int64)
+    Tk, Mk = np.zeros(B, dtype=np.int32), np.zeros(B, dtype=np.int32)
+    alive, kt, kf = np.zeros(B, dtype=np.uint8), np.zeros((B, T), dtype=np.uint8), np.zeros((B, F), dtype=np.uint8)
+    c = _lib.Cut()
+    c.struct_size = C.sizeof(_lib.Cut)
+    c.on_device, c.B, c.T, c.nfreq, c.weight_f32, c.remove_mean, c.scale_freq = 0, B, T, F, 1, 1, 0
+    c.time_frac, c.freq_frac, c.weight_boost = 0.0, 0.0, 2.0
+    for name, a in (("data", vis), ("weight", wgt), ("channel_ind", cind), ("data_out", out), ("Ni_out", Ni), ("fsel_out", fsel),
+                    ("T_out", Tk), ("M_out", Mk), ("alive", alive), ("keep_t", kt), ("keep_f", kf)):
+        setattr(c, name, a.ctypes.data)
+    h = gibbs.get_handle(0)
+    h.check(h.lib.dgibbs_cut_data(h._h, C.byref(c)), "dgibbs_cut_data")
+    assert alive.tolist() == [1, 1, 1, 0, 1]
+    for b in (0, 1, 2, 4):
+        d, w, nzf, nzt = oracle.cut_data(vis[b].copy(), wgt[b].copy(), weight_boost=2.0)
+        assert (Tk[b], Mk[b]) == d.shape
+        assert np.array_equal(out[b, : d.size].reshape(d.shape), d)
+        assert np.array_equal(Ni[b, : Mk[b]], w.astype(np.float64))
+        assert np.array_equal(fsel[b, : Mk[b]], cind[nzf])
+        assert np.array_equal(kt[b].astype(bool), nzt) and np.array_equal(kf[b].astype(bool), nzf)
+    c.struct_size = 8
+    assert h.lib.dgibbs_cut_data(h._h, C.byref(c)) < 0  # bad struct size is refused

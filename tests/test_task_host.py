@@ -33,6 +33,14 @@ def test_parameter_names_and_defaults():
         delay.DelayPowerSpectrumGibbs.from_config(dict(no_such_parameter=1))
 
 
+def test_nrml_task_parameters():
+    t = delay.DelayPowerSpectrumNRML()
+    assert t.maxpost_tol == 1e-3 and t._get_prior(3, 8, float) == [None, None, None]  # delay.py:1279-1283
+    for k, v in REFERENCE_DEFAULTS.items():
+        if hasattr(t, k):
+            assert getattr(t, k) == v, k
+
+
 def test_legacy_names():
     assert delay.DelayPowerSpectrumStochasticEstimator is delay.DelayPowerSpectrumGibbs
     assert delay.DelaySpectrumEstimator is delay.DelayPowerSpectrumGibbs
