@@ -491,6 +491,7 @@ __global__ void __launch_bounds__(MAXT, 1) diag_resident_kernel(DevBatch d, int 
         syy += v * v;
       }
     }
+    const int nwc = min(W, (Tb + 31) >> 5);  // warps that own a sample index t < Tb (thread t forms corr_t)
     const double sfac = d.cplx ? 2.0 : 1.0, inv_a = 1.0 / a, inv_T = 1.0 / (double)Tb;  // delay.py:1794
     double iv = 0.0;
     // A: D = a + 1/S on the owned column; per-warp partials of q = sum 1/D and of the non-positive count
@@ -507,13 +508,11 @@ __global__ void __launch_bounds__(MAXT, 1) diag_resident_kernel(DevBatch d, int 
       }
       if (tid < ncol) wsm[tid] = sg * iv;
 #pragma unroll
-      for (int o = 16; o > 0; o >>= 1) {
-        ql += __shfl_xor_sync(0xffffffffu, ql, o);
-        badl += __shfl_xor_sync(0xffffffffu, badl, o);
-      }
+      for (int o = 16; o > 0; o >>= 1) ql += __shfl_xor_sync(0xffffffffu, ql, o);
+      const bool anybad = __any_sync(0xffffffffu, badl != 0.0);
       if (lane == 0) {
         qw[warp] = ql;
-        qw[32 + warp] = badl;
+        qw[32 + warp] = anybad ? 1.0 : 0.0;
       }
     };
     stage_A();
@@ -588,24 +587,26 @@ __global__ void __launch_bounds__(MAXT, 1) diag_resident_kernel(DevBatch d, int 
         break;
       }
       if (bc != 0.0) {
-        const double beta = bc / den, sb = sqrt(-beta);
-        double scl = 0.0, sccl = 0.0;
-        for (int t = tid; t < Tb; t += blockDim.x) {
-          double P = 0.0;
-          for (int r = 0; r < C; r++) P += xb[(size_t)r * XQp + t];
-          const double cv = -beta * P + sb * xi[(it & 1) * Tm + t];
-          corr[t] = cv;
-          scl += cv;
-          sccl += cv * cv;
-        }
+        if (warp < nwc) {  // only the warps that hold a sample t < Tb form corr_t and its partial sums
+          const double beta = bc / den, sb = sqrt(-beta);
+          double scl = 0.0, sccl = 0.0;
+          for (int t = tid; t < Tb; t += blockDim.x) {
+            double P = 0.0;
+            for (int r = 0; r < C; r++) P += xb[(size_t)r * XQp + t];
+            const double cv = -beta * P + sb * xi[(it & 1) * Tm + t];
+            corr[t] = cv;
+            scl += cv;
+            sccl += cv * cv;
+          }
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-          scl += __shfl_xor_sync(0xffffffffu, scl, o);
-          sccl += __shfl_xor_sync(0xffffffffu, sccl, o);
-        }
-        if (lane == 0) {
-          scw[warp] = scl;
-          scw[32 + warp] = sccl;
+          for (int o = 16; o > 0; o >>= 1) {
+            scl += __shfl_xor_sync(0xffffffffu, scl, o);
+            sccl += __shfl_xor_sync(0xffffffffu, sccl, o);
+          }
+          if (lane == 0) {
+            scw[warp] = scl;
+            scw[32 + warp] = sccl;
+          }
         }
         __syncthreads();
       }
@@ -615,7 +616,7 @@ __global__ void __launch_bounds__(MAXT, 1) diag_resident_kernel(DevBatch d, int 
       if (owner) {
         double r0 = 0.0, r1 = 0.0, sc = 0.0, scc = 0.0;
         if (bc != 0.0) {
-          for (int w = 0; w < W; w++) {
+          for (int w = 0; w < nwc; w++) {
             sc += scw[w];
             scc += scw[32 + w];
           }
