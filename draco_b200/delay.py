@@ -596,27 +596,57 @@ class DelaySpectrumWienerFilter(DelaySpectrumBase):
                                                complex_timedomain=self.complex_timedomain, device=self._device())
         return np.fft.fftshift(y, axes=-1)
 
+    device_cut = config.Property(proptype=bool, default=True)
+
     def _evaluate(self, data_view, weight_view, out_cont, delays, channel_ind):
         nbase = out_cont.spectrum.global_shape[0]
         ndelay = len(delays)
         prior = self._get_prior(nbase)
         spec_out = _local(out_cont.spectrum)
         mask_out = _local(out_cont.datasets["spectrum_mask"]) if self.save_spectrum_mask else None
-        jobs = self._cut_all(data_view, weight_view, out_cont, channel_ind)
         handle = gibbs.get_handle(self._device())
+        window = self.window if self.apply_window else None
+
+        def store(lbi, bi, y, ok, nzt):
+            if not ok:
+                raise np.linalg.LinAlgError(f"Wiener covariance of baseline {bi} is not positive definite")
+            y = y.view(np.complex128) if self.complex_timedomain else y
+            spec_out[lbi, nzt] = np.fft.fftshift(y, axes=-1)
+            if mask_out is not None:
+                mask_out[lbi][~nzt] = 1
+
+        if self.device_cut and self.use_average_weights:
+            # _cut_data on the device for the whole local slab (dgibbs_cut_data); the batch stays in HBM
+            vis = np.ascontiguousarray(_local_array(data_view))
+            wgt = np.ascontiguousarray(_local_array(weight_view))
+            gids = np.array([bi for _, bi in out_cont.spectrum[:].enumerate(axis=0)], dtype=np.int64)
+            nloc = vis.shape[0]
+            step = self.batch_baselines if self.batch_baselines and self.batch_baselines > 0 else max(1, nloc)
+            for s0 in range(0, nloc, step):
+                s1 = min(nloc, s0 + step)
+                S = np.fft.fftshift(np.asarray(prior[s0:s1]), axes=-1)
+                cr = gibbs.cut_batch(vis[s0:s1], wgt[s0:s1], channel_ind, ndelay, S, time_frac=self.time_frac,
+                                     freq_frac=self.freq_frac, remove_mean=self.remove_mean, scale_freq=self.scale_freq,
+                                     weight_boost=self.weight_boost, window=window,
+                                     complex_timedomain=self.complex_timedomain, global_id=gids[s0:s1], handle=handle)
+                if mask_out is not None and self.save_spectrum_mask:
+                    for lb in np.flatnonzero(~cr.alive):
+                        mask_out[s0 + lb] = 1  # delay.py:1160-1162 (a skipped baseline flags all its samples)
+                if cr.batch is None:
+                    continue
+                ys, ok = gibbs.wiener_batch(cr.batch, handle=handle)
+                for n, lb in enumerate(cr.index):
+                    store(s0 + lb, gids[s0 + lb], ys[n], ok[n], cr.keep_t[lb])
+            return out_cont
+        jobs = self._cut_all(data_view, weight_view, out_cont, channel_ind)
         for chunk in self._chunks(jobs):
             S = np.stack([np.fft.fftshift(prior[j[0]]) for j in chunk])
             pb = gibbs.pack_batch([j[2] for j in chunk], [np.asarray(j[3], dtype=np.float64) for j in chunk],
-                                  [j[4] for j in chunk], ndelay, S, window=self.window if self.apply_window else None,
+                                  [j[4] for j in chunk], ndelay, S, window=window,
                                   complex_timedomain=self.complex_timedomain)
             ys, ok = gibbs.wiener_batch(pb, handle=handle)
             for n, (lbi, bi, _d, _w, _f, nzt) in enumerate(chunk):
-                if not ok[n]:
-                    raise np.linalg.LinAlgError(f"Wiener covariance of baseline {bi} is not positive definite")
-                y = ys[n].view(np.complex128) if self.complex_timedomain else ys[n]
-                spec_out[lbi, nzt] = np.fft.fftshift(y, axes=-1)
-                if mask_out is not None:
-                    mask_out[lbi][~nzt] = 1
+                store(lbi, bi, ys[n], ok[n], nzt)
         return out_cont
 
 

@@ -399,20 +399,31 @@ def delay_spectrum_wiener_filter(delay_PS, data, N, Ni, window="nuttall", fsel=N
 
 
 def wiener_batch(pb: PackedBatch, *, handle: Handle | None = None):
-    """Wiener-filter every baseline of a (host) packed batch; returns a list of (T_b, n_sys)
-    arrays and a success flag per baseline."""
-    if pb.on_device:
-        raise NotImplementedError("wiener_batch takes host batches")
-    h = handle or get_handle(0)
+    """Wiener-filter every baseline of a packed batch (host arrays, or the device-resident batch
+    :func:`cut_batch` leaves behind); returns a list of (T_b, n_sys) host arrays and a success flag per baseline."""
     n_sys = (2 if pb.complex_timedomain else 1) * int(pb.N)
-    out = np.empty(int(pb.T.astype(np.int64).sum()) * n_sys, dtype=np.float64)
-    ok = np.empty(pb.B, dtype=np.uint8)
-    p, _ = _problem(pb, 1, RNG_ZERO, 0, 0.5)
-    h.check(h.lib.dgibbs_wiener(h._h, C.byref(p), out.ctypes.data, ok.ctypes.data), "dgibbs_wiener")
+    p, keep = _problem(pb, 1, RNG_ZERO, 0, 0.5)
+    if pb.on_device:
+        import torch
+
+        dev = pb.data.device
+        h = handle or get_handle(dev.index or 0)
+        Ts = pb.T.cpu().numpy()
+        d_out = torch.empty(int(Ts.astype(np.int64).sum()) * n_sys, dtype=torch.float64, device=dev)
+        d_ok = torch.empty(pb.B, dtype=torch.uint8, device=dev)
+        h.check(h.lib.dgibbs_wiener(h._h, C.byref(p), _ptr(d_out), _ptr(d_ok)), "dgibbs_wiener")
+        out, ok = d_out.cpu().numpy(), d_ok.cpu().numpy()
+    else:
+        h = handle or get_handle(0)
+        Ts = np.asarray(pb.T)
+        out = np.empty(int(Ts.astype(np.int64).sum()) * n_sys, dtype=np.float64)
+        ok = np.empty(pb.B, dtype=np.uint8)
+        h.check(h.lib.dgibbs_wiener(h._h, C.byref(p), out.ctypes.data, ok.ctypes.data), "dgibbs_wiener")
+    del keep
     res, o = [], 0
     for b in range(pb.B):
-        n = int(pb.T[b]) * n_sys
-        res.append(out[o : o + n].reshape(int(pb.T[b]), n_sys))
+        n = int(Ts[b]) * n_sys
+        res.append(out[o : o + n].reshape(int(Ts[b]), n_sys))
         o += n
     return res, ok.astype(bool)
 

@@ -140,3 +140,19 @@ def test_gibbs_task_device_cut_matches_host_cut():
         assert np.array_equal(a.datasets["spectrum_samples"][:].local_array, x.datasets["spectrum_samples"][:].local_array)
         assert np.array_equal(a.datasets["spectrum_mask"][:].local_array, x.datasets["spectrum_mask"][:].local_array)
     assert a.datasets["spectrum_mask"][:].local_array[4] and np.all(a.spectrum[:].local_array[0] > 0)
+
+
+def test_wiener_task_device_cut_matches_host_cut():
+    from draco_b200 import delay
+
+    ss, _, _ = _stream(dead=(4,))
+    dps = delay.DelayPowerSpectrumGibbs.from_config(dict(sample_axis="ra", nsamp=6, seed=3)).process(ss)
+    outs = []
+    for kw in (dict(device_cut=True), dict(device_cut=False), dict(device_cut=True, batch_baselines=4)):
+        task = delay.DelaySpectrumWienerFilter.from_config(dict(sample_axis="ra", save_spectrum_mask=True, time_frac=0.01, **kw))
+        task.setup(dps)
+        outs.append(task.process(ss))
+    for x in outs[1:]:
+        assert np.array_equal(outs[0].spectrum[:].local_array, x.spectrum[:].local_array)
+        assert np.array_equal(outs[0].datasets["spectrum_mask"][:].local_array, x.datasets["spectrum_mask"][:].local_array)
+    assert np.abs(outs[0].spectrum[:].local_array[0]).max() > 0
