@@ -147,6 +147,34 @@ __global__ void hessian_kernel(const zc* __restrict__ G, const zc* __restrict__ 
   }
 }
 
+// rows of Z (M x T, column-major) scaled by the pseudo-inverse spectrum: 1 / lambda_i above the cut, else 0
+__global__ void scale_rows_pinv_kernel(zc* __restrict__ Z, const double* __restrict__ lam, int M, int T, double cut) {
+  const size_t n = (size_t)M * T;
+  for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < n; e += (size_t)gridDim.x * blockDim.x) {
+    const double l = lam[e % M];
+    const double f = l > cut ? 1.0 / l : 0.0;
+    Z[e] = make_cuDoubleComplex(Z[e].x * f, Z[e].y * f);
+  }
+}
+
+// var over the T columns of Z (N x T, column-major): out[n] = mean_t |z_nt - mean_t z_nt|^2
+__global__ void var_cols_kernel(const zc* __restrict__ Z, int N, int T, double* __restrict__ out) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= N) return;
+  double sr = 0.0, si = 0.0;
+  for (int t = 0; t < T; t++) {
+    sr += Z[(size_t)t * N + n].x;
+    si += Z[(size_t)t * N + n].y;
+  }
+  const double mr = sr / T, mi = si / T;
+  double v = 0.0;
+  for (int t = 0; t < T; t++) {
+    const double dx = Z[(size_t)t * N + n].x - mr, dy = Z[(size_t)t * N + n].y - mi;
+    v += dx * dx + dy * dy;
+  }
+  out[n] = v / T;
+}
+
 }  // namespace
 
 struct dgnrml_s {
@@ -313,6 +341,57 @@ extern "C" int dgnrml_eval(dgnrml s, const double* x, int32_t what, double* valu
   cudaEventElapsedTime(&ms, s->ev0, s->ev1);
   s->last_ms = ms;
   s->last_flop = flop;
+  return 0;
+}
+
+// Starting point of the optimiser, delayopt.py:505-506: (data @ pinv(MF^T, rtol)).var(axis=0).  With the Hermitian
+// eigendecomposition MF MF^H = V diag(lambda) V^H the pseudo-inverse is pinv(MF^T) = conj(V) diag(1/lambda) V^T conj(MF)
+// over the eigenvalues above (rtol sigma_max)^2 = rtol^2 lambda_max, and the variance does not see the conjugation:
+// three small GEMMs after one ZHERK + ZHEEVD instead of an SVD of the N x M matrix on the host.
+extern "C" int dgnrml_initial_guess(dgnrml s, const void* data, int32_t T, double rtol, double* S0) {
+  if (!s) return -1;
+  if (!data || T <= 0 || !S0 || !(rtol >= 0.0)) return -2;
+  NCU(cudaSetDevice(s->device));
+  Libs& L = g_libs[s->device];
+  NBL(cublasSetStream(L.blas, s->stream));
+  NBL(cusolverDnSetStream(L.solver, s->stream));
+  const int M = s->M, N = s->N;
+  const zc one = make_cuDoubleComplex(1.0, 0.0), zero = make_cuDoubleComplex(0.0, 0.0);
+  const double done = 1.0, dzero = 0.0;
+  zc *V = s->CiX, *D = nullptr, *Z1 = nullptr, *Z2 = nullptr, *Z3 = nullptr, *work = nullptr;
+  double* lam = nullptr;
+  int lwork = 0, info = 0;
+  auto cleanup = [&]() {
+    for (void* p : {(void*)D, (void*)Z1, (void*)Z2, (void*)Z3, (void*)work, (void*)lam})
+      if (p) cudaFree(p);
+  };
+  NCU(cudaMalloc(&D, (size_t)M * T * 16)); NCU(cudaMalloc(&Z1, (size_t)M * T * 16)); NCU(cudaMalloc(&Z2, (size_t)M * T * 16));
+  NCU(cudaMalloc(&Z3, (size_t)N * T * 16)); NCU(cudaMalloc(&lam, (size_t)M * 8));
+  // row-major data [T, M] is column-major [M, T]: column t = sample t
+  NCU(cudaMemcpyAsync(D, data, (size_t)M * T * 16, cudaMemcpyHostToDevice, s->stream));
+  NBL(cublasZherk(L.blas, CUBLAS_FILL_MODE_LOWER, CUBLAS_OP_N, M, N, &done, s->MF, M, &dzero, V, M));
+  NBL(cusolverDnZheevd_bufferSize(L.solver, CUSOLVER_EIG_MODE_VECTOR, CUBLAS_FILL_MODE_LOWER, M, V, M, lam, &lwork));
+  NCU(cudaMalloc(&work, (size_t)(lwork > 0 ? lwork : 1) * 16));
+  NBL(cusolverDnZheevd(L.solver, CUSOLVER_EIG_MODE_VECTOR, CUBLAS_FILL_MODE_LOWER, M, V, M, lam, work, lwork, s->info));
+  NCU(cudaMemcpyAsync(&info, s->info, sizeof(int), cudaMemcpyDeviceToHost, s->stream));
+  double lmax = 0.0;  // eigenvalues ascend
+  NCU(cudaMemcpyAsync(&lmax, lam + (M - 1), 8, cudaMemcpyDeviceToHost, s->stream));
+  NCU(cudaStreamSynchronize(s->stream));
+  if (info != 0) {
+    cleanup();
+    s->err = "eigendecomposition for the pseudo-inverse start did not converge (info " + std::to_string(info) + ")";
+    return 1;
+  }
+  NBL(cublasZgemm(L.blas, CUBLAS_OP_C, CUBLAS_OP_N, M, T, M, &one, V, M, D, M, &zero, Z1, M));       // V^H D
+  scale_rows_pinv_kernel<<<256, 256, 0, s->stream>>>(Z1, lam, M, T, rtol * rtol * lmax);
+  NBL(cublasZgemm(L.blas, CUBLAS_OP_N, CUBLAS_OP_N, M, T, M, &one, V, M, Z1, M, &zero, Z2, M));      // V (.)
+  NBL(cublasZgemm(L.blas, CUBLAS_OP_C, CUBLAS_OP_N, N, T, M, &one, s->MF, M, Z2, M, &zero, Z3, N));  // MF^H (.)
+  var_cols_kernel<<<(N + 127) / 128, 128, 0, s->stream>>>(Z3, N, T, s->sq);
+  NCU(cudaMemcpyAsync(S0, s->sq, (size_t)N * 8, cudaMemcpyDeviceToHost, s->stream));
+  NCU(cudaGetLastError());
+  NCU(cudaStreamSynchronize(s->stream));
+  cleanup();
+  s->factored = false;  // CiX / sq were used as scratch
   return 0;
 }
 

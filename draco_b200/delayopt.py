@@ -24,7 +24,8 @@ from . import _lib as _glib
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 NRML_LIB_PATH = os.path.join(HERE, "libdgnrml.so")
-NRML_EXPORTED = ["dgnrml_create", "dgnrml_eval", "dgnrml_destroy", "dgnrml_last_error", "dgnrml_last_timing"]
+NRML_EXPORTED = ["dgnrml_create", "dgnrml_eval", "dgnrml_initial_guess", "dgnrml_destroy", "dgnrml_last_error",
+                 "dgnrml_last_timing"]
 VALUE, GRADIENT, HESSIAN = 1, 2, 4
 
 _nlib = None
@@ -46,7 +47,8 @@ def load_nrml():
     lib.dgnrml_last_error.argtypes = [_vp]
     lib.dgnrml_last_error.restype = C.c_char_p
     lib.dgnrml_last_timing.argtypes = [_vp, C.POINTER(C.c_double), C.POINTER(C.c_double)]
-    for n in ("dgnrml_create", "dgnrml_eval", "dgnrml_destroy", "dgnrml_last_timing"):
+    lib.dgnrml_initial_guess.argtypes = [_vp, _vp, C.c_int32, C.c_double, _vp]
+    for n in ("dgnrml_create", "dgnrml_eval", "dgnrml_initial_guess", "dgnrml_destroy", "dgnrml_last_timing"):
         getattr(lib, n).restype = C.c_int
     _nlib = lib
     return lib
@@ -93,6 +95,7 @@ class LogLikePS:
     def __init__(self, X, MF, N, nsamp, fsel=None, exact_hessian=True, bounds=(1e-10, 1e10), *, device=0):
         if fsel is None:
             fsel = (MF != 0).any(axis=1)
+        self._rows = fsel
         self.X = np.ascontiguousarray(X[fsel][:, fsel], dtype=np.complex128)
         self.N = np.ascontiguousarray(N[fsel], dtype=np.float64)
         self.MF = np.ascontiguousarray(MF[fsel], dtype=np.complex128)
@@ -134,6 +137,20 @@ class LogLikePS:
         self.evals += 1
         return val.value, g, H
 
+    def initial_guess(self, data, rtol=1e-3):
+        """``(data @ la.pinv(MF.T, rtol=rtol)).var(axis=0)`` (delayopt.py:505-506) on the device; ``data`` [T, M] are
+        the windowed samples of the channels this object keeps."""
+        data = np.ascontiguousarray(data, dtype=np.complex128)
+        if data.ndim != 2 or data.shape[1] != self.MF.shape[0]:
+            raise ValueError(f"data must be [T, {self.MF.shape[0]}], got {data.shape}")
+        S0 = np.empty(self._ndelay)
+        rc = self._lib.dgnrml_initial_guess(self._h, data.ctypes.data, data.shape[0], float(rtol), S0.ctypes.data)
+        if rc == 1:
+            raise la.LinAlgError(self._lib.dgnrml_last_error(self._h).decode())
+        if rc != 0:
+            raise _glib.DGibbsError(f"dgnrml_initial_guess failed ({rc}): {self._lib.dgnrml_last_error(self._h).decode()}")
+        return S0
+
     def value(self, x):
         return self._eval(x, VALUE)[0]
 
@@ -172,14 +189,26 @@ def matern_kernel(N, width, alpha, nu):
     return Cm
 
 
+_prior_cache: dict = {}
+_fourier_cache: dict = {}
+
+
 class GaussianProcessPrior:
-    """Gaussian-process prior on the parameters (delayopt.py:239-355); the Matern kernel the estimator uses."""
+    """Gaussian-process prior on the parameters (delayopt.py:239-355); the Matern kernel the estimator uses.
+    The inverse covariance depends only on the constructor arguments, so it is kept between baselines (the reference
+    rebuilds and inverts the N x N kernel for every baseline, delayopt.py:518-523)."""
 
     def __init__(self, N, *, width=5, alpha=1, kernel="matern", reg=1e-8, nu=1.5):
         if kernel != "matern":
             raise ValueError("only the 'matern' kernel of delay_power_spectrum_maxpost is implemented")
-        Cm = matern_kernel(int(N), int(width), 1.0, nu)
-        self.Ci = la.inv(Cm + np.identity(N) * reg) / alpha**2
+        key = (int(N), int(width), float(alpha), float(reg), float(nu))
+        if key not in _prior_cache:
+            _prior_cache.clear()
+            Cm = matern_kernel(int(N), int(width), 1.0, nu)
+            Ci = la.inv(Cm + np.identity(N) * reg) / alpha**2
+            Ci.setflags(write=False)
+            _prior_cache[key] = Ci
+        self.Ci = _prior_cache[key]
 
     def value(self, x):
         return 0.5 * float(x @ (self.Ci @ x))
@@ -216,17 +245,23 @@ class AddFunctions:
 
 
 def delay_power_spectrum_maxpost(data, N, Ni, initial_S=None, window="nuttall", fsel=None, maxiter=100, tol=1e-3,
-                                 bounds=(1e-15, 1e10), *, device=0, stats=None):
+                                 bounds=(1e-15, 1e10), *, device=0, stats=None, host_pinv=False):
     """Maximum-posterior delay power spectrum (delayopt.py:424-561): ``(samples, success)``.
 
-    ``stats`` (optional dict) receives the device time, flop and number of likelihood evaluations."""
+    ``stats`` (optional dict) receives the device time, flop and number of likelihood evaluations.  The
+    pseudo-inverse starting point (delayopt.py:505-506) is computed on the device from a Hermitian
+    eigendecomposition unless ``host_pinv`` asks for scipy's SVD-based ``la.pinv`` as in the reference."""
     nsamp, Nf = data.shape
     if fsel is None:
         fsel = np.arange(Nf)
     elif len(fsel) != Nf:
         raise ValueError(f"Length of frequency selection must match frequencies passed. {len(fsel)} != {data.shape[-1]}")
     fsel = np.asarray(fsel)
-    F = np.exp(-2.0j * np.pi * np.arange(N)[np.newaxis, :] * fsel[:, np.newaxis] / N)  # fourier_matrix, delay.py:1588-1613
+    fkey = (int(N), fsel.tobytes())
+    if fkey not in _fourier_cache:  # consecutive baselines usually share their channel selection
+        _fourier_cache.clear()
+        _fourier_cache[fkey] = np.exp(-2.0j * np.pi * np.arange(N)[np.newaxis, :] * fsel[:, np.newaxis] / N)
+    F = _fourier_cache[fkey].copy()  # fourier_matrix, delay.py:1588-1613
     data = np.array(data, dtype=np.complex128, copy=True)
     if window is not None:
         w = window_generalised(fsel / N, window=window)
@@ -235,10 +270,12 @@ def delay_power_spectrum_maxpost(data, N, Ni, initial_S=None, window="nuttall", 
     X = (data.T @ data.conj()) / nsamp
     Nm = _invert_no_zero(Ni)
     F[np.asarray(Ni) == 0] = 0.0
-    if initial_S is None:
+    if initial_S is None and host_pinv:
         initial_S = (data @ la.pinv(F.T, rtol=1e-3)).var(axis=0)
-    samples = [initial_S]
     like = LogLikePS(X, F, Nm, nsamp, exact_hessian=True, bounds=bounds, device=device)
+    if initial_S is None:
+        initial_S = like.initial_guess(data[:, like._rows], rtol=1e-3)  # masked channels have zero rows in F
+    samples = [initial_S]
     optfunc = AddFunctions([like, GaussianProcessPrior(N, width=5, alpha=1.0, kernel="matern", nu=1.5)])
     try:
         res = minimize(optfunc.value, x0=np.log(initial_S), jac=optfunc.gradient, hess=optfunc.hessian, method="Newton-CG",

@@ -39,6 +39,11 @@ int dgnrml_create(int32_t device_id, int32_t M, int32_t N, int32_t nsamp, int32_
  * may be NULL when not requested).  Repeated calls with the same x reuse the factorisation (delayopt.py:134). */
 int dgnrml_eval(dgnrml s, const double* x, int32_t what, double* value, double* gradient, double* hessian);
 
+/* Starting point of the optimiser, delayopt.py:505-506: S0 [N] = (data @ pinv(MF^T, rtol)).var(axis=0) with data [T, M]
+ * the windowed samples (host, row-major complex128, the channels MF keeps).  Returns 1 if the eigendecomposition
+ * behind the pseudo-inverse fails. */
+int dgnrml_initial_guess(dgnrml s, const void* data, int32_t T, double rtol, double* S0);
+
 int dgnrml_destroy(dgnrml s);
 const char* dgnrml_last_error(dgnrml s);
 /* milliseconds spent on the device by the last dgnrml_eval (CUDA events) and its algorithmic fp64 flop */

@@ -62,6 +62,22 @@ def test_device_objective_matches_oracle_midsize():
     dev.close()
 
 
+@pytest.mark.parametrize("window", ["nuttall", None])
+def test_device_pinv_start_matches_scipy(window):
+    """The eigendecomposition-based starting point against the reference's SVD pseudo-inverse (delayopt.py:505-506)."""
+    from draco_b200 import delayopt
+
+    N, M, T = 256, 100, 24
+    data, Ni, fsel = make_nrml_case(N, M, T, 4, 11)
+    dataw, X, F, Nm = nrml_oracle.maxpost_inputs(data, N, Ni, window, fsel)
+    ref = (dataw @ la.pinv(F.T, rtol=1e-3)).var(axis=0)
+    like = delayopt.LogLikePS(X, F, Nm, T)
+    got = like.initial_guess(dataw[:, like._rows], rtol=1e-3)
+    np.testing.assert_allclose(got, ref, rtol=1e-8, atol=1e-10 * ref.max())
+    like.value(np.log(ref))  # the object still evaluates after its buffers served as scratch
+    like.close()
+
+
 def test_not_positive_definite_raises_linalgerror():
     from draco_b200 import delayopt
 
@@ -88,6 +104,10 @@ def test_maxpost_matches_reference_chain(golden, k):
     assert len(samples) == len(ref)
     np.testing.assert_allclose(np.array(samples), ref, rtol=1e-6)
     assert stats["evals"] > 0
+    samples_h, ok_h = delayopt.delay_power_spectrum_maxpost(data, N, Ni, None, window=window, fsel=fsel, maxiter=maxiter,
+                                                            tol=1e-3, host_pinv=True)
+    assert ok_h == ok and len(samples_h) == len(ref)
+    np.testing.assert_allclose(np.array(samples_h), ref, rtol=1e-6)
     with pytest.raises(ValueError):
         delayopt.delay_power_spectrum_maxpost(data, N, Ni, fsel=fsel[:-1])
 
