@@ -146,3 +146,25 @@ def test_streaming_kernel_vs_dense_kernel_cfg3_geometry(gibbs):
     assert np.mean(np.abs(z) < 3.0) >= 0.98 and np.max(np.abs(z)) < 5.0, (np.abs(z).max(), np.mean(np.abs(z) < 3))
     for k in range(0, N, 128):
         assert stats.ks_2samp(sa[-1, :, k], sb[-1, :, k]).pvalue > 0.01 / 16, k
+
+
+@pytest.mark.parametrize("N,T,nyquist,nb,niter", [(256, 72, True, 64, 60), (4096, 8, True, 32, 30), (128, 64, False, 64, 60)])
+def test_resident_kernel_variants_vs_dense_kernel(gibbs, N, T, nyquist, nb, niter):
+    """The other instantiations of the cluster-resident kernel -- T > 64 (no register-resident column), 512-column
+    slices (N = 4096) and b = 0 (no rank-1 term, no exchange of P) -- sample the posterior of the dense kernel."""
+    from scipy import stats
+
+    data, Ni, fsel, S0 = uniform_case(N, T, False, nyquist, seed=N + T)
+    pb = gibbs.pack_batch([data] * nb, [Ni] * nb, [fsel] * nb, N, np.full((nb, N), 10.0), window=None,
+                          global_id=np.arange(nb)).to_device(0)
+    a = gibbs.run_batch(pb, niter, seed=15, save_samples=True)
+    b = gibbs.run_batch(pb, niter, seed=16, save_samples=True, force_branch=DENSE)
+    assert bool((a.branch == DIAG).all()) and bool((b.branch == DENSE).all()) and bool(a.success.all())
+    sa = np.log(a.samples[niter // 2:].cpu().numpy())
+    sb = np.log(b.samples[niter // 2:].cpu().numpy())
+    ma, mb = sa.mean(axis=0), sb.mean(axis=0)
+    se = np.sqrt(ma.var(axis=0, ddof=1) / nb + mb.var(axis=0, ddof=1) / nb)
+    z = (ma.mean(axis=0) - mb.mean(axis=0)) / se
+    assert np.mean(np.abs(z) < 3.0) >= 0.98 and np.max(np.abs(z)) < 5.0, (np.abs(z).max(), np.mean(np.abs(z) < 3))
+    for k in range(0, N, max(1, N // 16)):
+        assert stats.ks_2samp(sa[-1, :, k], sb[-1, :, k]).pvalue > 0.01 / 16, k
