@@ -205,6 +205,19 @@ __device__ __forceinline__ void stage_acc(const Acc& acc, double* sT, const Lane
     for (int nb = 0; nb < 16; nb++) *reinterpret_cast<double2*>(row + nb * 8) = make_double2(acc[f][nb][0], acc[f][nb][1]);
   }
 }
+// stage_acc fused with add_generated for an interior tile strictly below the diagonal (real mode, no padding):
+// the entry (R, C) of circ(c) is ct[R - C] with 0 < R - C < N, added in registers on the way to shared memory
+__device__ __forceinline__ void stage_acc_circ(const Acc& acc, double* sT, const Lane& ln, const double* ct, int R0, int C0) {
+#pragma unroll
+  for (int f = 0; f < 2; f++) {
+    const int r = ln.rf[f] * 8 + ln.g;
+    double* row = sT + r * LDW + 2 * ln.q;
+    const double* cp = ct + (R0 + r) - (C0 + 2 * ln.q);
+#pragma unroll
+    for (int nb = 0; nb < 16; nb++)
+      *reinterpret_cast<double2*>(row + nb * 8) = make_double2(acc[f][nb][0] + cp[-nb * 8], acc[f][nb][1] + cp[-nb * 8 - 1]);
+  }
+}
 __device__ __forceinline__ void tile_store_global(const Acc& acc, double* base, int ld, const Lane& ln, bool do0,
                                                   bool do1) {
 #pragma unroll

@@ -203,10 +203,14 @@ __global__ void __launch_bounds__(THREADS, 1) dense_sampler_kernel(DevBatch d, i
           acc_zero(acc);
           gemm_nt(pipe, acc, ln, Wk + (size_t)i * TILE * npad, Bp, npad, j * (TILE / KC), var);
           PROF(6);
-          stage_acc(acc, pipe, ln, do0, do1);
-          __syncthreads();
-          if (i < nblk) add_generated(pipe, ct, Si, N, nsys, d.cplx, i, j, false);
-          else add_global(pipe, out, npad, nrows);
+          if (i < nblk && !d.cplx && (i + 1) * TILE <= nsys) {  // interior tile below the diagonal: generated in registers
+            stage_acc_circ(acc, pipe, ln, ct, i * TILE, j * TILE);
+          } else {
+            stage_acc(acc, pipe, ln, do0, do1);
+            __syncthreads();
+            if (i < nblk) add_generated(pipe, ct, Si, N, nsys, d.cplx, i, j, false);
+            else add_global(pipe, out, npad, nrows);
+          }
           __syncthreads();
           PROF(5);
           trisolve<false>(pipe, sWp, ln, var);
