@@ -384,40 +384,86 @@ __device__ __forceinline__ double2 tw_get(const double2* tw, int m, int N) {  //
 __device__ __forceinline__ double2 cmul(double2 a, double2 b) {
   return make_double2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x);
 }
+__device__ __forceinline__ double2 cadd(double2 a, double2 b) { return make_double2(a.x + b.x, a.y + b.y); }
+__device__ __forceinline__ double2 csub(double2 a, double2 b) { return make_double2(a.x - b.x, a.y - b.y); }
+// 4-point inverse DFT (w4 = +i) in place: (b0, b1, b2, b3) -> (X0, X1, X2, X3)
+__device__ __forceinline__ void dft4_inv(double2& b0, double2& b1, double2& b2, double2& b3) {
+  const double2 s02 = cadd(b0, b2), d02 = csub(b0, b2), s13 = cadd(b1, b3), d13 = csub(b1, b3);
+  b0 = cadd(s02, s13);
+  b1 = make_double2(d02.x - d13.y, d02.y + d13.x);  // d02 + i d13
+  b2 = csub(s02, s13);
+  b3 = make_double2(d02.x + d13.y, d02.y - d13.x);  // d02 - i d13
+}
+// The buffer written by the first radix-8 stage (element 8 j + q from thread j) and read by the second one is
+// XOR-swizzled inside every aligned group of 8 elements so that the 128-byte-strided stores of a warp spread over
+// the banks; reads of consecutive elements stay a permutation of consecutive elements.
+__device__ __forceinline__ int fft_swz(int p, bool on) { return on ? (p ^ ((p >> 3) & 7)) : p; }
+
 // Inverse (sign +) DFT of x[0:N) (N = 2^m >= 8); returns the buffer that holds the result (x or y).
+// Stockham autosort: radix-8 stages (8-point butterflies in registers: 4 passes over shared memory at N = 2048
+// instead of the 6 of a radix-4 chain), then one radix-4 or radix-2 stage; exact twiddles from the table.
 // All NT threads of the CTA must call it; the inputs must be visible (caller synchronises before).
 template <int NT = THREADS>
 static __device__ double2* fft_inverse_smem(double2* x, double2* y, const double2* tw, int N) {
   int Ns = 1;
-  const int quarter = N >> 2;
-  while (Ns * 4 <= N) {
-    const int s = N / (4 * Ns);
-    for (int j = threadIdx.x; j < quarter; j += NT) {
+  bool swz = false;  // is the current input buffer swizzled?
+  const int e8 = N >> 3;
+  while (Ns * 8 <= N) {
+    const int s = N / (8 * Ns);
+    const bool swz_out = Ns == 1 && N > 8;
+    for (int j = threadIdx.x; j < e8; j += NT) {
       const int k = j & (Ns - 1);
-      double2 v0 = x[j], v1 = x[j + quarter], v2 = x[j + 2 * quarter], v3 = x[j + 3 * quarter];
+      double2 v[8];
+#pragma unroll
+      for (int r = 0; r < 8; r++) v[r] = x[fft_swz(j + r * e8, swz)];
       if (Ns > 1) {
-        v1 = cmul(v1, tw_get(tw, k * s, N));
-        v2 = cmul(v2, tw_get(tw, 2 * k * s, N));
-        v3 = cmul(v3, tw_get(tw, 3 * k * s, N));
+        const int ks = k * s;  // r k s < N for r < 8
+#pragma unroll
+        for (int r = 1; r < 8; r++) v[r] = cmul(v[r], tw_get(tw, r * ks, N));
       }
-      const double2 a = make_double2(v0.x + v2.x, v0.y + v2.y), b = make_double2(v0.x - v2.x, v0.y - v2.y);
-      const double2 c = make_double2(v1.x + v3.x, v1.y + v3.y), e = make_double2(v1.x - v3.x, v1.y - v3.y);
-      const int j0 = ((j - k) << 2) + k;
-      y[j0] = make_double2(a.x + c.x, a.y + c.y);
-      y[j0 + Ns] = make_double2(b.x - e.y, b.y + e.x);      // b + i e
-      y[j0 + 2 * Ns] = make_double2(a.x - c.x, a.y - c.y);
-      y[j0 + 3 * Ns] = make_double2(b.x + e.y, b.y - e.x);  // b - i e
+      dft4_inv(v[0], v[2], v[4], v[6]);  // E_q
+      dft4_inv(v[1], v[3], v[5], v[7]);  // O_q
+      const double h = 0.70710678118654752440;
+      const double2 o1 = make_double2((v[3].x - v[3].y) * h, (v[3].x + v[3].y) * h);   // w8 O_1
+      const double2 o2 = make_double2(-v[5].y, v[5].x);                                  // i O_2
+      const double2 o3 = make_double2(-(v[7].x + v[7].y) * h, (v[7].x - v[7].y) * h);  // w8^3 O_3
+      const int j0 = ((j - k) << 3) + k;
+      y[fft_swz(j0, swz_out)] = cadd(v[0], v[1]);
+      y[fft_swz(j0 + Ns, swz_out)] = cadd(v[2], o1);
+      y[fft_swz(j0 + 2 * Ns, swz_out)] = cadd(v[4], o2);
+      y[fft_swz(j0 + 3 * Ns, swz_out)] = cadd(v[6], o3);
+      y[fft_swz(j0 + 4 * Ns, swz_out)] = csub(v[0], v[1]);
+      y[fft_swz(j0 + 5 * Ns, swz_out)] = csub(v[2], o1);
+      y[fft_swz(j0 + 6 * Ns, swz_out)] = csub(v[4], o2);
+      y[fft_swz(j0 + 7 * Ns, swz_out)] = csub(v[6], o3);
     }
     __syncthreads();
     double2* tmp = x; x = y; y = tmp;
-    Ns <<= 2;
+    Ns <<= 3;
+    swz = swz_out;
   }
-  if (Ns < N) {  // Ns == N/2: one radix-2 stage, twiddle stride 1
+  if (Ns * 4 == N) {  // one radix-4 stage
+    const int quarter = N >> 2, s = 1;
+    for (int j = threadIdx.x; j < quarter; j += NT) {  // k = j (Ns = N / 4)
+      double2 v0 = x[fft_swz(j, swz)], v1 = x[fft_swz(j + quarter, swz)], v2 = x[fft_swz(j + 2 * quarter, swz)],
+              v3 = x[fft_swz(j + 3 * quarter, swz)];
+      v1 = cmul(v1, tw_get(tw, j * s, N));
+      v2 = cmul(v2, tw_get(tw, 2 * j * s, N));
+      v3 = cmul(v3, tw_get(tw, 3 * j * s, N));
+      dft4_inv(v0, v1, v2, v3);
+      y[j] = v0;
+      y[j + quarter] = v1;
+      y[j + 2 * quarter] = v2;
+      y[j + 3 * quarter] = v3;
+    }
+    __syncthreads();
+    double2* tmp = x; x = y; y = tmp;
+  } else if (Ns * 2 == N) {  // one radix-2 stage, twiddle stride 1
     const int half = N >> 1;
     for (int j = threadIdx.x; j < half; j += NT) {
-      const double2 v0 = x[j], v1 = cmul(x[j + half], tw[j]);
-      y[j] = make_double2(v0.x + v1.x, v0.y + v1.y);
-      y[j + half] = make_double2(v0.x - v1.x, v0.y - v1.y);
+      const double2 v0 = x[fft_swz(j, swz)], v1 = cmul(x[fft_swz(j + half, swz)], tw[j]);
+      y[j] = cadd(v0, v1);
+      y[j + half] = csub(v0, v1);
     }
     __syncthreads();
     double2* tmp = x; x = y; y = tmp;

@@ -58,8 +58,7 @@ struct CrossBatch {
 struct CM {
   double2 a[NDMAX][NDMAX];
 };
-__device__ __forceinline__ double2 cadd(double2 a, double2 b) { return make_double2(a.x + b.x, a.y + b.y); }
-__device__ __forceinline__ double2 csub(double2 a, double2 b) { return make_double2(a.x - b.x, a.y - b.y); }
+// cadd / csub come from dense_core.cuh
 __device__ __forceinline__ double2 cmulc(double2 a, double2 b) {  // a * conj(b)
   return make_double2(a.x * b.x + a.y * b.y, a.y * b.x - a.x * b.y);
 }
