@@ -236,3 +236,17 @@ def test_full_size_properties(gibbs):
     cap = np.eye(1) - U.T @ (U / D[:, None])
     ref = Dinv_y + (U / D[:, None]) @ np.linalg.solve(cap, U.T @ Dinv_y)
     np.testing.assert_allclose(x, ref.T, rtol=1e-8, atol=1e-10 * np.abs(ref).max())
+
+
+@pytest.mark.parametrize("N,M,T", [(8192, 3000, 8), (1000, 400, 5)])
+def test_large_and_odd_sizes(gibbs, N, M, T):
+    """Sizes outside the tuned range: N = 8192 (beyond the in-smem FFT and the shared-memory circulant table: DMMA
+    projection, 64 block columns, 0.5 GB of factor workspace per slot) and an N that is neither a power of two nor a
+    multiple of the 128 tile (identity padding).  One baseline, two iterations, injected draws, against the oracle."""
+    data, Ni, fsel, S0 = make_case(N, M, T, False, True, seed=N)
+    s, ok, dr = recorded_chain(data, N, Ni, S0, "nuttall", fsel, 2, False, seed=N + 1)
+    assert ok
+    pb = gibbs.pack_batch([data], [Ni], [fsel], N, S0[None], window="nuttall")
+    res = gibbs.run_batch(pb, 2, draws=gibbs.pack_draws(pb, 2, [dr[0]], [dr[1]], [dr[2]]), save_samples=True)
+    assert bool(res.success.all())
+    np.testing.assert_allclose(res.samples[:, 0], s, rtol=RTOL_SAMPLES)
