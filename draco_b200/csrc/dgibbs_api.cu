@@ -422,7 +422,8 @@ extern "C" int dgibbs_run(dgibbs_handle h, const dgibbs_problem* p, dgibbs_resul
     CU(pool_get(h, "ycompact", sizeof(int) * d.B, &q)); d_yc = (int*)q;
     CU(cudaMemcpyAsync(d_diag, diag_list.data(), sizeof(int) * diag_list.size(), cudaMemcpyHostToDevice, h->stream));
     CU(cudaMemcpyAsync(d_yc, ycompact.data(), sizeof(int) * d.B, cudaMemcpyHostToDevice, h->stream));
-    CU(pool_get(h, "yhat", sizeof(double) * diag_list.size() * (size_t)d.Tmax * d.npad, &q));
+    d.ypitch = d.npad + 128;
+    CU(pool_get(h, "yhat", sizeof(double) * diag_list.size() * (size_t)d.Tmax * d.ypitch, &q));
     d.yhat = (double*)q;
     d.ycompact = d_yc;
   }

@@ -57,7 +57,8 @@ struct DevBatch {
   double* diag_ab;        // [B][2]  FTNiF = a I + b u u^T (u = (-1)^t) when branch == 3
   const int* blist;       // baselines this launch works on (null = all B)
   int nlist;
-  double* yhat;           // [ndiag][Tmax][npad] projected data of the diagonal-branch baselines
+  double* yhat;           // [ndiag][Tmax][ypitch] projected data of the diagonal-branch baselines (zero beyond nsys)
+  int ypitch;             // row pitch of yhat: npad + 128, so that any even column split of a cluster stays inside a row
   const int* ycompact;    // [B] row block of a baseline in yhat, or -1
 
   // shared tables

@@ -16,7 +16,7 @@ __global__ void __launch_bounds__(PTHREADS) diag_project_fft_kernel(DevBatch d, 
   extern __shared__ __align__(16) double2 fsm[];
   double2* bufA = fsm;
   double2* bufB = fsm + d.N;
-  const int N = d.N, nsys = d.nsys, npad = d.npad, nch = d.nch, Kpad = d.Kpad;
+  const int N = d.N, nsys = d.nsys, ypitch = d.ypitch, nch = d.nch, Kpad = d.Kpad;
   const int step = d.cplx ? 1 : 2;
   for (long long w = blockIdx.x; w < nwork; w += gridDim.x) {
     const int li = (int)(w / ppb), t0 = (int)(w % ppb) * step;
@@ -25,7 +25,7 @@ __global__ void __launch_bounds__(PTHREADS) diag_project_fft_kernel(DevBatch d, 
     if (t0 >= Tb || d.failed[b]) continue;  // CTA-uniform
     const double* h = d.h + (size_t)b * Kpad;
     const double* zT = d.zT + (size_t)b * d.Tmax * Kpad + (size_t)t0 * Kpad;
-    double* yo = d.yhat + ((size_t)d.ycompact[b] * d.Tmax + t0) * npad;
+    double* yo = d.yhat + ((size_t)d.ycompact[b] * d.Tmax + t0) * ypitch;
     const bool two = !d.cplx && t0 + 1 < Tb;
     __syncthreads();  // the previous epilogue is done with the buffers
     // masked / padded channels carry h = 0 and z = 0 (setup kernel), so no channel-index lookup is needed; the global
@@ -80,7 +80,7 @@ __global__ void __launch_bounds__(PTHREADS) diag_project_fft_kernel(DevBatch d, 
     __syncthreads();
     const double2* res = fft_inverse_smem<PTHREADS>(bufA, bufB, d.twtab, N);
     if (!d.cplx) {
-      for (int p = threadIdx.x; p < npad / 2; p += PTHREADS) {
+      for (int p = threadIdx.x; p < ypitch / 2; p += PTHREADS) {
         const int k = 2 * p;
         double2 ya = make_double2(0.0, 0.0), yb = ya;
         if (k < nsys) {
@@ -89,10 +89,10 @@ __global__ void __launch_bounds__(PTHREADS) diag_project_fft_kernel(DevBatch d, 
           yb = make_double2(r0.y, r1.y);
         }
         *reinterpret_cast<double2*>(yo + k) = ya;
-        if (two) *reinterpret_cast<double2*>(yo + npad + k) = yb;
+        if (two) *reinterpret_cast<double2*>(yo + ypitch + k) = yb;
       }
     } else {
-      for (int p = threadIdx.x; p < npad / 2; p += PTHREADS) {
+      for (int p = threadIdx.x; p < ypitch / 2; p += PTHREADS) {
         double2 ya = make_double2(0.0, 0.0);
         if (2 * p < nsys) ya = res[p];
         *reinterpret_cast<double2*>(yo + 2 * p) = ya;

@@ -157,10 +157,13 @@ __global__ void __launch_bounds__(THREADS, 1) dense_sampler_kernel(DevBatch d, i
       }
 
       if (d.project_only) {  // export y^T = (F^T h z)^T for the streaming diagonal kernel
-        double* yo = d.yhat + (size_t)d.ycompact[b] * d.Tmax * npad;
-        for (long long e = threadIdx.x; e < (long long)Tb * (npad / 2); e += THREADS) {
-          int t = (int)(e / (npad / 2)), k = (int)(e % (npad / 2)) * 2;
-          *reinterpret_cast<double2*>(yo + (size_t)t * npad + k) = *reinterpret_cast<const double2*>(Rh + (size_t)t * npad + k);
+        double* yo = d.yhat + (size_t)d.ycompact[b] * d.Tmax * d.ypitch;
+        const int hp = d.ypitch / 2;
+        for (long long e = threadIdx.x; e < (long long)Tb * hp; e += THREADS) {
+          int t = (int)(e / hp), k = (int)(e % hp) * 2;
+          double2 v = make_double2(0.0, 0.0);
+          if (k < npad) v = *reinterpret_cast<const double2*>(Rh + (size_t)t * npad + k);
+          *reinterpret_cast<double2*>(yo + (size_t)t * d.ypitch + k) = v;
         }
         break;
       }

@@ -101,13 +101,13 @@ template <int NPAIR, int TC>
 __global__ void __launch_bounds__(DTHREADS, 1) diag_sampler_kernel(DevBatch d, int it_begin, int it_end) {
   __shared__ double red[DWARPS * 2 * TC];
   const int tid = threadIdx.x;
-  const int N = d.N, nsys = d.nsys, npad = d.npad, npairs = nsys >> 1;
+  const int N = d.N, nsys = d.nsys, npairs = nsys >> 1;
   for (int li = blockIdx.x; li < d.nlist; li += gridDim.x) {
     const int b = d.blist[li];
     if (d.failed[b]) continue;
     const int Tb = d.T[b];
     const double a = d.diag_ab[2 * b], bc = d.diag_ab[2 * b + 1];
-    const double* yh = d.yhat + (size_t)d.ycompact[b] * d.Tmax * npad;
+    const double* yh = d.yhat + (size_t)d.ycompact[b] * d.Tmax * d.ypitch;
     double* S = d.S + (size_t)b * N;
     const Philox ph(mix_key(d.seed, d.gid ? (unsigned long long)d.gid[b] : (unsigned long long)b));
 
@@ -167,7 +167,7 @@ __global__ void __launch_bounds__(DTHREADS, 1) diag_sampler_kernel(DevBatch d, i
             for (int tt = 0; tt < TC; tt++) {
               const int t = t0 + tt;
               double2 v = make_double2(0.0, 0.0);
-              if (t < Tb) v = *reinterpret_cast<const double2*>(yh + (size_t)t * npad + 2 * p);
+              if (t < Tb) v = *reinterpret_cast<const double2*>(yh + (size_t)t * d.ypitch + 2 * p);
               y[i][0][tt] = v.x;
               y[i][1][tt] = v.y;
               pe[tt] += invD[i][0] * v.x - invD[i][1] * v.y;                                            // P_t
@@ -340,22 +340,17 @@ struct ResidentGeom {
 };
 
 // shared memory: [ysm: Tmax*ncol][wsm: ncol][corr: Tmax][xi: RBATCH*Tmax][qw: 64][scw: 64][xch: 2*C*XQp][mbar: 3]
-static ResidentGeom resident_geom(const DevBatch& d, size_t smem_cap, int maxC) {
+// Geometry of a cluster of C CTAs: an even number of columns per CTA, C * ncol >= nsys (the tail columns are the zero
+// padding of yhat rows).  C need not be a power of two: on B200 clusters of 6 keep 132 SMs busy, clusters of 8 only 120.
+static ResidentGeom resident_geom_for(const DevBatch& d, size_t smem_cap, int C) {
   ResidentGeom g{};
-  for (int C = 1; C <= maxC; C *= 2) {
-    if (d.npad % (2 * C)) continue;
-    const int ncol = d.npad / C;
-    if (ncol > 1024 || ncol % 2) continue;
-    const int nmain = (ncol + 31) / 32 * 32;
-    const int threads = nmain;
-    const int XQp = (d.Tmax + 2 + 1) & ~1;  // P_t[Tmax], q, bad
-    size_t doubles = (size_t)d.Tmax * ncol + (size_t)ncol + (size_t)corr_len(d.Tmax) + (size_t)RBATCH * d.Tmax + 128 +
-                     2 * (size_t)C * XQp + 4;
-    if (doubles * 8 <= smem_cap) {
-      g.C = C; g.ncol = ncol; g.threads = threads; g.XQp = XQp; g.smem = doubles * 8;
-      return g;
-    }
-  }
+  const int ncol = 2 * ((d.nsys + 2 * C - 1) / (2 * C));
+  if (ncol > 1024 || (long long)C * ncol > d.ypitch) return g;
+  const int XQp = (d.Tmax + 2 + 1) & ~1;  // P_t[Tmax], q, bad
+  size_t doubles = (size_t)d.Tmax * ncol + (size_t)ncol + (size_t)corr_len(d.Tmax) + (size_t)RBATCH * d.Tmax + 128 +
+                   2 * (size_t)C * XQp + 4;
+  if (doubles * 8 > smem_cap) return g;
+  g.C = C; g.ncol = ncol; g.threads = (ncol + 31) / 32 * 32; g.XQp = XQp; g.smem = doubles * 8;
   return g;
 }
 
@@ -429,7 +424,7 @@ __global__ void __launch_bounds__(MAXT, 1) diag_resident_kernel(DevBatch d, int 
   const int rank = (int)cluster.block_rank();
   const int cid = blockIdx.x / C, ncl = gridDim.x / C;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, W = blockDim.x >> 5;
-  const int N = d.N, nsys = d.nsys, npad = d.npad, Tm = d.Tmax;
+  const int N = d.N, nsys = d.nsys, Tm = d.Tmax;
   double* ysm = dsm;                                   // resident slice [Tb][ncol]
   double* wsm = ysm + (size_t)Tm * ncol;               // u_k / D_k of the local columns
   double* corr = wsm + ncol;                           // corr_t
@@ -459,7 +454,7 @@ __global__ void __launch_bounds__(MAXT, 1) diag_resident_kernel(DevBatch d, int 
     if (d.failed[b]) continue;  // uniform across the cluster (set by an earlier launch only)
     const int Tb = d.T[b];
     const double a = d.diag_ab[2 * b], bc = d.diag_ab[2 * b + 1];
-    const double* yh = d.yhat + (size_t)d.ycompact[b] * Tm * npad + col0;
+    const double* yh = d.yhat + (size_t)d.ycompact[b] * Tm * d.ypitch + col0;
     double* S = d.S + (size_t)b * N;
     const Philox ph(mix_key(d.seed, d.gid ? (unsigned long long)d.gid[b] : (unsigned long long)b));
     const unsigned dkey = (unsigned)(d.cplx ? (k >> 1) : k);  // delay index: key of the chi^2_T draw
@@ -467,7 +462,7 @@ __global__ void __launch_bounds__(MAXT, 1) diag_resident_kernel(DevBatch d, int 
     // ---- the column slice of yhat becomes resident (TMA bulk copies, one per sample row)
     if (tid == 0) {
       mbar_expect_tx(mbar, (unsigned)(Tb * ncol * 8));
-      for (int t = 0; t < Tb; t++) bulk_g2s(ysm + (size_t)t * ncol, yh + (size_t)t * npad, (unsigned)(ncol * 8), mbar);
+      for (int t = 0; t < Tb; t++) bulk_g2s(ysm + (size_t)t * ncol, yh + (size_t)t * d.ypitch, (unsigned)(ncol * 8), mbar);
     }
     double Sk = owner ? S[dkey] : 0.0;
     mbar_wait(mbar, phase);
@@ -701,48 +696,90 @@ __global__ void __launch_bounds__(MAXT, 1) diag_resident_kernel(DevBatch d, int 
   cluster.sync();  // no CTA exits while a peer may still write its shared memory
 }
 
+typedef void (*ResidentKernel)(DevBatch, int, int, int, int, int);
+static ResidentKernel resident_kernel_for(const DevBatch& d, const ResidentGeom& g) {
+  static const bool no_yreg = getenv("DGIBBS_DIAG_NO_YREG") != nullptr;
+  if (g.threads <= 256) return (d.Tmax <= 64 && !no_yreg) ? diag_resident_kernel<256, 64> : diag_resident_kernel<256, 0>;
+  if (g.threads <= 384) return diag_resident_kernel<384, 0>;
+  if (g.threads <= 512) return diag_resident_kernel<512, 0>;
+  return diag_resident_kernel<1024, 0>;
+}
+
+// Cluster size: the candidate with the best modelled throughput = concurrent chains / cycles per Gibbs iteration, with
+// cycles ~ 500 + 2500 [C > 1: the DSMEM exchange] + c ncol, c = 34 / 38 / 40 cycles per column for the register-column,
+// <= 384-thread and larger instantiations (measured at cfg3 geometry: 8 x 256 columns 12.18 ms, 6 x 342 12.01 ms,
+// 5 x 410 12.22 ms, 9 x 228 13.78 ms: an SM sustains ~35 cycles per column whatever the split, so what counts is how
+// many SMs the cluster size lets the hardware fill: 132 with clusters of 6, 120 with clusters of 8).
+// DGIBBS_DIAG_CLUSTER=C forces one.
 static cudaError_t launch_resident(const DevBatch& d, int it_begin, int it_end, cudaStream_t st, bool* launched) {
   *launched = false;
-  for (int maxC = 8; maxC <= RMAXC; maxC *= 2) {
-    ResidentGeom g = resident_geom(d, 227 * 1024, maxC);
+  static const char* cap_env = getenv("DGIBBS_DIAG_SMEM_CAP_KB");  // experiment: smaller slices, more CTAs per SM
+  static const char* c_env = getenv("DGIBBS_DIAG_CLUSTER");
+  const size_t cap = (size_t)(cap_env ? atoi(cap_env) : 227) * 1024;
+  ResidentGeom best{};
+  int best_ncl = 0;
+  double best_score = -1.0;
+  for (int C = 1; C <= RMAXC; C++) {
+    if (c_env && atoi(c_env) != C) continue;
+    if (!c_env && C > 8 && best.C != 0) break;  // non-portable sizes only when no portable one fits
+    ResidentGeom g = resident_geom_for(d, cap, C);
     if (g.C == 0) continue;
-    static const bool no_yreg = getenv("DGIBBS_DIAG_NO_YREG") != nullptr;
-    auto kern = g.threads <= 256 ? ((d.Tmax <= 64 && !no_yreg) ? diag_resident_kernel<256, 64> : diag_resident_kernel<256, 0>)
-                                 : diag_resident_kernel<1024, 0>;
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g.smem);
-    if (e != cudaSuccess) return e;
-    if (g.C > 8) {
-      e = cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
-      if (e != cudaSuccess) { (void)cudaGetLastError(); return cudaSuccess; }
+    ResidentKernel kern = resident_kernel_for(d, g);
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g.smem) != cudaSuccess) {
+      (void)cudaGetLastError();
+      continue;
+    }
+    if (C > 8 && cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) {
+      (void)cudaGetLastError();
+      continue;
     }
     cudaLaunchConfig_t cfg{};
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = g.C;
+    attr[0].val.clusterDim.x = C;
     attr[0].val.clusterDim.y = 1;
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
     cfg.blockDim = dim3(g.threads);
     cfg.dynamicSmemBytes = g.smem;
-    cfg.stream = st;
-    cfg.gridDim = dim3(g.C);
+    cfg.gridDim = dim3(C);
     int ncl = 0;
-    e = cudaOccupancyMaxActiveClusters(&ncl, kern, &cfg);
-    if (e != cudaSuccess || ncl <= 0) {
+    if (cudaOccupancyMaxActiveClusters(&ncl, kern, &cfg) != cudaSuccess || ncl <= 0) {
       (void)cudaGetLastError();
-      return cudaSuccess;  // not launchable on this device: the caller falls back to the streaming kernel
+      continue;
     }
     if (ncl > d.nlist) ncl = d.nlist;
-    cfg.gridDim = dim3(ncl * g.C);
-    if (getenv("DGIBBS_VERBOSE"))
-      fprintf(stderr, "[dgibbs] resident diagonal sampler: cluster %d x %d threads, %d clusters, %zu B smem\n", g.C, g.threads,
-              ncl, g.smem);
-    e = cudaLaunchKernelEx(&cfg, kern, d, it_begin, it_end, g.C, g.ncol, g.XQp);
-    if (e == cudaSuccess) *launched = true;
-    return e;
+    const double cpc = (g.threads <= 256 && d.Tmax <= 64) ? 34.3 : (g.threads <= 384 ? 37.8 : 40.0);
+    const double score = (double)ncl / (500.0 + (C > 1 ? 2500.0 : 0.0) + cpc * g.ncol);
+    if (score > best_score) {
+      best = g;
+      best_ncl = ncl;
+      best_score = score;
+    }
   }
-  return cudaSuccess;
+  if (best.C == 0) return cudaSuccess;  // not launchable on this device: the caller falls back to the streaming kernel
+  ResidentKernel kern = resident_kernel_for(d, best);
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)best.smem);
+  if (e != cudaSuccess) return e;
+  cudaLaunchConfig_t cfg{};
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = best.C;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  cfg.blockDim = dim3(best.threads);
+  cfg.dynamicSmemBytes = best.smem;
+  cfg.stream = st;
+  cfg.gridDim = dim3(best_ncl * best.C);
+  if (getenv("DGIBBS_VERBOSE"))
+    fprintf(stderr, "[dgibbs] resident diagonal sampler: cluster %d x %d threads (%d columns), %d clusters, %zu B smem\n", best.C,
+            best.threads, best.ncol, best_ncl, best.smem);
+  e = cudaLaunchKernelEx(&cfg, kern, d, it_begin, it_end, best.C, best.ncol, best.XQp);
+  if (e == cudaSuccess) *launched = true;
+  return e;
 }
 
 cudaError_t launch_diag_sampler(const DevBatch& d, int it_begin, int it_end, int sm_count, cudaStream_t st,
