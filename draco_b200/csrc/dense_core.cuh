@@ -657,8 +657,8 @@ static __device__ bool factor_diag(double* sT, double* sWp, double* misc, const 
       for (int k = 0; k < 8; k++) {
         double dk = a[k][k];
         if (!(dk > 0.0)) ok = false;
-        double piv = sqrt(dk);
-        double r = 1.0 / piv;
+        const double r = rsqrt(dk);  // one reciprocal square root instead of sqrt + division on the serial chain
+        const double piv = dk * r;
         rinv[k] = r;
         a[k][k] = piv;
 #pragma unroll
