@@ -6,7 +6,7 @@
 namespace dg {
 
 constexpr int TILE = 128;     // block-column width and row-tile height of the factorisation
-constexpr int KC = 16;        // K chunk staged per pipeline stage
+constexpr int KC = 32;        // K chunk staged per pipeline stage (one CTA barrier per chunk: 256 DMMAs per warp between barriers)
 constexpr int THREADS = 256;  // 8 warps per CTA, one CTA per SM
 constexpr int NWARP = THREADS / 32;
 constexpr int LDA_NT = KC + 4;    // smem row pitch (doubles) of a [rows][KC] tile: conflict-free fragments

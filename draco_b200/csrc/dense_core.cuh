@@ -7,13 +7,15 @@
 
 namespace dg {
 
-constexpr int STAGES = 3;
+constexpr int STAGES = 2;  // a KC = 32 chunk is ~4 us of DMMA work: one chunk in flight covers the L2 / HBM latency
 constexpr int STAGE_DOUBLES = 2 * TILE * LDA_NT;      // A[128][20] + B[128][20]  (NN form needs less)
 constexpr int TILE_DOUBLES = TILE * LDW;              // one staged 128x128 tile, pitch 132
 constexpr int PIPE_DOUBLES = (STAGES * STAGE_DOUBLES > TILE_DOUBLES) ? STAGES * STAGE_DOUBLES : TILE_DOUBLES;
 constexpr int WP_BLOCKS = 16 * 17 / 2;                // lower-triangular 8x8 blocks of a 128x128 tile
 constexpr int WP_DOUBLES = WP_BLOCKS * 64;            // 8704 doubles = 68 KB
-constexpr int MISC_DOUBLES = 16;                      // flag + reduction scratch
+constexpr int CWIN = 2 * TILE;                        // window of the circulant column that one tile touches
+constexpr int MISC_DOUBLES = 16 + CWIN;               // flag + reduction scratch, then the circulant window
+static_assert(CWIN == THREADS, "one window entry per thread");
 static_assert(TILE * LDA_NT + KC * LDB_NN <= STAGE_DOUBLES, "NN stage must fit");
 
 typedef double Acc[2][16][2];
@@ -59,10 +61,11 @@ __device__ __forceinline__ int wp_swz(int r) { return ((r >> 1) & 1) << 2; }
 __device__ __forceinline__ void load_nt(double* stage, const double* A, const double* Bm, int ld, int k0) {
   double* sA = stage;
   double* sB = stage + TILE * LDA_NT;
+  constexpr int PPR = KC / 2;  // 16-byte pieces per row
 #pragma unroll
-  for (int r = 0; r < 4; r++) {
-    int idx = threadIdx.x + THREADS * r;  // 0..1023
-    int row = idx >> 3, c16 = idx & 7;
+  for (int r = 0; r < TILE * PPR / THREADS; r++) {
+    int idx = threadIdx.x + THREADS * r;
+    int row = idx / PPR, c16 = idx % PPR;
     cp_async16(sA + row * LDA_NT + c16 * 2, A + (size_t)row * ld + k0 + c16 * 2);
     cp_async16(sB + row * LDA_NT + c16 * 2, Bm + (size_t)row * ld + k0 + c16 * 2);
   }
@@ -71,12 +74,13 @@ __device__ __forceinline__ void load_nt(double* stage, const double* A, const do
 __device__ __forceinline__ void load_nn(double* stage, const double* A, int lda, const double* Bm, int ldb, int k0) {
   double* sA = stage;
   double* sB = stage + TILE * LDA_NT;
+  constexpr int PPR = KC / 2;
 #pragma unroll
-  for (int r = 0; r < 4; r++) {
+  for (int r = 0; r < TILE * PPR / THREADS; r++) {
     int idx = threadIdx.x + THREADS * r;
-    int row = idx >> 3, c16 = idx & 7;
+    int row = idx / PPR, c16 = idx % PPR;
     cp_async16(sA + row * LDA_NT + c16 * 2, A + (size_t)row * lda + k0 + c16 * 2);
-    int krow = idx >> 6, c = idx & 63;
+    int krow = idx >> 6, c = idx & 63;  // KC rows of 64 pieces
     cp_async16(sB + krow * LDB_NN + c * 2, Bm + (size_t)(k0 + krow) * ldb + c * 2);
   }
 }
@@ -205,17 +209,36 @@ __device__ __forceinline__ void stage_acc(const Acc& acc, double* sT, const Lane
     for (int nb = 0; nb < 16; nb++) *reinterpret_cast<double2*>(row + nb * 8) = make_double2(acc[f][nb][0], acc[f][nb][1]);
   }
 }
-// stage_acc fused with add_generated for an interior tile strictly below the diagonal (real mode, no padding):
-// the entry (R, C) of circ(c) is ct[R - C] with 0 < R - C < N, added in registers on the way to shared memory
-__device__ __forceinline__ void stage_acc_circ(const Acc& acc, double* sT, const Lane& ln, const double* ct, int R0, int C0) {
+// Interior tiles (real mode, no padding) only touch c[(ti - tj) 128 - 127 .. (ti - tj) 128 + 127] of the circulant's first
+// column: cwin[m] = c[(ti - tj) 128 - 128 + m] is fetched (one entry per thread, from L2) before the tile's GEMM and is
+// visible after the GEMM's barriers.  Entry (r, c) of the tile is cwin[128 + r - c].
+__device__ __forceinline__ void load_circ_window(double* cwin, const double* ct, int N, int dt) {
+  int k = dt * TILE - TILE + (int)threadIdx.x;
+  if (k < 0) k += N;
+  cwin[threadIdx.x] = k < N ? ct[k] : 0.0;
+}
+// stage_acc fused with add_generated for an interior tile strictly below the diagonal: the circulant entry is added in
+// registers on the way to shared memory
+__device__ __forceinline__ void stage_acc_circ(const Acc& acc, double* sT, const Lane& ln, const double* cwin) {
 #pragma unroll
   for (int f = 0; f < 2; f++) {
     const int r = ln.rf[f] * 8 + ln.g;
     double* row = sT + r * LDW + 2 * ln.q;
-    const double* cp = ct + (R0 + r) - (C0 + 2 * ln.q);
+    const double* cp = cwin + TILE + r - 2 * ln.q;
 #pragma unroll
     for (int nb = 0; nb < 16; nb++)
       *reinterpret_cast<double2*>(row + nb * 8) = make_double2(acc[f][nb][0] + cp[-nb * 8], acc[f][nb][1] + cp[-nb * 8 - 1]);
+  }
+}
+// lower triangle of an interior diagonal tile: sT += circ window + diag(Si)
+__device__ __forceinline__ void add_generated_diag_win(double* sT, const double* cwin, const double* Si, int R0) {
+#pragma unroll 2
+  for (int e = threadIdx.x; e < TILE * TILE; e += THREADS) {
+    const int r = e >> 7, c = e & 127;
+    if (c > r) continue;
+    double v = cwin[TILE + r - c];
+    if (r == c) v += Si[R0 + r];
+    sT[r * LDW + c] += v;
   }
 }
 __device__ __forceinline__ void tile_store_global(const Acc& acc, double* base, int ld, const Lane& ln, bool do0,

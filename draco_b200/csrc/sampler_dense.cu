@@ -30,6 +30,7 @@ __global__ void __launch_bounds__(THREADS, 1) dense_sampler_kernel(DevBatch d, i
   double* sWp = smem + (d.ctab_smem ? nsys : 0);
   double* pipe = sWp + WP_DOUBLES;
   double* misc = pipe + PIPE_DOUBLES;
+  double* cwin = misc + 16;  // circulant window of the current tile
 
   const size_t wrows = (size_t)npad + (size_t)RT * TILE;
   double* Wk = d.work + (size_t)slot * d.work_stride;   // L rows then RHS rows, pitch npad
@@ -174,12 +175,15 @@ __global__ void __launch_bounds__(THREADS, 1) dense_sampler_kernel(DevBatch d, i
       for (int j = 0; j < nblk && alive && !isdiag; j++) {
         const double* Bp = Wk + (size_t)j * TILE * npad;
         // diagonal tile
+        const bool interior_j = !d.cplx && (j + 1) * TILE <= nsys;
+        if (interior_j) load_circ_window(cwin, ctg, N, 0);
         acc_zero(acc);
         gemm_nt(pipe, acc, ln, Bp, Bp, npad, j * (TILE / KC), ln.warp < 4 ? V_DIAG_LO : V_DIAG_HI);
         PROF(2);
         stage_acc(acc, pipe, ln, true, true);
         __syncthreads();
-        add_generated(pipe, ct, Si, N, nsys, d.cplx, j, j, true);
+        if (interior_j) add_generated_diag_win(pipe, cwin, Si, j * TILE);
+        else add_generated(pipe, ct, Si, N, nsys, d.cplx, j, j, true);
         __syncthreads();
         alive = factor_diag(pipe, sWp, misc, ln);
         if (!alive) break;
@@ -203,11 +207,13 @@ __global__ void __launch_bounds__(THREADS, 1) dense_sampler_kernel(DevBatch d, i
             out = Rh + (size_t)rt * TILE * npad + j * TILE;
           }
           const int var = rhs_variant(do0, do1);
+          const bool interior = i < nblk && !d.cplx && (i + 1) * TILE <= nsys;
+          if (interior) load_circ_window(cwin, ctg, N, i - j);
           acc_zero(acc);
           gemm_nt(pipe, acc, ln, Wk + (size_t)i * TILE * npad, Bp, npad, j * (TILE / KC), var);
           PROF(6);
-          if (i < nblk && !d.cplx && (i + 1) * TILE <= nsys) {  // interior tile below the diagonal: generated in registers
-            stage_acc_circ(acc, pipe, ln, ct, i * TILE, j * TILE);
+          if (interior) {  // interior tile below the diagonal: generated in registers (gemm_nt ends with a barrier)
+            stage_acc_circ(acc, pipe, ln, cwin);
           } else {
             stage_acc(acc, pipe, ln, do0, do1);
             __syncthreads();
