@@ -193,11 +193,11 @@ def fp64_peak_tflops():
 
 
 # dram__bytes_read.sum + dram__bytes_write.sum of dense_sampler_kernel from the committed `ncu --set full`
-# captures profiles/r01e_dense_sampler_ncu_raw.csv (72.76 GB) and r01h_dense_sampler_ncu_raw.csv (66.67 GB read + 6.23 GB
-# written = 72.89 GB) for a launch of 296 baseline-iterations of cfg2
+# captures profiles/r01e (72.76 GB), r01h (72.89 GB) and r01i_dense_sampler_ncu_raw.csv (66.73 GB read + 6.22 GB written =
+# 72.96 GB) for a launch of 296 baseline-iterations of cfg2
 # geometry = 245.8 MB per baseline-iteration (L panels re-read from DRAM; 14 % of DRAM peak, not the bound).
 # Reported per launch of THIS run by scaling with the launch's baseline-iterations (cfg2 geometry only).
-DENSE_TRAFFIC_PER_UNIT = 72.893e9 / 296
+DENSE_TRAFFIC_PER_UNIT = 72.957e9 / 296
 
 
 def hbm_roofline(nbytes, ms):
@@ -340,7 +340,7 @@ def main():
         else:
             roof = {"bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
                     "traffic": (DENSE_TRAFFIC_PER_UNIT * nbase * nsamp) if cfg.ndelay == 2048 else None,
-                    "traffic_source": "ncu --set full capture of 296 baseline-iterations scaled to this launch (profiles/r01h_dense_sampler_ncu_raw.csv)",
+                    "traffic_source": "ncu --set full capture of 296 baseline-iterations scaled to this launch (profiles/r01i_dense_sampler_ncu_raw.csv)",
                     "peak_source": "fp64: cuBLAS DGEMM 8192^3 measured in this run (MEASURED_PEAKS.json has no fp64 entry; "
                                    "tcgen05 has no fp64 kind, DMMA pipe probe = 37.0 TFLOP/s, profiles/r01_fp64_pipe_probe.log)",
                     "kernel": "dense_sampler_kernel", "flop_model": "W_f = n^3/3 + 2 n^2 T + 4 n M T per baseline-iteration"}
