@@ -11,7 +11,8 @@ used by ``draco/analysis/delay.py:347-866, 1114-1267`` is provided:
   ``global_shape``, ``local_shape``, ``enumerate(axis)``, distributed axis 0 blocks),
 * ``Container`` / ``FreqContainer`` / ``SiderealStream`` / ``DelaySpectrum`` / ``DelayTransform`` with
   ``index_map``, ``attrs``, ``datasets``, ``axes``, dataset ``attrs['axis']`` (the output layout contract
-  of ``draco/core/containers.py:2049-2182``).
+  of ``draco/core/containers.py:2049-2182``),
+* ``RingMap`` / ``DelayTransformOperator``: the datasets ``draco/analysis/powerspec.py:118-320`` reads and writes.
 
 Distribution mirrors caput: the flattened baseline axis is split in contiguous balanced blocks,
 one per rank; ranks come from ``torch.distributed`` when it is initialised (NCCL on GPUs, gloo in
@@ -390,3 +391,93 @@ class DelayTransform(Container):
     @property
     def freq(self):
         return self.attrs["freq"]
+
+
+# --------------------------------------------------------------------------- ringmap side (powerspec.py)
+class LocalArray(np.ndarray):
+    """Single-process slice of an ``MPIArray``: ``dataset[pp]`` keeps ``.local_array`` / ``.allgather()``
+    (the two calls ``draco/analysis/powerspec.py:241, 251-252`` make on such slices)."""
+
+    @property
+    def local_array(self):
+        return np.asarray(self)
+
+    def allgather(self):
+        return np.asarray(self)
+
+
+class _SliceDataset(Dataset):
+    def __getitem__(self, key):
+        got = super().__getitem__(key)
+        return got.view(LocalArray) if isinstance(got, np.ndarray) else got
+
+
+class RingMap(FreqContainer):
+    """The datasets of ``containers.RingMap`` (draco/core/containers.py:1594-1700) the Wiener delay-transform
+    tasks read: ``map``, ``weight``, ``dirty_beam_power``, ``filter`` / ``complex_filter``,
+    ``freq_cov`` / ``complex_freq_cov``.  Single process (the elevation axis is not split)."""
+
+    _dataset_spec = {
+        "map": {"axes": ["beam", "pol", "freq", "ra", "el"], "dtype": np.float64},
+        "weight": {"axes": ["pol", "freq", "ra", "el"], "dtype": np.float64},
+        "dirty_beam_power": {"axes": ["beam", "pol", "freq", "el"], "dtype": np.float64},
+        "filter": {"axes": ["pol", "freq", "freq_sum", "ra"], "dtype": np.float64},
+        "complex_filter": {"axes": ["pol", "freq", "freq_sum", "ra"], "dtype": np.complex128},
+        "freq_cov": {"axes": ["pol", "freq", "freq_sum", "ra"], "dtype": np.float64},
+        "complex_freq_cov": {"axes": ["pol", "freq", "freq_sum", "ra"], "dtype": np.complex128},
+    }
+
+    def __init__(self, freq, ra, el, pol=("XX", "YY"), beam=1, attrs_from=None):
+        super().__init__(attrs_from=attrs_from, beam=beam, pol=np.asarray(pol), freq=freq, freq_sum=freq, ra=ra, el=el)
+        self.add_dataset("map")
+        self.add_dataset("weight")
+
+    def add_dataset(self, name):
+        spec = self._dataset_spec[name]
+        shape = [len(self.index_map[a]) for a in spec["axes"]]
+        arr = np.zeros(shape, dtype=spec["dtype"])
+        data = DistArray(arr, axis=spec["axes"].index("el")) if name in ("map", "weight") else arr
+        self.datasets[name] = _SliceDataset(data, spec["axes"])
+        return self.datasets[name]
+
+    map = property(lambda self: self.datasets["map"])
+    weight = property(lambda self: self.datasets["weight"])
+    dirty_beam_power = property(lambda self: self.datasets["dirty_beam_power"])
+
+    @property
+    def filter(self):
+        for name in ("filter", "complex_filter"):
+            if name in self.datasets:
+                return self.datasets[name]
+        raise KeyError("Dataset 'filter' not initialised.")
+
+    @property
+    def freq_cov(self):
+        for name in ("freq_cov", "complex_freq_cov"):
+            if name in self.datasets:
+                return self.datasets[name]
+        raise KeyError("Dataset 'freq_cov' not initialised.")
+
+
+class DelayTransformOperator(FreqContainer):
+    """Wiener filter that takes each pixel from frequency to delay (draco/core/containers.py:2185-2203):
+    ``filter [pol, ra, el, delay, freq]`` complex64, distributed over ``el``."""
+
+    _dataset_spec = {
+        "filter": {"axes": ["pol", "ra", "el", "delay", "freq"], "dtype": np.complex64, "distributed_axis": "el"},
+    }
+
+    def __init__(self, delay, axes_from=None, attrs_from=None, **axes):
+        for ax in ("pol", "ra", "el", "freq"):
+            if ax not in axes and axes_from is not None:
+                axes[ax] = axes_from.index_map[ax]
+        super().__init__(attrs_from=attrs_from, delay=delay, **axes)
+        self.add_dataset("filter")
+
+    @property
+    def filter(self):
+        return self.datasets["filter"]
+
+    @property
+    def delay(self):
+        return self.index_map["delay"]

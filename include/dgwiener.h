@@ -1,0 +1,63 @@
+/* dgwiener.h -- C ABI of the Wiener delay-transform operator on the GPU (part of libdgnrml.so).
+ *
+ * SURVEY 8 row f4.  Replaces the loops over polarisation / elevation / right ascension of
+ * ConstructWienerDelayTransform.process, draco/analysis/powerspec.py:229-319: for every pixel the signal + noise
+ * covariance in the masked, filtered frequency domain
+ *     A = H (F S F^H o b b^T) H^H + C o r r^T,   H = diag(M) K,
+ * its Cholesky factorisation (scipy.linalg.cho_factor / cho_solve there) and the projection
+ *     D = S (F^H H^H A^-1) window   ->  [delay, freq]
+ * that takes a filtered, masked map spectrum to delay space.  One call builds the operators of ONE polarisation
+ * (the unit over which the reference gathers the filter and the covariance, powerspec.py:251-252).  The task class
+ * (draco_b200/powerspec.py) keeps the container handling, the window, the delay axis and the prior on the host,
+ * exactly as the reference does.
+ *
+ * All pointers are HOST pointers to C-contiguous (numpy row-major) arrays owned by the caller; nothing is
+ * retained after the call returns.
+ *
+ * Return codes: 0 ok; 1 = a covariance is not positive definite (scipy raises LinAlgError there,
+ * powerspec.py:296; a failing pixel is reported through bad_el / bad_ra);
+ * <0 bad argument (its index); >1 CUDA / library error (dgwiener_last_error).
+ */
+#ifndef DGWIENER_H
+#define DGWIENER_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct {
+  int32_t device_id;
+  int32_t nfreq;            /* F: channels of the map                                        */
+  int32_t ndelay;           /* delays kept (tau >= 0), powerspec.py:214                      */
+  int32_t nra, nel;         /* pixels: right ascension, local elevations                     */
+  int32_t filter_is_complex; /* 0: filter is float64, 1: complex128 (RingMap "complex_filter") */
+  int32_t cov_is_complex;    /* 0: freq_cov is float64, 1: complex128                          */
+  int32_t solver;           /* 0 auto, 1 batched factorisation, 2 per-matrix on several streams */
+  const void* fourier;      /* [F, ndelay] complex128: exp(2 pi i freq tau) / sqrt(ntau), powerspec.py:229 */
+  const double* prior;      /* [ndelay] diagonal signal prior, powerspec.py:233              */
+  const double* window;     /* [F] spectral window (zero = channel not used), powerspec.py:207 */
+  const void* filter;       /* [nra, F, F]  K, powerspec.py:252 after its transpose          */
+  const void* freq_cov;     /* [nra, F, F]  C, powerspec.py:251                              */
+  const double* weight;     /* [nel, nra, F] map weights, powerspec.py:265                   */
+  const double* beam_power; /* [nel, F] dirty-beam power (its square root scales the prior), powerspec.py:266 */
+  void* out;                /* complex64; operator of pixel (ra, el) = [ndelay, F] block at out + 8 * (ra * out_stride_ra + el * out_stride_el) */
+  int64_t out_stride_ra, out_stride_el; /* in complex64 elements                               */
+  int64_t workspace_bytes;  /* device memory budget for one chunk of pixels (0: 8 GiB)       */
+  /* results */
+  int32_t bad_el, bad_ra;   /* a pixel whose factorisation failed (return code 1)            */
+  double ms_device;         /* CUDA-event time of the whole call on the device, copies included */
+  double ms_compute;        /* sum of the CUDA-event times of the kernels + library calls alone */
+  double flop;              /* algorithmic fp64 flop of the call (complex MAC = 8)           */
+  int64_t launches;         /* kernels + library calls launched                              */
+} dgwiener_problem;
+
+int dgwiener_construct(dgwiener_problem* p);
+int dgwiener_sizeof(void);
+const char* dgwiener_last_error(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DGWIENER_H */

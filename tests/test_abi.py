@@ -84,3 +84,26 @@ def test_nrml_library_exports_header_symbols(lib):
     if not torch.cuda.is_available():
         with pytest.raises(_lib.DGibbsError):
             delayopt.LogLikePS(np.eye(3, dtype=complex), np.ones((3, 4), dtype=complex), np.ones(3), 5)
+
+
+def test_wiener_operator_entry_points():
+    """The dgwiener_* entry points of libdgnrml.so (include/dgwiener.h): exported, struct layout agreed,
+    and a loud failure -- not a CPU fallback -- when there is no GPU."""
+    import numpy as np
+    import torch
+
+    from draco_b200 import _lib, powerspec
+
+    hdr = open(os.path.join(ROOT, "include", "dgwiener.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    names = sorted(set(re.findall(r"\b(dgwiener_[a-z_]+)\s*\(", hdr)))
+    wl = powerspec.load_wiener()
+    assert names == sorted(powerspec.WIENER_EXPORTED)
+    for n in names:
+        assert hasattr(wl, n), f"{n} declared in include/dgwiener.h but not exported"
+    assert wl.dgwiener_sizeof() == C.sizeof(powerspec.WienerProblem)
+    if not torch.cuda.is_available():
+        F = np.ones((4, 2), dtype=complex)
+        with pytest.raises(_lib.DGibbsError):
+            powerspec.wiener_delay_operator(F, np.ones(2), np.ones(4), np.eye(4)[None], np.eye(4)[None],
+                                            np.ones((1, 1, 4)), np.ones((1, 4)))

@@ -1,0 +1,111 @@
+"""Device Wiener delay-transform operator (include/dgwiener.h, draco_b200/powerspec.py) against the reference's
+golden operators (tests/golden/reference_wiener_op.npz, from powerspec.py:118-369) and against the oracle."""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+HERE = os.path.dirname(__file__)
+sys.path.insert(0, os.path.join(HERE, "golden"))
+from make_golden_wiener_op import WIENER_CASES, make_ringmap, make_wiener_case  # noqa: E402
+
+from draco_b200 import powerspec  # noqa: E402
+from oracle import wiener_op_oracle as wo  # noqa: E402
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def golden():
+    return np.load(os.path.join(HERE, "golden", "reference_wiener_op.npz"))
+
+
+def close_c64(got, ref):
+    """The container stores complex64: agreement to a few ulp of float32 relative to the operator's scale."""
+    scale = np.abs(ref).max()
+    np.testing.assert_allclose(got, ref.astype(np.complex64), rtol=2e-5, atol=2e-6 * scale)
+
+
+@pytest.mark.parametrize("k", range(len(WIENER_CASES)))
+def test_task_matches_reference_operator(golden, k):
+    """ConstructWienerDelayTransform.process, same YAML parameters, against the reference's own output."""
+    name, nfreq, nra, nel, npol, cplx, params = WIENER_CASES[k]
+    case = make_wiener_case(nfreq, nra, nel, npol, cplx, 300 + k)
+    task = powerspec.ConstructWienerDelayTransform.from_config(params)
+    op = task.process(make_ringmap(case))
+    ref = golden[f"{name}_filter"]
+    got = op.filter[:].local_array
+    assert got.dtype == np.complex64 and got.shape == ref.shape
+    assert list(op.filter.attrs["axis"]) == ["pol", "ra", "el", "delay", "freq"]
+    np.testing.assert_array_equal(op.index_map["delay"], golden[f"{name}_delay"])
+    for attr in ("window", "window_lower_freq", "window_upper_freq"):
+        assert op.attrs[attr] == params.get(attr, "uniform" if attr == "window" else None)
+    close_c64(got, ref)
+    assert not got[:, nra - 1, nel - 1].any()  # the pixel without a valid channel
+    dead = case["weight"].transpose(0, 2, 3, 1) == 0
+    assert not got[np.broadcast_to(dead[:, :, :, None, :], got.shape)].any()
+    assert all(t["launches"] > 0 for t in task.last_timing)
+
+
+def random_problem(F, nra, nel, cplx_filter, cplx_cov, seed, window="blackman"):
+    case = make_wiener_case(F, nra, nel, 1, True, seed)
+    freq = case["freq"]
+    win = wo.get_window(freq, window)
+    tau, ntau = wo.delay_axis(freq, win)
+    S = wo.get_prior(tau, 2.8e-5, 0.02)
+    filt = np.ascontiguousarray(case["filter"][0].transpose(2, 0, 1))
+    cov = np.ascontiguousarray(case["freq_cov"][0].transpose(2, 0, 1))
+    if not cplx_filter:
+        filt = np.ascontiguousarray(filt.real)
+    if not cplx_cov:
+        cov = np.ascontiguousarray(cov.real)
+    weight = np.ascontiguousarray(case["weight"][0].transpose(2, 1, 0))
+    beam = np.ascontiguousarray(case["dirty_beam_power"][0, 0].T)
+    return freq, weight, beam, filt, cov, win, S, tau, ntau
+
+
+@pytest.mark.parametrize("solver", [1, 2])
+@pytest.mark.parametrize("cplx_filter,cplx_cov", [(False, False), (True, True), (True, False), (False, True)])
+def test_operator_matches_oracle(solver, cplx_filter, cplx_cov):
+    """Both factorisation paths (batched / per-matrix on several streams), every dtype combination, F not a
+    multiple of anything, several chunks of pixels (tiny workspace budget)."""
+    freq, weight, beam, filt, cov, win, S, tau, ntau = random_problem(52, 7, 3, cplx_filter, cplx_cov, 77)
+    ref = wo.construct_operator(freq, weight, beam, filt, cov, win, S, tau, ntau)
+    t = {}
+    got = powerspec.wiener_delay_operator(wo.fourier_operator(freq, tau, ntau), S, win, filt, cov, weight, beam,
+                                          solver=solver, workspace_bytes=3 * 52 * 52 * 100, timing=t)
+    close_c64(got, ref)
+    assert t["launches"] > 0 and t["flop"] > 0
+
+
+def test_strided_output_and_larger_band():
+    """F = 160 (per-matrix path by default), the output written into a [pol, ra, el, delay, freq] slab."""
+    freq, weight, beam, filt, cov, win, S, tau, ntau = random_problem(160, 5, 2, False, False, 78, window="uniform")
+    ref = wo.construct_operator(freq, weight, beam, filt, cov, win, S, tau, ntau)
+    slab = np.full((2, 5, 2, tau.size, 160), 7.0, dtype=np.complex64)
+    powerspec.wiener_delay_operator(wo.fourier_operator(freq, tau, ntau), S, win, filt, cov, weight, beam, out=slab[1])
+    close_c64(slab[1], ref)
+    assert (slab[0] == 7.0).all()
+
+
+def test_not_positive_definite_raises():
+    """scipy.linalg.cho_factor raises LinAlgError in the reference (powerspec.py:296); so does the device path."""
+    from test_wiener_op_oracle import make_indefinite
+
+    name, nfreq, nra, nel, npol, cplx, params = WIENER_CASES[0]
+    case = make_wiener_case(nfreq, nra, nel, npol, cplx, 300)
+    make_indefinite(case)
+    with pytest.raises(np.linalg.LinAlgError):
+        powerspec.ConstructWienerDelayTransform.from_config(params).process(make_ringmap(case))
+
+
+def test_empty_and_bad_arguments():
+    freq, weight, beam, filt, cov, win, S, tau, ntau = random_problem(16, 2, 1, False, False, 5)
+    Fm = wo.fourier_operator(freq, tau, ntau)
+    out = powerspec.wiener_delay_operator(Fm, S, win, filt[:0], cov[:0], weight[:, :0], beam)
+    assert out.shape == (0, 1, tau.size, 16)
+    with pytest.raises(ValueError):
+        powerspec.wiener_delay_operator(Fm, S, win, filt, cov[:, :-1], weight, beam)
+    with pytest.raises(ValueError):
+        powerspec.wiener_delay_operator(Fm, S[:-1], win, filt, cov, weight, beam)
