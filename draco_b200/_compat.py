@@ -372,6 +372,7 @@ class DelayTransform(Container):
 
     _dataset_spec = {
         "spectrum": {"axes": ["baseline", "sample", "delay"], "dtype": np.complex128, "distributed_axis": "baseline"},
+        "weight": {"axes": ["baseline", "sample", "delay"], "dtype": np.float32, "distributed_axis": "baseline"},
         "spectrum_mask": {"axes": ["baseline", "sample"], "dtype": bool, "distributed_axis": "baseline"},
     }
 
@@ -383,6 +384,10 @@ class DelayTransform(Container):
     @property
     def spectrum(self):
         return self.datasets["spectrum"]
+
+    @property
+    def weight(self):
+        return self.datasets["weight"]
 
     @property
     def delay(self):

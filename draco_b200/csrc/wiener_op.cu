@@ -166,6 +166,66 @@ __global__ void fill_ptrs_kernel(zc** Aptr, zc** Yptr, zc* A, zc* Y, int R, size
   Yptr[r] = Y + (size_t)r * sy;
 }
 
+// ApplyWienerDelayTransform, powerspec.py:430-452: one CTA per pixel (ra, el).  The map and the inverse weights of the
+// pixel are gathered into shared memory once (they are strided by nra * nel in the container's [freq, ra, el] layout);
+// every warp then streams rows of the complex64 operator (16 bytes per lane and load, four loads in flight) and keeps
+// the three sums in fp64.  |op|^2 is formed in fp32 as numpy does for a complex64 operand (np.abs(op) ** 2).
+template <int NT>
+__global__ void __launch_bounds__(NT) apply_kernel(const float2* __restrict__ op, long long stride_ra, long long stride_el,
+                                                   int ra0, const double* __restrict__ map, const double* __restrict__ wgt,
+                                                   double2* __restrict__ spec, float* __restrict__ sw, int F, int nd, int nra,
+                                                   int nel) {
+  extern __shared__ double sm[];
+  double* m = sm;
+  double* v = sm + F;
+  const int ee = blockIdx.x % nel, rl = blockIdx.x / nel, rr = ra0 + rl;
+  for (int f = threadIdx.x; f < F; f += NT) {
+    const size_t o = ((size_t)f * nra + rr) * nel + ee;
+    m[f] = map[o];
+    const double w = wgt[o];
+    v[f] = w != 0.0 ? 1.0 / w : 0.0;
+  }
+  __syncthreads();
+  const float2* base = op + (size_t)rl * stride_ra + (size_t)ee * stride_el;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const bool vec = (F % 2 == 0) && ((((size_t)base) & 15) == 0);
+  for (int d = warp; d < nd; d += NT / 32) {
+    const float2* row = base + (size_t)d * F;
+    double sr = 0.0, si = 0.0, sv = 0.0;
+    if (vec) {
+      const float4* row4 = reinterpret_cast<const float4*>(row);
+      const int n4 = F / 2;
+#pragma unroll 4
+      for (int q = lane; q < n4; q += 32) {
+        const float4 c = __ldg(row4 + q);
+        const double m0 = m[2 * q], m1 = m[2 * q + 1];
+        const float a0 = hypotf(c.x, c.y), a1 = hypotf(c.z, c.w);
+        sr += (double)c.x * m0 + (double)c.z * m1;
+        si += (double)c.y * m0 + (double)c.w * m1;
+        sv += (double)(a0 * a0) * v[2 * q] + (double)(a1 * a1) * v[2 * q + 1];
+      }
+    } else {
+      for (int f = lane; f < F; f += 32) {
+        const float2 c = row[f];
+        const float a = hypotf(c.x, c.y);
+        sr += (double)c.x * m[f];
+        si += (double)c.y * m[f];
+        sv += (double)(a * a) * v[f];
+      }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+      sr += __shfl_xor_sync(0xffffffffu, sr, o);
+      si += __shfl_xor_sync(0xffffffffu, si, o);
+      sv += __shfl_xor_sync(0xffffffffu, sv, o);
+    }
+    if (lane == 0) {
+      const size_t o = ((size_t)ee * nra + rr) * nd + d;
+      spec[o] = make_double2(sr, si);
+      sw[o] = sv != 0.0 ? (float)(1.0 / sv) : 0.f;
+    }
+  }
+}
+
 int init_libs(int dev) {
   WLibs& L = g_wlibs[dev];
   if (L.ready) return 0;
@@ -203,6 +263,7 @@ struct DevBufs {
 }  // namespace
 
 extern "C" int dgwiener_sizeof(void) { return (int)sizeof(dgwiener_problem); }
+extern "C" int dgwiener_apply_sizeof(void) { return (int)sizeof(dgwiener_apply_problem); }
 extern "C" const char* dgwiener_last_error(void) { return g_err.c_str(); }
 
 extern "C" int dgwiener_construct(dgwiener_problem* p) {
@@ -333,7 +394,8 @@ extern "C" int dgwiener_construct(dgwiener_problem* p) {
       WCU(cudaEventRecord(L.ev1, st));
       WCU(cudaMemcpyAsync(hinfo.data(), info, (size_t)Rc * sizeof(int), cudaMemcpyDeviceToHost, st));
       char* dst = (char*)p->out + 8 * ((size_t)r0 * p->out_stride_ra + (size_t)ee * p->out_stride_el);
-      WCU(cudaMemcpy2DAsync(dst, (size_t)p->out_stride_ra * 8, outd, FD * 8, FD * 8, (size_t)Rc, cudaMemcpyDeviceToHost, st));
+      WCU(cudaMemcpy2DAsync(dst, (size_t)p->out_stride_ra * 8, outd, FD * 8, FD * 8, (size_t)Rc,
+                            p->out_on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, st));
       WCU(cudaGetLastError());
       WCU(cudaStreamSynchronize(st));
       float ms = 0.f;
@@ -358,5 +420,91 @@ extern "C" int dgwiener_construct(dgwiener_problem* p) {
   p->ms_compute = ms_compute;
   p->flop = flop;
   p->launches = launches;
+  return 0;
+}
+
+extern "C" int dgwiener_apply(dgwiener_apply_problem* p) {
+  g_err.clear();
+  if (!p) return -1;
+  const int F = p->nfreq, nd = p->ndelay, nra = p->nra, nel = p->nel;
+  if (p->device_id < 0 || p->device_id >= 64) return -2;
+  if (F <= 0 || nd <= 0 || nra < 0 || nel < 0) return -3;
+  p->ms_kernel = p->bytes = 0.0;
+  p->launches = 0;
+  {
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || p->device_id >= count) {
+      g_err = "no CUDA device " + std::to_string(p->device_id) + " (there is no CPU fallback)";
+      cudaGetLastError();
+      return 100;
+    }
+  }
+  if (nra == 0 || nel == 0) return 0;
+  if (!p->op || !p->map || !p->weight || !p->spectrum || !p->spectrum_weight) return -4;
+  if ((size_t)F * 16 > 200 * 1024) {
+    g_err = "nfreq too large for the shared-memory staging of the apply kernel";
+    return -3;
+  }
+  WCU(cudaSetDevice(p->device_id));
+  if (int rc = init_libs(p->device_id)) return rc;
+  WLibs& L = g_wlibs[p->device_id];
+  cudaStream_t st = L.stream;
+  constexpr int NT = 256;
+  const size_t smem = (size_t)F * 16;
+  WCU(cudaFuncSetAttribute(apply_kernel<NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+
+  const size_t nmap = (size_t)F * nra * nel, nout = (size_t)nel * nra * nd, FD = (size_t)F * nd;
+  DevBufs bufs;
+  double *map, *wgt;
+  double2* spec;
+  float* sw;
+  float2* opd = nullptr;
+  WCU(bufs.alloc(&map, nmap * 8)); WCU(bufs.alloc(&wgt, nmap * 8));
+  WCU(bufs.alloc(&spec, nout * 16)); WCU(bufs.alloc(&sw, nout * 4));
+  WCU(cudaMemcpyAsync(map, p->map, nmap * 8, cudaMemcpyHostToDevice, st));
+  WCU(cudaMemcpyAsync(wgt, p->weight, nmap * 8, cudaMemcpyHostToDevice, st));
+  int R = nra;
+  if (!p->op_on_device) {
+    const size_t budget = p->workspace_bytes > 0 ? (size_t)p->workspace_bytes : ((size_t)2 << 30);
+    R = (int)std::max<size_t>(1, std::min<size_t>((size_t)nra, budget / ((size_t)nel * FD * 8)));
+    WCU(bufs.alloc(&opd, (size_t)R * nel * FD * 8));
+  }
+  double ms_kernel = 0.0;
+  for (int r0 = 0; r0 < nra; r0 += R) {
+    const int Rc = std::min(R, nra - r0);
+    const float2* opc;
+    long long sra, sel;
+    if (p->op_on_device) {
+      opc = (const float2*)p->op;
+      sra = p->op_stride_ra;
+      sel = p->op_stride_el;
+    } else {  // pack the chunk's [ndelay, F] blocks as [Rc, nel, ndelay, F]
+      const char* src = (const char*)p->op + 8 * (size_t)r0 * p->op_stride_ra;
+      if (p->op_stride_el == (long long)FD && p->op_stride_ra == (long long)(nel * FD)) {
+        WCU(cudaMemcpyAsync(opd, src, (size_t)Rc * nel * FD * 8, cudaMemcpyHostToDevice, st));
+      } else {
+        for (int r = 0; r < Rc; r++)
+          WCU(cudaMemcpy2DAsync(opd + (size_t)r * nel * FD, FD * 8, src + 8 * (size_t)r * p->op_stride_ra,
+                                (size_t)p->op_stride_el * 8, FD * 8, (size_t)nel, cudaMemcpyHostToDevice, st));
+      }
+      opc = opd;
+      sra = (long long)(nel * FD);
+      sel = (long long)FD;
+    }
+    WCU(cudaEventRecord(L.evA, st));
+    apply_kernel<NT><<<(unsigned)((size_t)Rc * nel), NT, smem, st>>>(opc, sra, sel, r0, map, wgt, spec, sw, F, nd, nra, nel);
+    WCU(cudaEventRecord(L.ev1, st));
+    WCU(cudaGetLastError());
+    WCU(cudaStreamSynchronize(st));
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, L.evA, L.ev1);
+    ms_kernel += ms;
+    p->launches += 1;
+  }
+  WCU(cudaMemcpyAsync(p->spectrum, spec, nout * 16, cudaMemcpyDeviceToHost, st));
+  WCU(cudaMemcpyAsync(p->spectrum_weight, sw, nout * 4, cudaMemcpyDeviceToHost, st));
+  WCU(cudaStreamSynchronize(st));
+  p->ms_kernel = ms_kernel;
+  p->bytes = (double)nra * nel * (8.0 * FD + 16.0 * F + 20.0 * nd);
   return 0;
 }

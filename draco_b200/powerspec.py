@@ -34,7 +34,7 @@ else:
     _ContainerTask = _compat.ContainerTask
     containers = _compat
 
-WIENER_EXPORTED = ["dgwiener_construct", "dgwiener_sizeof", "dgwiener_last_error"]
+WIENER_EXPORTED = ["dgwiener_construct", "dgwiener_apply", "dgwiener_sizeof", "dgwiener_apply_sizeof", "dgwiener_last_error"]
 _vp = C.c_void_p
 
 
@@ -47,8 +47,20 @@ class WienerProblem(C.Structure):
         ("fourier", _vp), ("prior", _vp), ("window", _vp), ("filter", _vp), ("freq_cov", _vp), ("weight", _vp),
         ("beam_power", _vp), ("out", _vp),
         ("out_stride_ra", C.c_int64), ("out_stride_el", C.c_int64), ("workspace_bytes", C.c_int64),
+        ("out_on_device", C.c_int32), ("reserved", C.c_int32),
         ("bad_el", C.c_int32), ("bad_ra", C.c_int32),
         ("ms_device", C.c_double), ("ms_compute", C.c_double), ("flop", C.c_double), ("launches", C.c_int64),
+    ]
+
+
+class WienerApplyProblem(C.Structure):
+    """``dgwiener_apply_problem`` of include/dgwiener.h."""
+
+    _fields_ = [
+        ("device_id", C.c_int32), ("nfreq", C.c_int32), ("ndelay", C.c_int32), ("nra", C.c_int32), ("nel", C.c_int32),
+        ("op_on_device", C.c_int32), ("op", _vp), ("op_stride_ra", C.c_int64), ("op_stride_el", C.c_int64),
+        ("map", _vp), ("weight", _vp), ("spectrum", _vp), ("spectrum_weight", _vp), ("workspace_bytes", C.c_int64),
+        ("ms_kernel", C.c_double), ("bytes", C.c_double), ("launches", C.c_int64),
     ]
 
 
@@ -64,9 +76,13 @@ def load_wiener():
         lib.dgwiener_construct.restype = C.c_int
         lib.dgwiener_sizeof.restype = C.c_int
         lib.dgwiener_last_error.restype = C.c_char_p
-        if lib.dgwiener_sizeof() != C.sizeof(WienerProblem):
-            raise RuntimeError(f"ABI mismatch: dgwiener_problem is {C.sizeof(WienerProblem)} bytes here, "
-                               f"{lib.dgwiener_sizeof()} in libdgnrml.so; rebuild the library")
+        lib.dgwiener_apply.argtypes = [C.POINTER(WienerApplyProblem)]
+        lib.dgwiener_apply.restype = C.c_int
+        lib.dgwiener_apply_sizeof.restype = C.c_int
+        for st, fn in ((WienerProblem, lib.dgwiener_sizeof), (WienerApplyProblem, lib.dgwiener_apply_sizeof)):
+            if fn() != C.sizeof(st):
+                raise RuntimeError(f"ABI mismatch: {st.__name__} is {C.sizeof(st)} bytes here, {fn()} in libdgnrml.so; "
+                                   "rebuild the library")
         _wlib = lib
     return _wlib
 
@@ -84,13 +100,36 @@ def _window(x, name):
     return window_generalised(x, window=name)
 
 
+def _operator_view(op, shape):
+    """(pointer, ra stride, el stride, on_device) of an operator [nra, nel, ndelay, nfreq] complex64 held either in a
+    numpy array or in a CUDA ``torch`` tensor; its [ndelay, nfreq] blocks must be contiguous."""
+    if isinstance(op, np.ndarray):
+        if op.dtype != np.complex64 or op.shape != tuple(shape):
+            raise ValueError(f"the operator must be complex64 {list(shape)}")
+        es = op.itemsize
+        st = [x // es for x in op.strides]
+        bad = any(x % es for x in op.strides)
+        ptr, on_dev = op.ctypes.data, False
+    else:
+        import torch
+
+        if not (isinstance(op, torch.Tensor) and op.is_cuda and op.dtype == torch.complex64 and tuple(op.shape) == tuple(shape)):
+            raise ValueError(f"the operator must be a numpy array or a CUDA torch tensor, complex64 {list(shape)}")
+        st, bad = list(op.stride()), False
+        ptr, on_dev = op.data_ptr(), True
+    if int(np.prod(shape)) and (bad or st[3] != 1 or st[2] != shape[3]):
+        raise ValueError("the [ndelay, nfreq] blocks of the operator must be contiguous")
+    return ptr, (st[0] if int(np.prod(shape)) else 0), (st[1] if int(np.prod(shape)) else 0), on_dev
+
+
 def wiener_delay_operator(fourier, prior, window, filt, freq_cov, weight, beam_power, out=None, device=0, solver=0,
                           workspace_bytes=0, timing=None):
     """Wiener delay-transform operators of one polarisation on the GPU (powerspec.py:245-319).
 
     fourier [F, ndelay] complex (delay -> frequency DFT, powerspec.py:229), prior [ndelay], window [F],
     filt / freq_cov [nra, F, F] (float64 or complex128), weight [nel, nra, F], beam_power [nel, F].
-    Returns (or fills ``out``, any complex64 array whose [ra, el] blocks are contiguous [ndelay, F]) the operator
+    Returns (or fills ``out``, any complex64 numpy array or CUDA torch tensor whose [ra, el] blocks are contiguous
+    [ndelay, F]; a device tensor keeps the operator in HBM for ``apply_wiener_operator``) the operator
     [nra, nel, ndelay, F].  Raises ``numpy.linalg.LinAlgError`` where ``scipy.linalg.cho_factor`` would.
     """
     lib = load_wiener()
@@ -111,18 +150,18 @@ def wiener_delay_operator(fourier, prior, window, filt, freq_cov, weight, beam_p
         raise ValueError("weight must be [nel, nra, nfreq] and beam_power [nel, nfreq]")
     if out is None:
         out = np.zeros((nra, nel, ndelay, nfreq), dtype=np.complex64)
-    if out.dtype != np.complex64 or out.shape != (nra, nel, ndelay, nfreq):
-        raise ValueError("out must be complex64 [nra, nel, ndelay, nfreq]")
-    es = out.itemsize
-    if out.size and (out.strides[3] != es or out.strides[2] != es * nfreq or out.strides[0] % es or out.strides[1] % es):
-        raise ValueError("the [ndelay, nfreq] blocks of out must be contiguous")
+    ptr, sra, sel, on_dev = _operator_view(out, (nra, nel, ndelay, nfreq))
+    if on_dev:
+        import torch
+
+        device = out.device.index
+        torch.cuda.synchronize(out.device)  # the library works on its own stream
     p = WienerProblem(
         device_id=int(device), nfreq=nfreq, ndelay=ndelay, nra=nra, nel=nel,
         filter_is_complex=int(np.iscomplexobj(filt)), cov_is_complex=int(np.iscomplexobj(freq_cov)), solver=int(solver),
         fourier=fourier.ctypes.data, prior=prior.ctypes.data, window=window.ctypes.data, filter=filt.ctypes.data,
         freq_cov=freq_cov.ctypes.data, weight=weight.ctypes.data, beam_power=beam_power.ctypes.data,
-        out=out.ctypes.data, out_stride_ra=out.strides[0] // es if out.size else 0,
-        out_stride_el=out.strides[1] // es if out.size else 0, workspace_bytes=int(workspace_bytes))
+        out=ptr, out_stride_ra=sra, out_stride_el=sel, workspace_bytes=int(workspace_bytes), out_on_device=int(on_dev))
     rc = lib.dgwiener_construct(C.byref(p))
     if rc == 1:
         raise np.linalg.LinAlgError(lib.dgwiener_last_error().decode())
@@ -131,6 +170,42 @@ def wiener_delay_operator(fourier, prior, window, filt, freq_cov, weight, beam_p
     if timing is not None:
         timing.update(ms_device=p.ms_device, ms_compute=p.ms_compute, flop=p.flop, launches=p.launches)
     return out
+
+
+def apply_wiener_operator(op, map_, weight, device=0, workspace_bytes=0, timing=None):
+    """Apply the operators of one polarisation to its map on the GPU (powerspec.py:430-452).
+
+    op [nra, nel, ndelay, F] complex64 (numpy, or a CUDA torch tensor: no upload), map_ / weight [F, nra, nel] (the
+    container's own slices).  Returns ``spectrum [nel, nra, ndelay]`` complex128 and its ``weight`` float32.
+    """
+    lib = load_wiener()
+    map_ = np.ascontiguousarray(map_, dtype=np.float64)
+    weight = np.ascontiguousarray(weight, dtype=np.float64)
+    nfreq, nra, nel = map_.shape
+    if weight.shape != map_.shape:
+        raise ValueError("map and weight must both be [nfreq, nra, nel]")
+    if len(op.shape) != 4 or tuple(op.shape[:2]) != (nra, nel) or op.shape[3] != nfreq:
+        raise ValueError(f"the operator must be [{nra}, {nel}, ndelay, {nfreq}]")
+    ndelay = int(op.shape[2])
+    ptr, sra, sel, on_dev = _operator_view(op, (nra, nel, ndelay, nfreq))
+    spec = np.zeros((nel, nra, ndelay), dtype=np.complex128)
+    sw = np.zeros((nel, nra, ndelay), dtype=np.float32)
+    if on_dev:
+        device = op.device.index
+    p = WienerApplyProblem(
+        device_id=int(device), nfreq=nfreq, ndelay=ndelay, nra=nra, nel=nel, op_on_device=int(on_dev), op=ptr,
+        op_stride_ra=sra, op_stride_el=sel, map=map_.ctypes.data, weight=weight.ctypes.data, spectrum=spec.ctypes.data,
+        spectrum_weight=sw.ctypes.data, workspace_bytes=int(workspace_bytes))
+    if on_dev:
+        import torch
+
+        torch.cuda.synchronize(op.device)  # the library works on its own stream
+    rc = lib.dgwiener_apply(C.byref(p))
+    if rc != 0:
+        raise _glib.DGibbsError(f"dgwiener_apply failed ({rc}): {lib.dgwiener_last_error().decode()}")
+    if timing is not None:
+        timing.update(ms_kernel=p.ms_kernel, bytes=p.bytes, launches=p.launches)
+    return spec, sw
 
 
 class ConstructWienerDelayTransform(_ContainerTask):
@@ -222,3 +297,50 @@ def _gathered(arr):
     """The full array behind a distributed slice (``MPIArray.allgather``), or the array itself."""
     gather = getattr(arr, "allgather", None)
     return np.asarray(gather() if gather is not None else arr)
+
+
+class ApplyWienerDelayTransform(_ContainerTask):
+    """Apply a precomputed Wiener filter to project a ring map into delay space (powerspec.py:372-458).
+
+    Same inputs and output as the reference: ``process(data, operator)`` with a ``RingMap`` (``map``, ``weight``) and
+    the ``DelayTransformOperator`` of ``ConstructWienerDelayTransform``; returns a ``DelayTransform`` whose
+    ``baseline`` axis flattens (pol, el) and whose ``sample`` axis is the right ascension, with a ``weight`` dataset.
+    """
+
+    device = config.Property(proptype=int, default=None)
+    _device = ConstructWienerDelayTransform._device
+
+    def process(self, data, operator):
+        data.redistribute("ra")
+        operator.redistribute("ra")
+        npol, _, nra, nel = data.weight[:].local_shape
+
+        out = containers.DelayTransform(baseline=npol * nel, sample=data.index_map["ra"],
+                                        delay=operator.index_map["delay"], attrs_from=data)
+        out.add_dataset("weight")
+        out.redistribute("sample")
+
+        # index maps of the flattened axes and their order (powerspec.py:416-426)
+        bl_axes = np.array(["pol", "el"])
+        for ax in bl_axes:
+            out.create_index_map(ax, data.index_map[ax])
+        out.attrs["baseline_axes"] = bl_axes
+        out.attrs["freq"] = data.freq
+        for attr in ["window", "window_lower_freq", "window_upper_freq"]:
+            out.attrs[attr.replace("window", "window_los")] = operator.attrs[attr]
+
+        weight = data.weight[:].local_array
+        maps = data.map[0].local_array
+        filt = operator.filter[:].local_array
+        spec = out.spectrum[:].local_array
+        sweight = out.weight[:].local_array
+        device = self._device()
+        self.last_timing = []
+        for pp in range(npol):
+            eslc = slice(pp * nel, (pp + 1) * nel)
+            t = {}
+            sp, sw = apply_wiener_operator(filt[pp], maps[pp], weight[pp], device=device, timing=t)
+            spec[eslc] = sp
+            sweight[eslc] = sw
+            self.last_timing.append(t)
+        return out

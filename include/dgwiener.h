@@ -45,6 +45,8 @@ typedef struct {
   void* out;                /* complex64; operator of pixel (ra, el) = [ndelay, F] block at out + 8 * (ra * out_stride_ra + el * out_stride_el) */
   int64_t out_stride_ra, out_stride_el; /* in complex64 elements                               */
   int64_t workspace_bytes;  /* device memory budget for one chunk of pixels (0: 8 GiB)       */
+  int32_t out_on_device;    /* 1: out is a device pointer (same strides): the operator never visits the host */
+  int32_t reserved;
   /* results */
   int32_t bad_el, bad_ra;   /* a pixel whose factorisation failed (return code 1)            */
   double ms_device;         /* CUDA-event time of the whole call on the device, copies included */
@@ -54,7 +56,34 @@ typedef struct {
 } dgwiener_problem;
 
 int dgwiener_construct(dgwiener_problem* p);
+
+/* Apply stored operators to a ring map: ApplyWienerDelayTransform.process, powerspec.py:430-458, for ONE
+ * polarisation: for every pixel (ra, el)
+ *     spectrum[el, ra, :] = op[ra, el] @ map[:, ra, el]                                  (powerspec.py:446)
+ *     weight[el, ra, :]   = invert_no_zero(|op[ra, el]|^2 @ invert_no_zero(w[:, ra, el])) (powerspec.py:449-452)
+ * one hand-written kernel, bound by the single read of the complex64 operator from HBM.  map / weight are the
+ * container's own [freq, ra, el] slices; the outputs are the [el, ra, delay] block of the DelayTransform
+ * container's [baseline = pol * nel + el, sample = ra, delay] datasets. */
+typedef struct {
+  int32_t device_id;
+  int32_t nfreq, ndelay, nra, nel;
+  int32_t op_on_device;     /* 1: op is a device pointer (e.g. written by dgwiener_construct with out_on_device) */
+  const void* op;           /* complex64; [ndelay, F] block of pixel (ra, el) at op + 8 * (ra * op_stride_ra + el * op_stride_el) */
+  int64_t op_stride_ra, op_stride_el;
+  const double* map;        /* [F, nra, nel] host */
+  const double* weight;     /* [F, nra, nel] host */
+  void* spectrum;           /* [nel, nra, ndelay] complex128 host */
+  float* spectrum_weight;   /* [nel, nra, ndelay] float32 host */
+  int64_t workspace_bytes;  /* device budget for one chunk of host-resident operators (0: 2 GiB) */
+  /* results */
+  double ms_kernel;         /* CUDA-event time of the apply kernel launches alone */
+  double bytes;             /* algorithmic bytes: 8 ndelay F + 16 F + 20 ndelay per pixel */
+  int64_t launches;
+} dgwiener_apply_problem;
+
+int dgwiener_apply(dgwiener_apply_problem* p);
 int dgwiener_sizeof(void);
+int dgwiener_apply_sizeof(void);
 const char* dgwiener_last_error(void);
 
 #ifdef __cplusplus

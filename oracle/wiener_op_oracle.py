@@ -91,3 +91,21 @@ def construct_operator(freq, weight, beam_power, filt, cov, window, Sdiag, tau, 
         RT = FT @ HT
         out[:, ee] = Sdiag[np.newaxis, :, np.newaxis] * (RT @ A_inv) * window
     return out
+
+
+def apply_operator(op, map_, weight):
+    """One polarisation of ``ApplyWienerDelayTransform.process`` (powerspec.py:430-455).
+
+    op [nra, nel, ndelay, F] (complex64 as stored), map_ / weight [F, nra, nel] (the container's slices) ->
+    spectrum [nel, nra, ndelay] complex128, weight [nel, nra, ndelay] float32.
+    """
+    nra, nel, nd, _ = op.shape
+    spec = np.zeros((nel, nra, nd), dtype=np.complex128)
+    sweight = np.zeros((nel, nra, nd), dtype=np.float32)
+    for rr in range(nra):
+        m = np.ascontiguousarray(map_[:, rr, :].T[..., np.newaxis])
+        w = np.ascontiguousarray(weight[:, rr, :].T[..., np.newaxis])
+        spec[:, rr, :] = np.matmul(op[rr], m)[..., 0]
+        v = invert_no_zero(w)
+        sweight[:, rr, :] = invert_no_zero(np.matmul(np.abs(op[rr]) ** 2, v)[..., 0])
+    return spec, sweight

@@ -103,6 +103,46 @@ def load_reference_task():
     return ns["ConstructWienerDelayTransform"]
 
 
+def load_reference_apply_task():
+    """exec powerspec.py:372-458 (class ApplyWienerDelayTransform) over the stand-ins."""
+    from draco_b200 import _compat
+    from oracle import ref_loader
+
+    def invert_no_zero(x):
+        x = np.asarray(x)
+        with np.errstate(divide="ignore", invalid="ignore"):
+            return np.where(x == 0, 0.0, 1.0 / np.where(x == 0, 1.0, x))
+
+    ns = {
+        "np": np,
+        "tasklib": types.SimpleNamespace(base=types.SimpleNamespace(ContainerTask=_compat.ContainerTask)),
+        "containers": types.SimpleNamespace(DelayTransform=_compat.DelayTransform),
+        "tools": types.SimpleNamespace(invert_no_zero=invert_no_zero),
+        "__name__": "draco_reference_powerspec",
+    }
+    rel = "draco/analysis/powerspec.py"
+    exec(compile(ref_loader._lines(rel, 372, 458), rel, "exec"), ns)
+    return ns["ApplyWienerDelayTransform"]
+
+
+def make_map(case, seed):
+    """A seeded map [beam, pol, freq, ra, el] for the weights of ``case``."""
+    r = np.random.default_rng(seed)
+    npol, nfreq, nra, nel = case["weight"].shape
+    return r.standard_normal((1, npol, nfreq, nra, nel)) * 1e-2 * (case["weight"] > 0)
+
+
+def make_operator(case, filt64, delay, params):
+    """``_compat.DelayTransformOperator`` (complex64, as the real container) holding the rounded golden operator."""
+    from draco_b200 import _compat
+
+    op = _compat.DelayTransformOperator(delay=delay, axes_from=make_ringmap(case))
+    op.filter[:].local_array[:] = filt64
+    for attr in ["window", "window_lower_freq", "window_upper_freq"]:
+        op.attrs[attr] = params.get(attr, "uniform" if attr == "window" else None)
+    return op
+
+
 def main():
     Task = load_reference_task()
     out = {}
@@ -113,6 +153,12 @@ def main():
         out[f"{name}_filter"] = op.filter[:].local_array.copy()
         out[f"{name}_delay"] = np.asarray(op.index_map["delay"])
         print(name, out[f"{name}_filter"].shape, "max |D|", np.abs(out[f"{name}_filter"]).max())
+        # ApplyWienerDelayTransform on the operator as the real container stores it (complex64)
+        rm = make_ringmap(case)
+        rm.map[:].local_array[:] = make_map(case, 700 + k)
+        dt = load_reference_apply_task()().process(rm, make_operator(case, out[f"{name}_filter"], out[f"{name}_delay"], params))
+        out[f"{name}_apply_spectrum"] = dt.spectrum[:].local_array.copy()
+        out[f"{name}_apply_weight"] = dt.weight[:].local_array.copy()
     path = os.path.join(HERE, "reference_wiener_op.npz")
     np.savez_compressed(path, **out)
     print(f"wrote {path}: {len(out)} arrays, {os.path.getsize(path) / 1024:.0f} KiB")

@@ -8,7 +8,7 @@ import pytest
 
 HERE = os.path.dirname(__file__)
 sys.path.insert(0, os.path.join(HERE, "golden"))
-from make_golden_wiener_op import WIENER_CASES, make_ringmap, make_wiener_case  # noqa: E402
+from make_golden_wiener_op import WIENER_CASES, make_map, make_operator, make_ringmap, make_wiener_case  # noqa: E402
 
 from draco_b200 import powerspec  # noqa: E402
 from oracle import wiener_op_oracle as wo  # noqa: E402
@@ -109,3 +109,66 @@ def test_empty_and_bad_arguments():
         powerspec.wiener_delay_operator(Fm, S, win, filt, cov[:, :-1], weight, beam)
     with pytest.raises(ValueError):
         powerspec.wiener_delay_operator(Fm, S[:-1], win, filt, cov, weight, beam)
+
+
+# ------------------------------------------------------------------------------------------------ apply
+@pytest.mark.parametrize("k", range(len(WIENER_CASES)))
+def test_apply_task_matches_reference(golden, k):
+    """ApplyWienerDelayTransform.process against the reference's own output (powerspec.py:372-458)."""
+    name, nfreq, nra, nel, npol, cplx, params = WIENER_CASES[k]
+    case = make_wiener_case(nfreq, nra, nel, npol, cplx, 300 + k)
+    rm = make_ringmap(case)
+    rm.map[:].local_array[:] = make_map(case, 700 + k)
+    op = make_operator(case, golden[f"{name}_filter"], golden[f"{name}_delay"], params)
+    out = powerspec.ApplyWienerDelayTransform().process(rm, op)
+    ref = golden[f"{name}_apply_spectrum"]
+    got = out.spectrum[:].local_array
+    assert got.shape == ref.shape == (npol * nel, nra, golden[f"{name}_delay"].size) and got.dtype == np.complex128
+    np.testing.assert_allclose(got, ref, rtol=1e-10, atol=1e-13 * np.abs(ref).max())
+    gw, rw = out.weight[:].local_array, golden[f"{name}_apply_weight"]
+    assert gw.dtype == np.float32
+    np.testing.assert_allclose(gw, rw, rtol=2e-6)
+    assert (gw == 0).sum() == (rw == 0).sum()
+    assert list(out.attrs["baseline_axes"]) == ["pol", "el"]
+    assert out.attrs["window_los"] == params.get("window", "uniform")
+    np.testing.assert_array_equal(out.attrs["freq"], case["freq"])
+    np.testing.assert_array_equal(out.index_map["el"], rm.index_map["el"])
+
+
+@pytest.mark.parametrize("F", [33, 96, 258])
+def test_apply_matches_oracle(F):
+    """Odd and even channel counts (scalar and 16-byte loads), several chunks of a host-resident operator, a strided
+    operator slab, zero weights."""
+    r = np.random.default_rng(F)
+    nra, nel, nd = 6, 3, F // 2 + 1
+    slab = (r.standard_normal((2, nra, nel, nd, F)) + 1j * r.standard_normal((2, nra, nel, nd, F))).astype(np.complex64)
+    op = slab[1]
+    m = r.standard_normal((F, nra, nel))
+    w = r.uniform(0.5, 2.0, (F, nra, nel))
+    w[r.random(w.shape) < 0.2] = 0.0
+    w[:, 2, 1] = 0.0
+    ref_s, ref_w = wo.apply_operator(op, m, w)
+    t = {}
+    got_s, got_w = powerspec.apply_wiener_operator(op, m, w, workspace_bytes=2 * nel * nd * F * 8, timing=t)
+    np.testing.assert_allclose(got_s, ref_s, rtol=1e-10, atol=1e-13 * np.abs(ref_s).max())
+    np.testing.assert_allclose(got_w, ref_w, rtol=2e-6)
+    assert not got_w[1, 2].any() and t["launches"] == 3
+
+
+def test_construct_then_apply_on_device():
+    """The operator written into a CUDA tensor (never copied to the host) gives the same spectra as the host path."""
+    import torch
+
+    freq, weight, beam, filt, cov, win, S, tau, ntau = random_problem(48, 5, 2, True, False, 91)
+    Fm = wo.fourier_operator(freq, tau, ntau)
+    host = powerspec.wiener_delay_operator(Fm, S, win, filt, cov, weight, beam)
+    dev = torch.zeros((5, 2, tau.size, 48), dtype=torch.complex64, device="cuda:0")
+    powerspec.wiener_delay_operator(Fm, S, win, filt, cov, weight, beam, out=dev)
+    np.testing.assert_array_equal(dev.cpu().numpy(), host)
+    r = np.random.default_rng(3)
+    m = r.standard_normal((48, 5, 2))
+    w = np.ascontiguousarray(weight.transpose(2, 1, 0))
+    s0, w0 = powerspec.apply_wiener_operator(host, m, w)
+    s1, w1 = powerspec.apply_wiener_operator(dev, m, w)
+    np.testing.assert_array_equal(s0, s1)
+    np.testing.assert_array_equal(w0, w1)
