@@ -164,6 +164,32 @@ def test_cfg2_geometry_short_chain(gibbs):
         np.testing.assert_allclose(res.samples[:, b], refs[b], rtol=RTOL_SAMPLES)
 
 
+def test_cfg5_geometry_short_chain(gibbs):
+    """BASELINE config 5 geometry (N=4096, M~1229, T=16, 40 % of the channels flagged in contiguous RFI-like bands,
+    non-uniform weights): 2 baselines from different mask blocks x 2 iterations against the oracle with injected draws."""
+    from draco_b200 import synth
+
+    cfg = synth.CONFIGS["cfg5"]
+    niter = 2
+    datas, Nis, fsels, refs, draws = [], [], [], [], []
+    for b, off in enumerate((0, 500)):  # the masks are redrawn per block of 500 baselines
+        freq, vis, wgt = synth.make_stack(cfg, nbase=1, base_offset=off)
+        delays, chan = oracle.calculate_delays(freq)
+        N = len(delays)
+        assert N == 4096
+        d, w, nzf, _ = oracle.cut_data(vis[0], wgt[0])
+        assert 0.25 * N < d.shape[1] < 0.35 * N  # dense (_f) branch, heavy masking
+        s, ok, dr = recorded_chain(d, N, w, np.full(N, 10.0), cfg.window, chan[nzf], niter, False, seed=500 + b)
+        assert ok
+        datas.append(d); Nis.append(w); fsels.append(chan[nzf]); refs.append(s); draws.append(dr)
+    assert not np.array_equal(fsels[0], fsels[1])
+    pb = gibbs.pack_batch(datas, Nis, fsels, N, np.full((2, N), 10.0), window=cfg.window)
+    res = gibbs.run_batch(pb, niter, draws=gibbs.pack_draws(pb, niter, *zip(*draws)), save_samples=True)
+    assert res.success.all()
+    for b in range(2):
+        np.testing.assert_allclose(res.samples[:, b], refs[b], rtol=RTOL_SAMPLES)
+
+
 def test_device_resident_equals_host_path(gibbs):
     """on_device=1 (inputs in HBM) and host-pointer calls give bit-identical chains (Philox)."""
     import torch
