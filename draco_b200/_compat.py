@@ -299,8 +299,11 @@ class SiderealStream(FreqContainer):
         "vis_weight": {"axes": ["freq", "stack", "ra"], "dtype": np.float64, "distributed_axis": "freq"},
     }
 
-    def __init__(self, freq, stack, ra, attrs_from=None):
+    def __init__(self, freq, stack, ra, attrs_from=None, native_dtypes=False):
         super().__init__(attrs_from=attrs_from, freq=freq, stack=stack, ra=ra)
+        if native_dtypes:  # what draco's own container stores (core/containers.py:503-520): complex64 / float32
+            self._dataset_spec = {"vis": {**self._dataset_spec["vis"], "dtype": np.complex64},
+                                  "vis_weight": {**self._dataset_spec["vis_weight"], "dtype": np.float32}}
         # the stand-in keeps inputs replicated; the baseline split happens in flatten_axes
         self._make("vis")
         self._make("vis_weight")

@@ -127,6 +127,8 @@ class Cut(C.Structure):
         ("weight_f32", C.c_int32),
         ("remove_mean", C.c_int32),
         ("scale_freq", C.c_int32),
+        ("data_c64", C.c_int32),
+        ("reserved0", C.c_int32),
         ("time_frac", C.c_double),
         ("freq_frac", C.c_double),
         ("weight_boost", C.c_double),

@@ -26,7 +26,7 @@ struct CutArgs {
   int B, T, F;
   int remove_mean, scale_freq;
   double time_frac, freq_frac, boost;
-  const double2* data;
+  const void* data;  // complex128 or complex64 (template parameter D)
   const void* weight;
   const long long* cind;
   double2* dout;
@@ -46,10 +46,25 @@ __device__ __forceinline__ double boosted_mean(float s, int n, double boost) {
 }
 __device__ __forceinline__ double boosted_mean(double s, int n, double boost) { return (s / (double)n) * boost; }
 
-struct cplx {
-  double x, y;
+template <typename R>
+struct cplx_t {
+  R x, y;
 };
-__device__ __forceinline__ cplx operator+(cplx a, cplx b) { return cplx{a.x + b.x, a.y + b.y}; }
+template <typename R>
+__device__ __forceinline__ cplx_t<R> operator+(cplx_t<R> a, cplx_t<R> b) {
+  return cplx_t<R>{a.x + b.x, a.y + b.y};
+}
+using cplx = cplx_t<double>;
+template <typename R>
+struct vec2_of;
+template <>
+struct vec2_of<double> {
+  using type = double2;
+};
+template <>
+struct vec2_of<float> {
+  using type = float2;
+};
 
 // numpy's pairwise summation (numpy/_core/src/umath/loops_utils.h, pairwise_sum_@TYPE@) of g(s) .. g(s + n - 1).
 // L accumulators interleaved over consecutive elements: 8 for real scalars, 4 for complex (= 8 scalars).
@@ -127,8 +142,14 @@ __device__ double cta_sum(double v, double* red) {
   return s;
 }
 
-template <typename W>
+// W: weight scalar (float / double); D: scalar of the complex visibilities (double = complex128, float = complex64).
+// A complex64 slab is cut in the arithmetic numpy uses for it (delay.py:574 on a complex64 array): the column sums are
+// float32 pairwise sums, the division by the count runs in complex128 (the count is an int64 scalar, so numpy picks the
+// complex128 loop and casts the quotient back), the subtraction is float32; the result is widened to complex128 exactly
+// as _complex_to_alternating_real does afterwards (delay.py:1631).
+template <typename W, typename D>
 __global__ void __launch_bounds__(CUT_THREADS) cut_data_kernel(CutArgs a) {
+  using D2 = typename vec2_of<D>::type;
   extern __shared__ __align__(16) unsigned char cut_smem[];
   const int T = a.T, F = a.F, b = blockIdx.x;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -140,7 +161,7 @@ __global__ void __launch_bounds__(CUT_THREADS) cut_data_kernel(CutArgs a) {
   int* flist = fflag + F;                              // [F] kept frequencies, ascending
   int* sc = flist + F;                                 // [16]
   const W* w = reinterpret_cast<const W*>(a.weight) + (size_t)b * T * F;
-  const double2* dat = a.data + (size_t)b * T * F;
+  const D2* dat = reinterpret_cast<const D2*>(a.data) + (size_t)b * T * F;
 
   // ---- non_zero_time: fraction of positive weights of each sample > time_frac (delay.py:548-554)
   for (int t = warp; t < T; t += CUT_WARPS) {
@@ -217,19 +238,19 @@ __global__ void __launch_bounds__(CUT_THREADS) cut_data_kernel(CutArgs a) {
   double sr_all = 0.0, si_all = 0.0;
   for (int m = tid; m < M; m += CUT_THREADS) {
     const int f = flist[m];
-    double mr = 0.0, mi = 0.0;
+    D mr = (D)0, mi = (D)0;
     if (a.remove_mean) {
-      const cplx sm = pw_sum<cplx, 4>([&](int i) {
-        const double2 v = dat[(size_t)tlist[i] * F + f];
-        return cplx{v.x, v.y};
+      const cplx_t<D> sm = pw_sum<cplx_t<D>, 4>([&](int i) {
+        const D2 v = dat[(size_t)tlist[i] * F + f];
+        return cplx_t<D>{v.x, v.y};
       }, nkt);
-      mr = sm.x * scl;
-      mi = sm.y * scl;
+      mr = (D)((double)sm.x * scl);
+      mi = (D)((double)sm.y * scl);
     }
     for (int i = 0; i < nkt; i++) {
-      double2 v = dat[(size_t)tlist[i] * F + f];
-      v.x -= mr;
-      v.y -= mi;
+      const D2 raw = dat[(size_t)tlist[i] * F + f];
+      const D dx = raw.x - mr, dy = raw.y - mi;  // in the input precision, then widened
+      double2 v = make_double2((double)dx, (double)dy);
       if (v.x != 0.0 || v.y != 0.0) allzero = false;
       out[(size_t)i * M + m] = v;
       sr_all += v.x;
@@ -306,12 +327,14 @@ extern "C" int dgibbs_cut_data(dgibbs_handle h, const dgibbs_cut* c) {
   };
   if (!c || c->struct_size != (int32_t)sizeof(dgibbs_cut)) return bad("cut struct");
   if (c->B <= 0 || c->T <= 0 || c->nfreq <= 0) return bad("B, T, nfreq must be positive");
+  if (c->data_c64 && c->scale_freq)
+    return bad("scale_freq on complex64 data is not served on the device (numpy's float32 std is not reproduced); cut on the host");
   if (!c->data || !c->weight || !c->channel_ind) return bad("data, weight and channel_ind are required");
   if (!c->data_out || !c->Ni_out || !c->fsel_out || !c->T_out || !c->M_out || !c->alive)
     return bad("data_out, Ni_out, fsel_out, T_out, M_out and alive are required");
   KCU(cudaSetDevice(dg_device(h)));
   cudaStream_t st = dg_stream(h);
-  const size_t B = c->B, T = c->T, F = c->nfreq, wsz = c->weight_f32 ? 4 : 8;
+  const size_t B = c->B, T = c->T, F = c->nfreq, wsz = c->weight_f32 ? 4 : 8, dsz = c->data_c64 ? 8 : 16;
   const bool dev = c->on_device != 0;
 
   CutArgs a{};
@@ -331,7 +354,7 @@ extern "C" int dgibbs_cut_data(dgibbs_handle h, const dgibbs_cut* c) {
     return dg_pool_get(h, name, bytes, out);
   };
   const void* pin;
-  KCU(in("cut_data", c->data, B * T * F * 16, &pin)); a.data = (const double2*)pin;
+  KCU(in("cut_data", c->data, B * T * F * dsz, &pin)); a.data = pin;
   KCU(in("cut_weight", c->weight, B * T * F * wsz, &pin)); a.weight = pin;
   KCU(in("cut_cind", c->channel_ind, F * 8, &pin)); a.cind = (const long long*)pin;
   void* po;
@@ -346,13 +369,10 @@ extern "C" int dgibbs_cut_data(dgibbs_handle h, const dgibbs_cut* c) {
 
   const size_t smem = 8 * (F + 16) + 4 * (2 * T + 2 * F + 16);
   if (smem > 200 * 1024) return bad("T and nfreq too large for the cut kernel's shared memory");
-  if (c->weight_f32) {
-    KCU(cudaFuncSetAttribute(cut_data_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    cut_data_kernel<float><<<(unsigned)B, CUT_THREADS, smem, st>>>(a);
-  } else {
-    KCU(cudaFuncSetAttribute(cut_data_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    cut_data_kernel<double><<<(unsigned)B, CUT_THREADS, smem, st>>>(a);
-  }
+  void (*kern)(CutArgs) = c->data_c64 ? (c->weight_f32 ? cut_data_kernel<float, float> : cut_data_kernel<double, float>)
+                                      : (c->weight_f32 ? cut_data_kernel<float, double> : cut_data_kernel<double, double>);
+  KCU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  kern<<<(unsigned)B, CUT_THREADS, smem, st>>>(a);
   KCU(cudaGetLastError());
   if (!dev) {
     auto back = [&](void* dst, const void* src, size_t bytes) -> cudaError_t {

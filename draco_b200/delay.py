@@ -281,6 +281,11 @@ class _BatchedEvaluate:
             jobs.append((lbi, bi, data, weight, channel_ind[nzf], nzt))
         return jobs
 
+    def _device_cut_serves(self, data_view):
+        """complex64 slabs (draco's container dtype) are cut on the device in numpy's complex64 arithmetic, except
+        under ``scale_freq`` (numpy's float32 std is not reproduced there): those go through the host ``_cut_data``."""
+        return not (self.scale_freq and _local_array(data_view).dtype == np.complex64)
+
     def _chunks(self, jobs):
         step = self.batch_baselines if self.batch_baselines and self.batch_baselines > 0 else max(1, len(jobs))
         for i in range(0, len(jobs), step):
@@ -359,7 +364,7 @@ class DelayPowerSpectrumGibbs(DelayPowerSpectrumBase, _RandomTask):
         samp_out = _local(out_cont.datasets["spectrum_samples"]) if self.save_samples else None
         handle = gibbs.get_handle(self._device())
         seed = self._device_seed()
-        if self.device_cut and self.rng_mode == "philox":
+        if self.device_cut and self.rng_mode == "philox" and self._device_cut_serves(data_view):
             return self._evaluate_device_cut(data_view, weight_view, out_cont, channel_ind, ndelay, prior, handle, seed)
         jobs = self._cut_all(data_view, weight_view, out_cont, channel_ind)
         nsys = (2 if self.complex_timedomain else 1) * ndelay
@@ -615,7 +620,7 @@ class DelaySpectrumWienerFilter(DelaySpectrumBase):
             if mask_out is not None:
                 mask_out[lbi][~nzt] = 1
 
-        if self.device_cut and self.use_average_weights:
+        if self.device_cut and self.use_average_weights and self._device_cut_serves(data_view):
             # _cut_data on the device for the whole local slab (dgibbs_cut_data); the batch stays in HBM
             vis = np.ascontiguousarray(_local_array(data_view))
             wgt = np.ascontiguousarray(_local_array(weight_view))

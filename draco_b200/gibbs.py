@@ -146,9 +146,11 @@ def cut_batch(vis, weight, channel_ind, N, S0, *, time_frac=-1.0, freq_frac=-1.0
     """``DelayTransformBase._cut_data`` (delay.py:516-597) for a whole raw slab on the GPU, packed in place as
     the ragged batch :func:`run_batch` / :func:`wiener_batch` consume (replaces the loop delay.py:1146-1167).
 
-    ``vis`` [B, T, nfreq] complex128 and ``weight`` [B, T, nfreq] float32/float64 (numpy, or CUDA torch tensors with
-    ``vis`` viewed as float64 [..., 2]); ``channel_ind`` [nfreq]; ``S0`` broadcastable to [B, N].  Weights are
-    always averaged over the kept samples (``use_average_weights=True``)."""
+    ``vis`` [B, T, nfreq] complex128 or complex64 (the dtype draco's containers store, core/containers.py:503; it is
+    uploaded as it is -- half the bytes -- and cut in numpy's complex64 arithmetic, bit for bit) and ``weight``
+    [B, T, nfreq] float32/float64 (numpy, or CUDA torch tensors with ``vis`` viewed as float64 / float32 [..., 2]);
+    ``channel_ind`` [nfreq]; ``S0`` broadcastable to [B, N].  Weights are always averaged over the kept samples
+    (``use_average_weights=True``).  ``scale_freq`` needs complex128 input."""
     import torch
 
     h = handle or get_handle(device)
@@ -158,6 +160,8 @@ def cut_batch(vis, weight, channel_ind, N, S0, *, time_frac=-1.0, freq_frac=-1.0
         if isinstance(a, np.ndarray):
             if a.dtype == np.complex128:
                 a = np.ascontiguousarray(a).view(np.float64)
+            elif a.dtype == np.complex64:
+                a = np.ascontiguousarray(a).view(np.float32)
             elif dtype is not None:
                 a = np.ascontiguousarray(a, dtype=dtype)
             else:
@@ -166,10 +170,17 @@ def cut_batch(vis, weight, channel_ind, N, S0, *, time_frac=-1.0, freq_frac=-1.0
         return a.contiguous()
 
     if isinstance(vis, np.ndarray):
-        vis = np.asarray(vis, dtype=np.complex128)
+        if vis.dtype != np.complex64:
+            vis = np.asarray(vis, dtype=np.complex128)
         B, T, F = vis.shape
+        c64 = vis.dtype == np.complex64
     else:
         B, T, F = vis.shape[:3]
+        c64 = vis.dtype == torch.float32
+        if not c64 and vis.dtype != torch.float64:
+            raise ValueError("device-resident vis must be float64 or float32 [B, T, nfreq, 2]")
+    if c64 and scale_freq:
+        raise ValueError("scale_freq on complex64 data is not served by the device cut; use the host _cut_data")
     if isinstance(weight, np.ndarray) and weight.dtype not in (np.float32, np.float64):
         weight = weight.astype(np.float64)
     d_vis, d_w = to_dev(vis), to_dev(weight)
@@ -192,6 +203,7 @@ def cut_batch(vis, weight, channel_ind, N, S0, *, time_frac=-1.0, freq_frac=-1.0
     c.on_device = 1
     c.B, c.T, c.nfreq = B, T, F
     c.weight_f32 = 1 if w32 else 0
+    c.data_c64 = 1 if c64 else 0
     c.remove_mean, c.scale_freq = int(bool(remove_mean)), int(bool(scale_freq))
     c.time_frac, c.freq_frac, c.weight_boost = float(time_frac), float(freq_frac), float(weight_boost)
     c.data, c.weight, c.channel_ind = _ptr(d_vis), _ptr(d_w), _ptr(d_cind)

@@ -249,10 +249,14 @@ typedef struct {
   int32_t weight_f32;  /* element type of weight: 1 = float32, 0 = float64 */
   int32_t remove_mean; /* delay.py:570-574 */
   int32_t scale_freq;  /* delay.py:580-587 */
+  int32_t data_c64;    /* element type of data: 1 = complex64 (draco's containers store visibilities as complex64,
+                          core/containers.py:503; the mean is then removed in numpy's complex64 arithmetic, bit for bit),
+                          0 = complex128.  scale_freq needs complex128. */
+  int32_t reserved0;   /* keep 0 */
   double time_frac;    /* delay.py:552 */
   double freq_frac;    /* delay.py:560 */
   double weight_boost; /* delay.py:593 */
-  const void* data;           /* [B, T, nfreq] complex128 */
+  const void* data;           /* [B, T, nfreq] complex128 (complex64 with data_c64) */
   const void* weight;         /* [B, T, nfreq] */
   const int64_t* channel_ind; /* [nfreq] channel of each input frequency on the padded grid (delay.py:461-512) */
   void* data_out;    /* [B, T*nfreq] complex128 */

@@ -17,3 +17,8 @@ def recorded_chain(data, N, Ni, S0, window, fsel, niter, cplx, seed=7):
     rec = oracle.RecordingDraws(np.random.default_rng(seed))
     samples, ok = oracle.gibbs_chain(data, N, Ni, S0, window, fsel, niter, rec, cplx)
     return np.array(samples), ok, rec.packed()
+
+
+# parameter sets of tests/golden/make_golden_cut_c64.py (complex64 / float32 _cut_data)
+C64_CASES = [("default", {}), ("timefrac", dict(time_frac=0.3)), ("freqfrac", dict(freq_frac=0.85)),
+             ("nomean", dict(remove_mean=False)), ("boost", dict(weight_boost=2.5, time_frac=0.1))]

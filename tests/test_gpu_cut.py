@@ -53,6 +53,64 @@ def test_cut_matches_reference_golden(golden):
     assert not gibbs.cut_batch(vis[None], wgt[None], cind, 2 * F, 1.0, time_frac=0.0, freq_frac=1.0).alive[0]
 
 
+@pytest.mark.parametrize("tag", ["short", "long"])
+def test_cut_complex64_matches_reference_golden(tag):
+    """complex64 visibilities + float32 weights (draco's container dtypes) go up as they are and come out as the
+    reference's own complex64 ``_cut_data`` result, widened -- bit for bit."""
+    import os
+
+    from draco_b200 import gibbs
+    from _cases import C64_CASES
+
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "reference_cut_c64.npz"))
+    vis, wgt = g[f"{tag}_vis"], g[f"{tag}_wgt"]
+    T, F = vis.shape
+    cind = np.arange(F) * 2 + 1
+    for name, kw in C64_CASES:
+        full = dict(time_frac=0.0, freq_frac=0.0, remove_mean=True, scale_freq=False, weight_boost=1.0)
+        full.update(kw)
+        cr = gibbs.cut_batch(vis[None], wgt[None], cind, 2 * F, 1.0, **full)
+        assert cr.alive.tolist() == [True]
+        assert np.array_equal(cr.keep_t[0], g[f"{tag}_{name}_nzt"])
+        assert np.array_equal(cr.keep_f[0], g[f"{tag}_{name}_nzf"])
+        d, ni, fs = _unpack(cr, 0, T, F)
+        assert np.array_equal(fs, cind[g[f"{tag}_{name}_nzf"]])
+        assert np.array_equal(d, g[f"{tag}_{name}_data"].astype(np.complex128)), name
+        assert np.array_equal(ni, g[f"{tag}_{name}_weight"].astype(np.float64)), name
+    with pytest.raises(ValueError):  # numpy's float32 std is not reproduced on the device: the task cuts on the host
+        gibbs.cut_batch(vis[None], wgt[None], cind, 2 * F, 1.0, scale_freq=True)
+
+
+def test_cut_complex64_ragged_matches_oracle():
+    import oracle
+    from draco_b200 import gibbs
+
+    rng = np.random.default_rng(77)
+    B, T, F = 9, 200, 70
+    vis = ((rng.standard_normal((B, T, F)) + 1j * rng.standard_normal((B, T, F))) * 1e3 + 250.0).astype(np.complex64)
+    wgt = rng.uniform(0.2, 3.0, (B, T, F)).astype(np.float32)
+    for b in range(B):
+        wgt[b][rng.random(T) < 0.1 * b] = 0.0
+        wgt[b][:, rng.random(F) < 0.07 * b] = 0.0
+    wgt[4] = 0.0  # dead baseline
+    vis[wgt == 0] = 0.0
+    cind = np.arange(F)
+    kw = dict(time_frac=0.05, freq_frac=0.05, remove_mean=True, weight_boost=3.0)
+    cr = gibbs.cut_batch(vis, wgt, cind, 2 * F, 1.0, **kw)
+    n = 0
+    for b in range(B):
+        t = oracle.cut_data(vis[b].copy(), wgt[b].copy(), use_average_weights=True, **kw)
+        assert (t is not None) == bool(cr.alive[b])
+        if t is None:
+            continue
+        d, ni, fs = _unpack(cr, n, T, F)
+        n += 1
+        assert t[0].dtype == np.complex64
+        assert np.array_equal(d, t[0].astype(np.complex128))
+        assert np.array_equal(ni, t[1].astype(np.float64))
+        assert np.array_equal(fs, cind[t[2]])
+
+
 @pytest.mark.parametrize("wdtype", [np.float64, np.float32])
 @pytest.mark.parametrize("kw", [dict(remove_mean=True), dict(remove_mean=False, time_frac=0.4, freq_frac=0.3),
                                 dict(remove_mean=True, scale_freq=True, weight_boost=1e3, time_frac=0.2)])

@@ -142,6 +142,40 @@ def test_gibbs_task_device_cut_matches_host_cut():
     assert a.datasets["spectrum_mask"][:].local_array[4] and np.all(a.spectrum[:].local_array[0] > 0)
 
 
+def test_tasks_on_container_dtypes_complex64_float32():
+    """draco's SiderealStream stores complex64 visibilities and float32 weights: the raw slab is uploaded as it is and
+    cut on the device in numpy's complex64 / float32 arithmetic, so both tasks return what the host ``_cut_data``
+    route returns, bit for bit; under ``scale_freq`` the task falls back to the host cut by itself."""
+    from draco_b200 import _compat, delay
+
+    ss64, vis, wgt = _stream()
+    ss = _compat.SiderealStream(freq=ss64.freq, stack=vis.shape[0], ra=vis.shape[1], native_dtypes=True)
+    ss.vis[:] = np.transpose(vis, (2, 0, 1))
+    ss.weight[:] = np.transpose(wgt, (2, 0, 1))
+    assert ss.vis[:].dtype == np.complex64 and ss.weight[:].dtype == np.float32
+    cfg = dict(sample_axis="ra", nsamp=8, seed=5, save_samples=True, save_spectrum_mask=True, time_frac=0.01,
+               weight_boost=3.0)
+    for extra in ({}, {"scale_freq": True}):
+        a = delay.DelayPowerSpectrumGibbs.from_config({**cfg, **extra, "device_cut": True}).process(ss)
+        b = delay.DelayPowerSpectrumGibbs.from_config({**cfg, **extra, "device_cut": False}).process(ss)
+        assert np.array_equal(a.spectrum[:].local_array, b.spectrum[:].local_array)
+        assert np.array_equal(a.datasets["spectrum_samples"][:].local_array, b.datasets["spectrum_samples"][:].local_array)
+        assert np.array_equal(a.datasets["spectrum_mask"][:].local_array, b.datasets["spectrum_mask"][:].local_array)
+        assert np.all(a.spectrum[:].local_array[0] > 0)
+    # not the complex128 result: the float32 rounding of the inputs is visible
+    c = delay.DelayPowerSpectrumGibbs.from_config({**cfg, "device_cut": True}).process(ss64)
+    a = delay.DelayPowerSpectrumGibbs.from_config({**cfg, "device_cut": True}).process(ss)
+    assert not np.array_equal(a.spectrum[:].local_array, c.spectrum[:].local_array)
+    np.testing.assert_allclose(a.spectrum[:].local_array, c.spectrum[:].local_array, rtol=1e-2)
+    dps = delay.DelayPowerSpectrumGibbs.from_config(dict(sample_axis="ra", nsamp=6, seed=3)).process(ss)
+    outs = []
+    for kw in (dict(device_cut=True), dict(device_cut=False)):
+        task = delay.DelaySpectrumWienerFilter.from_config(dict(sample_axis="ra", time_frac=0.01, **kw))
+        task.setup(dps)
+        outs.append(task.process(ss))
+    assert np.array_equal(outs[0].spectrum[:].local_array, outs[1].spectrum[:].local_array)
+
+
 def test_wiener_task_device_cut_matches_host_cut():
     from draco_b200 import delay
 

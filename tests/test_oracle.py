@@ -108,6 +108,24 @@ def test_cut_data(golden):
     assert oracle.cut_data(np.zeros_like(vis), wgt, remove_mean=False) is None and bool(golden["cut_zero_is_none"])
 
 
+def test_cut_data_complex64():
+    """The container dtypes (complex64 visibilities, float32 weights): the oracle keeps the reference's dtypes and
+    arithmetic, bit for bit (tests/golden/make_golden_cut_c64.py)."""
+    import os
+
+    from _cases import C64_CASES
+
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "reference_cut_c64.npz"))
+    for tag in ("short", "long"):
+        vis, wgt = g[f"{tag}_vis"], g[f"{tag}_wgt"]
+        assert vis.dtype == np.complex64 and wgt.dtype == np.float32
+        for name, kw in C64_CASES:
+            res = oracle.cut_data(vis.copy(), wgt.copy(), **kw)
+            for nm, a in zip(("data", "weight", "nzf", "nzt"), res):
+                ref = g[f"{tag}_{name}_{nm}"]
+                assert a.dtype == ref.dtype and np.array_equal(a, ref), (tag, name, nm)
+
+
 def test_ftnif_is_circulant():
     # structure the CUDA path relies on: FTNiF[t,t'] = c[(t-t') mod N] for any mask/weights/window
     data, Ni, fsel, _ = make_case(64, 29, 8, False, False, seed=2)
