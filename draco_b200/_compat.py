@@ -331,7 +331,13 @@ class DelaySpectrum(Container):
         "spectrum_mask": {"axes": ["baseline"], "dtype": bool, "distributed_axis": "baseline"},
     }
 
-    def __init__(self, baseline, delay, sample=1, attrs_from=None, weight_boost=1.0):
+    def __init__(self, baseline=None, delay=None, sample=1, attrs_from=None, weight_boost=1.0, axes_from=None):
+        if axes_from is not None:  # memh5's axes_from: take the axis definitions of another container
+            baseline = axes_from.index_map["baseline"] if baseline is None else baseline
+            delay = axes_from.index_map["delay"] if delay is None else delay
+            if "sample" in axes_from.index_map:
+                sample = axes_from.index_map["sample"]
+            weight_boost = getattr(axes_from, "attrs", {}).get("weight_boost", weight_boost)
         super().__init__(attrs_from=attrs_from, baseline=baseline, sample=sample, delay=delay)
         self.attrs["weight_boost"] = weight_boost
         self.add_dataset("spectrum")

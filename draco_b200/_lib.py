@@ -40,6 +40,8 @@ EXPORTED = [
     "dgibbs_fourier_matrix",
     "dgibbs_cross_run",
     "dgibbs_cut_data",
+    "dgibbs_delay_fft",
+    "dgibbs_sample_variance",
 ]
 CROSS_MAX_DATASETS = 4
 
@@ -191,6 +193,10 @@ def load():
     lib.dgibbs_fourier_matrix.argtypes = [_vp, C.c_int32, C.c_int32, _vp, C.c_int32, _vp]
     lib.dgibbs_cross_run.argtypes = [_vp, C.POINTER(CrossProblem), _vp, _vp, _vp]
     lib.dgibbs_cut_data.argtypes = [_vp, C.POINTER(Cut)]
+    lib.dgibbs_delay_fft.argtypes = [_vp, C.c_int32, C.c_int64, C.c_int32, C.c_int32, C.c_int32, _vp, _vp,
+                                     C.POINTER(C.c_double)]
+    lib.dgibbs_sample_variance.argtypes = [_vp, C.c_int32, C.c_int32, C.c_int32, C.c_int32, _vp, _vp, _vp, _vp,
+                                           C.POINTER(C.c_double)]
     for name in EXPORTED:
         if name not in ("dgibbs_last_error", "dgibbs_version"):
             getattr(lib, name).restype = C.c_int

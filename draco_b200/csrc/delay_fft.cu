@@ -1,0 +1,275 @@
+// Plain (unmasked) delay transform by inverse FFT: delay_spectrum_fft, draco/analysis/delay.py:2102-2130, as used by
+// the task DelaySpectrumFFT (delay.py:960-980): every row (one time sample of one baseline, N complex channels) is
+// multiplied by the generalised cosine window at x = i / N (delay.py:2124-2127), transformed with numpy's ifft
+// convention (sign +, scale 1/N) and, for the task, fftshifted (delay.py:980).
+//
+// HBM-bound: 16 N bytes read and 16 N bytes written per row.  N = 2^m <= 4096 runs as the in-smem Stockham FFT of
+// dense_core.cuh (several CTAs per SM so that the shared-memory passes of one overlap the loads / stores of the
+// others); any other N <= 6400 is a direct O(N^2) DFT against an exact twiddle table in shared memory.
+#include <cstdio>
+#include <string>
+
+#include "dense_core.cuh"
+#include "window.cuh"
+
+#include "../../include/dgibbs.h"
+
+namespace dg {
+
+constexpr int FTHREADS = 256;
+
+__global__ void delay_fft_window_kernel(double* __restrict__ wtab, int N, int window_id) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < N) wtab[i] = window_value(window_id, (double)i / (double)N);
+}
+
+// tw[m] = e^{2 pi i m / N}, all m < N (the direct DFT needs the full circle)
+__global__ void delay_fft_fulltw_kernel(double2* __restrict__ tw, int N) {
+  const int m = blockIdx.x * blockDim.x + threadIdx.x;
+  if (m >= N) return;
+  double c, s;
+  twiddle(m, N, c, s);
+  tw[m] = make_double2(c, s);
+}
+
+__global__ void __launch_bounds__(FTHREADS) delay_fft_pow2_kernel(const double2* __restrict__ x, double2* __restrict__ y,
+                                                                  const double* __restrict__ wtab,
+                                                                  const double2* __restrict__ tw, long long nrows, int N,
+                                                                  int shift) {
+  extern __shared__ __align__(16) double2 fsm[];
+  double2* bufA = fsm;
+  double2* bufB = fsm + N;
+  const double invN = 1.0 / (double)N;
+  const int off = shift ? N / 2 : 0;
+  for (long long r = blockIdx.x; r < nrows; r += gridDim.x) {
+    const double2* xr = x + r * N;
+    __syncthreads();  // the previous row's stores are done with the buffers
+    for (int i = threadIdx.x; i < N; i += FTHREADS) {
+      const double2 v = xr[i];
+      const double w = wtab[i];
+      bufA[i] = make_double2(v.x * w, v.y * w);
+    }
+    __syncthreads();
+    const double2* res = fft_inverse_smem<FTHREADS>(bufA, bufB, tw, N);
+    double2* yr = y + r * N;
+    for (int k = threadIdx.x; k < N; k += FTHREADS) {
+      const double2 v = res[k];
+      yr[(k + off) & (N - 1)] = make_double2(v.x * invN, v.y * invN);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(FTHREADS) delay_dft_direct_kernel(const double2* __restrict__ x, double2* __restrict__ y,
+                                                                    const double* __restrict__ wtab,
+                                                                    const double2* __restrict__ twg, long long nrows, int N,
+                                                                    int shift) {
+  extern __shared__ __align__(16) double2 fsm[];
+  double2* tw = fsm;      // [N]
+  double2* xw = fsm + N;  // [N] windowed row
+  for (int m = threadIdx.x; m < N; m += FTHREADS) tw[m] = twg[m];
+  const double invN = 1.0 / (double)N;
+  const int off = shift ? N / 2 : 0;
+  for (long long r = blockIdx.x; r < nrows; r += gridDim.x) {
+    const double2* xr = x + r * N;
+    __syncthreads();
+    for (int i = threadIdx.x; i < N; i += FTHREADS) {
+      const double2 v = xr[i];
+      const double w = wtab[i];
+      xw[i] = make_double2(v.x * w, v.y * w);
+    }
+    __syncthreads();
+    double2* yr = y + r * N;
+    for (int k = threadIdx.x; k < N; k += FTHREADS) {
+      double ar = 0.0, ai = 0.0;
+      int m = 0;
+      for (int f = 0; f < N; f++) {
+        const double2 a = xw[f], t = tw[m];
+        ar += a.x * t.x - a.y * t.y;
+        ai += a.x * t.y + a.y * t.x;
+        m += k;
+        if (m >= N) m -= N;
+      }
+      int ko = k + off;
+      if (ko >= N) ko -= N;
+      yr[ko] = make_double2(ar * invN, ai * invN);
+    }
+  }
+}
+
+// DelaySpectrumToPowerSpectrum.process (delay.py:1061-1106): ps[b, n] = var_t spec[b, t, n] over the unmasked samples
+// (numpy's _var: mean = sum * (1 / count) per component, sum of |x - mean|^2 in sample order, divided by the count);
+// with a mask, a baseline without any unmasked sample gives NaN -> 0 and sets the baseline's flag.
+__global__ void __launch_bounds__(256) sample_variance_kernel(const double2* __restrict__ spec,
+                                                             const unsigned char* __restrict__ mask, double* __restrict__ var,
+                                                             unsigned char* __restrict__ bad, int T, int N) {
+  const int b = blockIdx.y;
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= N) return;
+  const double2* x = spec + (size_t)b * T * N + n;
+  const unsigned char* mk = mask ? mask + (size_t)b * T : nullptr;
+  double sr = 0.0, si = 0.0;
+  int cnt = 0;
+  for (int t = 0; t < T; t++) {
+    if (mk && mk[t]) continue;
+    const double2 v = x[(size_t)t * N];
+    sr += v.x;
+    si += v.y;
+    cnt++;
+  }
+  const double scl = 1.0 / (double)cnt;  // inf for an empty selection: 0 * inf = NaN, as numpy's 0 / 0
+  const double mr = sr * scl, mi = si * scl;
+  double acc = 0.0;
+  for (int t = 0; t < T; t++) {
+    if (mk && mk[t]) continue;
+    const double2 v = x[(size_t)t * N];
+    const double dx = v.x - mr, dy = v.y - mi;
+    acc += __dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy));
+  }
+  double out = cnt > 0 ? acc / (double)cnt : __longlong_as_double(0x7ff8000000000000LL);
+  if (mask && out != out) {  // delay.py:1099-1104
+    out = 0.0;
+    if (bad) bad[b] = 1;  // every thread that sees a NaN writes the same value
+  }
+  var[(size_t)b * N + n] = out;
+}
+
+}  // namespace dg
+
+using namespace dg;
+
+#define FCU(call)                                                                                             \
+  do {                                                                                                        \
+    cudaError_t e_ = (call);                                                                                  \
+    if (e_ != cudaSuccess) {                                                                                  \
+      char msg_[512];                                                                                         \
+      snprintf(msg_, sizeof msg_, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+      dg_set_error(h, msg_);                                                                                  \
+      return (int)e_;                                                                                         \
+    }                                                                                                         \
+  } while (0)
+
+// delay_spectrum_fft (delay.py:2102-2130) for nrows rows at once; shift = 1 adds the fftshift of
+// DelaySpectrumFFT._estimator (delay.py:980).
+extern "C" int dgibbs_delay_fft(dgibbs_handle h, int32_t on_device, int64_t nrows, int32_t N, int32_t window_id,
+                                int32_t shift, const void* data, void* out, double* ms_kernel) {
+  if (!h) return -1;
+  auto bad = [&](const char* what) {
+    dg_set_error(h, (std::string("bad argument: ") + what).c_str());
+    return -2;
+  };
+  if (nrows < 0 || N <= 0) return bad("nrows >= 0 and N > 0 are required");
+  if (window_id < -1 || window_id > 7) return bad("window_id");
+  if (ms_kernel) *ms_kernel = 0.0;
+  if (nrows == 0) return 0;
+  if (!data || !out) return bad("data and out are required");
+  const bool pow2 = N >= 8 && (N & (N - 1)) == 0 && N <= 4096;
+  if (!pow2 && (size_t)N * 32 > 200 * 1024) return bad("N must be a power of two <= 4096 or any N <= 6400");
+  FCU(cudaSetDevice(dg_device(h)));
+  cudaStream_t st = dg_stream(h);
+  const size_t bytes = (size_t)nrows * (size_t)N * 16;
+  const double2* x = (const double2*)data;
+  double2* y = (double2*)out;
+  void* q;
+  if (!on_device) {
+    FCU(dg_pool_get(h, "dfft_in", bytes, &q));
+    FCU(cudaMemcpyAsync(q, data, bytes, cudaMemcpyHostToDevice, st));
+    x = (const double2*)q;
+    FCU(dg_pool_get(h, "dfft_out", bytes, &q));
+    y = (double2*)q;
+  }
+  FCU(dg_pool_get(h, "dfft_window", sizeof(double) * (size_t)N, &q));
+  double* wtab = (double*)q;
+  delay_fft_window_kernel<<<(N + 255) / 256, 256, 0, st>>>(wtab, N, window_id);
+  FCU(dg_pool_get(h, "dfft_tw", sizeof(double2) * (size_t)N, &q));
+  double2* tw = (double2*)q;
+  if (pow2)
+    FCU(launch_build_twtab(N, tw, st));
+  else
+    delay_fft_fulltw_kernel<<<(N + 255) / 256, 256, 0, st>>>(tw, N);
+  FCU(cudaGetLastError());
+
+  const size_t smem = (size_t)N * 2 * sizeof(double2);
+  void (*kern)(const double2*, double2*, const double*, const double2*, long long, int, int) =
+      pow2 ? delay_fft_pow2_kernel : delay_dft_direct_kernel;
+  FCU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int occ = 0;
+  FCU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, FTHREADS, smem));
+  if (occ < 1) return bad("the transform does not fit in shared memory");
+  long long grid = (long long)occ * dg_sm_count(h);
+  if (grid > nrows) grid = nrows;
+  cudaEvent_t e0, e1;
+  FCU(cudaEventCreate(&e0));
+  FCU(cudaEventCreate(&e1));
+  FCU(cudaEventRecord(e0, st));
+  kern<<<(unsigned)grid, FTHREADS, smem, st>>>(x, y, wtab, tw, (long long)nrows, N, shift ? 1 : 0);
+  FCU(cudaEventRecord(e1, st));
+  FCU(cudaGetLastError());
+  if (!on_device) FCU(cudaMemcpyAsync(out, y, bytes, cudaMemcpyDeviceToHost, st));
+  FCU(cudaStreamSynchronize(st));
+  float ms = 0.f;
+  FCU(cudaEventElapsedTime(&ms, e0, e1));
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  if (ms_kernel) *ms_kernel = (double)ms;
+  return 0;
+}
+
+// DelaySpectrumToPowerSpectrum (delay.py:1061-1106): variance over the sample axis of a [B, T, N] complex128 delay
+// spectrum; mask [B, T] (1 = masked sample, may be NULL); bad [B] receives 1 where the variance was NaN (may be NULL,
+// only written with a mask, as in the reference).
+extern "C" int dgibbs_sample_variance(dgibbs_handle h, int32_t on_device, int32_t B, int32_t T, int32_t N, const void* spec,
+                                      const uint8_t* mask, double* var, uint8_t* bad, double* ms_kernel) {
+  if (!h) return -1;
+  auto badarg = [&](const char* what) {
+    dg_set_error(h, (std::string("bad argument: ") + what).c_str());
+    return -2;
+  };
+  if (B < 0 || T <= 0 || N <= 0) return badarg("B >= 0, T > 0 and N > 0 are required");
+  if (B > 65535) return badarg("at most 65535 baselines per call");
+  if (ms_kernel) *ms_kernel = 0.0;
+  if (B == 0) return 0;
+  if (!spec || !var) return badarg("spec and var are required");
+  FCU(cudaSetDevice(dg_device(h)));
+  cudaStream_t st = dg_stream(h);
+  const size_t nb = (size_t)B * T * N * 16;
+  const double2* x = (const double2*)spec;
+  const unsigned char* mk = mask;
+  double* v = var;
+  unsigned char* bd = bad;
+  void* q;
+  if (!on_device) {
+    FCU(dg_pool_get(h, "svar_in", nb, &q));
+    FCU(cudaMemcpyAsync(q, spec, nb, cudaMemcpyHostToDevice, st));
+    x = (const double2*)q;
+    if (mask) {
+      FCU(dg_pool_get(h, "svar_mask", (size_t)B * T, &q));
+      FCU(cudaMemcpyAsync(q, mask, (size_t)B * T, cudaMemcpyHostToDevice, st));
+      mk = (const unsigned char*)q;
+    }
+    FCU(dg_pool_get(h, "svar_out", (size_t)B * N * 8, &q));
+    v = (double*)q;
+    if (bad) {
+      FCU(dg_pool_get(h, "svar_bad", (size_t)B, &q));
+      bd = (unsigned char*)q;
+    }
+  }
+  if (bd) FCU(cudaMemsetAsync(bd, 0, (size_t)B, st));
+  cudaEvent_t e0, e1;
+  FCU(cudaEventCreate(&e0));
+  FCU(cudaEventCreate(&e1));
+  FCU(cudaEventRecord(e0, st));
+  sample_variance_kernel<<<dim3((N + 255) / 256, B), 256, 0, st>>>(x, mk, v, bd, T, N);
+  FCU(cudaEventRecord(e1, st));
+  FCU(cudaGetLastError());
+  if (!on_device) {
+    FCU(cudaMemcpyAsync(var, v, (size_t)B * N * 8, cudaMemcpyDeviceToHost, st));
+    if (bad) FCU(cudaMemcpyAsync(bad, bd, (size_t)B, cudaMemcpyDeviceToHost, st));
+  }
+  FCU(cudaStreamSynchronize(st));
+  float ms = 0.f;
+  FCU(cudaEventElapsedTime(&ms, e0, e1));
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  if (ms_kernel) *ms_kernel = (double)ms;
+  return 0;
+}

@@ -655,9 +655,123 @@ class DelaySpectrumWienerFilter(DelaySpectrumBase):
         return out_cont
 
 
+class DelaySpectrumFFT(DelaySpectrumBase):
+    """Delay spectrum of a general container via a windowed inverse FFT (delay.py:960-980 over
+    ``delay_spectrum_fft``, delay.py:2102-2130).  As in the reference, the transform ignores masking and needs the full
+    channel set (``complex_timedomain: true`` and no frequency cut: the window has one entry per delay).  All local
+    baselines go through ONE device call (``dgibbs_delay_fft``: window, inverse FFT, 1/N and the fftshift fused)."""
+
+    device_cut = config.Property(proptype=bool, default=True)
+
+    def _get_prior(self, nbase):
+        return [None] * nbase
+
+    def _estimator(self, data, weight, S, ndelay, channel_ind):
+        y_spec = gibbs.delay_spectrum_fft(data, ndelay, self.window if self.apply_window else None, device=self._device())
+        return np.fft.fftshift(y_spec, axes=-1)
+
+    @staticmethod
+    def _check_width(nchan, ndelay):
+        if nchan != ndelay:  # the reference's `data *= window` (delay.py:2127) fails to broadcast
+            raise ValueError(f"operands could not be broadcast together with shapes (nsample,{nchan}) (1,{ndelay})")
+
+    def _evaluate(self, data_view, weight_view, out_cont, delays, channel_ind):
+        """Batched replacement of the loop delay.py:899-930."""
+        ndelay = len(delays)
+        spec_out = _local(out_cont.spectrum)
+        mask_out = _local(out_cont.datasets["spectrum_mask"]) if self.save_spectrum_mask else None
+        handle = gibbs.get_handle(self._device())
+        window = self.window if self.apply_window else None
+        if self.device_cut and self._device_cut_serves(data_view):
+            vis = np.ascontiguousarray(_local_array(data_view))
+            wgt = np.ascontiguousarray(_local_array(weight_view))
+            nloc, T, F = vis.shape
+            step = self.batch_baselines if self.batch_baselines and self.batch_baselines > 0 else max(1, nloc)
+            for s0 in range(0, nloc, step):
+                s1 = min(nloc, s0 + step)
+                cr = gibbs.cut_batch(vis[s0:s1], wgt[s0:s1], channel_ind, ndelay, 1.0, time_frac=self.time_frac,
+                                     freq_frac=self.freq_frac, remove_mean=self.remove_mean, scale_freq=self.scale_freq,
+                                     weight_boost=self.weight_boost, window=window,
+                                     complex_timedomain=self.complex_timedomain, handle=handle)
+                if mask_out is not None:
+                    mask_out[s0:s1][~cr.alive] = 1  # delay.py:917-920
+                if cr.batch is None:
+                    continue
+                for m in cr.batch.M.cpu().numpy():
+                    self._check_width(int(m), ndelay)
+                self._check_width(F, ndelay)
+                # every surviving baseline kept all F = ndelay channels: its kept samples are the leading rows of its
+                # [T, F] slot of the cut slab, which is transformed as it lies in HBM
+                y = gibbs.fft_rows(cr.batch.data.view(-1, F, 2), window, shift=True, handle=handle)
+                y = y.cpu().numpy().view(np.complex128).reshape(s1 - s0, T, F)
+                for lb in cr.index:
+                    nzt = cr.keep_t[lb]
+                    spec_out[s0 + lb, nzt] = y[lb, : int(nzt.sum())]
+                    if mask_out is not None:
+                        mask_out[s0 + lb][~nzt] = 1  # delay.py:929-930
+            return out_cont
+        jobs = self._cut_all(data_view, weight_view, out_cont, channel_ind)
+        for chunk in self._chunks(jobs):
+            for j in chunk:
+                self._check_width(j[2].shape[1], ndelay)
+            rows = np.concatenate([np.asarray(j[2], dtype=np.complex128) for j in chunk], axis=0)
+            y = gibbs.fft_rows(rows, window, shift=True, handle=handle)
+            o = 0
+            for lbi, bi, d, _w, _f, nzt in chunk:
+                spec_out[lbi, nzt] = y[o : o + d.shape[0]]
+                o += d.shape[0]
+                if mask_out is not None:
+                    mask_out[lbi][~nzt] = 1
+        return out_cont
+
+
+class DelaySpectrumToPowerSpectrum(_ContainerTask):
+    """Delay power spectrum = variance over the sample axis of a delay spectrum (delay.py:1061-1106), one device
+    reduction (``dgibbs_sample_variance``) over the local ``[baseline, sample, delay]`` slab."""
+
+    device = config.Property(proptype=int, default=None)
+
+    def process(self, dspec):
+        dspec.redistribute("baseline")
+        pspec = containers.DelaySpectrum(attrs_from=dspec, axes_from=dspec)
+        pspec.redistribute("baseline")
+        mask = None
+        if "spectrum_mask" in dspec.datasets:
+            mask = _local(dspec.datasets["spectrum_mask"])
+            pspec.add_dataset("spectrum_mask")
+            pspec.datasets["spectrum_mask"][:] = 0
+        dev = self.device
+        if dev is None:
+            import torch
+
+            dev = comm_rank_size()[0] % max(1, torch.cuda.device_count())
+        var, bad = gibbs.sample_variance(_local(dspec.spectrum), mask, device=dev)
+        _local(pspec.spectrum)[:] = var
+        if mask is not None:
+            _local(pspec.datasets["spectrum_mask"])[:] = bad
+        return pspec
+
+
 class DelaySpectrumWienerFilterIteratePS(DelaySpectrumWienerFilter):
     """Variant whose power spectrum arrives with every ``process`` call (delay.py:1027-1053)."""
 
     def process(self, ss, dps):
         self.dps = dps
         return super().process(ss)
+
+
+class DelayPowerSpectrumStokesIEstimator(DelayPowerSpectrumGibbs):
+    """Deprecated (delay.py:1451-1461)."""
+
+    def setup(self, requires=None):
+        raise DeprecationWarning("`DelayPowerSpectrumStokesIEstimator` is deprecated. Use `draco.transform.StokesI` to "
+                                 "generate Stokes I visibilities, then use `DelayPowerSpectrumGibbs` or "
+                                 "`DelayPowerSpectrumNRML`.")
+
+
+class DelayPowerSpectrumGeneralEstimator(DelayPowerSpectrumGibbs):
+    """Deprecated (delay.py:1464-1472)."""
+
+    def setup(self, requires=None):
+        raise DeprecationWarning("`DelayPowerSpectrumGeneralEstimator` is deprecated. Use `DelayPowerSpectrumGibbs` or "
+                                 "`DelayPowerSpectrumNRML`.")

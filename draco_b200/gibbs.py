@@ -440,6 +440,68 @@ def wiener_batch(pb: PackedBatch, *, handle: Handle | None = None):
     return res, ok.astype(bool)
 
 
+def fft_rows(rows, window="nuttall", *, shift=False, handle: Handle | None = None, device=0, timing=None):
+    """``delay_spectrum_fft`` (delay.py:2102-2130) for a stack of rows ``[..., N]`` complex128 on the GPU
+    (``dgibbs_delay_fft``): ``ifft(rows * window(i / N))``, optionally fftshifted along the delay axis (the task's
+    ``np.fft.fftshift``, delay.py:980).  numpy in / numpy out, or a CUDA float64 tensor ``[..., N, 2]`` in / out."""
+    if window not in WINDOW_IDS:
+        raise ValueError(f"window {window!r} is not one of {sorted(k for k in WINDOW_IDS if k)}")
+    ms = C.c_double(0.0)
+    if isinstance(rows, np.ndarray):
+        x = np.ascontiguousarray(rows, dtype=np.complex128)
+        N = x.shape[-1]
+        out = np.empty_like(x)
+        h = handle or get_handle(device)
+        h.check(h.lib.dgibbs_delay_fft(h._h, 0, x.size // max(N, 1), N, WINDOW_IDS[window], int(bool(shift)), _ptr(x),
+                                       _ptr(out), C.byref(ms)), "dgibbs_delay_fft")
+    else:
+        import torch
+
+        x = rows.contiguous()
+        if x.dtype != torch.float64 or x.shape[-1] != 2:
+            raise ValueError("device rows must be float64 [..., N, 2]")
+        N = x.shape[-2]
+        out = torch.empty_like(x)
+        h = handle or get_handle(x.device.index or 0)
+        torch.cuda.current_stream(x.device).synchronize()
+        h.check(h.lib.dgibbs_delay_fft(h._h, 1, x.numel() // max(2 * N, 1), N, WINDOW_IDS[window], int(bool(shift)),
+                                       _ptr(x), _ptr(out), C.byref(ms)), "dgibbs_delay_fft")
+    if timing is not None:
+        timing["ms_kernel"] = ms.value
+    return out
+
+
+def delay_spectrum_fft(data, N, window="nuttall", *, device=0):
+    """Drop-in for ``delay_spectrum_fft`` (delay.py:2102-2130): ``data[nsample, N]`` -> ``[nsample, N]`` complex128,
+    unshifted.  (The reference multiplies ``data`` by the window in place; the input is left untouched here.)"""
+    data = np.asarray(data)
+    if data.shape[-1] != N:  # the reference's `data *= window` cannot broadcast otherwise
+        raise ValueError(f"operands could not be broadcast together with shapes {data.shape} (1,{N})")
+    return fft_rows(data, window, shift=False, device=device)
+
+
+def sample_variance(spec, mask=None, *, handle: Handle | None = None, device=0, timing=None):
+    """``np.var(spec, axis=1, where=~mask[..., None])`` of a ``[B, T, N]`` complex128 delay spectrum on the GPU
+    (``dgibbs_sample_variance``; DelaySpectrumToPowerSpectrum.process, delay.py:1061-1106).  Returns ``(var[B, N],
+    bad[B])``; with a mask, NaN variances are replaced by 0 and flagged in ``bad`` (delay.py:1099-1104)."""
+    x = np.ascontiguousarray(spec, dtype=np.complex128)
+    if x.ndim != 3:
+        raise ValueError("spec must be [baseline, sample, delay]")
+    B, T, N = x.shape
+    var = np.empty((B, N), dtype=np.float64)
+    bad = np.zeros(B, dtype=np.uint8)
+    mk = None if mask is None else np.ascontiguousarray(np.asarray(mask).astype(bool).reshape(B, T), dtype=np.uint8)
+    ms = C.c_double(0.0)
+    h = handle or get_handle(device)
+    for b0 in range(0, B, 65535):
+        b1 = min(B, b0 + 65535)
+        h.check(h.lib.dgibbs_sample_variance(h._h, 0, b1 - b0, T, N, _ptr(x[b0:b1]), None if mk is None else _ptr(mk[b0:b1]),
+                                             _ptr(var[b0:b1]), _ptr(bad[b0:b1]), C.byref(ms)), "dgibbs_sample_variance")
+    if timing is not None:
+        timing["ms_kernel"] = ms.value
+    return var, bad.astype(bool)
+
+
 def compute_delay_spectrum_inputs(data, N, Ni, fsel, window, complex_timedomain, *, device=0):
     """Device evaluation of ``_compute_delay_spectrum_inputs`` (delay.py:1657-1710):
     ``(data_w (2M,T), FTNih (n_sys,2M), FTNiF (n_sys,n_sys))``."""

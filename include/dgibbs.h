@@ -271,6 +271,23 @@ typedef struct {
 
 int dgibbs_cut_data(dgibbs_handle h, const dgibbs_cut* c);
 
+/* ---------------------------------------------------------------------------------------------
+ * Plain delay transform by inverse FFT: delay_spectrum_fft, draco/analysis/delay.py:2102-2130 (task DelaySpectrumFFT,
+ * delay.py:960-980), for nrows rows of N complex128 channels at once: out[r] = ifft(data[r] * window(i / N)) in
+ * numpy's convention (sign +, scale 1/N); shift = 1 adds the fftshift of DelaySpectrumFFT._estimator (delay.py:980).
+ * window_id as in dgibbs_problem (-1 = none).  N = 2^m <= 4096 runs as an in-smem FFT, any other N <= 6400 as a
+ * direct DFT.  data / out are host pointers (on_device = 0) or device pointers; out may not alias data.
+ * ms_kernel (may be NULL) receives the CUDA-event time of the transform kernel. */
+int dgibbs_delay_fft(dgibbs_handle h, int32_t on_device, int64_t nrows, int32_t N, int32_t window_id, int32_t shift,
+                     const void* data, void* out, double* ms_kernel);
+
+/* DelaySpectrumToPowerSpectrum.process, draco/analysis/delay.py:1061-1106: var[b, n] = variance over the unmasked
+ * samples t of spec[b, t, n] (complex128, [B, T, N]); mask [B, T] with 1 = masked sample (the DelayTransform's
+ * spectrum_mask) or NULL.  With a mask, NaN results (no unmasked sample) become 0 and bad[b] = 1 (delay.py:1099-1104);
+ * bad may be NULL. */
+int dgibbs_sample_variance(dgibbs_handle h, int32_t on_device, int32_t B, int32_t T, int32_t N, const void* spec,
+                           const uint8_t* mask, double* var, uint8_t* bad, double* ms_kernel);
+
 #ifdef __cplusplus
 }
 #endif

@@ -36,3 +36,4 @@ from .cross_oracle import (  # noqa: F401,E402
     standard_complex_normal,
     standard_complex_wishart,
 )
+from .transform_oracle import delay_spectrum_fft, delay_spectrum_to_power_spectrum  # noqa: F401,E402
