@@ -23,6 +23,36 @@ __global__ void delay_fft_window_kernel(double* __restrict__ wtab, int N, int wi
   if (i < N) wtab[i] = window_value(window_id, (double)i / (double)N);
 }
 
+// One stage's twiddle tables: t[i * cnt + k] = e^{2 pi i (m_i k s) / N}, k < cnt, i < ntab (exact integer phase)
+__global__ void delay_fft_stage_tw_kernel(double2* __restrict__ t, int N, int cnt, int s, int m0, int m1, int m2, int ntab) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= cnt) return;
+  const int mult[3] = {m0, m1, m2};
+  for (int i = 0; i < ntab; i++) {
+    double c, sn;
+    twiddle(((long long)mult[i] * k * s) % N, N, c, sn);
+    t[(size_t)i * cnt + k] = make_double2(c, sn);
+  }
+}
+
+// Tables of every stage after the first, in stage order (the layout fft_inverse_fused walks through).
+static cudaError_t build_stage_twiddles(double2* t, int N, cudaStream_t st) {
+  int Ns = 1;
+  size_t off = 0;
+  while (Ns * 8 <= N) {
+    if (Ns > 1) {
+      delay_fft_stage_tw_kernel<<<(Ns + 255) / 256, 256, 0, st>>>(t + off, N, Ns, N / (8 * Ns), 1, 2, 4, 3);
+      off += 3 * (size_t)Ns;
+    }
+    Ns <<= 3;
+  }
+  if (Ns * 4 == N)
+    delay_fft_stage_tw_kernel<<<(N / 4 + 255) / 256, 256, 0, st>>>(t + off, N, N / 4, 1, 1, 2, 3, 3);
+  else if (Ns * 2 == N)
+    delay_fft_stage_tw_kernel<<<(N / 2 + 255) / 256, 256, 0, st>>>(t + off, N, N / 2, 1, 1, 0, 0, 1);
+  return cudaGetLastError();
+}
+
 // tw[m] = e^{2 pi i m / N}, all m < N (the direct DFT needs the full circle)
 __global__ void delay_fft_fulltw_kernel(double2* __restrict__ tw, int N) {
   const int m = blockIdx.x * blockDim.x + threadIdx.x;
@@ -32,31 +62,134 @@ __global__ void delay_fft_fulltw_kernel(double2* __restrict__ tw, int N) {
   tw[m] = make_double2(c, s);
 }
 
-__global__ void __launch_bounds__(FTHREADS) delay_fft_pow2_kernel(const double2* __restrict__ x, double2* __restrict__ y,
-                                                                  const double* __restrict__ wtab,
-                                                                  const double2* __restrict__ tw, long long nrows, int N,
-                                                                  int shift) {
+// Inverse (sign +) Stockham FFT of N = 2^m >= 8 points whose first stage reads its inputs through ld(i) (global
+// memory: the windowed row) and whose last stage hands its outputs to st(k, value) (global memory: scaled, shifted)
+// -- two passes over shared memory and two barriers fewer than staging the row first.  Same butterflies and swizzle
+// as fft_inverse_smem (dense_core.cuh); the twiddles come from per-stage tables laid out contiguously in the butterfly
+// index (build_stage_twiddles): a table look-up costs 4 L1 wavefronts per warp, where the strided look-ups into one
+// shared e^(2 pi i m / N) table cost up to 32 each and made the LSU data pipe the bound (ncu: 79 % busy, two thirds
+// of it twiddle loads); af() runs once the thread's own first-stage inputs are consumed
+// (the hook for prefetching the next transform's inputs).  The caller synchronises the CTA between two transforms.
+template <int NT, class Load, class AfterFirst, class Store>
+__device__ __forceinline__ void fft_inverse_fused(double2* x, double2* y, const double2* stw, int N, Load ld, AfterFirst af,
+                                                  Store st) {
+  int Ns = 1;
+  bool swz = false;
+  const int e8 = N >> 3;
+  while (Ns * 8 <= N) {
+    const int s = N / (8 * Ns);
+    const bool first = Ns == 1, last = Ns * 8 == N;
+    const bool swz_out = first && !last;
+    for (int j = threadIdx.x; j < e8; j += NT) {
+      const int k = j & (Ns - 1);
+      double2 v[8];
+      if (first) {
+#pragma unroll
+        for (int r = 0; r < 8; r++) v[r] = ld(j + r * e8);
+      } else {
+#pragma unroll
+        for (int r = 0; r < 8; r++) v[r] = x[fft_swz(j + r * e8, swz)];
+        // w^(k s), w^(2 k s), w^(4 k s) from this stage's table (contiguous in k: coalesced), the rest by products
+        const double2 w1 = stw[k], w2 = stw[Ns + k], w4 = stw[2 * Ns + k];
+        const double2 w3 = cmul(w1, w2), w5 = cmul(w1, w4), w6 = cmul(w2, w4);
+        const double2 w7 = cmul(w3, w4);
+        v[1] = cmul(v[1], w1); v[2] = cmul(v[2], w2); v[3] = cmul(v[3], w3); v[4] = cmul(v[4], w4);
+        v[5] = cmul(v[5], w5); v[6] = cmul(v[6], w6); v[7] = cmul(v[7], w7);
+      }
+      dft4_inv(v[0], v[2], v[4], v[6]);
+      dft4_inv(v[1], v[3], v[5], v[7]);
+      const double h = 0.70710678118654752440;
+      const double2 o1 = make_double2((v[3].x - v[3].y) * h, (v[3].x + v[3].y) * h);
+      const double2 o2 = make_double2(-v[5].y, v[5].x);
+      const double2 o3 = make_double2(-(v[7].x + v[7].y) * h, (v[7].x - v[7].y) * h);
+      const int j0 = ((j - k) << 3) + k;
+      const double2 r0 = cadd(v[0], v[1]), r1 = cadd(v[2], o1), r2 = cadd(v[4], o2), r3 = cadd(v[6], o3);
+      const double2 r4 = csub(v[0], v[1]), r5 = csub(v[2], o1), r6 = csub(v[4], o2), r7 = csub(v[6], o3);
+      if (last) {
+        st(j0, r0); st(j0 + Ns, r1); st(j0 + 2 * Ns, r2); st(j0 + 3 * Ns, r3);
+        st(j0 + 4 * Ns, r4); st(j0 + 5 * Ns, r5); st(j0 + 6 * Ns, r6); st(j0 + 7 * Ns, r7);
+      } else {
+        y[fft_swz(j0, swz_out)] = r0;
+        y[fft_swz(j0 + Ns, swz_out)] = r1;
+        y[fft_swz(j0 + 2 * Ns, swz_out)] = r2;
+        y[fft_swz(j0 + 3 * Ns, swz_out)] = r3;
+        y[fft_swz(j0 + 4 * Ns, swz_out)] = r4;
+        y[fft_swz(j0 + 5 * Ns, swz_out)] = r5;
+        y[fft_swz(j0 + 6 * Ns, swz_out)] = r6;
+        y[fft_swz(j0 + 7 * Ns, swz_out)] = r7;
+      }
+    }
+    if (first) af();  // the first-stage inputs of this thread are consumed
+    if (last) return;
+    __syncthreads();
+    double2* tmp = x; x = y; y = tmp;
+    if (!first) stw += 3 * Ns;
+    Ns <<= 3;
+    swz = swz_out;
+  }
+  if (Ns * 4 == N) {  // last stage, radix 4
+    const int quarter = N >> 2;
+    for (int j = threadIdx.x; j < quarter; j += NT) {
+      double2 v0 = x[fft_swz(j, swz)], v1 = x[fft_swz(j + quarter, swz)], v2 = x[fft_swz(j + 2 * quarter, swz)],
+              v3 = x[fft_swz(j + 3 * quarter, swz)];
+      v1 = cmul(v1, stw[j]);
+      v2 = cmul(v2, stw[quarter + j]);
+      v3 = cmul(v3, stw[2 * quarter + j]);
+      dft4_inv(v0, v1, v2, v3);
+      st(j, v0); st(j + quarter, v1); st(j + 2 * quarter, v2); st(j + 3 * quarter, v3);
+    }
+  } else {  // last stage, radix 2
+    const int half = N >> 1;
+    for (int j = threadIdx.x; j < half; j += NT) {
+      const double2 v0 = x[fft_swz(j, swz)], v1 = cmul(x[fft_swz(j + half, swz)], stw[j]);
+      st(j, cadd(v0, v1));
+      st(j + half, csub(v0, v1));
+    }
+  }
+}
+
+// One CTA of NT = clamp(N / 8, 32, 256) threads per row at a time (every thread owns a radix-8 butterfly), as many
+// CTAs per SM as three N-point buffers allow.  The row after the current one is prefetched with cp.async into the
+// third buffer while the current one is transformed: a thread copies exactly the elements its own first-stage
+// butterflies will read (j + r N/8), so its own cp.async.wait_group is all the synchronisation the inputs need, and
+// it refills a slot only after it has consumed it.  HBM reads, the shared-memory passes and the stores overlap.
+template <int NT>
+__global__ void __launch_bounds__(NT) delay_fft_pow2_kernel(const double2* __restrict__ x, double2* __restrict__ y,
+                                                            const double* __restrict__ wtab,
+                                                            const double2* __restrict__ tw, long long nrows, int N,
+                                                            int shift) {
   extern __shared__ __align__(16) double2 fsm[];
   double2* bufA = fsm;
   double2* bufB = fsm + N;
+  double2* bufC = fsm + 2 * N;  // raw inputs of the next row
   const double invN = 1.0 / (double)N;
   const int off = shift ? N / 2 : 0;
+  const int e8 = N >> 3;
+  auto prefetch = [&](long long r) {
+    if (r < nrows) {
+      const double2* xr = x + r * N;
+      for (int j = threadIdx.x; j < e8; j += NT)
+#pragma unroll
+        for (int q = 0; q < 8; q++) cp_async16(bufC + j + q * e8, xr + j + q * e8);
+    }
+    cp_async_commit();
+  };
+  prefetch(blockIdx.x);
   for (long long r = blockIdx.x; r < nrows; r += gridDim.x) {
-    const double2* xr = x + r * N;
-    __syncthreads();  // the previous row's stores are done with the buffers
-    for (int i = threadIdx.x; i < N; i += FTHREADS) {
-      const double2 v = xr[i];
-      const double w = wtab[i];
-      bufA[i] = make_double2(v.x * w, v.y * w);
-    }
-    __syncthreads();
-    const double2* res = fft_inverse_smem<FTHREADS>(bufA, bufB, tw, N);
     double2* yr = y + r * N;
-    for (int k = threadIdx.x; k < N; k += FTHREADS) {
-      const double2 v = res[k];
-      yr[(k + off) & (N - 1)] = make_double2(v.x * invN, v.y * invN);
-    }
+    cp_async_wait<0>();
+    __syncthreads();  // the previous row's last stage is done reading bufA / bufB
+    fft_inverse_fused<NT>(
+        bufA, bufB, tw, N,
+        [&](int i) {
+          const double2 v = bufC[i];
+          const double w = wtab[i];
+          return make_double2(v.x * w, v.y * w);
+        },
+        [&]() { prefetch(r + gridDim.x); },
+        [&](int k, double2 v) { yr[(k + off) & (N - 1)] = make_double2(v.x * invN, v.y * invN); });
   }
+  cp_async_wait<0>();
 }
 
 __global__ void __launch_bounds__(FTHREADS) delay_dft_direct_kernel(const double2* __restrict__ x, double2* __restrict__ y,
@@ -180,20 +313,26 @@ extern "C" int dgibbs_delay_fft(dgibbs_handle h, int32_t on_device, int64_t nrow
   FCU(dg_pool_get(h, "dfft_window", sizeof(double) * (size_t)N, &q));
   double* wtab = (double*)q;
   delay_fft_window_kernel<<<(N + 255) / 256, 256, 0, st>>>(wtab, N, window_id);
-  FCU(dg_pool_get(h, "dfft_tw", sizeof(double2) * (size_t)N, &q));
+  FCU(dg_pool_get(h, "dfft_tw", sizeof(double2) * 2 * (size_t)N, &q));  // stage tables: <= 3 (8 + 64 + 512) + 3 N / 4 entries
   double2* tw = (double2*)q;
   if (pow2)
-    FCU(launch_build_twtab(N, tw, st));
+    FCU(build_stage_twiddles(tw, N, st));
   else
     delay_fft_fulltw_kernel<<<(N + 255) / 256, 256, 0, st>>>(tw, N);
   FCU(cudaGetLastError());
 
-  const size_t smem = (size_t)N * 2 * sizeof(double2);
-  void (*kern)(const double2*, double2*, const double*, const double2*, long long, int, int) =
-      pow2 ? delay_fft_pow2_kernel : delay_dft_direct_kernel;
+  const size_t smem = (size_t)N * (pow2 ? 3 : 2) * sizeof(double2);
+  void (*kern)(const double2*, double2*, const double*, const double2*, long long, int, int) = delay_dft_direct_kernel;
+  int nthreads = FTHREADS;
+  if (pow2) {
+    if (N >= 2048) { kern = delay_fft_pow2_kernel<256>; nthreads = 256; }
+    else if (N == 1024) { kern = delay_fft_pow2_kernel<128>; nthreads = 128; }
+    else if (N == 512) { kern = delay_fft_pow2_kernel<64>; nthreads = 64; }
+    else { kern = delay_fft_pow2_kernel<32>; nthreads = 32; }
+  }
   FCU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int occ = 0;
-  FCU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, FTHREADS, smem));
+  FCU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, nthreads, smem));
   if (occ < 1) return bad("the transform does not fit in shared memory");
   long long grid = (long long)occ * dg_sm_count(h);
   if (grid > nrows) grid = nrows;
@@ -201,7 +340,7 @@ extern "C" int dgibbs_delay_fft(dgibbs_handle h, int32_t on_device, int64_t nrow
   FCU(cudaEventCreate(&e0));
   FCU(cudaEventCreate(&e1));
   FCU(cudaEventRecord(e0, st));
-  kern<<<(unsigned)grid, FTHREADS, smem, st>>>(x, y, wtab, tw, (long long)nrows, N, shift ? 1 : 0);
+  kern<<<(unsigned)grid, nthreads, smem, st>>>(x, y, wtab, tw, (long long)nrows, N, shift ? 1 : 0);
   FCU(cudaEventRecord(e1, st));
   FCU(cudaGetLastError());
   if (!on_device) FCU(cudaMemcpyAsync(out, y, bytes, cudaMemcpyDeviceToHost, st));
