@@ -295,13 +295,18 @@ static int stage_batch(dgibbs_handle h, const dgibbs_problem* p, Staged& s, bool
   // in-smem FFT for the masked inverse DFT when N is a power of two that fits the pipeline buffers
   d.use_fft = (d.N >= 8 && (d.N & (d.N - 1)) == 0 && d.N <= 4096 && !getenv("DGIBBS_NO_FFT")) ? 1 : 0;
   d.twtab = nullptr;
+  d.stwtab = nullptr;
   if (d.use_fft) {
     bool fresh = h->tw_N != d.N;
     CU(pool_get(h, "twtab", sizeof(double2) * (size_t)(d.N / 2), &q));
     d.twtab = (const double2*)q;
+    void* q2;
+    CU(pool_get(h, "stwtab", sizeof(double2) * 2 * (size_t)d.N, &q2));
+    d.stwtab = (const double2*)q2;
     if (fresh) {
       CU(launch_build_twtab(d.N, (double2*)q, h->stream));
-      h->timing.launches++;
+      CU(launch_build_stage_twiddles(d.N, (double2*)q2, h->stream));
+      h->timing.launches += 2;
       h->tw_N = d.N;
     }
   }

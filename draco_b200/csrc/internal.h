@@ -64,6 +64,7 @@ struct DevBatch {
   // shared tables
   const double* Ftab;  // [Kpad][npad] projection table  F[k][col]
   const double2* twtab;  // [N/2] exact twiddles e^{2 pi i m / N} (N a power of two), else null
+  const double2* stwtab; // per-stage twiddle tables of fft_inverse_fused (fft_fused.cuh), else null
   int use_fft;           // 1: masked inverse DFT of phase 0 runs as an in-smem FFT (N = 2^m <= 4096)
 
   // per-slot workspace
@@ -91,6 +92,7 @@ namespace dg {
 // setup_kernels.cu
 cudaError_t launch_build_ftab(const DevBatch& d, double* Ftab, cudaStream_t st);
 cudaError_t launch_build_twtab(int N, double2* tw, cudaStream_t st);
+cudaError_t launch_build_stage_twiddles(int N, double2* tw, cudaStream_t st);  // project_fft.cu; 2 N entries
 cudaError_t launch_setup_baselines(const DevBatch& d, const double* S0, cudaStream_t st);
 cudaError_t launch_materialize_inputs(const DevBatch& d, int b, double* data_w, double* FTNih,
                                       double* FTNiF, cudaStream_t st);
