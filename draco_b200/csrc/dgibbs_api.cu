@@ -267,6 +267,7 @@ static int stage_batch(dgibbs_handle h, const dgibbs_problem* p, Staged& s, bool
   CU(pool_get(h, "cidx", sizeof(int) * (size_t)B * d.nch, &q)); d.cidx = (int*)q;
   CU(pool_get(h, "h", sizeof(double) * (size_t)B * d.Kpad, &q)); d.h = (double*)q;
   CU(pool_get(h, "zT", sizeof(double) * (size_t)B * d.Tmax * d.Kpad, &q)); d.zT = (double*)q;
+  CU(pool_get(h, "wsre", sizeof(double2) * (size_t)B * (d.Kpad / 2), &q)); d.wsre = (double2*)q;
   CU(pool_get(h, "ctab", sizeof(double) * (size_t)B * d.nsys, &q)); d.ctab = (double*)q;
   CU(pool_get(h, "S", sizeof(double) * (size_t)B * d.N, &q)); d.S = (double*)q;
   CU(pool_get(h, "n_done", sizeof(int) * (size_t)B, &q)); d.n_done = (int*)q;
@@ -310,6 +311,9 @@ static int stage_batch(dgibbs_handle h, const dgibbs_problem* p, Staged& s, bool
       h->tw_N = d.N;
     }
   }
+  // diagonal-branch baselines that will be projected by diag_project_fft_kernel (same conditions as in dgibbs_run)
+  d.skip_zT_diag = (d.rng_mode == DGIBBS_RNG_PHILOX && d.nsys <= 4096 && d.niter > 0 && !d.wiener && diag_project_fft_fits(d) &&
+                    !getenv("DGIBBS_NO_PROJECT_KERNEL")) ? 1 : 0;
   CU(launch_setup_baselines(d, s.S0, h->stream));
   h->timing.launches++;
   CU(dense_configure(d));

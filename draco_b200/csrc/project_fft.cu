@@ -26,10 +26,15 @@ __global__ void __launch_bounds__(PTHREADS) diag_project_fft_kernel(DevBatch d, 
     const int b = d.blist[li];
     const int Tb = d.T[b];
     if (t0 >= Tb || d.failed[b]) continue;  // CTA-uniform
-    // masked / padded channels carry h = 0 and z = 0 (setup kernel), so no channel-index lookup is needed
+    // The whitened samples are formed on the fly from the raw data with the setup kernel's per-channel factors, in
+    // the setup kernel's order of operations (z = ((v w) sqrt(Ni_r)), u = h z): same bits as going through zT, which
+    // is never written for these baselines (DevBatch::skip_zT_diag).
     const double2* h2 = reinterpret_cast<const double2*>(d.h + (size_t)b * Kpad);
-    const double2* za = reinterpret_cast<const double2*>(d.zT + (size_t)b * d.Tmax * Kpad + (size_t)t0 * Kpad);
-    const double2* zb = za + Kpad / 2;
+    const double2* wf = d.wsre + (size_t)b * (Kpad / 2);
+    const int* cidx = d.cidx + (size_t)b * d.nch;
+    const int Mb = d.M[b];
+    const double2* da = d.data + d.data_off[b] + (size_t)t0 * Mb;
+    const double2* db = da + Mb;
     double* yo = d.yhat + ((size_t)d.ycompact[b] * d.Tmax + t0) * ypitch;
     const bool two = !d.cplx && t0 + 1 < Tb;
     __syncthreads();  // the previous transform's last stage is done with the buffers
@@ -39,11 +44,14 @@ __global__ void __launch_bounds__(PTHREADS) diag_project_fft_kernel(DevBatch d, 
           bufA, bufB, d.stwtab, N,
           [&](int p) {
             const int i = p <= half ? p : N - p;
-            const double2 hh = h2[i], a = za[i];
-            double2 bb = make_double2(0.0, 0.0);
-            if (two) bb = zb[i];
-            const double2 U0 = make_double2(hh.x * a.x, hh.y * a.y);
-            const double2 U1 = make_double2(hh.x * bb.x, hh.y * bb.y);
+            const int ci = cidx[i];
+            if (ci < 0) return make_double2(0.0, 0.0);  // masked channel: h = 0
+            const double2 hh = h2[i], f = wf[i], va = da[ci];
+            const double fim = (i == 0 || i == half) ? 0.0 : f.y;  // delay.py:1692: DC and Nyquist are real
+            double2 vb = make_double2(0.0, 0.0);
+            if (two) vb = db[ci];
+            const double2 U0 = make_double2(hh.x * ((va.x * f.x) * f.y), hh.y * ((va.y * f.x) * fim));
+            const double2 U1 = make_double2(hh.x * ((vb.x * f.x) * f.y), hh.y * ((vb.y * f.x) * fim));
             if (p == 0 || p == half) return make_double2(U0.x, U1.x);
             if (p < half) return make_double2(0.5 * (U0.x - U1.y), 0.5 * (U0.y + U1.x));  // (U0 + i U1) / 2
             return make_double2(0.5 * (U0.x + U1.y), 0.5 * (U1.x - U0.y));               // (conj U0 + i conj U1) / 2
@@ -61,8 +69,10 @@ __global__ void __launch_bounds__(PTHREADS) diag_project_fft_kernel(DevBatch d, 
       fft_inverse_fused<PTHREADS>(
           bufA, bufB, d.stwtab, N,
           [&](int p) {
-            const double2 hh = h2[p], a = za[p];
-            return make_double2(hh.x * a.x, hh.y * a.y);
+            const int ci = cidx[p];
+            if (ci < 0) return make_double2(0.0, 0.0);
+            const double2 hh = h2[p], f = wf[p], va = da[ci];
+            return make_double2(hh.x * ((va.x * f.x) * f.y), hh.y * ((va.y * f.x) * f.y));
           },
           []() {}, [&](int k, double2 v) { *reinterpret_cast<double2*>(yo + 2 * k) = v; });
       for (int k = nsys + threadIdx.x; k < ypitch; k += PTHREADS) yo[k] = 0.0;

@@ -88,6 +88,7 @@ __global__ void __launch_bounds__(THREADS) setup_baseline_kernel(DevBatch d, con
   // window * sqrt(Ni_r) on the full grid (delay.py:1679-1703)
   for (int i = threadIdx.x; i < d.Kpad / 2; i += blockDim.x) {
     double hre = 0.0, him = 0.0;
+    double2 wre = make_double2(0.0, 0.0);
     if (i < nch) {
       int ci = cidx[i];
       if (ci >= 0) {
@@ -102,31 +103,15 @@ __global__ void __launch_bounds__(THREADS) setup_baseline_kernel(DevBatch d, con
         s_w[i] = w;
         s_re[i] = sre;
         s_im[i] = sim;
+        wre = make_double2(w, sre);
       }
       hsq[i] = hre * hre;
     }
     h[2 * i] = hre;
     h[2 * i + 1] = him;
+    d.wsre[(size_t)b * (d.Kpad / 2) + i] = wre;
   }
   __syncthreads();
-
-  // whitened, windowed data, sample-major (delay.py:1676,1687,1707); a thread keeps its channels' factors
-  const int halfK = d.Kpad / 2;
-  for (int i = threadIdx.x; i < halfK; i += blockDim.x) {
-    const int ci = i < nch ? cidx[i] : -1;
-    const double w = ci >= 0 ? s_w[i] : 0.0, fre = ci >= 0 ? s_re[i] : 0.0, fim = ci >= 0 ? s_im[i] : 0.0;
-    const double2* src = d.data + doff + (ci >= 0 ? ci : 0);
-    double* dst = zT + 2 * i;
-#pragma unroll 4
-    for (int t = 0; t < d.Tmax; t++) {
-      double2 z = make_double2(0.0, 0.0);
-      if (t < Tb && ci >= 0) {
-        const double2 v = src[(long long)t * Mb];
-        z = make_double2((v.x * w) * fre, (v.y * w) * fim);
-      }
-      *reinterpret_cast<double2*>(dst + (size_t)t * d.Kpad) = z;
-    }
-  }
 
   // first column of the circulant  FTNiF[t,t'] = c[(t-t') mod N] = sum_i hsq_i e^{2 pi i (i k) / N}  (real part in
   // real mode)
@@ -160,6 +145,7 @@ __global__ void __launch_bounds__(THREADS) setup_baseline_kernel(DevBatch d, con
   // channel set (b = 0), or with only the Nyquist channel missing (b = -Ni): SURVEY 8d.  Gate on
   // the computed first column, not on configuration flags.
   __syncthreads();
+  bool isdiag = false;
   {
     const double tol = 1e-12;
     const double c0 = ct[0];
@@ -175,11 +161,32 @@ __global__ void __launch_bounds__(THREADS) setup_baseline_kernel(DevBatch d, con
         if ((k > 0 && fabs(ct[k]) > tol * c0) || fabs(ct[N + k]) > tol * c0) ok = false;
     }
     int all = __syncthreads_and(ok ? 1 : 0);
+    isdiag = all && d.force_branch != 1 && (c0 - bc) > 0.0;  // CTA-uniform
     if (threadIdx.x == 0) {
-      bool isdiag = all && d.force_branch != 1 && (c0 - bc) > 0.0;
       d.branch[b] = isdiag ? 3 : 1;
       d.diag_ab[2 * b] = c0 - bc;
       d.diag_ab[2 * b + 1] = bc;
+    }
+  }
+
+  // A diagonal-branch baseline whose projection reads the raw data (project_fft.cu) needs no whitened copy.
+  if (!(isdiag && d.skip_zT_diag)) {
+    // whitened, windowed data, sample-major (delay.py:1676,1687,1707); a thread keeps its channels' factors
+    const int halfK = d.Kpad / 2;
+    for (int i = threadIdx.x; i < halfK; i += blockDim.x) {
+      const int ci = i < nch ? cidx[i] : -1;
+      const double w = ci >= 0 ? s_w[i] : 0.0, fre = ci >= 0 ? s_re[i] : 0.0, fim = ci >= 0 ? s_im[i] : 0.0;
+      const double2* src = d.data + doff + (ci >= 0 ? ci : 0);
+      double* dst = zT + 2 * i;
+  #pragma unroll 4
+      for (int t = 0; t < d.Tmax; t++) {
+        double2 z = make_double2(0.0, 0.0);
+        if (t < Tb && ci >= 0) {
+          const double2 v = src[(long long)t * Mb];
+          z = make_double2((v.x * w) * fre, (v.y * w) * fim);
+        }
+        *reinterpret_cast<double2*>(dst + (size_t)t * d.Kpad) = z;
+      }
     }
   }
 
