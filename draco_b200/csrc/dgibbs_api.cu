@@ -267,6 +267,7 @@ static int stage_batch(dgibbs_handle h, const dgibbs_problem* p, Staged& s, bool
   CU(pool_get(h, "cidx", sizeof(int) * (size_t)B * d.nch, &q)); d.cidx = (int*)q;
   CU(pool_get(h, "h", sizeof(double) * (size_t)B * d.Kpad, &q)); d.h = (double*)q;
   CU(pool_get(h, "zT", sizeof(double) * (size_t)B * d.Tmax * d.Kpad, &q)); d.zT = (double*)q;
+  CU(pool_get(h, "cident", (size_t)B, &q)); d.cident = (unsigned char*)q;
   CU(pool_get(h, "wsre", sizeof(double2) * (size_t)B * (d.Kpad / 2), &q)); d.wsre = (double2*)q;
   CU(pool_get(h, "ctab", sizeof(double) * (size_t)B * d.nsys, &q)); d.ctab = (double*)q;
   CU(pool_get(h, "S", sizeof(double) * (size_t)B * d.N, &q)); d.S = (double*)q;

@@ -49,6 +49,7 @@ struct DevBatch {
   double* h;     // [B][Kpad]  window * sqrt(Ni_r) on the full grid (0 where masked)
   double* zT;    // [B][Tmax][Kpad] whitened data, transposed (sample-major)
   double2* wsre; // [B][Kpad/2] (window, sqrt(Ni_r) of the real part) per channel of the full grid, 0 where masked
+  unsigned char* cident;  // [B] 1: the kept channels are 0 .. M-1 in order (cidx[i] = i for i < M): no index look-up needed
   int skip_zT_diag;  // 1: diagonal-branch baselines get no zT (their projection reads the raw data, project_fft.cu)
   double* ctab;  // [B][nsys]  first column of the circulant FTNiF (cplx: cr[N] then ci[N])
   double* S;     // [B][N]     chain state

@@ -2,9 +2,9 @@
 // the diagonal shortcut taken out: they are added analytically by the diagonal sampler).
 //
 // One masked inverse DFT per sample as the Stockham FFT of fft_fused.cuh (two real samples per complex FFT in real
-// mode): the first radix-8 stage takes h z straight from global memory (Hermitian extension built on the fly: element
-// p of the transform input comes from channel min(p, N - p)), the last stage writes y straight to yhat, and the
-// twiddles come from per-stage tables -- two shared-memory passes fewer and coalesced twiddle loads.  Unlike the dense
+// mode): the Hermitian extension of h z is staged once per channel (complex mode: the first radix-8 stage takes h z
+// straight from global memory), the last stage writes y straight to yhat, and the twiddles come from per-stage tables
+// with coalesced loads.  Unlike the dense
 // sampler's fused prepass this kernel has no factorisation to share the SM with, so a CTA keeps only the two FFT
 // buffers (2 N double2) and several CTAs are resident per SM: the FFT stages of one overlap the global loads / stores
 // of the others.  HBM-bound work: reads T*M*16 B, writes T*npad*8 B per baseline.
@@ -33,30 +33,49 @@ __global__ void __launch_bounds__(PTHREADS) diag_project_fft_kernel(DevBatch d, 
     const double2* wf = d.wsre + (size_t)b * (Kpad / 2);
     const int* cidx = d.cidx + (size_t)b * d.nch;
     const int Mb = d.M[b];
+    const bool ident = d.cident[b] != 0;  // kept channels are 0 .. Mb-1: no dependent index load (masked ones have h = 0)
     const double2* da = d.data + d.data_off[b] + (size_t)t0 * Mb;
     const double2* db = da + Mb;
     double* yo = d.yhat + ((size_t)d.ycompact[b] * d.Tmax + t0) * ypitch;
     const bool two = !d.cplx && t0 + 1 < Tb;
     __syncthreads();  // the previous transform's last stage is done with the buffers
     if (!d.cplx) {
+      // Stage the Hermitian extension A + iB of the two samples: a thread forms u of channel i once and writes both
+      // element i and element N - i (half the global loads of taking them per transform input); PU channels in flight.
       const int half = N >> 1;
-      fft_inverse_fused<PTHREADS>(
-          bufA, bufB, d.stwtab, N,
-          [&](int p) {
-            const int i = p <= half ? p : N - p;
-            const int ci = cidx[i];
-            if (ci < 0) return make_double2(0.0, 0.0);  // masked channel: h = 0
+      constexpr int PU = 4;
+      for (int i0 = threadIdx.x; i0 <= half; i0 += PU * PTHREADS) {
+        double2 U0[PU], U1[PU];
+#pragma unroll
+        for (int j = 0; j < PU; j++) {
+          const int i = i0 + j * PTHREADS;
+          U0[j] = U1[j] = make_double2(0.0, 0.0);
+          int ci = -1;
+          if (i <= half) ci = ident ? (i < Mb ? i : Mb - 1) : cidx[i];
+          if (ci >= 0) {
             const double2 hh = h2[i], f = wf[i], va = da[ci];
             const double fim = (i == 0 || i == half) ? 0.0 : f.y;  // delay.py:1692: DC and Nyquist are real
             double2 vb = make_double2(0.0, 0.0);
             if (two) vb = db[ci];
-            const double2 U0 = make_double2(hh.x * ((va.x * f.x) * f.y), hh.y * ((va.y * f.x) * fim));
-            const double2 U1 = make_double2(hh.x * ((vb.x * f.x) * f.y), hh.y * ((vb.y * f.x) * fim));
-            if (p == 0 || p == half) return make_double2(U0.x, U1.x);
-            if (p < half) return make_double2(0.5 * (U0.x - U1.y), 0.5 * (U0.y + U1.x));  // (U0 + i U1) / 2
-            return make_double2(0.5 * (U0.x + U1.y), 0.5 * (U1.x - U0.y));               // (conj U0 + i conj U1) / 2
-          },
-          []() {},
+            U0[j] = make_double2(hh.x * ((va.x * f.x) * f.y), hh.y * ((va.y * f.x) * fim));
+            U1[j] = make_double2(hh.x * ((vb.x * f.x) * f.y), hh.y * ((vb.y * f.x) * fim));
+          }
+        }
+#pragma unroll
+        for (int j = 0; j < PU; j++) {
+          const int i = i0 + j * PTHREADS;
+          if (i > half) break;
+          if (i == 0 || i == half) {
+            bufA[i] = make_double2(U0[j].x, U1[j].x);
+          } else {
+            bufA[i] = make_double2(0.5 * (U0[j].x - U1[j].y), 0.5 * (U0[j].y + U1[j].x));      // (U0 + i U1) / 2
+            bufA[N - i] = make_double2(0.5 * (U0[j].x + U1[j].y), 0.5 * (U1[j].x - U0[j].y));  // (conj U0 + i conj U1) / 2
+          }
+        }
+      }
+      __syncthreads();
+      fft_inverse_fused<PTHREADS>(
+          bufA, bufB, d.stwtab, N, [&](int p) { return bufA[p]; }, []() {},
           [&](int k, double2 v) {
             yo[k] = v.x;
             if (two) yo[ypitch + k] = v.y;
@@ -69,7 +88,7 @@ __global__ void __launch_bounds__(PTHREADS) diag_project_fft_kernel(DevBatch d, 
       fft_inverse_fused<PTHREADS>(
           bufA, bufB, d.stwtab, N,
           [&](int p) {
-            const int ci = cidx[p];
+            const int ci = ident ? (p < Mb ? p : Mb - 1) : cidx[p];
             if (ci < 0) return make_double2(0.0, 0.0);
             const double2 hh = h2[p], f = wf[p], va = da[ci];
             return make_double2(hh.x * ((va.x * f.x) * f.y), hh.y * ((va.y * f.x) * f.y));

@@ -79,11 +79,14 @@ __global__ void __launch_bounds__(THREADS) setup_baseline_kernel(DevBatch d, con
       if (tabs) tabs[m] = s;
     }
   __syncthreads();
+  bool inorder = true;
   for (int ci = threadIdx.x; ci < Mb; ci += blockDim.x) {
     long long f = d.fsel[coff + ci];
     if (f >= 0 && f < nch) cidx[f] = ci;
+    inorder = inorder && f == ci;
   }
-  __syncthreads();
+  const int ident = __syncthreads_and(inorder ? 1 : 0);
+  if (threadIdx.x == 0) d.cident[b] = ident ? 1 : 0;
 
   // window * sqrt(Ni_r) on the full grid (delay.py:1679-1703)
   for (int i = threadIdx.x; i < d.Kpad / 2; i += blockDim.x) {
