@@ -3,9 +3,10 @@
 // multiplied by the generalised cosine window at x = i / N (delay.py:2124-2127), transformed with numpy's ifft
 // convention (sign +, scale 1/N) and, for the task, fftshifted (delay.py:980).
 //
-// HBM-bound: 16 N bytes read and 16 N bytes written per row.  N = 2^m <= 4096 runs as the in-smem Stockham FFT of
-// dense_core.cuh (several CTAs per SM so that the shared-memory passes of one overlap the loads / stores of the
-// others); any other N <= 6400 is a direct O(N^2) DFT against an exact twiddle table in shared memory.
+// HBM-bound: 16 N bytes read and 16 N bytes written per row.  N = 2^m <= 4096 runs as the fused-stage Stockham FFT of
+// fft_fused.cuh (first stage fed from a cp.async-prefetched row, last stage stored straight to HBM, per-stage twiddle
+// tables; several CTAs per SM); any other N <= 6400 is a direct O(N^2) DFT against an exact twiddle table in shared
+// memory.
 #include <cstdio>
 #include <string>
 
