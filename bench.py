@@ -200,7 +200,13 @@ def fp64_peak_tflops():
 DENSE_TRAFFIC_PER_UNIT = 72.957e9 / 296
 
 
-def hbm_roofline(nbytes, ms):
+# dram__bytes_read.sum + dram__bytes_write.sum of diag_resident_kernel from the committed `ncu --set full` capture
+# profiles/r01n_diag_path_ncu_raw.csv: 257.65 MB read + 61.77 MB written for a launch of 240 baselines x 20 iterations of
+# cfg3 geometry (the projected data is read once per baseline and then stays in distributed shared memory).
+DIAG_TRAFFIC_PER_UNIT = (257.651712e6 + 61.768704e6) / (240 * 20)
+
+
+def hbm_roofline(nbytes, ms, units=None):
     peaks = {}
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
@@ -210,7 +216,9 @@ def hbm_roofline(nbytes, ms):
     peak = float(peaks.get("hbm_gbs", 6650.0))
     src = "MEASURED_PEAKS.json hbm_gbs (of measured)" if "hbm_gbs" in peaks else "6650 GB/s (of fallback)"
     ach = nbytes / (ms / 1e3) / 1e9 if ms > 0 else 0.0
-    return {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
+    return {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+            "traffic": DIAG_TRAFFIC_PER_UNIT * units if units else None,
+            "traffic_source": "ncu --set full capture of 4800 baseline-iterations scaled to this launch (profiles/r01n_diag_path_ncu_raw.csv)",
             "peak_source": src, "kernel": "diag_resident_kernel (cluster-resident; diag_sampler_kernel when a slice does not fit)",
             "byte_model": "Q_d = 8 n T + 16 N bytes per baseline-iteration (read projected data once, read+write S)"}
 
@@ -335,7 +343,7 @@ def main():
         ach = flop / (max(ms_sampler, 1e-9) / 1e3) / 1e12
         if n_diag > 0:
             # diagonal(+rank-1) branch: cluster-resident kernel, judged against the HBM stream of its algorithmic bytes (SURVEY 8d Q_d = 8 n T + 16 N per baseline-iteration)
-            roof = hbm_roofline(nbytes, ms_diag)
+            roof = hbm_roofline(nbytes, ms_diag, units=n_diag * nsamp if cfg.ndelay == 2048 else None)
             branch = f"diagonal(+rank-1) cluster-resident sampler ({n_diag} of {nbase} baselines)"
         else:
             roof = {"bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
