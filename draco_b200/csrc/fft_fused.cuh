@@ -50,7 +50,6 @@ __device__ __forceinline__ void fft_inverse_fused(double2* x, double2* y, const 
   bool swz = false;
   const int e8 = N >> 3;
   while (Ns * 8 <= N) {
-    const int s = N / (8 * Ns);
     const bool first = Ns == 1, last = Ns * 8 == N;
     const bool swz_out = first && !last;
     for (int j = threadIdx.x; j < e8; j += NT) {
