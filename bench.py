@@ -197,7 +197,7 @@ def fp64_peak_tflops():
 # 72.96 GB) for a launch of 296 baseline-iterations of cfg2
 # geometry = 245.8 MB per baseline-iteration (L panels re-read from DRAM; 14 % of DRAM peak, not the bound).
 # Reported per launch of THIS run by scaling with the launch's baseline-iterations (cfg2 geometry only).
-DENSE_TRAFFIC_PER_UNIT = 72.957e9 / 296
+DENSE_TRAFFIC_PER_UNIT = 72.985e9 / 296  # r01o capture: 66.76 GB read + 6.22 GB written
 
 
 # dram__bytes_read.sum + dram__bytes_write.sum of diag_resident_kernel from the committed `ncu --set full` capture
@@ -348,7 +348,7 @@ def main():
         else:
             roof = {"bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
                     "traffic": (DENSE_TRAFFIC_PER_UNIT * nbase * nsamp) if cfg.ndelay == 2048 else None,
-                    "traffic_source": "ncu --set full capture of 296 baseline-iterations scaled to this launch (profiles/r01i_dense_sampler_ncu_raw.csv)",
+                    "traffic_source": "ncu --set full capture of 296 baseline-iterations scaled to this launch (profiles/r01o_dense_sampler_ncu_raw.csv)",
                     "peak_source": "fp64: cuBLAS DGEMM 8192^3 measured in this run (MEASURED_PEAKS.json has no fp64 entry; "
                                    "tcgen05 has no fp64 kind, DMMA pipe probe = 37.0 TFLOP/s, profiles/r01_fp64_pipe_probe.log)",
                     "kernel": "dense_sampler_kernel", "flop_model": "W_f = n^3/3 + 2 n^2 T + 4 n M T per baseline-iteration"}
