@@ -211,7 +211,8 @@ extern "C" int dgibbs_delay_fft(dgibbs_handle h, int32_t on_device, int64_t nrow
   void (*kern)(const double2*, double2*, const double*, const double2*, long long, int, int) = delay_dft_direct_kernel;
   int nthreads = FTHREADS;
   if (pow2) {
-    if (N >= 2048) { kern = delay_fft_pow2_kernel<256>; nthreads = 256; }
+    if (N >= 4096) { kern = delay_fft_pow2_kernel<512>; nthreads = 512; }  // one CTA per SM: every butterfly its own thread
+    else if (N >= 2048) { kern = delay_fft_pow2_kernel<256>; nthreads = 256; }
     else if (N == 1024) { kern = delay_fft_pow2_kernel<128>; nthreads = 128; }
     else if (N == 512) { kern = delay_fft_pow2_kernel<64>; nthreads = 64; }
     else { kern = delay_fft_pow2_kernel<32>; nthreads = 32; }
