@@ -75,7 +75,7 @@ class Problem(C.Structure):
         ("w2_off", _vp),
         ("chi2", _vp),
         ("force_branch", C.c_int32),
-        ("reserved", C.c_int32),
+        ("cluster_size", C.c_int32),
     ]
 
 

@@ -50,6 +50,21 @@ struct Lane {
   }
 };
 
+// ----------------------------------------------------------------------------- thread-block cluster helpers
+// A chain may be shared by the C CTAs of a cluster (sampler_dense.cu): they exchange data through the chain's global
+// workspace (L2) and order it with the split-phase cluster barrier (release on arrive, acquire on wait, cluster scope).
+__device__ __forceinline__ int cluster_ctarank() {
+  unsigned r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return (int)r;
+}
+__device__ __forceinline__ void cluster_arrive() { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); }
+__device__ __forceinline__ void cluster_wait() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
+__device__ __forceinline__ void cluster_sync_all() {
+  cluster_arrive();
+  cluster_wait();
+}
+
 // which 8-column blocks each of the two row fragments of a warp computes (compile-time variants:
 // predicated-off DMMAs still occupy the fp64 tensor pipe, so skipping must be a real branch)
 enum Variant { V_FULL = 0, V_ROW0 = 1, V_ROW1 = 2, V_NONE = 3, V_DIAG_LO = 4, V_DIAG_HI = 5 };
@@ -337,9 +352,9 @@ __device__ __forceinline__ void add_generated(double* sT, const double* ct, cons
     sT[r * LDW + c] += v;
   }
 }
-// sT[0:nrows] += src[0:nrows][0:128]  (row pitch ld in global)
-__device__ __forceinline__ void add_global(double* sT, const double* src, int ld, int nrows) {
-  for (int e = threadIdx.x; e < nrows * (TILE / 2); e += THREADS) {
+// sT[r0:r1] += src[r0:r1][0:128]  (row pitch ld in global)
+__device__ __forceinline__ void add_global(double* sT, const double* src, int ld, int r1, int r0 = 0) {
+  for (int e = r0 * (TILE / 2) + threadIdx.x; e < r1 * (TILE / 2); e += THREADS) {
     int r = e >> 6, c = (e & 63) * 2;
     double2 v = *reinterpret_cast<const double2*>(src + (size_t)r * ld + c);
     double2* p = reinterpret_cast<double2*>(sT + r * LDW + c);
@@ -432,9 +447,9 @@ __device__ __forceinline__ void trisolve(double* sT, const double* sWp, const La
     default: break;
   }
 }
-// staged tile rows [0, nrows) -> global (row pitch ld), coalesced
-__device__ __forceinline__ void copy_tile_out(const double* sT, double* dst, int ld, int nrows) {
-  for (int e = threadIdx.x; e < nrows * (TILE / 2); e += THREADS) {
+// staged tile rows [r0, r1) -> global (row pitch ld), coalesced
+__device__ __forceinline__ void copy_tile_out(const double* sT, double* dst, int ld, int r1, int r0 = 0) {
+  for (int e = r0 * (TILE / 2) + threadIdx.x; e < r1 * (TILE / 2); e += THREADS) {
     int r = e >> 6, c = (e & 63) * 2;
     *reinterpret_cast<double2*>(dst + (size_t)r * ld + c) = *reinterpret_cast<const double2*>(sT + r * LDW + c);
   }
@@ -610,8 +625,9 @@ __device__ __forceinline__ void w1_pair2(const DrawCtx& c, int t0, int k, int ns
 // zero in the padding rows / columns the factorisation sweeps over.
 //   real mode    : two samples per complex FFT (their spectra are Hermitian-extended and combined as A + iB)
 //   complex mode : one sample per FFT, output interleaved re/im
+// A cluster of `nrank` CTAs shares the rows: CTA `rank` takes every nrank-th sample (pair).
 static __device__ void project_rows_fft(const DevBatch& d, const DrawCtx& c, double* Rh, const double* Si, double2* bufA,
-                                 double2* bufB, double2* tw_s, int rows) {
+                                 double2* bufB, double2* tw_s, int rows, int rank = 0, int nrank = 1) {
   const int N = d.N, nsys = d.nsys, npad = d.npad, nch = d.nch;
   for (int m = threadIdx.x; m < N / 2; m += THREADS) tw_s[m] = d.twtab[m];
   const int step = d.cplx ? 1 : 2;
@@ -624,7 +640,7 @@ static __device__ void project_rows_fft(const DevBatch& d, const DrawCtx& c, dou
       tp = t_;                                                                           \
     }                                                                                    \
   } while (0)
-  for (int t0 = 0; t0 < rows; t0 += step) {
+  for (int t0 = rank * step; t0 < rows; t0 += nrank * step) {
     __syncthreads();  // previous epilogue finished with the buffers (and tw_s is loaded)
     PROFX(14);
     if (t0 >= c.Tb) {  // padding rows: zeros (CTA-uniform branch)
@@ -791,8 +807,9 @@ static __device__ bool factor_diag(double* sT, double* sWp, double* misc, const 
 // Ci = D + b u u^T with D = diag(a + Si), u_k = (-1)^k: solve every RHS row in place by
 // Sherman-Morrison.  Returns false when the system is not positive definite (some D_k <= 0 or
 // 1 + b u^T D^-1 u <= 0), which is when the reference's Cholesky would fail.
+// Every CTA of a cluster evaluates the (identical) positivity test; CTA `rank` solves every nrank-th group of rows.
 static __device__ bool diag_solve_rows(double* Rh, const double* Si, double a, double bc, int nsys, int npad, int Tb,
-                                double* misc) {
+                                double* misc, int rank = 0, int nrank = 1) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   double ql = 0.0;
   bool pos = true;
@@ -812,7 +829,7 @@ static __device__ bool diag_solve_rows(double* Rh, const double* Si, double a, d
   const double den = 1.0 + bc * q;
   if (!allpos || !(den > 0.0)) return false;
   const double beta = bc / den;
-  for (int t = warp; t < Tb; t += NWARP) {
+  for (int t = warp + rank * NWARP; t < Tb; t += NWARP * nrank) {
     double* row = Rh + (size_t)t * npad;
     double s = 0.0;
     if (bc != 0.0) {

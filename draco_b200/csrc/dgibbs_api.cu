@@ -181,6 +181,8 @@ static int check_problem(dgibbs_handle h, const dgibbs_problem* p) {
   if (p->niter < 0) return bad_arg(h, 2, "niter must be >= 0");
   if (p->window_id < -1 || p->window_id > 7) return bad_arg(h, 2, "unknown window_id");
   if (p->rng_mode < 0 || p->rng_mode > 2) return bad_arg(h, 2, "unknown rng_mode");
+  if (p->cluster_size != 0 && p->cluster_size != 1 && p->cluster_size != 2 && p->cluster_size != 4)
+    return bad_arg(h, 2, "cluster_size must be 0 (auto), 1, 2 or 4");
   if (!p->T || !p->M || !p->data_off || !p->chan_off || !p->data || !p->Ni || !p->fsel || !p->S0)
     return bad_arg(h, 2, "a required input pointer is NULL");
   if (p->rng_mode == DGIBBS_RNG_INJECTED && p->niter > 0 && (!p->w1 || !p->w2 || !p->chi2 || !p->w1_off || !p->w2_off))
@@ -279,9 +281,10 @@ static int stage_batch(dgibbs_handle h, const dgibbs_problem* p, Staged& s, bool
   const size_t wrows = (size_t)d.npad + (size_t)d.RT * TILE;
   d.work_stride = wrows * d.npad + (size_t)d.N * d.Tmax;
   CU(pool_get(h, "work", sizeof(double) * (size_t)d.nslots * d.work_stride, &q)); d.work = (double*)q;
-  CU(pool_get(h, "Wp", sizeof(double) * (size_t)d.nslots * dense_wp_doubles_per_slot(d), &q)); d.Wp = (double*)q;
+  // Wp and Si are indexed per CTA (a chain may be shared by a cluster of CTAs, each with its own copy)
+  CU(pool_get(h, "Wp", sizeof(double) * (size_t)h->sm_count * dense_wp_doubles_per_slot(d), &q)); d.Wp = (double*)q;
   CU(pool_get(h, "uT", sizeof(double) * (size_t)d.nslots * d.RT * TILE * d.Kpad, &q)); d.uT = (double*)q;
-  CU(pool_get(h, "Si", sizeof(double) * (size_t)d.nslots * d.npad, &q)); d.Si = (double*)q;
+  CU(pool_get(h, "Si", sizeof(double) * (size_t)h->sm_count * d.npad, &q)); d.Si = (double*)q;
   {
     size_t ftbytes = sizeof(double) * (size_t)d.Kpad * d.npad;
     bool fresh = h->pool["Ftab"].cap < ftbytes || h->ft_N != d.N || h->ft_cplx != d.cplx;
@@ -319,6 +322,13 @@ static int stage_batch(dgibbs_handle h, const dgibbs_problem* p, Staged& s, bool
   h->timing.launches++;
   CU(dense_configure(d));
   return 0;
+}
+
+// CTAs per chain of the dense kernel: the problem's cluster_size, else DGIBBS_DENSE_CLUSTER, else 0 (planned per launch)
+static int cluster_request(const dgibbs_problem* p) {
+  if (p->cluster_size > 0) return p->cluster_size;
+  const char* e = getenv("DGIBBS_DENSE_CLUSTER");
+  return e ? atoi(e) : 0;
 }
 
 static double dense_flop_per_iter(const DevBatch& d, int T, int M) {
@@ -450,7 +460,7 @@ extern "C" int dgibbs_run(dgibbs_handle h, const dgibbs_problem* p, dgibbs_resul
     dp.nslots = dp.nlist < d.nslots ? dp.nlist : d.nslots;
     static const bool no_pk = getenv("DGIBBS_NO_PROJECT_KERNEL") != nullptr;
     if (!no_pk && diag_project_fft_fits(dp)) CU(launch_diag_project_fft(dp, h->sm_count, h->stream));
-    else CU(launch_dense_sampler(dp, 0, 1, h->stream));
+    else CU(launch_dense_sampler(dp, 0, 1, h->stream, h->sm_count, 1));
     h->timing.launches++;
     CU(cudaEventRecord(h->ev[6], h->stream));
     DevBatch dd = d;
@@ -479,9 +489,10 @@ extern "C" int dgibbs_run(dgibbs_handle h, const dgibbs_problem* p, dgibbs_resul
       dn.nlist = (int)dense_list.size();
       dn.nslots = dn.nlist < d.nslots ? dn.nlist : d.nslots;
     }
-    CU(launch_dense_sampler(dn, 0, d.niter, h->stream));
-    h->timing.launches++;
-    h->timing.sampler_launches++;
+    int nl = 0;
+    CU(launch_dense_sampler(dn, 0, d.niter, h->stream, h->sm_count, cluster_request(p), &nl));
+    h->timing.launches += nl;
+    h->timing.sampler_launches += nl;
   }
   if (d.niter > 0 && !freq_list.empty()) {
     DevBatch df = d;
@@ -605,9 +616,10 @@ extern "C" int dgibbs_wiener(dgibbs_handle h, const dgibbs_problem* p, double* o
   CU(pool_get(h, "samples", sizeof(double) * (size_t)d.B * d.N, &q));
   d.samples = (double*)q;
   CU(cudaEventRecord(h->ev[2], h->stream));
-  CU(launch_dense_sampler(d, 0, 1, h->stream));
-  h->timing.launches++;
-  h->timing.sampler_launches++;
+  int nl = 0;
+  CU(launch_dense_sampler(d, 0, 1, h->stream, h->sm_count, cluster_request(p), &nl));
+  h->timing.launches += nl;
+  h->timing.sampler_launches += nl;
   CU(cudaEventRecord(h->ev[3], h->stream));
   if (!dev) CU(cudaMemcpyAsync(out, d_out, 8 * nout, cudaMemcpyDeviceToHost, h->stream));
   std::vector<int> failed(d.B);

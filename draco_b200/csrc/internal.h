@@ -60,6 +60,7 @@ struct DevBatch {
   double* diag_ab;        // [B][2]  FTNiF = a I + b u u^T (u = (-1)^t) when branch == 3
   const int* blist;       // baselines this launch works on (null = all B)
   int nlist;
+  int li_begin, li_end;   // dense kernel: positions [li_begin, li_end) of the list this launch covers (li_end 0 = to the end)
   double* yhat;           // [ndiag][Tmax][ypitch] projected data of the diagonal-branch baselines (zero beyond nsys)
   int ypitch;             // row pitch of yhat: npad + 128, so that any even column split of a cluster stays inside a row
   const int* ycompact;    // [B] row block of a baseline in yhat, or -1
@@ -106,7 +107,15 @@ cudaError_t launch_fourier_matrix(int kind, int N, const long long* fsel, int M,
 size_t dense_smem_bytes(const DevBatch& d);
 size_t dense_wp_doubles_per_slot(const DevBatch& d);
 cudaError_t dense_configure(const DevBatch& d);
-cudaError_t launch_dense_sampler(const DevBatch& d, int it_begin, int it_end, cudaStream_t st);
+// How a dense launch is divided: the full waves run one CTA per chain, the remainder on clusters of C_tail CTAs per chain.
+struct DensePlan {
+  int n_main, grid_main;          // chains / CTAs of the C = 1 launch (0: none)
+  int n_tail, grid_tail, C_tail;  // chains / clusters / cluster size of the second launch (n_tail 0: none)
+};
+DensePlan plan_dense(const DevBatch& d, int nchains, int sm_count, int force_cluster);
+// force_cluster: 0 = plan as above; 1, 2, 4 = every chain on clusters of that size.  *launches is incremented per launch.
+cudaError_t launch_dense_sampler(const DevBatch& d, int it_begin, int it_end, cudaStream_t st, int sm_count = 0,
+                                 int force_cluster = 0, int* launches = nullptr);
 
 // sampler_diag.cu
 // allow_resident: every listed baseline has b <= 0, so the cluster-resident kernel may be used

@@ -12,19 +12,43 @@
 // W_j = inv(L_jj) is kept (packed by 8x8 blocks, bank-swizzled) in shared memory for the whole
 // block column, so every triangular solve is a DMMA multiply against a smem-staged tile.
 //
+// Sharing a chain.  A chain is serial over its iterations, so with B chains on S SMs the last wave of a launch runs
+// with (B mod S) busy SMs (4096 baselines over 8 GPUs: 512 chains = 3.46 waves executed as 4).  The kernel is therefore
+// also instantiated for thread-block clusters of C = 2 and 4 CTAs that work on ONE chain: the sample rows of the
+// prepass / backward solve, the row tiles below the diagonal of every block column and the delays of the
+// power-spectrum draw are divided over the cluster ranks; every rank factors the diagonal tile itself (identical
+// arithmetic, so no broadcast of W_j).  Row tile i belongs to rank i mod C for the whole factorisation, so a rank only
+// ever reads foreign data through row panel j at step j: the split-phase cluster barrier (arrive after tile (j+1, j)
+// is stored, wait at the top of step j+1) is the only synchronisation of a block column.  Every tile is computed by
+// exactly the code and data of the single-CTA kernel, so the samples are bit-identical for every C.  The host
+// (launch_dense_sampler) runs the full waves with C = 1 and picks C for the remainder.
+//
 // All hot loops are ROLLED or small: straight-line code larger than the instruction caches costs
 // ~140 cycles per 128 B line on this part (measured, profiles/r01a), so register-tile code that
 // touches all 64 accumulators is kept to loads/stores only.
+#include <cstdio>
+#include <cstdlib>
+
 #include "dense_core.cuh"
+
+#ifndef DGIBBS_COST_C2
+#define DGIBBS_COST_C2 0.59
+#endif
+#ifndef DGIBBS_COST_C4
+#define DGIBBS_COST_C4 0.42
+#endif
 
 namespace dg {
 
 // ----------------------------------------------------------------------------- the sampler
 // Shared memory:  [ctab: nsys (optional)] [sWp: WP_DOUBLES] [pipe/tile: PIPE_DOUBLES] [misc]
+template <int C>
 __global__ void __launch_bounds__(THREADS, 1) dense_sampler_kernel(DevBatch d, int it_begin, int it_end) {
   extern __shared__ __align__(16) double smem[];
   const Lane ln;
-  const int slot = blockIdx.x;
+  const int rank = C > 1 ? cluster_ctarank() : 0;              // rank of this CTA among the C that share a chain
+  const int slot = C > 1 ? (int)blockIdx.x / C : (int)blockIdx.x;  // chain slot (workspace) of the cluster
+  const int nslot = (int)gridDim.x / C;
   const int N = d.N, nsys = d.nsys, npad = d.npad, nblk = d.nblk, Kpad = d.Kpad, RT = d.RT;
   double* s_ct = smem;
   double* sWp = smem + (d.ctab_smem ? nsys : 0);
@@ -35,13 +59,13 @@ __global__ void __launch_bounds__(THREADS, 1) dense_sampler_kernel(DevBatch d, i
   const size_t wrows = (size_t)npad + (size_t)RT * TILE;
   double* Wk = d.work + (size_t)slot * d.work_stride;   // L rows then RHS rows, pitch npad
   double* Rh = Wk + (size_t)npad * npad;               // RHS rows (sample-major)
-  double* Wpg = d.Wp + (size_t)slot * nblk * WP_DOUBLES;  // packed inv(L_jj), one per block column
+  double* Wpg = d.Wp + (size_t)blockIdx.x * nblk * WP_DOUBLES;  // packed inv(L_jj), one per block column (per CTA)
   double* uT = d.uT + (size_t)slot * RT * TILE * Kpad;
-  double* Si = d.Si + (size_t)slot * npad;
+  double* Si = d.Si + (size_t)blockIdx.x * npad;                // per CTA
 
   long long tlast = clock64();
-  const int nl = d.blist ? d.nlist : d.B;
-  for (int li = slot; li < nl; li += gridDim.x) {
+  const int nl = d.li_end > 0 ? d.li_end : (d.blist ? d.nlist : d.B);
+  for (int li = d.li_begin + slot; li < nl; li += nslot) {
     const int b = d.blist ? d.blist[li] : li;
     if (d.failed[b]) continue;
     const bool isdiag = d.branch[b] == 3;
@@ -63,8 +87,12 @@ __global__ void __launch_bounds__(THREADS, 1) dense_sampler_kernel(DevBatch d, i
 
     if (d.use_fft) {  // RHS rows the FFT projection never writes (skipped by every tile variant): keep them finite
       const long long r0 = (long long)rhs_frags * 8 * (npad / 2), r1 = (long long)RT * TILE * (npad / 2);
-      for (long long e = r0 + threadIdx.x; e < r1; e += THREADS) reinterpret_cast<double2*>(Rh)[e] = make_double2(0.0, 0.0);
+      for (long long e = r0 + threadIdx.x + rank * THREADS; e < r1; e += THREADS * C)
+        reinterpret_cast<double2*>(Rh)[e] = make_double2(0.0, 0.0);
     }
+    // fragments (8 sample rows each) of the right-hand sides this rank solves backwards
+    const int frag_per = (rhs_frags + C - 1) / C;
+    const int frag_lo = rank * frag_per, frag_hi = min(rhs_frags, frag_lo + frag_per);
     bool alive = true;
     for (int it = it_begin; it < it_end && alive; it++) {
       // ---------------- prepass
@@ -88,13 +116,13 @@ __global__ void __launch_bounds__(THREADS, 1) dense_sampler_kernel(DevBatch d, i
         dc.w2 = (d.rng_mode == 0) ? d.w2 + d.w2_off[b] + (long long)it * 2 * Mb * Tb : nullptr;
         dc.Tb = Tb; dc.it = it; dc.half = Kpad >> 1;
         double2* fbuf = reinterpret_cast<double2*>(pipe);
-        project_rows_fft(d, dc, Rh, Si, fbuf, fbuf + N, reinterpret_cast<double2*>(sWp), rhs_frags * 8);
+        project_rows_fft(d, dc, Rh, Si, fbuf, fbuf + N, reinterpret_cast<double2*>(sWp), rhs_frags * 8, rank, C);
         PROF(0);
       } else {
       {  // Y = sqrt(Si) * w1  (two adjacent delays per thread), zero in the padding
         const int half = npad >> 1;
         const long long tot = (long long)RT * TILE * half;
-        for (long long e = threadIdx.x; e < tot; e += THREADS) {
+        for (long long e = threadIdx.x + rank * THREADS; e < tot; e += THREADS * C) {
           int t = (int)(e / half), k = (int)(e % half) * 2;
           double y0 = 0.0, y1 = 0.0;
           if (t < Tb && k < nsys && d.rng_mode != 2) {
@@ -116,7 +144,7 @@ __global__ void __launch_bounds__(THREADS, 1) dense_sampler_kernel(DevBatch d, i
       {  // u = h * (z + w2)  on the full channel grid (delay.py:1814,1817), zero where masked/padded
         const int half = Kpad >> 1;
         const long long tot = (long long)RT * TILE * half;
-        for (long long e = threadIdx.x; e < tot; e += THREADS) {
+        for (long long e = threadIdx.x + rank * THREADS; e < tot; e += THREADS * C) {
           int t = (int)(e / half), i = (int)(e % half);
           double u0 = 0.0, u1 = 0.0;
           if (t < Tb && i < d.nch) {
@@ -140,13 +168,14 @@ __global__ void __launch_bounds__(THREADS, 1) dense_sampler_kernel(DevBatch d, i
         }
       }
       __syncthreads();
+      if (C > 1) cluster_sync_all();  // Y and u complete before any rank's projection tiles read them
       PROF(0);
 
-      // ---------------- phase 0: Y += u F
+      // ---------------- phase 0: Y += u F   (column blocks divided over the ranks)
       for (int rt = 0; rt < RT; rt++) {
         const bool do0 = rt * 16 + ln.rf[0] < rhs_frags, do1 = rt * 16 + ln.rf[1] < rhs_frags;
         const int var = rhs_variant(do0, do1);
-        for (int cb = 0; cb < nblk; cb++) {
+        for (int cb = rank; cb < nblk; cb += C) {
           double* ytile = Rh + (size_t)rt * TILE * npad + cb * TILE;
           tile_load_global(acc, ytile, npad, ln);
           gemm_nn<false>(pipe, acc, ln, uT + (size_t)rt * TILE * Kpad, Kpad, d.Ftab + cb * TILE, npad, 0, Kpad / KC, var);
@@ -157,7 +186,8 @@ __global__ void __launch_bounds__(THREADS, 1) dense_sampler_kernel(DevBatch d, i
       PROF(1);
       }
 
-      if (d.project_only) {  // export y^T = (F^T h z)^T for the streaming diagonal kernel
+      if (C > 1) cluster_sync_all();  // every sample row of y is in place
+      if (C == 1 && d.project_only) {  // export y^T = (F^T h z)^T for the streaming diagonal kernel
         double* yo = d.yhat + (size_t)d.ycompact[b] * d.Tmax * d.ypitch;
         const int hp = d.ypitch / 2;
         for (long long e = threadIdx.x; e < (long long)Tb * hp; e += THREADS) {
@@ -169,10 +199,15 @@ __global__ void __launch_bounds__(THREADS, 1) dense_sampler_kernel(DevBatch d, i
         break;
       }
 
-      if (isdiag) alive = diag_solve_rows(Rh, Si, dg_a, dg_b, nsys, npad, Tb, misc);
+      if (isdiag) alive = diag_solve_rows(Rh, Si, dg_a, dg_b, nsys, npad, Tb, misc, rank, C);
 
       // ---------------- factor (+ forward solve on the RHS row tiles)
+      bool pending = false;  // a cluster arrive whose wait is still to come
       for (int j = 0; j < nblk && alive && !isdiag; j++) {
+        if (C > 1 && pending) {  // row panel j is complete: tile (j, j-1) was stored before its owner arrived
+          cluster_wait();
+          pending = false;
+        }
         const double* Bp = Wk + (size_t)j * TILE * npad;
         // diagonal tile
         const bool interior_j = !d.cplx && (j + 1) * TILE <= nsys;
@@ -194,6 +229,13 @@ __global__ void __launch_bounds__(THREADS, 1) dense_sampler_kernel(DevBatch d, i
         PROF(4);
         // tiles below the diagonal, then the RHS row tiles
         for (int i = j + 1; i < nblk + RT; i++) {
+          if (C > 1 && i % C != rank) {  // another rank's row tile
+            if (i == j + 1) {
+              cluster_arrive();
+              pending = true;
+            }
+            continue;
+          }
           bool do0 = true, do1 = true;
           int nrows = TILE;
           double* out;
@@ -227,11 +269,19 @@ __global__ void __launch_bounds__(THREADS, 1) dense_sampler_kernel(DevBatch d, i
           copy_tile_out(pipe, out, npad, nrows);
           __syncthreads();
           PROF(8);
+          if (C > 1 && i == j + 1) {  // next step's row panel is stored: let the other ranks go on
+            cluster_arrive();
+            pending = true;
+          }
         }
+      }
+      if (C > 1) {
+        if (pending) cluster_wait();
+        cluster_sync_all();  // every right-hand-side tile (forward solve) and, on the diagonal branch, every row is stored
       }
       if (!alive) {
         __syncthreads();
-        if (threadIdx.x == 0) {
+        if (threadIdx.x == 0 && rank == 0) {
           d.failed[b] = 1;
           d.n_done[b] = it;
         }
@@ -240,9 +290,12 @@ __global__ void __launch_bounds__(THREADS, 1) dense_sampler_kernel(DevBatch d, i
 
       // ---------------- backward solve  x^T = z^T L^-1
       for (int rt = 0; rt < RT && !isdiag; rt++) {
-        const bool do0 = rt * 16 + ln.rf[0] < rhs_frags, do1 = rt * 16 + ln.rf[1] < rhs_frags;
+        // the sample rows are independent: this rank solves the fragments [frag_lo, frag_hi)
+        const int f0 = rt * 16 + ln.rf[0], f1 = rt * 16 + ln.rf[1];
+        const bool do0 = f0 >= frag_lo && f0 < frag_hi, do1 = f1 >= frag_lo && f1 < frag_hi;
         const int var = rhs_variant(do0, do1);
-        const int nrows = min(TILE, max(0, rhs_frags * 8 - rt * TILE));
+        const int row_lo = min(TILE, max(0, frag_lo * 8 - rt * TILE)), nrows = min(TILE, max(0, frag_hi * 8 - rt * TILE));
+        if (nrows <= row_lo) continue;  // CTA-uniform
         double* rrow = Rh + (size_t)rt * TILE * npad;
         for (int j = nblk - 1; j >= 0; j--) {
           double* xt = rrow + j * TILE;
@@ -255,28 +308,29 @@ __global__ void __launch_bounds__(THREADS, 1) dense_sampler_kernel(DevBatch d, i
           PROF(9);
           stage_acc(acc, pipe, ln, do0, do1);
           __syncthreads();
-          add_global(pipe, xt, npad, nrows);
+          add_global(pipe, xt, npad, nrows, row_lo);
           __syncthreads();
           trisolve<true>(pipe, sWp, ln, var);
           __syncthreads();
-          copy_tile_out(pipe, xt, npad, nrows);
+          copy_tile_out(pipe, xt, npad, nrows, row_lo);
           __syncthreads();
           PROF(10);
         }
       }
 
+      if (C > 1) cluster_sync_all();  // x complete (rows solved by different ranks)
       if (d.wiener) {
         double* xo = d.xout + (size_t)d.xoff[b] * nsys;
-        for (long long e = threadIdx.x; e < (long long)Tb * nsys; e += THREADS) {
+        for (long long e = threadIdx.x + rank * THREADS; e < (long long)Tb * nsys; e += THREADS * C) {
           int t = (int)(e / nsys), k = (int)(e % nsys);
           xo[e] = Rh[(size_t)t * npad + k];
         }
-        if (threadIdx.x == 0) d.n_done[b] = 1;
+        if (threadIdx.x == 0 && rank == 0) d.n_done[b] = 1;
         break;
       }
 
       // ---------------- power-spectrum draw (delay.py:1862-1880)
-      for (int k = threadIdx.x; k < N; k += THREADS) {
+      for (int k = threadIdx.x + rank * THREADS; k < N; k += THREADS * C) {
         double var = 0.0;
         const int ncomp = d.cplx ? 2 : 1;
         for (int comp = 0; comp < ncomp; comp++) {
@@ -316,8 +370,9 @@ __global__ void __launch_bounds__(THREADS, 1) dense_sampler_kernel(DevBatch d, i
         S[k] = snew;
         d.samples[((size_t)it * d.B + b) * N + k] = snew;
       }
-      if (threadIdx.x == 0) d.n_done[b] = it + 1;
+      if (threadIdx.x == 0 && rank == 0) d.n_done[b] = it + 1;
       __syncthreads();
+      if (C > 1) cluster_sync_all();  // S of the next iteration; the right-hand sides may be overwritten
       PROF(11);
     }
   }
@@ -329,13 +384,130 @@ size_t dense_smem_bytes(const DevBatch& d) {
 size_t dense_wp_doubles_per_slot(const DevBatch& d) { return (size_t)d.nblk * WP_DOUBLES; }
 
 cudaError_t dense_configure(const DevBatch& d) {
-  return cudaFuncSetAttribute(dense_sampler_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                              (int)dense_smem_bytes(d));
+  const int bytes = (int)dense_smem_bytes(d);
+  cudaError_t e = cudaFuncSetAttribute(dense_sampler_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(dense_sampler_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  if (e != cudaSuccess) return e;
+  return cudaFuncSetAttribute(dense_sampler_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
 }
 
-cudaError_t launch_dense_sampler(const DevBatch& d, int it_begin, int it_end, cudaStream_t st) {
-  dense_sampler_kernel<<<d.nslots, THREADS, dense_smem_bytes(d), st>>>(d, it_begin, it_end);
-  return cudaGetLastError();
+template <int C>
+static cudaError_t launch_one(const DevBatch& d, int it_begin, int it_end, int nclusters, cudaStream_t st) {
+  if (C == 1) {
+    dense_sampler_kernel<1><<<nclusters, THREADS, dense_smem_bytes(d), st>>>(d, it_begin, it_end);
+    return cudaGetLastError();
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(nclusters * C);
+  cfg.blockDim = dim3(THREADS);
+  cfg.dynamicSmemBytes = dense_smem_bytes(d);
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = C;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, dense_sampler_kernel<C>, d, it_begin, it_end);
+}
+
+// clusters of C CTAs that the device keeps resident at once (C = 1: one CTA per SM)
+template <int C>
+static int max_clusters(const DevBatch& d, int sm_count) {
+  if (C == 1) return sm_count;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((sm_count / C) * C);
+  cfg.blockDim = dim3(THREADS);
+  cfg.dynamicSmemBytes = dense_smem_bytes(d);
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = C;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  int n = 0;
+  if (cudaOccupancyMaxActiveClusters(&n, dense_sampler_kernel<C>, &cfg) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  return n;
+}
+
+// Relative duration of one chain on a cluster of C CTAs (C = 1: 1.0), measured at cfg2 geometry
+// (profiles/r02a_cluster_split.json.log): the diagonal tile is factored by every rank and the backward
+// solve is latency-bound, so the split is worth less than C.
+static double chain_cost(int C) { return C == 1 ? 1.0 : (C == 2 ? DGIBBS_COST_C2 : DGIBBS_COST_C4); }
+
+DensePlan plan_dense(const DevBatch& d, int nchains, int sm_count, int force_cluster) {
+  DensePlan p{};
+  const int slots = d.nslots;  // workspace slots = concurrent chains
+  int ncl[5] = {0, slots < sm_count ? slots : sm_count, 0, 0, 0};
+  ncl[2] = max_clusters<2>(d, sm_count);
+  ncl[4] = max_clusters<4>(d, sm_count);
+  for (int C = 2; C <= 4; C *= 2) ncl[C] = ncl[C] < slots ? ncl[C] : slots;
+  if (force_cluster == 1 || force_cluster == 2 || force_cluster == 4) {
+    if (ncl[force_cluster] > 0) {
+      p.C_tail = force_cluster;
+      p.n_tail = nchains;
+      p.grid_tail = nchains < ncl[force_cluster] ? nchains : ncl[force_cluster];
+      return p;
+    }
+  }
+  const int S = ncl[1];
+  p.n_main = (nchains / S) * S;
+  p.grid_main = S;
+  const int rem = nchains - p.n_main;
+  if (rem == 0) return p;
+  double best = 1e300;
+  for (int C = 1; C <= 4; C *= 2) {
+    if (ncl[C] <= 0) continue;
+    if (C > 1 && (d.project_only || d.nblk < 2)) continue;  // nothing to divide
+    const int rounds = (rem + ncl[C] - 1) / ncl[C];
+    const double cost = rounds * chain_cost(C);
+    if (cost < best - 1e-9) {
+      best = cost;
+      p.C_tail = C;
+      p.grid_tail = rem < ncl[C] ? rem : ncl[C];
+    }
+  }
+  p.n_tail = rem;
+  return p;
+}
+
+cudaError_t launch_dense_sampler(const DevBatch& d, int it_begin, int it_end, cudaStream_t st, int sm_count,
+                                 int force_cluster, int* launches) {
+  const int nchains = d.blist ? d.nlist : d.B;
+  if (sm_count <= 0) sm_count = d.nslots;
+  const DensePlan p = plan_dense(d, nchains, sm_count, force_cluster);
+  static const bool verbose = getenv("DGIBBS_VERBOSE") != nullptr;
+  if (verbose)
+    fprintf(stderr, "[dgibbs] dense plan: %d chains = %d on %d CTAs + %d on %d clusters of %d\n", nchains, p.n_main,
+            p.grid_main, p.n_tail, p.grid_tail, p.C_tail);
+  cudaError_t e = cudaSuccess;
+  if (p.n_main > 0) {
+    DevBatch dm = d;
+    dm.li_begin = 0;
+    dm.li_end = p.n_main;
+    e = launch_one<1>(dm, it_begin, it_end, p.grid_main, st);
+    if (e != cudaSuccess) return e;
+    if (launches) ++*launches;
+  }
+  if (p.n_tail > 0) {
+    DevBatch dt = d;
+    dt.li_begin = p.n_main;
+    dt.li_end = p.n_main + p.n_tail;
+    switch (p.C_tail) {
+      case 4: e = launch_one<4>(dt, it_begin, it_end, p.grid_tail, st); break;
+      case 2: e = launch_one<2>(dt, it_begin, it_end, p.grid_tail, st); break;
+      default: e = launch_one<1>(dt, it_begin, it_end, p.grid_tail, st); break;
+    }
+    if (e != cudaSuccess) return e;
+    if (launches) ++*launches;
+  }
+  return e;
 }
 
 }  // namespace dg

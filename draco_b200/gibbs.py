@@ -231,7 +231,7 @@ def cut_batch(vis, weight, channel_ind, N, S0, *, time_frac=-1.0, freq_frac=-1.0
 
 
 
-def _problem(pb: PackedBatch, niter, rng_mode, seed, median_frac, draws=None, force_branch=0):
+def _problem(pb: PackedBatch, niter, rng_mode, seed, median_frac, draws=None, force_branch=0, cluster_size=0):
     p = _lib.Problem()
     p.struct_size = C.sizeof(_lib.Problem)
     p.on_device = 1 if pb.on_device else 0
@@ -244,6 +244,7 @@ def _problem(pb: PackedBatch, niter, rng_mode, seed, median_frac, draws=None, fo
     p.seed = int(seed) & 0xFFFFFFFFFFFFFFFF
     p.median_frac = float(median_frac)
     p.force_branch = int(force_branch)
+    p.cluster_size = int(cluster_size)
     for name in ("T", "M", "data_off", "chan_off", "data", "Ni", "fsel", "S0", "global_id"):
         setattr(p, name, _ptr(getattr(pb, name)))
     keep = []
@@ -291,8 +292,12 @@ def run_batch(
     save_samples=False,
     want_final_S=False,
     force_branch=0,
+    cluster_size=0,
 ) -> BatchResult:
-    """Run every chain of a packed batch on the GPU (replaces the loop delay.py:1146-1178)."""
+    """Run every chain of a packed batch on the GPU (replaces the loop delay.py:1146-1178).
+
+    ``cluster_size``: CTAs that share one chain of the dense branch (0 = planned per launch so that the last wave
+    fills the GPU; 1, 2, 4 force it).  The samples do not depend on it."""
     device = pb.data.device.index if pb.on_device else 0
     h = handle or get_handle(device or 0)
     B, N = pb.B, int(pb.N)
@@ -319,7 +324,7 @@ def run_batch(
         success = np.empty(B, dtype=np.uint8)
         branch = np.empty(B, dtype=np.uint8)
         final_S = np.empty((B, N), dtype=np.float64) if want_final_S else None
-    p, keep = _problem(pb, niter, rng_mode, seed, median_frac, draws, force_branch)
+    p, keep = _problem(pb, niter, rng_mode, seed, median_frac, draws, force_branch, cluster_size)
     r = _lib.Result()
     r.struct_size = C.sizeof(_lib.Result)
     r.on_device = p.on_device
@@ -410,11 +415,11 @@ def delay_spectrum_wiener_filter(delay_PS, data, N, Ni, window="nuttall", fsel=N
     return y.view(np.complex128) if complex_timedomain else y
 
 
-def wiener_batch(pb: PackedBatch, *, handle: Handle | None = None):
+def wiener_batch(pb: PackedBatch, *, handle: Handle | None = None, cluster_size=0):
     """Wiener-filter every baseline of a packed batch (host arrays, or the device-resident batch
     :func:`cut_batch` leaves behind); returns a list of (T_b, n_sys) host arrays and a success flag per baseline."""
     n_sys = (2 if pb.complex_timedomain else 1) * int(pb.N)
-    p, keep = _problem(pb, 1, RNG_ZERO, 0, 0.5)
+    p, keep = _problem(pb, 1, RNG_ZERO, 0, 0.5, cluster_size=cluster_size)
     if pb.on_device:
         import torch
 

@@ -108,7 +108,10 @@ typedef struct {
   const double* chi2;
   int32_t force_branch;  /* 0 = choose as the reference does (delay.py:1884-1886); else a
                             DGIBBS_BRANCH_* value to force where mathematically valid */
-  int32_t reserved;
+  int32_t cluster_size;  /* CTAs (one thread-block cluster) that share one chain of the dense branch: 0 = chosen per
+                            launch (full waves one CTA per chain, the remainder on clusters so that the last wave
+                            fills the GPU); 1, 2, 4 = every chain on clusters of that size.  The samples do not
+                            depend on it (bit-identical). */
 } dgibbs_problem;
 
 typedef struct {
