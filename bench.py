@@ -8,10 +8,20 @@ batch of synthetic visibilities of the named config; at N GPUs each rank runs th
 shard of the baseline axis (weak scaling; per-rank work fixed), followed by the NCCL all-reduce of
 the baseline-group averages.  `value` has the inputs resident in HBM; `e2e` goes through the
 host-pointer C-ABI call (H2D + D2H inside the timed region).  Rank 0 prints ONE JSON line.
+
+The same line carries three more records (each skippable with --no-strong / --no-diag / --no-task):
+  strong    ONE step of BASELINE config 4 at FIXED total size: 4096 baselines x nsamp 200 divided over the ranks in
+            contiguous blocks (dist.split_range, the reference's MPI layout delay.py:2297-2298), 64 groups of 64
+            averaged with an NCCL all-reduce, spectra all-gathered; `result_checksum` must be identical at 1/2/4/8 GPUs.
+  diag      BASELINE config 3 (diagonal branch, HBM-bound): 16384 pixels / GPUs per rank, device-resident `value`
+            with its HBM roofline and `e2e` from pinned complex64 host buffers through the pipelined upload.
+  e2e_task  wall time of DelayPowerSpectrumGibbs.process() on a complex64 / float32 SiderealStream shard
+            (cut + pack + H2D + chains + D2H: SURVEY 8d's definition of the metric).
 """
 from __future__ import annotations
 
 import argparse
+import hashlib
 import json
 import os
 import subprocess
@@ -38,7 +48,20 @@ def parse():
     ap.add_argument("--nbase", type=int, default=None, help="override baselines per rank (debug)")
     ap.add_argument("--nsamp", type=int, default=None, help="override Gibbs iterations (debug)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-strong", action="store_true", help="skip the fixed-size cfg4 record")
+    ap.add_argument("--no-diag", action="store_true", help="skip the cfg3 (diagonal branch) record")
+    ap.add_argument("--no-task", action="store_true", help="skip the task-level end-to-end record")
+    ap.add_argument("--strong-nbase", type=int, default=None, help="override the TOTAL baselines of the strong record (debug)")
+    ap.add_argument("--strong-nsamp", type=int, default=None)
+    ap.add_argument("--diag-nbase", type=int, default=None, help="override the TOTAL pixels of the diag record (debug)")
+    ap.add_argument("--e2e-steps", type=int, default=5, help="e2e is timed on min(steps, this) steps")
     return ap.parse_args()
+
+
+def workload_label(cfg, nbase, nsamp):
+    """Identical in both arms so that the driver's same_config check compares like with like."""
+    return (f"{cfg.name}: {nbase} baselines/GPU x {cfg.nfreq} freq (N={cfg.ndelay}), T={cfg.ntime}, nsamp={nsamp}, "
+            f"window={cfg.window}, weights={cfg.weights}, mask={cfg.mask}")
 
 
 # --------------------------------------------------------------------------- inputs
@@ -65,6 +88,27 @@ def make_inputs(cfg, nbase, base_offset):
                             N, S0, window=cfg.window, global_id=gid)
 
 
+def make_device_batch(cfg, lo, hi, device, chunk=512):
+    """Device-resident packed batch of the global baselines [lo, hi) of a config with a common channel set, built
+    chunk by chunk so that the host never holds more than `chunk` baselines."""
+    import torch
+
+    from draco_b200 import gibbs
+
+    parts = [make_inputs(cfg, min(chunk, hi - b0), b0).to_device(device) for b0 in range(lo, hi, chunk)]
+    if len(parts) == 1:
+        return parts[0]
+    T0, M0 = int(parts[0].T[0]), int(parts[0].M[0])
+    for p in parts:
+        assert bool((p.T == T0).all()) and bool((p.M == M0).all()), "chunks must share (T, M)"
+    B = hi - lo
+    dev = parts[0].data.device
+    cat = lambda name: torch.cat([getattr(p, name) for p in parts])  # noqa: E731
+    return gibbs.PackedBatch(parts[0].N, cat("T"), cat("M"), torch.arange(B + 1, dtype=torch.int64, device=dev) * (T0 * M0),
+                             torch.arange(B + 1, dtype=torch.int64, device=dev) * M0, cat("data"), cat("Ni"), cat("fsel"),
+                             cat("S0"), cat("global_id"), parts[0].complex_timedomain, parts[0].window)
+
+
 def pin(pb):
     """Copy the batch's arrays into pinned host memory (numpy views of pinned torch tensors)."""
     import dataclasses
@@ -75,10 +119,10 @@ def pin(pb):
     for f in dataclasses.fields(pb):
         v = getattr(pb, f.name)
         if isinstance(v, np.ndarray):
-            raw = v.view(np.float64) if v.dtype == np.complex128 else v
+            raw = v.view(np.float64) if v.dtype == np.complex128 else (v.view(np.float32) if v.dtype == np.complex64 else v)
             t = torch.empty(raw.shape, dtype=torch.from_numpy(raw[:0].copy()).dtype, pin_memory=True)
             t.numpy()[...] = raw
-            v = t.numpy().view(np.complex128) if v.dtype == np.complex128 else t.numpy()
+            v = t.numpy().view(v.dtype) if v.dtype in (np.complex128, np.complex64) else t.numpy()
             kw.setdefault("_keep", []).append(t)
         kw[f.name] = v
     keep = kw.pop("_keep", [])
@@ -92,11 +136,11 @@ class ClockSampler:
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
-    def __init__(self, index):
+    def __init__(self, index, period_ms=200):
         self.rows, self.proc = [], None
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-lms", "200", "-i", str(index)], stdout=subprocess.PIPE, text=True)
+                                          "-lms", str(period_ms), "-i", str(index)], stdout=subprocess.PIPE, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
         except OSError:
@@ -120,24 +164,27 @@ class ClockSampler:
 
 
 # --------------------------------------------------------------------------- CPU baseline
-def _cpu_worker(args):
-    os.environ["OPENBLAS_NUM_THREADS"] = os.environ["OMP_NUM_THREADS"] = os.environ["MKL_NUM_THREADS"] = "1"
-    cfg_name, b, niter = args
-    try:
-        from threadpoolctl import threadpool_limits
-        ctx = threadpool_limits(1)
-    except Exception:  # pragma: no cover
-        import contextlib
-        ctx = contextlib.nullcontext()
+def _cpu_chain(cfg, b, niter, use_reference):
+    """One baseline of the config through the reference's CPU arithmetic: (t_setup, t_per_iteration, iterations)."""
     import oracle
     from draco_b200 import synth
 
-    cfg = synth.CONFIGS[cfg_name]
-    with ctx:
-        freq, vis, wgt = synth.make_stack(cfg, nbase=1, base_offset=b)
-        _, chan = oracle.calculate_delays(freq)
-        d, w, nzf, _ = oracle.cut_data(vis[0], wgt[0])
-        N = cfg.ndelay
+    freq, vis, wgt = synth.make_stack(cfg, nbase=1, base_offset=b, threads=1)
+    _, chan = oracle.calculate_delays(freq)
+    d, w, nzf, _ = oracle.cut_data(vis[0], wgt[0])
+    N = cfg.ndelay
+    if use_reference:  # the reference's own functions, executed where they lie (build container only)
+        from oracle import ref_loader
+
+        ref = ref_loader.load()
+        t0 = time.perf_counter()
+        ref._compute_delay_spectrum_inputs(d.copy(), N, w, chan[nzf], cfg.window, False)
+        t_setup = time.perf_counter() - t0
+        t0 = time.perf_counter()
+        s, ok = ref.delay_power_spectrum_gibbs(d.copy(), N, w, np.full(N, 10.0), window=cfg.window, fsel=chan[nzf],
+                                               niter=niter, rng=np.random.default_rng(b))
+        t_chain = time.perf_counter() - t0
+    else:
         t0 = time.perf_counter()
         oracle.whiten_inputs(d, N, w, chan[nzf], cfg.window, False)
         t_setup = time.perf_counter() - t0
@@ -147,27 +194,87 @@ def _cpu_worker(args):
     return t_setup, (t_chain - t_setup) / max(1, len(s)), len(s)
 
 
-def cpu_baseline(cfg, nsamp, niter_sample=6, procs=None):
-    """The oracle (numpy + LAPACK, the reference's own arithmetic) on this box's host cores:
-    P single-threaded worker processes, one baseline block each -- the reference's MPI layout
-    (no mpirun/mpi4py on the box, so multiprocessing).  Times a bounded sample and extrapolates
-    linearly in baselines x nsamp."""
+def _cpu_worker(args):
+    os.environ["OPENBLAS_NUM_THREADS"] = os.environ["OMP_NUM_THREADS"] = os.environ["MKL_NUM_THREADS"] = "1"
+    cfg_name, b0, nb, niter, use_reference = args
+    try:
+        from threadpoolctl import threadpool_limits
+        ctx = threadpool_limits(1)
+    except Exception:  # pragma: no cover
+        import contextlib
+        ctx = contextlib.nullcontext()
+    from draco_b200 import synth
+
+    cfg = synth.CONFIGS[cfg_name]
+    with ctx:
+        return [_cpu_chain(cfg, b0 + i, niter, use_reference) for i in range(nb)]
+
+
+def _cpu_model():
+    try:
+        with open("/proc/cpuinfo") as f:
+            for line in f:
+                if line.lower().startswith("model name"):
+                    return line.split(":", 1)[1].strip()
+    except OSError:
+        pass
+    return "unknown"
+
+
+def _blas_info():
+    try:
+        from threadpoolctl import threadpool_info
+
+        return [{k: i.get(k) for k in ("internal_api", "version", "num_threads", "threading_layer", "architecture")}
+                for i in threadpool_info() if i.get("user_api") == "blas"]
+    except Exception:  # pragma: no cover
+        return []
+
+
+def cpu_baseline(cfg, nsamp, niter_sample=10, per_proc=2, procs=None, all_threads=True):
+    """BASELINE.md section 3.  The reference's CPU arithmetic on this box's host cores: P single-BLAS-thread worker
+    processes (P = host cores), each owning a contiguous block of `per_proc` baselines -- the reference's MPI layout
+    (no mpirun / mpi4py on the box, so multiprocessing) -- for `niter_sample` iterations, set-up timed separately,
+    extrapolated linearly in baselines x nsamp.  Also 1 process x all BLAS threads.  Where the reference tree is
+    present (build container) the reference's own functions are timed (kind "reference"), else the oracle port."""
     import multiprocessing as mp
 
+    from oracle import ref_loader
+
+    use_ref = ref_loader.available()
     P = procs or os.cpu_count() or 1
     ctx = mp.get_context("spawn")
     t0 = time.perf_counter()
     with ctx.Pool(P) as pool:
-        res = pool.map(_cpu_worker, [(cfg.name, b, niter_sample) for b in range(P)])
+        res = pool.map(_cpu_worker, [(cfg.name, p * per_proc, per_proc, niter_sample, use_ref) for p in range(P)])
     wall = time.perf_counter() - t0
-    t_setup = float(np.mean([r[0] for r in res]))
-    t_iter = float(np.mean([r[1] for r in res]))
+    flat = [r for rr in res for r in rr]
+    t_setup = float(np.mean([r[0] for r in flat]))
+    t_iter = float(np.mean([r[1] for r in flat]))
     value = P * nsamp / (t_setup + nsamp * t_iter)  # P baselines advance concurrently
-    return {"value": value, "unit": UNIT, "cores": P, "kind": "port",
-            "sample": f"{P} baselines x {niter_sample} iterations of {cfg.name} geometry (N={cfg.ndelay}, T={cfg.ntime}), "
-                      f"1 BLAS thread per process; t_setup={t_setup:.3f}s t_iter={t_iter:.4f}s, extrapolated to nsamp={nsamp}; "
-                      f"sample wall {wall:.1f}s",
-            "t_setup_s": t_setup, "t_iter_s": t_iter}
+    out = {"value": value, "unit": UNIT, "cores": P, "kind": "reference" if use_ref else "port",
+           "layout": "multiprocessing (spawn), one process per core, 1 BLAS thread each; mpirun/mpi4py absent",
+           "sample": f"{P * per_proc} baselines ({per_proc} per process) x {niter_sample} iterations of {cfg.name} geometry "
+                     f"(N={cfg.ndelay}, T={cfg.ntime}); t_setup={t_setup:.3f}s t_iter={t_iter:.4f}s per baseline, "
+                     f"extrapolated to nsamp={nsamp}; sample wall {wall:.1f}s",
+           "sample_wall_s": wall, "sample_units": P * per_proc * niter_sample,
+           "t_setup_s": t_setup, "t_iter_s": t_iter, "cpu_model": _cpu_model(), "blas": _blas_info(),
+           "numpy": np.__version__}
+    try:
+        import scipy
+
+        out["scipy"] = scipy.__version__
+    except Exception:  # pragma: no cover
+        pass
+    if all_threads:
+        _cpu_chain(cfg, 0, 1, use_ref)  # BLAS thread pool warm-up
+        t0 = time.perf_counter()
+        ts, ti, n = _cpu_chain(cfg, 0, max(2, niter_sample // 2), use_ref)
+        out["one_process_all_blas_threads"] = {
+            "value": nsamp / (ts + nsamp * ti), "unit": UNIT, "t_setup_s": ts, "t_iter_s": ti,
+            "sample": f"1 baseline x {n} iterations, BLAS threads = library default ({os.cpu_count()} cores)",
+            "sample_wall_s": time.perf_counter() - t0}
+    return out
 
 
 # --------------------------------------------------------------------------- main
@@ -198,6 +305,7 @@ def fp64_peak_tflops():
 # geometry = 245.8 MB per baseline-iteration (L panels re-read from DRAM; 14 % of DRAM peak, not the bound).
 # Reported per launch of THIS run by scaling with the launch's baseline-iterations (cfg2 geometry only).
 DENSE_TRAFFIC_PER_UNIT = 72.985e9 / 296  # r01o capture: 66.76 GB read + 6.22 GB written
+DENSE_TRAFFIC_SOURCE = "ncu --set full capture of 296 baseline-iterations scaled to this launch (profiles/r01o_dense_sampler_ncu_raw.csv)"
 
 
 # dram__bytes_read.sum + dram__bytes_write.sum of diag_resident_kernel from the committed `ncu --set full` capture
@@ -224,26 +332,144 @@ def hbm_roofline(nbytes, ms, units=None):
 
 
 def run_reference(args, cfg, nsamp):
+    """Reference arm: the reference's CPU implementation of the path on the box's host cores (oracle port; the
+    reference's own functions where /root/reference exists).  Each step is a bounded sample (2 baselines per core x 10
+    iterations); `value` is that sample extrapolated linearly to the workload's nsamp, `ms_per_step` the wall time of
+    one sample step as actually run."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    vals, last = [], None
+    vals, walls, last = [], [], None
     for i in range(args.warmup + args.steps):
-        last = cpu_baseline(cfg, nsamp)
+        last = cpu_baseline(cfg, nsamp, all_threads=(i == args.warmup + args.steps - 1))
         if i >= args.warmup:
             vals.append(last["value"])
+            walls.append(last["sample_wall_s"])
     v = float(np.mean(vals)) if vals else last["value"]
     last["value"] = v
     nb = args.nbase or cfg.nbase
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": 1e3 * nb * nsamp / v, "higher_is_better": True, "scaling": "weak",
+        "warmup": args.warmup, "ms_per_step": 1e3 * float(np.mean(walls)) if walls else None,
+        "ms_per_full_step_extrapolated": 1e3 * nb * nsamp / v, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": f"{cfg.name}: {nb} baselines x {cfg.nfreq} freq (N={cfg.ndelay}), T={cfg.ntime}, nsamp={nsamp}",
-                   "note": "reference CPU path (numpy + scipy LAPACK restatement; the Python reference cannot travel) on all host cores"},
+        "config": {"workload": workload_label(cfg, nb, nsamp),
+                   "note": "reference CPU path on all host cores; every step is a BOUNDED SAMPLE of the workload "
+                           "(cpu_baseline.sample), value = sample extrapolated linearly in baselines x nsamp"},
         "cpu_baseline": last,
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
+
+
+def sha16(t):
+    """First 16 hex digits of the SHA-256 of a tensor's / array's bytes."""
+    a = t.detach().cpu().numpy() if hasattr(t, "detach") else np.asarray(t)
+    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()[:16]
+
+
+def strong_record(args, handle, rank, world, local, sync):
+    """ONE step of BASELINE config 4 at fixed total size, divided over the ranks like the reference's baseline axis."""
+    import torch
+    import torch.distributed as dist
+
+    from draco_b200 import dist as ddist
+    from draco_b200 import gibbs, synth
+
+    cfg = synth.CONFIGS["cfg4"]
+    total = args.strong_nbase or cfg.nbase
+    nsamp = args.strong_nsamp or cfg.nsamp
+    group_size = 64
+    ngroup = -(-total // group_size)
+    lo, hi = ddist.split_range(total, world, rank)
+    t0 = time.perf_counter()
+    pb = make_device_batch(cfg, lo, hi, local)
+    t_gen = time.perf_counter() - t0
+    gids = np.arange(lo, hi)
+    seed = 4242  # one seed for every N: Philox is keyed on the global baseline id
+
+    def step():
+        res = gibbs.run_batch(pb, nsamp, handle=handle, seed=seed)
+        avg, cnt = ddist.group_average(res.spectrum, gids, ngroup, group_size, weights=res.success)
+        full = ddist.gather_spectra(res.spectrum, total)
+        return res, avg, cnt, full
+
+    sync()
+    clocks = ClockSampler(local, 500)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    res, avg, cnt, full = step()
+    e1.record()
+    sync()
+    clk = clocks.stop()
+    ms = torch.tensor([e0.elapsed_time(e1), float(res.timing["ms_sampler"])], dtype=torch.float64, device="cuda")
+    nok = torch.tensor([float(res.success.sum().item())], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        dist.all_reduce(nok)
+    if rank != 0:
+        return None
+    # group averages recomputed from the gathered spectra in a fixed order (identical at every N); the all-reduced
+    # averages (summation order depends on N) must agree with them to rounding
+    fixed = full[: ngroup * group_size].view(ngroup, group_size, -1).mean(dim=1) if total % group_size == 0 else None
+    nsm = torch.cuda.get_device_properties(local).multi_processor_count
+    nloc = hi - lo
+    out = {
+        "workload": f"cfg4: {total} baselines TOTAL x {cfg.nfreq} freq (N={cfg.ndelay}), T={cfg.ntime}, nsamp={nsamp}, "
+                    f"{ngroup} groups of {group_size}, window={cfg.window}, weights={cfg.weights}",
+        "scaling": "strong", "n_gpus": world, "steps": 1,
+        "partition": f"contiguous blocks of the baseline axis (dist.split_range), rank 0 owns [{lo}, {hi})",
+        "baseline_iter_per_s": total * nsamp / (float(ms[0].item()) / 1e3), "unit": UNIT,
+        "ms_step": float(ms[0].item()), "ms_sampler_max": float(ms[1].item()),
+        "chains_per_gpu": nloc, "waves_per_gpu_ideal": nloc / nsm,
+        "dense_plan": "full waves one CTA per chain + remainder on thread-block clusters (dgibbs_problem.cluster_size = 0)",
+        "sampler_launches": int(res.timing["sampler_launches"]),
+        "collectives": "NCCL all-reduce of [ngroup, N+1] group sums + all-gather of [B, N] spectra" if world > 1
+                       else "none (1 GPU)",
+        "chains_ok": int(nok.item()), "inputs": f"device-resident (generated in {t_gen:.1f} s, outside the timed region)",
+        "result_checksum": sha16(full), "group_average_checksum": sha16(fixed) if fixed is not None else None,
+        "allreduce_vs_fixed_order_max_rel": float(((avg - fixed).abs().max() / fixed.abs().max()).item()) if fixed is not None else None,
+        "clocks": clk,
+    }
+    return out
+
+
+def task_record(args, cfg, nsamp, nbase, rank, world, local, sync, handle):
+    """Wall time of DelayPowerSpectrumGibbs.process() on a complex64 / float32 SiderealStream holding this rank's shard:
+    device cut + pack + H2D + all chains + D2H ('wall time of _evaluate')."""
+    import torch
+    import torch.distributed as dist
+
+    from draco_b200 import _compat, delay, synth
+
+    freq, vis, wgt = synth.make_stack(cfg, nbase=nbase, base_offset=rank * nbase)
+    vis32, wgt32 = vis.astype(np.complex64), wgt.astype(np.float32)
+    del vis, wgt
+    # container layout of draco's SiderealStream: vis [freq, stack, ra], weight likewise
+    ss = _compat.SiderealStream(freq=freq, stack=nbase, ra=cfg.ntime, native_dtypes=True)
+    ss.vis[:] = np.ascontiguousarray(vis32.transpose(2, 0, 1))
+    ss.weight[:] = np.ascontiguousarray(wgt32.transpose(2, 0, 1))
+    task = delay.DelayPowerSpectrumGibbs()
+    task.read_config({"nsamp": nsamp, "sample_axis": "ra", "window": cfg.window or "nuttall",
+                      "apply_window": cfg.window is not None, "seed": 31, "device": local})
+    task.setup()
+    task.process(ss)  # warm-up
+    sync()
+    n = 1
+    t0 = time.perf_counter()
+    for _ in range(n):
+        out = task.process(ss)
+    torch.cuda.synchronize()
+    dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+    if rank != 0:
+        return None
+    spec = np.asarray(getattr(out.spectrum[:], "local_array", out.spectrum[:]))
+    return {"value": world * nbase * nsamp * n / float(dt.item()), "unit": UNIT, "steps": n,
+            "what": "DelayPowerSpectrumGibbs.process(SiderealStream complex64/float32): flatten_axes + device _cut_data + "
+                    "pack + H2D + chains + D2H into the DelaySpectrum container, host wall clock",
+            "h2d_bytes_per_step": int(vis32.nbytes + wgt32.nbytes), "d2h_bytes_per_step": int(spec.nbytes),
+            "spectrum_finite": bool(np.isfinite(spec).all())}
 
 
 def main():
@@ -314,11 +540,13 @@ def main():
     ms = float(ms.item())
     n_ok = int(res.success.sum().item())
     value = world * nbase * nsamp * args.steps / (ms / 1e3)
+    weak_checksum = sha16(res.spectrum[: min(nbase, 64)])
 
     # ---- end to end through the host-pointer C-ABI call (pinned host buffers, H2D + D2H timed)
     pb_pin = pin(pb_host)
     h2d = sum(getattr(pb_pin, f).nbytes for f in ("T", "M", "data_off", "chan_off", "data", "Ni", "fsel", "S0", "global_id"))
     d2h = nbase * cfg.ndelay * 8 + nbase * 5
+    e2e_steps = max(1, min(args.steps, args.e2e_steps))
 
     def step_e2e(i):
         r = gibbs.run_batch(pb_pin, nsamp, handle=handle, seed=2000 + i)
@@ -330,26 +558,41 @@ def main():
     step_e2e(0)
     sync()
     e0.record()
-    for i in range(args.steps):
+    for i in range(e2e_steps):
         step_e2e(1 + i)
     e1.record()
     sync()
     ms2 = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(ms2, op=dist.ReduceOp.MAX)
-    e2e_value = world * nbase * nsamp * args.steps / (float(ms2.item()) / 1e3)
+    e2e_value = world * nbase * nsamp * e2e_steps / (float(ms2.item()) / 1e3)
+    del pb_pin
+
+    extra = {}
+    if not args.no_task:
+        extra["e2e_task"] = task_record(args, cfg, nsamp, nbase, rank, world, local, sync, handle)
+    del pb_dev
+    torch.cuda.empty_cache()
+    if not args.no_strong:
+        extra["strong"] = strong_record(args, handle, rank, world, local, sync)
+        torch.cuda.empty_cache()
+    if not args.no_diag:
+        import bench_diag
+
+        extra["diag"] = bench_diag.diag_record(args, handle, rank, world, local, sync)
+        torch.cuda.empty_cache()
 
     if rank == 0:
         ach = flop / (max(ms_sampler, 1e-9) / 1e3) / 1e12
         if n_diag > 0:
             # diagonal(+rank-1) branch: cluster-resident kernel, judged against the HBM stream of its algorithmic bytes (SURVEY 8d Q_d = 8 n T + 16 N per baseline-iteration)
-            roof = hbm_roofline(nbytes, ms_diag, units=n_diag * nsamp if cfg.ndelay == 2048 else None)
+            roof = hbm_roofline(nbytes, ms_diag, units=n_diag * nsamp * args.steps if cfg.ndelay == 2048 else None)
             branch = f"diagonal(+rank-1) cluster-resident sampler ({n_diag} of {nbase} baselines)"
         else:
             roof = {"bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
                     "traffic": (DENSE_TRAFFIC_PER_UNIT * nbase * nsamp) if cfg.ndelay == 2048 else None,
-                    "traffic_source": "ncu --set full capture of 296 baseline-iterations scaled to this launch (profiles/r01o_dense_sampler_ncu_raw.csv)",
-                    "peak_source": "fp64: cuBLAS DGEMM 8192^3 measured in this run (MEASURED_PEAKS.json has no fp64 entry; "
+                    "traffic_source": DENSE_TRAFFIC_SOURCE,
+                    "peak_source": "fp64: builder-measured cuBLAS DGEMM 8192^3 in this run (MEASURED_PEAKS.json has no fp64 entry; "
                                    "tcgen05 has no fp64 kind, DMMA pipe probe = 37.0 TFLOP/s, profiles/r01_fp64_pipe_probe.log)",
                     "kernel": "dense_sampler_kernel", "flop_model": "W_f = n^3/3 + 2 n^2 T + 4 n M T per baseline-iteration"}
             branch = "dense (_f), fp64 DMMA Cholesky"
@@ -358,19 +601,24 @@ def main():
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic",
             "config": {
-                "workload": f"{cfg.name}: {nbase} baselines/GPU x {cfg.nfreq} freq (N={cfg.ndelay}), T={cfg.ntime}, "
-                            f"nsamp={nsamp}, window={cfg.window}, weights={cfg.weights}, mask={cfg.mask}",
-                "branch": branch, "rng": "device Philox4x32-10",
+                "workload": workload_label(cfg, nbase, nsamp),
+                "branch": branch, "rng": gibbs.rng_description(),
                 "parallelism": f"baseline-sharded x{world}, group-average allreduce ({ngroup} groups of {group_size})",
                 "l2": "inputs (1 GiB visibilities + 5 GiB factor workspace) larger than L2; no flush needed",
-                "chains_ok": n_ok,
+                "chains_ok": n_ok, "spectrum_checksum_first64": weak_checksum,
             },
             "clocks": clk,
-            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                    "steps": e2e_steps},
             "gpu_launches": launches,
             "timing_last_step_ms": {k: round(float(v), 3) for k, v in res.timing.items() if k.startswith("ms_")},
             "roofline": roof,
         }
+        if extra.get("e2e_task"):
+            out["e2e_task"] = extra.pop("e2e_task")
+        if extra.get("strong"):
+            out["strong"] = extra.pop("strong")
+        out["extra"] = {k: v for k, v in extra.items() if v is not None}
         if not args.no_cpu_baseline and world == 1:
             out["cpu_baseline"] = cpu_baseline(cfg, nsamp)
         print(json.dumps(out))

@@ -28,6 +28,7 @@ BRANCH_SKIPPED, BRANCH_DELAY_SPACE, BRANCH_FREQ_SPACE, BRANCH_DIAGONAL = 0, 1, 2
 
 EXPORTED = [
     "dgibbs_version",
+    "dgibbs_rng_info",
     "dgibbs_sizeof",
     "dgibbs_create",
     "dgibbs_destroy",
@@ -76,6 +77,8 @@ class Problem(C.Structure):
         ("chi2", _vp),
         ("force_branch", C.c_int32),
         ("cluster_size", C.c_int32),
+        ("data_c64", C.c_int32),
+        ("reserved", C.c_int32),
     ]
 
 
@@ -180,6 +183,7 @@ def load():
         )
     lib = C.CDLL(LIB_PATH)
     lib.dgibbs_version.restype = C.c_int
+    lib.dgibbs_rng_info.restype = C.c_char_p
     lib.dgibbs_sizeof.argtypes = [C.c_int]
     lib.dgibbs_create.argtypes = [C.c_int, C.c_uint64, C.POINTER(_vp)]
     lib.dgibbs_destroy.argtypes = [_vp]
@@ -198,7 +202,7 @@ def load():
     lib.dgibbs_sample_variance.argtypes = [_vp, C.c_int32, C.c_int32, C.c_int32, C.c_int32, _vp, _vp, _vp, _vp,
                                            C.POINTER(C.c_double)]
     for name in EXPORTED:
-        if name not in ("dgibbs_last_error", "dgibbs_version"):
+        if name not in ("dgibbs_last_error", "dgibbs_version", "dgibbs_rng_info"):
             getattr(lib, name).restype = C.c_int
     for which, st in enumerate((Problem, Result, Timing, CrossProblem, Cut)):
         if lib.dgibbs_sizeof(which) != C.sizeof(st):

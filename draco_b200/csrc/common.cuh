@@ -33,6 +33,17 @@ __device__ __forceinline__ void cp_async_wait() {
   asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
 }
 
+// ---------------------------------------------------------------- visibilities
+// Element `idx` of the caller's visibility array: complex128, or complex64 widened exactly (draco's containers store
+// complex64, core/containers.py:503; shipping them as they are halves the PCIe bytes of the host-pointer path).
+__device__ __forceinline__ double2 ld_vis(const double2* data, int c64, long long idx) {
+  if (c64) {
+    const float2 v = reinterpret_cast<const float2*>(data)[idx];
+    return make_double2((double)v.x, (double)v.y);
+  }
+  return data[idx];
+}
+
 // ---------------------------------------------------------------- Philox4x32-10
 struct Philox {
   uint32_t k0, k1;
@@ -84,7 +95,26 @@ __device__ __forceinline__ void normal_pair_fast(const uint4& r, double& z0, dou
 }
 
 // RNG stream ids inside one (baseline, iteration)
-enum { STREAM_W1 = 0, STREAM_W2 = 1, STREAM_CHI2 = 2 };
+enum { STREAM_W1 = 0, STREAM_W2 = 1, STREAM_CHI2 = 2, STREAM_W1_ODD = 9, STREAM_W2_ODD = 10 };
+
+// The four N(0,1) perturbations that share one counter (c0, c1, iteration): two for the even sample of a pair (z0, z1)
+// and two for the odd one (z2, z3).  Default: fp64 Box-Muller (53-bit uniforms, fp64 log / sincospi -- the resolution of
+// the reference's numpy normals), one Philox block per sample: `stream` for the even, `stream_odd` for the odd sample.
+// -DDGIBBS_FAST_NORMALS=1 restores the fp32 variant (all four from the `stream` block; 1 % faster at cfg2).
+#ifndef DGIBBS_FAST_NORMALS
+#define DGIBBS_FAST_NORMALS 0
+#endif
+__device__ __forceinline__ void normal_quad(const Philox& ph, uint32_t c0, uint32_t c1, uint32_t it, uint32_t stream,
+                                            uint32_t stream_odd, bool even, bool odd, double& z0, double& z1, double& z2,
+                                            double& z3) {
+#if DGIBBS_FAST_NORMALS
+  normal_pair_fast(ph(c0, c1, it, stream), z0, z1, z2, z3);
+#else
+  z0 = z1 = z2 = z3 = 0.0;
+  if (even) normal_pair(ph(c0, c1, it, stream), z0, z1);
+  if (odd) normal_pair(ph(c0, c1, it, stream_odd), z2, z3);
+#endif
+}
 
 __device__ __forceinline__ uint64_t mix_key(uint64_t seed, uint64_t gid) {
   // splitmix64 of (seed, global baseline id): the Philox key of a baseline

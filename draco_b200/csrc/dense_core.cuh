@@ -570,7 +570,7 @@ struct DrawCtx {
   int Tb, it, half;
 };
 // Device-RNG layout of the FFT path: one Philox block serves the sample pair (t & ~1, t | 1): words (x, y) give
-// the two normals of the even sample, (z, w) those of the odd one (fp32 Box-Muller, see normal_pair_fast).
+// the two normals of the even sample, (z, w) those of the odd one (normal_quad, common.cuh: fp64 Box-Muller by default).
 __device__ __forceinline__ void u_value2(const DrawCtx& c, int t0, int i, bool pair, double2& U0, double2& U1) {
   U0 = U1 = make_double2(0.0, 0.0);
   const int ci = c.cidx[i];
@@ -579,9 +579,9 @@ __device__ __forceinline__ void u_value2(const DrawCtx& c, int t0, int i, bool p
   const bool has1 = pair && t0 + 1 < c.Tb;
   if (c.d->rng_mode == 1) {
     unsigned long long blk = (unsigned long long)(t0 >> 1) * c.half + i;
-    uint4 r = (*c.ph)((unsigned)blk, (unsigned)(blk >> 32), (unsigned)c.it, STREAM_W2);
     double e0, e1, e2, e3;
-    normal_pair_fast(r, e0, e1, e2, e3);
+    normal_quad(*c.ph, (unsigned)blk, (unsigned)(blk >> 32), (unsigned)c.it, STREAM_W2, STREAM_W2_ODD, pair || !(t0 & 1),
+                has1 || (!pair && (t0 & 1)), e0, e1, e2, e3);
     if (pair || !(t0 & 1)) { a0 = e0; a1 = e1; b0 = e2; b1 = e3; }
     else { a0 = e2; a1 = e3; }
   } else if (c.d->rng_mode == 0) {
@@ -606,9 +606,9 @@ __device__ __forceinline__ void w1_pair2(const DrawCtx& c, int t0, int k, int ns
   a0 = a1 = b0 = b1 = 0.0;
   if (c.d->rng_mode == 1) {
     unsigned long long blk = ((unsigned long long)(t0 >> 1) * nsys + k) >> 1;
-    uint4 r = (*c.ph)((unsigned)blk, (unsigned)(blk >> 32), (unsigned)c.it, STREAM_W1);
     double e0, e1, e2, e3;
-    normal_pair_fast(r, e0, e1, e2, e3);
+    normal_quad(*c.ph, (unsigned)blk, (unsigned)(blk >> 32), (unsigned)c.it, STREAM_W1, STREAM_W1_ODD, pair || !(t0 & 1),
+                (pair && t0 + 1 < c.Tb) || (!pair && (t0 & 1)), e0, e1, e2, e3);
     if (pair || !(t0 & 1)) { a0 = e0; a1 = e1; b0 = e2; b1 = e3; }
     else { a0 = e2; a1 = e3; }
   } else if (c.d->rng_mode == 0) {

@@ -3,6 +3,7 @@
 // requires a CUDA device and returns the CUDA error otherwise.
 #include <cstdio>
 #include <cstdlib>
+#include <algorithm>
 #include <cstring>
 #include <map>
 #include <string>
@@ -28,6 +29,9 @@ struct dgibbs_handle_s {
   dgibbs_timing timing{};
   std::map<std::string, Buf> pool;  // grow-only device workspace, freed in destroy
   cudaEvent_t ev[8]{};
+  // pipelined host-pointer path: uploads / downloads on their own streams, two buffer sets
+  cudaStream_t up_stream = nullptr, down_stream = nullptr;
+  cudaEvent_t up_done[2]{}, down_done[2]{}, up_t0 = nullptr, up_t1 = nullptr;
   // cached projection table
   int ft_N = -1, ft_cplx = -1, tw_N = -1;
 };
@@ -75,6 +79,17 @@ void dg_set_error(dgibbs_handle h, const char* msg) { h->err = msg; }
 
 extern "C" int dgibbs_version(void) { return DGIBBS_VERSION; }
 
+extern "C" const char* dgibbs_rng_info(void) {
+#if DGIBBS_FAST_NORMALS
+  return "device Philox4x32-10 keyed on (seed, global baseline id), counter (element, iteration, stream); N(0,1): fp32 Box-Muller "
+         "widened to fp64 (-DDGIBBS_FAST_NORMALS); chi^2_T: -2 sum ln u, fp64; diagonal branch: fp32 Marsaglia-Tsang chi^2";
+#else
+  return "device Philox4x32-10 keyed on (seed, global baseline id), counter (element, iteration, stream); N(0,1): fp64 Box-Muller "
+         "(53-bit uniforms, fp64 log / sincospi); chi^2_T: -2 sum ln u, fp64; diagonal branch: collapsed-moment draws, fp32 "
+         "Marsaglia-Tsang chi^2";
+#endif
+}
+
 extern "C" int dgibbs_sizeof(int which) {
   switch (which) {
     case 0: return (int)sizeof(dgibbs_problem);
@@ -109,6 +124,14 @@ extern "C" int dgibbs_create(int device_id, uint64_t stream, dgibbs_handle* out)
     h->own_stream = true;
   }
   for (auto& ev : h->ev) cudaEventCreate(&ev);
+  cudaStreamCreateWithFlags(&h->up_stream, cudaStreamNonBlocking);
+  cudaStreamCreateWithFlags(&h->down_stream, cudaStreamNonBlocking);
+  for (int i = 0; i < 2; i++) {
+    cudaEventCreateWithFlags(&h->up_done[i], cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&h->down_done[i], cudaEventDisableTiming);
+  }
+  cudaEventCreate(&h->up_t0);
+  cudaEventCreate(&h->up_t1);
   *out = h;
   return 0;
 }
@@ -120,6 +143,16 @@ extern "C" int dgibbs_destroy(dgibbs_handle h) {
   for (auto& kv : h->pool)
     if (kv.second.p) cudaFree(kv.second.p);
   for (auto& ev : h->ev) cudaEventDestroy(ev);
+  for (int i = 0; i < 2; i++) {
+    cudaEventDestroy(h->up_done[i]);
+    cudaEventDestroy(h->down_done[i]);
+  }
+  cudaEventDestroy(h->up_t0);
+  cudaEventDestroy(h->up_t1);
+  cudaStreamSynchronize(h->up_stream);
+  cudaStreamSynchronize(h->down_stream);
+  cudaStreamDestroy(h->up_stream);
+  cudaStreamDestroy(h->down_stream);
   if (h->own_stream) cudaStreamDestroy(h->stream);
   delete h;
   return 0;
@@ -145,6 +178,12 @@ struct Staged {
 };
 
 static int round_up(int x, int m) { return (x + m - 1) / m * m; }
+
+// Host copies of a batch's small arrays (the pipelined path has them already: no device -> host round trip)
+struct HostSmall {
+  std::vector<int> T, M;
+  std::vector<long long> data_off, chan_off;
+};
 
 template <typename Tp>
 static cudaError_t fetch(std::vector<Tp>& dst, const Tp* src, size_t n, bool on_device, cudaStream_t st) {
@@ -191,15 +230,19 @@ static int check_problem(dgibbs_handle h, const dgibbs_problem* p) {
 }
 
 // Builds the device-side batch: geometry, staged inputs, derived tables (setup kernels enqueued).
-static int stage_batch(dgibbs_handle h, const dgibbs_problem* p, Staged& s, bool wiener) {
+static int stage_batch(dgibbs_handle h, const dgibbs_problem* p, Staged& s, bool wiener, const HostSmall* hs = nullptr) {
   DevBatch& d = s.d;
   const bool dev = p->on_device != 0;
   const int B = p->B;
   CU(cudaSetDevice(h->device));
-  CU(fetch(s.T, p->T, B, dev, h->stream));
-  CU(fetch(s.M, p->M, B, dev, h->stream));
-  CU(fetch(s.data_off, (const long long*)p->data_off, (size_t)B + 1, dev, h->stream));
-  CU(fetch(s.chan_off, (const long long*)p->chan_off, (size_t)B + 1, dev, h->stream));
+  if (hs) {
+    s.T = hs->T; s.M = hs->M; s.data_off = hs->data_off; s.chan_off = hs->chan_off;
+  } else {
+    CU(fetch(s.T, p->T, B, dev, h->stream));
+    CU(fetch(s.M, p->M, B, dev, h->stream));
+    CU(fetch(s.data_off, (const long long*)p->data_off, (size_t)B + 1, dev, h->stream));
+    CU(fetch(s.chan_off, (const long long*)p->chan_off, (size_t)B + 1, dev, h->stream));
+  }
 
   d.B = B;
   d.N = p->N;
@@ -241,7 +284,12 @@ static int stage_batch(dgibbs_handle h, const dgibbs_problem* p, Staged& s, bool
   CU(stage_in(h, "in_M", (const int*)p->M, B, dev, &d.M));
   CU(stage_in(h, "in_doff", (const long long*)p->data_off, (size_t)B + 1, dev, &d.data_off));
   CU(stage_in(h, "in_coff", (const long long*)p->chan_off, (size_t)B + 1, dev, &d.chan_off));
-  CU(stage_in(h, "in_data", (const double2*)p->data, (size_t)ndata, dev, &d.data));
+  d.data_c64 = p->data_c64 ? 1 : 0;
+  {
+    const char* dptr = nullptr;  // complex128 (16 B) or complex64 (8 B) elements
+    CU(stage_in(h, "in_data", (const char*)p->data, (size_t)ndata * (d.data_c64 ? 8 : 16), dev, &dptr));
+    d.data = (const double2*)dptr;
+  }
   CU(stage_in(h, "in_Ni", p->Ni, (size_t)nchan, dev, &d.Ni));
   CU(stage_in(h, "in_fsel", (const long long*)p->fsel, (size_t)nchan, dev, &d.fsel));
   CU(stage_in(h, "in_S0", p->S0, (size_t)B * d.N, dev, &s.S0));
@@ -363,19 +411,17 @@ extern "C" int dgibbs_workspace_bytes(dgibbs_handle h, const dgibbs_problem* p, 
   return 0;
 }
 
-extern "C" int dgibbs_run(dgibbs_handle h, const dgibbs_problem* p, dgibbs_result* r) {
-  int rc = check_problem(h, p);
-  if (rc) return rc;
-  if (!r || r->struct_size != (int32_t)sizeof(dgibbs_result)) return bad_arg(h, 3, "result struct");
-  if (!r->spectrum || !r->n_done || !r->success) return bad_arg(h, 3, "result.spectrum/n_done/success required");
-  if ((r->on_device != 0) != (p->on_device != 0)) return bad_arg(h, 3, "problem and result must live on the same side");
+// One batch, start to finish, on the handle's stream (synchronous).  `hs`: host copies of T / M / offsets when the
+// caller has them (device-resident problem built by the pipelined path).
+static int run_core(dgibbs_handle h, const dgibbs_problem* p, dgibbs_result* r, const HostSmall* hs) {
+  int rc;
   const bool dev = p->on_device != 0;
   h->timing = dgibbs_timing{};
   CU(cudaSetDevice(h->device));
   CU(cudaEventRecord(h->ev[0], h->stream));
 
   Staged s;
-  rc = stage_batch(h, p, s, false);
+  rc = stage_batch(h, p, s, false, hs);
   if (rc) return rc;
   DevBatch& d = s.d;
   const size_t BN = (size_t)d.B * d.N;
@@ -561,6 +607,155 @@ extern "C" int dgibbs_run(dgibbs_handle h, const dgibbs_problem* p, dgibbs_resul
   h->timing.flop_sampler = flop;
   h->timing.bytes_sampler = bytes;
   return 0;
+}
+
+// ------------------------------------------------------------------------------ pipelined host-pointer path
+// Host inputs of a large batch go up in chunks on their own stream, double-buffered: the upload of chunk c+1 runs
+// under the set-up / projection / sampler kernels of chunk c, and the results of chunk c come down on a third stream
+// under chunk c+1.  Chunks are multiples of the SM count, so the dense branch keeps full waves.  Every chain is keyed
+// on its global baseline id, so the results are those of the single-shot call, bit for bit.
+static void add_timing(dgibbs_timing& a, const dgibbs_timing& b) {
+  a.ms_setup += b.ms_setup; a.ms_sampler += b.ms_sampler; a.ms_finish += b.ms_finish;
+  a.launches += b.launches; a.sampler_launches += b.sampler_launches;
+  a.flop_sampler += b.flop_sampler; a.bytes_sampler += b.bytes_sampler;
+  a.ms_diag_project += b.ms_diag_project; a.ms_sampler_diag += b.ms_sampler_diag;
+  a.n_dense += b.n_dense; a.n_diag += b.n_diag;
+}
+
+static int pipeline_chunk(dgibbs_handle h, const dgibbs_problem* p) {
+  // baselines per chunk: 0 = never split.  Default 8 waves of the dense kernel (1184 on a B200).
+  const char* e = getenv("DGIBBS_PIPELINE_CHUNK");
+  int c = e ? atoi(e) : 8 * h->sm_count;
+  if (c > 0) c = (c + h->sm_count - 1) / h->sm_count * h->sm_count;
+  return c;
+}
+
+static int run_pipelined(dgibbs_handle h, const dgibbs_problem* p, dgibbs_result* r, int chunk) {
+  const int B = p->B, N = p->N, niter = p->niter;
+  const size_t esz = p->data_c64 ? 8 : 16;
+  CU(cudaSetDevice(h->device));
+  const int nchunks = (B + chunk - 1) / chunk;
+  const long long* doff = (const long long*)p->data_off;
+  const long long* coff = (const long long*)p->chan_off;
+  // capacity of one buffer set
+  size_t max_data = 0, max_chan = 0;
+  for (int c = 0; c < nchunks; c++) {
+    const int lo = c * chunk, hi = lo + chunk < B ? lo + chunk : B;
+    if (doff[hi] < doff[lo] || coff[hi] < coff[lo]) return bad_arg(h, 2, "data_off / chan_off must be non-decreasing");
+    max_data = std::max(max_data, (size_t)(doff[hi] - doff[lo]));
+    max_chan = std::max(max_chan, (size_t)(coff[hi] - coff[lo]));
+  }
+  const size_t cb = (size_t)chunk;
+  struct Set {
+    int *T, *M; long long *doff, *coff, *fsel, *gid; char* data; double *Ni, *S0;
+    double *spec, *samples, *finalS; int* ndone; unsigned char *succ, *branch;
+  } set[2];
+  for (int k = 0; k < 2; k++) {
+    char nm[32];
+    void* q;
+#define PGET(field, type, count)                                       \
+    snprintf(nm, sizeof nm, "pl%d_" #field, k);                         \
+    CU(pool_get(h, nm, sizeof(type) * (size_t)(count), &q));            \
+    set[k].field = (type*)q;
+    PGET(T, int, cb) PGET(M, int, cb) PGET(doff, long long, cb + 1) PGET(coff, long long, cb + 1)
+    PGET(fsel, long long, max_chan) PGET(gid, long long, cb) PGET(data, char, max_data * esz) PGET(Ni, double, max_chan)
+    PGET(S0, double, cb * N) PGET(spec, double, cb * N) PGET(ndone, int, cb) PGET(succ, unsigned char, cb)
+    PGET(branch, unsigned char, cb)
+    set[k].samples = nullptr;
+    set[k].finalS = nullptr;
+    if (r->samples) { PGET(samples, double, (size_t)(niter > 0 ? niter : 1) * cb * N) }
+    if (r->final_S) { PGET(finalS, double, cb * N) }
+#undef PGET
+  }
+  std::vector<HostSmall> hs(2);
+  std::vector<long long> gid_host[2];
+
+  auto upload = [&](int c) -> int {
+    const int k = c & 1, lo = c * chunk, hi = lo + chunk < B ? lo + chunk : B, nb = hi - lo;
+    HostSmall& s = hs[k];
+    s.T.assign(p->T + lo, p->T + hi);
+    s.M.assign(p->M + lo, p->M + hi);
+    s.data_off.resize(nb + 1);
+    s.chan_off.resize(nb + 1);
+    for (int i = 0; i <= nb; i++) {
+      s.data_off[i] = doff[lo + i] - doff[lo];
+      s.chan_off[i] = coff[lo + i] - coff[lo];
+    }
+    gid_host[k].resize(nb);
+    for (int i = 0; i < nb; i++) gid_host[k][i] = p->global_id ? p->global_id[lo + i] : (long long)(lo + i);
+    cudaStream_t us = h->up_stream;
+    CU(cudaMemcpyAsync(set[k].T, s.T.data(), sizeof(int) * nb, cudaMemcpyHostToDevice, us));
+    CU(cudaMemcpyAsync(set[k].M, s.M.data(), sizeof(int) * nb, cudaMemcpyHostToDevice, us));
+    CU(cudaMemcpyAsync(set[k].doff, s.data_off.data(), sizeof(long long) * (nb + 1), cudaMemcpyHostToDevice, us));
+    CU(cudaMemcpyAsync(set[k].coff, s.chan_off.data(), sizeof(long long) * (nb + 1), cudaMemcpyHostToDevice, us));
+    CU(cudaMemcpyAsync(set[k].gid, gid_host[k].data(), sizeof(long long) * nb, cudaMemcpyHostToDevice, us));
+    CU(cudaMemcpyAsync(set[k].data, (const char*)p->data + (size_t)doff[lo] * esz, (size_t)(doff[hi] - doff[lo]) * esz,
+                       cudaMemcpyHostToDevice, us));
+    CU(cudaMemcpyAsync(set[k].Ni, p->Ni + coff[lo], sizeof(double) * (size_t)(coff[hi] - coff[lo]), cudaMemcpyHostToDevice, us));
+    CU(cudaMemcpyAsync(set[k].fsel, p->fsel + coff[lo], sizeof(long long) * (size_t)(coff[hi] - coff[lo]), cudaMemcpyHostToDevice, us));
+    CU(cudaMemcpyAsync(set[k].S0, p->S0 + (size_t)lo * N, sizeof(double) * (size_t)nb * N, cudaMemcpyHostToDevice, us));
+    CU(cudaEventRecord(h->up_done[k], us));
+    return 0;
+  };
+
+  dgibbs_timing total{};
+  CU(cudaEventRecord(h->up_t0, h->up_stream));
+  int rc = upload(0);
+  if (rc) return rc;
+  for (int c = 0; c < nchunks; c++) {
+    const int k = c & 1, lo = c * chunk, hi = lo + chunk < B ? lo + chunk : B, nb = hi - lo;
+    // the other input set was last read by chunk c-1, whose run_core has returned (stream synchronised)
+    if (c + 1 < nchunks && (rc = upload(c + 1))) return rc;
+    if (c + 1 == nchunks) CU(cudaEventRecord(h->up_t1, h->up_stream));
+    CU(cudaStreamWaitEvent(h->stream, h->up_done[k], 0));
+    if (c >= 2) CU(cudaStreamWaitEvent(h->stream, h->down_done[k], 0));  // result set k drained
+    dgibbs_problem pc = *p;
+    pc.on_device = 1;
+    pc.B = nb;
+    pc.T = set[k].T; pc.M = set[k].M;
+    pc.data_off = (const int64_t*)set[k].doff; pc.chan_off = (const int64_t*)set[k].coff;
+    pc.data = set[k].data; pc.Ni = set[k].Ni; pc.fsel = (const int64_t*)set[k].fsel; pc.S0 = set[k].S0;
+    pc.global_id = (const int64_t*)set[k].gid;
+    dgibbs_result rcn{};
+    rcn.struct_size = (int32_t)sizeof(dgibbs_result);
+    rcn.on_device = 1;
+    rcn.spectrum = set[k].spec; rcn.samples = set[k].samples; rcn.n_done = set[k].ndone;
+    rcn.success = set[k].succ; rcn.branch = r->branch ? set[k].branch : nullptr; rcn.final_S = set[k].finalS;
+    rc = run_core(h, &pc, &rcn, &hs[k]);
+    if (rc) return rc;
+    add_timing(total, h->timing);
+    cudaStream_t ds = h->down_stream;  // run_core has synchronised the compute stream: the results are complete
+    CU(cudaMemcpyAsync(r->spectrum + (size_t)lo * N, set[k].spec, sizeof(double) * (size_t)nb * N, cudaMemcpyDeviceToHost, ds));
+    CU(cudaMemcpyAsync(r->n_done + lo, set[k].ndone, sizeof(int) * nb, cudaMemcpyDeviceToHost, ds));
+    CU(cudaMemcpyAsync(r->success + lo, set[k].succ, nb, cudaMemcpyDeviceToHost, ds));
+    if (r->branch) CU(cudaMemcpyAsync(r->branch + lo, set[k].branch, nb, cudaMemcpyDeviceToHost, ds));
+    if (r->final_S)
+      CU(cudaMemcpyAsync(r->final_S + (size_t)lo * N, set[k].finalS, sizeof(double) * (size_t)nb * N, cudaMemcpyDeviceToHost, ds));
+    if (r->samples && niter > 0)  // [niter][B][N] on the host, [niter][nb][N] on the device
+      CU(cudaMemcpy2DAsync(r->samples + (size_t)lo * N, sizeof(double) * (size_t)B * N, set[k].samples,
+                           sizeof(double) * (size_t)nb * N, sizeof(double) * (size_t)nb * N, niter, cudaMemcpyDeviceToHost, ds));
+    CU(cudaEventRecord(h->down_done[k], ds));
+  }
+  CU(cudaStreamSynchronize(h->down_stream));
+  CU(cudaStreamSynchronize(h->up_stream));
+  float ms = 0.f;
+  cudaEventElapsedTime(&ms, h->up_t0, h->up_t1);
+  total.ms_h2d = ms;  // span of the uploads (they overlap the kernels of the previous chunk)
+  h->timing = total;
+  return 0;
+}
+
+extern "C" int dgibbs_run(dgibbs_handle h, const dgibbs_problem* p, dgibbs_result* r) {
+  int rc = check_problem(h, p);
+  if (rc) return rc;
+  if (!r || r->struct_size != (int32_t)sizeof(dgibbs_result)) return bad_arg(h, 3, "result struct");
+  if (!r->spectrum || !r->n_done || !r->success) return bad_arg(h, 3, "result.spectrum/n_done/success required");
+  if ((r->on_device != 0) != (p->on_device != 0)) return bad_arg(h, 3, "problem and result must live on the same side");
+  if (!p->on_device && p->rng_mode != DGIBBS_RNG_INJECTED) {
+    const int chunk = pipeline_chunk(h, p);
+    if (chunk > 0 && p->B >= 2 * chunk) return run_pipelined(h, p, r, chunk);
+  }
+  return run_core(h, p, r, nullptr);
 }
 
 extern "C" int dgibbs_setup_inputs(dgibbs_handle h, const dgibbs_problem* p, int32_t b, double* data_w,

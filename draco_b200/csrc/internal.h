@@ -34,7 +34,8 @@ struct DevBatch {
   const int* M;
   const long long* data_off;
   const long long* chan_off;
-  const double2* data;
+  const double2* data;   // visibilities: complex128, or complex64 (float2) when data_c64 (read through ld_vis)
+  int data_c64;
   const double* Ni;
   const long long* fsel;
   const long long* gid;  // may be null

@@ -34,8 +34,8 @@ __global__ void __launch_bounds__(PTHREADS) diag_project_fft_kernel(DevBatch d, 
     const int* cidx = d.cidx + (size_t)b * d.nch;
     const int Mb = d.M[b];
     const bool ident = d.cident[b] != 0;  // kept channels are 0 .. Mb-1: no dependent index load (masked ones have h = 0)
-    const double2* da = d.data + d.data_off[b] + (size_t)t0 * Mb;
-    const double2* db = da + Mb;
+    const long long da = d.data_off[b] + (long long)t0 * Mb, db = da + Mb;  // element offsets of the two samples
+    const int c64 = d.data_c64;
     double* yo = d.yhat + ((size_t)d.ycompact[b] * d.Tmax + t0) * ypitch;
     const bool two = !d.cplx && t0 + 1 < Tb;
     __syncthreads();  // the previous transform's last stage is done with the buffers
@@ -53,10 +53,10 @@ __global__ void __launch_bounds__(PTHREADS) diag_project_fft_kernel(DevBatch d, 
           int ci = -1;
           if (i <= half) ci = ident ? (i < Mb ? i : Mb - 1) : cidx[i];
           if (ci >= 0) {
-            const double2 hh = h2[i], f = wf[i], va = da[ci];
+            const double2 hh = h2[i], f = wf[i], va = ld_vis(d.data, c64, da + ci);
             const double fim = (i == 0 || i == half) ? 0.0 : f.y;  // delay.py:1692: DC and Nyquist are real
             double2 vb = make_double2(0.0, 0.0);
-            if (two) vb = db[ci];
+            if (two) vb = ld_vis(d.data, c64, db + ci);
             U0[j] = make_double2(hh.x * ((va.x * f.x) * f.y), hh.y * ((va.y * f.x) * fim));
             U1[j] = make_double2(hh.x * ((vb.x * f.x) * f.y), hh.y * ((vb.y * f.x) * fim));
           }
@@ -90,7 +90,7 @@ __global__ void __launch_bounds__(PTHREADS) diag_project_fft_kernel(DevBatch d, 
           [&](int p) {
             const int ci = ident ? (p < Mb ? p : Mb - 1) : cidx[p];
             if (ci < 0) return make_double2(0.0, 0.0);
-            const double2 hh = h2[p], f = wf[p], va = da[ci];
+            const double2 hh = h2[p], f = wf[p], va = ld_vis(d.data, c64, da + ci);
             return make_double2(hh.x * ((va.x * f.x) * f.y), hh.y * ((va.y * f.x) * f.y));
           },
           []() {}, [&](int k, double2 v) { *reinterpret_cast<double2*>(yo + 2 * k) = v; });

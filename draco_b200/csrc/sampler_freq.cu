@@ -118,7 +118,7 @@ __global__ void __launch_bounds__(THREADS, 1) freq_sampler_kernel(DevBatch d, in
           }
         } else if (d.rng_mode == 1) {
           const unsigned long long blk = (unsigned long long)(s0 >> 1) * (N >> 1) + p;
-          normal_pair_fast(ph((unsigned)blk, (unsigned)(blk >> 32), (unsigned)it, STREAM_W1), a0, a1, b0, b1);
+          normal_quad(ph, (unsigned)blk, (unsigned)(blk >> 32), (unsigned)it, STREAM_W1, STREAM_W1_ODD, true, two, a0, a1, b0, b1);
         }
       };
       __syncthreads();
@@ -163,7 +163,8 @@ __global__ void __launch_bounds__(THREADS, 1) freq_sampler_kernel(DevBatch d, in
           double e[4] = {0.0, 0.0, 0.0, 0.0};  // w2 of (s0: re, im), (s0+1: re, im)
           if (d.rng_mode == 1) {
             const unsigned long long blk = (unsigned long long)(s0 >> 1) * (Kpad >> 1) + f;
-            normal_pair_fast(ph((unsigned)blk, (unsigned)(blk >> 32), (unsigned)it, STREAM_W2), e[0], e[1], e[2], e[3]);
+            normal_quad(ph, (unsigned)blk, (unsigned)(blk >> 32), (unsigned)it, STREAM_W2, STREAM_W2_ODD, true, s0 + 1 < Tb, e[0], e[1],
+                        e[2], e[3]);
           }
 #pragma unroll
           for (int k = 0; k < 2; k++) {

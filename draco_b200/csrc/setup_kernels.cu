@@ -179,13 +179,13 @@ __global__ void __launch_bounds__(THREADS) setup_baseline_kernel(DevBatch d, con
     for (int i = threadIdx.x; i < halfK; i += blockDim.x) {
       const int ci = i < nch ? cidx[i] : -1;
       const double w = ci >= 0 ? s_w[i] : 0.0, fre = ci >= 0 ? s_re[i] : 0.0, fim = ci >= 0 ? s_im[i] : 0.0;
-      const double2* src = d.data + doff + (ci >= 0 ? ci : 0);
+      const long long src = doff + (ci >= 0 ? ci : 0);
       double* dst = zT + 2 * i;
   #pragma unroll 4
       for (int t = 0; t < d.Tmax; t++) {
         double2 z = make_double2(0.0, 0.0);
         if (t < Tb && ci >= 0) {
-          const double2 v = src[(long long)t * Mb];
+          const double2 v = ld_vis(d.data, d.data_c64, src + (long long)t * Mb);
           z = make_double2((v.x * w) * fre, (v.y * w) * fim);
         }
         *reinterpret_cast<double2*>(dst + (size_t)t * d.Kpad) = z;

@@ -67,6 +67,13 @@ def flatten_axes(dset, axes_to_keep, match_dset=None):
         if ax not in data_axes:
             raise ValueError(f"Specified axis={ax!r} not present in dataset.")
     arr = dset[:]
+    comm = getattr(arr, "comm", None)
+    if getattr(comm, "size", 1) > 1:
+        # a real caput MPIArray distributed over several MPI ranks: its local block is NOT the global array this
+        # stand-in splits.  The reference's own flatten_axes (delay.py:2278-2298) does the all-to-all; keep it.
+        raise RuntimeError("draco_b200.delay.flatten_axes got an MPIArray distributed over several MPI ranks.  Under "
+                           "caput + MPI run the reference's task classes with `draco_b200.install()` (only _evaluate / "
+                           "_estimator are rebound; the redistribution stays caput's), not the stand-alone classes.")
     arr = np.asarray(getattr(arr, "local_array", arr))
     if match_dset is not None and tuple(data_axes) != tuple(match_dset.attrs["axis"]):
         full = match_dset[:]
@@ -113,12 +120,20 @@ class DelayTransformBase(_ContainerTask):
         return self._evaluate(data_view, weight_view, out_cont, delays, channel_ind)
 
     def _device(self):
+        """CUDA device of this rank: the ``device`` parameter, else local rank modulo the visible GPUs (the MPI
+        communicator of a caput task when there is one, else torch.distributed / the launcher's environment)."""
         if self.device is not None:
             return int(self.device)
+        import os
+
         import torch
 
-        rank, _ = comm_rank_size()
         n = torch.cuda.device_count()
+        for var in ("LOCAL_RANK", "OMPI_COMM_WORLD_LOCAL_RANK", "MV2_COMM_WORLD_LOCAL_RANK", "SLURM_LOCALID"):
+            if os.environ.get(var, "").isdigit():
+                return int(os.environ[var]) % n if n else 0
+        comm = getattr(self, "comm", None)
+        rank = comm.rank if hasattr(comm, "rank") else comm_rank_size()[0]
         return rank % n if n else 0
 
     def _calculate_delays(self, ss):
@@ -344,8 +359,15 @@ class DelayPowerSpectrumGibbs(DelayPowerSpectrumBase, _RandomTask):
         """One 64-bit Philox seed shared by all ranks (results independent of the sharding)."""
         from . import dist as ddist
 
-        base = self.seed if getattr(self, "seed", None) is not None else ddist.broadcast_int(
-            int(np.random.SeedSequence().generate_state(1, dtype=np.uint64)[0] >> 1))
+        if getattr(self, "seed", None) is not None:
+            base = self.seed
+        else:
+            base = int(np.random.SeedSequence().generate_state(1, dtype=np.uint64)[0] >> 1)
+            comm = getattr(self, "comm", None)
+            if hasattr(comm, "bcast"):  # a caput task under MPI
+                base = comm.bcast(base, root=0)
+            else:
+                base = ddist.broadcast_int(base, device=self._device())
         self._ncalls += 1
         return int(np.random.SeedSequence([int(base), self._ncalls]).generate_state(1, dtype=np.uint64)[0])
 
@@ -388,7 +410,7 @@ class DelayPowerSpectrumGibbs(DelayPowerSpectrumBase, _RandomTask):
                     samp_out[:, lbi] = res.samples[:, n]  # already front-padded with zeros (delay.py:1177-1178)
             self.log.debug(f"device batch of {len(chunk)} baselines: {res.timing['ms_sampler']:.1f} ms in the sampler")
         if self.save_spectrum_mask:
-            n_conv = nbase - ddist.allreduce_count(int(mask_out.sum()))  # delay.py:1182
+            n_conv = nbase - ddist.allreduce_count(int(mask_out.sum()), device=self._device())  # delay.py:1182
             self.log.debug(f"{n_conv}/{nbase} unflagged baselines.")
         return out_cont
 
@@ -399,8 +421,9 @@ class DelayPowerSpectrumGibbs(DelayPowerSpectrumBase, _RandomTask):
         compacted batch stays in HBM and feeds the sampler in place."""
         from . import dist as ddist
 
-        vis = np.ascontiguousarray(_local_array(data_view))
-        wgt = np.ascontiguousarray(_local_array(weight_view))
+        # no host-side ascontiguousarray: cut_batch ships the slab as it lies in memory and permutes on the device
+        vis = np.asarray(_local_array(data_view))
+        wgt = np.asarray(_local_array(weight_view))
         spec_out = _local(out_cont.spectrum)
         mask_out = _local(out_cont.datasets["spectrum_mask"]) if self.save_spectrum_mask else None
         samp_out = _local(out_cont.datasets["spectrum_samples"]) if self.save_samples else None
@@ -428,7 +451,7 @@ class DelayPowerSpectrumGibbs(DelayPowerSpectrumBase, _RandomTask):
             self.log.debug(f"device batch of {len(lbis)} baselines: {res.timing['ms_sampler']:.1f} ms in the sampler")
         if self.save_spectrum_mask:
             nbase = out_cont.spectrum.global_shape[0]
-            n_conv = nbase - ddist.allreduce_count(int(mask_out.sum()))  # delay.py:1182
+            n_conv = nbase - ddist.allreduce_count(int(mask_out.sum()), device=self._device())  # delay.py:1182
             self.log.debug(f"{n_conv}/{nbase} unflagged baselines.")
         return out_cont
 
@@ -473,7 +496,7 @@ class DelayPowerSpectrumNRML(DelayPowerSpectrumBase):
                 samp_out[:, lbi] = 0.0
                 samp_out[-len(arr):, lbi] = arr
         if self.save_spectrum_mask:
-            n_conv = nbase - ddist.allreduce_count(int(mask_out.sum()))  # delay.py:1182
+            n_conv = nbase - ddist.allreduce_count(int(mask_out.sum()), device=self._device())  # delay.py:1182
             self.log.debug(f"{n_conv}/{nbase} unflagged baselines.")
         return out_cont
 
@@ -622,8 +645,8 @@ class DelaySpectrumWienerFilter(DelaySpectrumBase):
 
         if self.device_cut and self.use_average_weights and self._device_cut_serves(data_view):
             # _cut_data on the device for the whole local slab (dgibbs_cut_data); the batch stays in HBM
-            vis = np.ascontiguousarray(_local_array(data_view))
-            wgt = np.ascontiguousarray(_local_array(weight_view))
+            vis = np.asarray(_local_array(data_view))
+            wgt = np.asarray(_local_array(weight_view))
             gids = np.array([bi for _, bi in out_cont.spectrum[:].enumerate(axis=0)], dtype=np.int64)
             nloc = vis.shape[0]
             step = self.batch_baselines if self.batch_baselines and self.batch_baselines > 0 else max(1, nloc)
@@ -683,8 +706,8 @@ class DelaySpectrumFFT(DelaySpectrumBase):
         handle = gibbs.get_handle(self._device())
         window = self.window if self.apply_window else None
         if self.device_cut and self._device_cut_serves(data_view):
-            vis = np.ascontiguousarray(_local_array(data_view))
-            wgt = np.ascontiguousarray(_local_array(weight_view))
+            vis = np.asarray(_local_array(data_view))
+            wgt = np.asarray(_local_array(weight_view))
             nloc, T, F = vis.shape
             step = self.batch_baselines if self.batch_baselines and self.batch_baselines > 0 else max(1, nloc)
             for s0 in range(0, nloc, step):

@@ -66,24 +66,38 @@ def group_average(local, global_ids, ngroup, group_size, weights=None):
     return torch.where(cnt > 0, acc[:, :-1] / cnt.clamp(min=1e-300), torch.zeros_like(acc[:, :-1])), cnt[:, 0]
 
 
-def allreduce_count(n):
+def _collective_device(device=None):
+    """Where a small collective's tensor lives: the CPU under gloo; under NCCL the task's own GPU (``device``), never
+    the process-wide current device -- several ranks of one node would otherwise all land on cuda:0."""
+    import torch
+
+    dist = _dist()
+    if dist is None or dist.get_backend() != "nccl":
+        return torch.device("cpu")
+    if device is None:
+        device = torch.cuda.current_device()
+    return torch.device("cuda", int(device))
+
+
+def allreduce_count(n, device=None):
     """Scalar all-reduce used for the converged-baseline debug count (delay.py:1182)."""
     import torch
 
     dist = _dist()
     if dist is None or dist.get_world_size() == 1:
         return int(n)
-    dev = "cuda" if dist.get_backend() == "nccl" else "cpu"
-    t = torch.tensor([int(n)], dtype=torch.int64, device=dev)
+    t = torch.tensor([int(n)], dtype=torch.int64, device=_collective_device(device))
     dist.all_reduce(t)
     return int(t.item())
 
 
-def broadcast_int(value, src=0):
-    """Make one Python int identical on every rank (rank ``src`` wins)."""
+def broadcast_int(value, src=0, device=None):
+    """Make one Python int (< 2**63) identical on every rank (rank ``src`` wins)."""
+    import torch
+
     dist = _dist()
     if dist is None or dist.get_world_size() == 1:
         return int(value)
-    box = [int(value)]
-    dist.broadcast_object_list(box, src=src)
-    return int(box[0])
+    t = torch.tensor([int(value)], dtype=torch.int64, device=_collective_device(device))
+    dist.broadcast(t, src=src)
+    return int(t.item())

@@ -25,12 +25,24 @@ def get_handle(device=0) -> Handle:
     return h
 
 
+def rng_description() -> str:
+    """Which generator ``rng_mode = RNG_PHILOX`` uses in the loaded build (``dgibbs_rng_info``)."""
+    return _lib.load().dgibbs_rng_info().decode()
+
+
 def _ptr(a):
     if a is None:
         return None
     if isinstance(a, np.ndarray):
         return a.ctypes.data
     return a.data_ptr()  # torch tensor
+
+
+def _is_c64(a):
+    """complex64 visibilities (numpy complex64, or a CUDA float32 tensor of interleaved re / im)."""
+    if isinstance(a, np.ndarray):
+        return a.dtype == np.complex64
+    return str(a.dtype) == "torch.float32"
 
 
 def _is_device(a):
@@ -73,6 +85,8 @@ class PackedBatch:
             if isinstance(v, np.ndarray):
                 if v.dtype == np.complex128:
                     v = torch.from_numpy(v.view(np.float64)).to(dev)
+                elif v.dtype == np.complex64:
+                    v = torch.from_numpy(v.view(np.float32)).to(dev)
                 else:
                     v = torch.from_numpy(np.ascontiguousarray(v).copy() if not v.flags.writeable else v).to(dev)
             kw[f.name] = v
@@ -106,7 +120,7 @@ def pack_batch(datas, Nis, fsels, N, S0, window="nuttall", complex_timedomain=Fa
 
 def pack_uniform(vis, weight, fsel, N, S0, window="nuttall", complex_timedomain=False, global_id=None) -> PackedBatch:
     """Fast path of :func:`pack_batch` when every baseline has the same (T, M):
-    ``vis[B,T,M]`` c128, ``weight[B,M]``, common ``fsel[M]``."""
+    ``vis[B,T,M]`` c128 (complex64 is kept as it is: ``data_c64`` of the C ABI), ``weight[B,M]``, common ``fsel[M]``."""
     B, T, M = vis.shape
     data_off = np.arange(B + 1, dtype=np.int64) * (T * M)
     chan_off = np.arange(B + 1, dtype=np.int64) * M
@@ -118,7 +132,7 @@ def pack_uniform(vis, weight, fsel, N, S0, window="nuttall", complex_timedomain=
         np.full(B, M, dtype=np.int32),
         data_off,
         chan_off,
-        np.ascontiguousarray(vis, dtype=np.complex128).reshape(-1),
+        np.ascontiguousarray(vis, dtype=np.complex64 if vis.dtype == np.complex64 else np.complex128).reshape(-1),
         np.ascontiguousarray(weight, dtype=np.float64).reshape(-1),
         np.ascontiguousarray(np.broadcast_to(np.asarray(fsel, dtype=np.int64), (B, M))).reshape(-1),
         S0,
@@ -126,6 +140,21 @@ def pack_uniform(vis, weight, fsel, N, S0, window="nuttall", complex_timedomain=
         bool(complex_timedomain),
         window,
     )
+
+
+def _upload_as_it_lies(a, dev):
+    """``a`` (numpy) as a contiguous CUDA tensor.  A transposed view of a C-contiguous block -- what ``flatten_axes``
+    (delay.py:2238-2302) hands over for a container stored [freq, stack, ra] -- is shipped in its memory order and
+    permuted on the device (a strided host copy of 1 GB costs seconds; the device permutation well under a millisecond)."""
+    import torch
+
+    if a.flags.c_contiguous or a.ndim < 2 or 0 in a.strides:
+        return torch.from_numpy(np.ascontiguousarray(a)).to(dev, non_blocking=True)
+    order = np.argsort([-st for st in a.strides], kind="stable")
+    block = a.transpose(order)
+    if not block.flags.c_contiguous:
+        return torch.from_numpy(np.ascontiguousarray(a)).to(dev, non_blocking=True)
+    return torch.from_numpy(block).to(dev, non_blocking=True).permute(*np.argsort(order).tolist()).contiguous()
 
 
 @dataclasses.dataclass
@@ -158,19 +187,14 @@ def cut_batch(vis, weight, channel_ind, N, S0, *, time_frac=-1.0, freq_frac=-1.0
 
     def to_dev(a, dtype=None):
         if isinstance(a, np.ndarray):
-            if a.dtype == np.complex128:
-                a = np.ascontiguousarray(a).view(np.float64)
-            elif a.dtype == np.complex64:
-                a = np.ascontiguousarray(a).view(np.float32)
-            elif dtype is not None:
+            if dtype is not None and a.dtype != dtype:
                 a = np.ascontiguousarray(a, dtype=dtype)
-            else:
-                a = np.ascontiguousarray(a)
-            return torch.from_numpy(a).to(dev, non_blocking=True)
+            t = _upload_as_it_lies(a, dev)
+            return torch.view_as_real(t) if t.is_complex() else t
         return a.contiguous()
 
     if isinstance(vis, np.ndarray):
-        if vis.dtype != np.complex64:
+        if vis.dtype not in (np.complex64, np.complex128):
             vis = np.asarray(vis, dtype=np.complex128)
         B, T, F = vis.shape
         c64 = vis.dtype == np.complex64
@@ -247,6 +271,7 @@ def _problem(pb: PackedBatch, niter, rng_mode, seed, median_frac, draws=None, fo
     p.cluster_size = int(cluster_size)
     for name in ("T", "M", "data_off", "chan_off", "data", "Ni", "fsel", "S0", "global_id"):
         setattr(p, name, _ptr(getattr(pb, name)))
+    p.data_c64 = 1 if _is_c64(pb.data) else 0
     keep = []
     if draws is not None:
         w1, w1_off, w2, w2_off, chi2 = draws

@@ -69,7 +69,7 @@ typedef struct dgibbs_handle_s* dgibbs_handle;
  * One batch of baselines sharing N (number of delays), window and mode.
  * Ragged per-baseline shapes are described by offset arrays, i.e. each baseline is stored
  * exactly as DelayTransformBase._cut_data (delay.py:516-597) returns it:
- *   data  : complex128, baseline b occupies data[data_off[b] .. data_off[b+1]) (complex
+ *   data  : complex128 (complex64 with data_c64), baseline b occupies data[data_off[b] .. data_off[b+1]) (complex
  *           elements), row-major (T[b], M[b])
  *   Ni    : float64 inverse noise variance, baseline b at Ni[chan_off[b] .. chan_off[b+1])
  *   fsel  : int64 channel indices (values in [0, N/2] real mode, [0, N) complex mode),
@@ -112,6 +112,9 @@ typedef struct {
                             launch (full waves one CTA per chain, the remainder on clusters so that the last wave
                             fills the GPU); 1, 2, 4 = every chain on clusters of that size.  The samples do not
                             depend on it (bit-identical). */
+  int32_t data_c64;      /* element type of `data`: 0 = complex128, 1 = complex64 (what draco's containers store,
+                            core/containers.py:503): widened exactly on the device, half the host->device bytes */
+  int32_t reserved;      /* keep 0 */
 } dgibbs_problem;
 
 typedef struct {
@@ -143,6 +146,8 @@ typedef struct {
 } dgibbs_timing;
 
 int dgibbs_version(void);
+/* Which generator DGIBBS_RNG_PHILOX uses for the N(0,1) / chi^2 variates in this build (static string). */
+const char* dgibbs_rng_info(void);
 /* sizeof of the ABI structs as compiled (0: dgibbs_problem, 1: dgibbs_result, 2: dgibbs_timing, 3: dgibbs_cross_problem);
  * lets a binding verify its struct layout without a GPU. */
 int dgibbs_sizeof(int which);
@@ -156,7 +161,11 @@ const char* dgibbs_last_error(dgibbs_handle h);
 /* Upper bound of device workspace (bytes) dgibbs_run would allocate for this problem. */
 int dgibbs_workspace_bytes(dgibbs_handle h, const dgibbs_problem* p, int64_t* bytes);
 
-/* Run every chain of the batch on the device (replaces delay.py:1146-1178). */
+/* Run every chain of the batch on the device (replaces delay.py:1146-1178).
+ * Host-pointer problems of at least 16 waves of baselines (2 x 8 x SM count; DGIBBS_PIPELINE_CHUNK overrides the chunk,
+ * 0 = never) are processed in chunks: the upload of a chunk overlaps the kernels of the previous one and the
+ * download of its results the next one (pinned host buffers make the copies asynchronous).  Results do not depend
+ * on the chunking. */
 int dgibbs_run(dgibbs_handle h, const dgibbs_problem* p, dgibbs_result* r);
 int dgibbs_get_timing(dgibbs_handle h, dgibbs_timing* t);
 
