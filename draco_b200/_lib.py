@@ -10,7 +10,8 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libdgibbs.so")
+# DGIBBS_LIB_PATH: load another build of the library (A/B timing of kernel variants, scratch/build_variant.sh)
+LIB_PATH = os.environ.get("DGIBBS_LIB_PATH") or os.path.join(HERE, "libdgibbs.so")
 
 WINDOW_IDS = {
     None: -1,

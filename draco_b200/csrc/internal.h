@@ -71,6 +71,7 @@ struct DevBatch {
   const double2* twtab;  // [N/2] exact twiddles e^{2 pi i m / N} (N a power of two), else null
   const double2* stwtab; // per-stage twiddle tables of fft_inverse_fused (fft_fused.cuh), else null
   int use_fft;           // 1: masked inverse DFT of phase 0 runs as an in-smem FFT (N = 2^m <= 4096)
+  int use_tma;           // dense kernel: NT updates fed by the TMA ring (tma_pipe.cuh); set per launch
 
   // per-slot workspace
   size_t work_stride;  // doubles per slot of `work`: (npad + RT*TILE) * npad for L + RHS, then N * Tmax (Sh w1, _t branch)

@@ -28,8 +28,10 @@
 // touches all 64 accumulators is kept to loads/stores only.
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
 
 #include "dense_core.cuh"
+#include "tma_pipe.cuh"
 
 #ifndef DGIBBS_COST_C2
 #define DGIBBS_COST_C2 0.59
@@ -43,8 +45,9 @@ namespace dg {
 // ----------------------------------------------------------------------------- the sampler
 // Shared memory:  [ctab: nsys (optional)] [sWp: WP_DOUBLES] [pipe/tile: PIPE_DOUBLES] [misc]
 template <int C>
-__global__ void __launch_bounds__(THREADS, 1) dense_sampler_kernel(DevBatch d, int it_begin, int it_end) {
-  extern __shared__ __align__(16) double smem[];
+__global__ void __launch_bounds__(THREADS, 1) dense_sampler_kernel(DevBatch d, int it_begin, int it_end,
+                                                                   const __grid_constant__ CUtensorMap tmap) {
+  extern __shared__ __align__(128) double smem[];
   const Lane ln;
   const int rank = C > 1 ? cluster_ctarank() : 0;              // rank of this CTA among the C that share a chain
   const int slot = C > 1 ? (int)blockIdx.x / C : (int)blockIdx.x;  // chain slot (workspace) of the cluster
@@ -55,6 +58,9 @@ __global__ void __launch_bounds__(THREADS, 1) dense_sampler_kernel(DevBatch d, i
   double* pipe = sWp + WP_DOUBLES;
   double* misc = pipe + PIPE_DOUBLES;
   double* cwin = misc + 16;  // circulant window of the current tile
+  TmaRing ring;
+  const bool use_tma = d.use_tma != 0;  // NT updates through the TMA ring (tma_pipe.cuh) instead of cp.async
+  if (use_tma) tma_ring_init(ring, reinterpret_cast<unsigned long long*>(misc + 16 + CWIN));
 
   const size_t wrows = (size_t)npad + (size_t)RT * TILE;
   double* Wk = d.work + (size_t)slot * d.work_stride;   // L rows then RHS rows, pitch npad
@@ -213,7 +219,8 @@ __global__ void __launch_bounds__(THREADS, 1) dense_sampler_kernel(DevBatch d, i
         const bool interior_j = !d.cplx && (j + 1) * TILE <= nsys;
         if (interior_j) load_circ_window(cwin, ctg, N, 0);
         acc_zero(acc);
-        gemm_nt(pipe, acc, ln, Bp, Bp, npad, j * (TILE / KC), ln.warp < 4 ? V_DIAG_LO : V_DIAG_HI);
+        if (use_tma) gemm_nt_tma(&tmap, ring, pipe, acc, ln, slot, j * TILE, j * TILE, j * (TILE / TKC), ln.warp < 4 ? V_DIAG_LO : V_DIAG_HI);
+        else gemm_nt(pipe, acc, ln, Bp, Bp, npad, j * (TILE / KC), ln.warp < 4 ? V_DIAG_LO : V_DIAG_HI);
         PROF(2);
         stage_acc(acc, pipe, ln, true, true);
         __syncthreads();
@@ -252,7 +259,8 @@ __global__ void __launch_bounds__(THREADS, 1) dense_sampler_kernel(DevBatch d, i
           const bool interior = i < nblk && !d.cplx && (i + 1) * TILE <= nsys;
           if (interior) load_circ_window(cwin, ctg, N, i - j);
           acc_zero(acc);
-          gemm_nt(pipe, acc, ln, Wk + (size_t)i * TILE * npad, Bp, npad, j * (TILE / KC), var);
+          if (use_tma) gemm_nt_tma(&tmap, ring, pipe, acc, ln, slot, i * TILE, j * TILE, j * (TILE / TKC), var);
+          else gemm_nt(pipe, acc, ln, Wk + (size_t)i * TILE * npad, Bp, npad, j * (TILE / KC), var);
           PROF(6);
           if (interior) {  // interior tile below the diagonal: generated in registers (gemm_nt ends with a barrier)
             stage_acc_circ(acc, pipe, ln, cwin);
@@ -379,7 +387,7 @@ __global__ void __launch_bounds__(THREADS, 1) dense_sampler_kernel(DevBatch d, i
 }
 
 size_t dense_smem_bytes(const DevBatch& d) {
-  return sizeof(double) * ((d.ctab_smem ? (size_t)d.nsys : 0) + WP_DOUBLES + PIPE_DOUBLES + MISC_DOUBLES);
+  return sizeof(double) * ((d.ctab_smem ? (size_t)d.nsys : 0) + WP_DOUBLES + PIPE_DOUBLES + MISC_DOUBLES + 2 * TNST);
 }
 size_t dense_wp_doubles_per_slot(const DevBatch& d) { return (size_t)d.nblk * WP_DOUBLES; }
 
@@ -392,10 +400,49 @@ cudaError_t dense_configure(const DevBatch& d) {
   return cudaFuncSetAttribute(dense_sampler_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
 }
 
+// ---- tensor map of the chain workspaces (tma_pipe.cuh): (k mod 4, row, k div 4, slot)
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = []() -> EncodeTiledFn {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qr;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qr) != cudaSuccess ||
+        qr != cudaDriverEntryPointSuccess) {
+      cudaGetLastError();
+      return nullptr;
+    }
+    return (EncodeTiledFn)p;
+  }();
+  return fn;
+}
+
+// true: `tm` describes d.work for the TMA ring; false: this geometry keeps the cp.async loaders
+static bool make_work_tensor_map(const DevBatch& d, CUtensorMap* tm) {
+  memset(tm, 0, sizeof *tm);
+  static const bool off = getenv("DGIBBS_NO_TMA") != nullptr;
+  if (off || d.project_only) return false;
+  const size_t ring_off = sizeof(double) * ((d.ctab_smem ? (size_t)d.nsys : 0) + WP_DOUBLES);
+  if (ring_off % 128 != 0 || (d.work_stride * sizeof(double)) % 16 != 0 || ((uintptr_t)d.work) % 16 != 0) return false;
+  EncodeTiledFn enc = encode_fn();
+  if (!enc) return false;
+  const cuuint64_t wrows = (cuuint64_t)d.npad + (cuuint64_t)d.RT * TILE;
+  const cuuint64_t dims[4] = {4, wrows, (cuuint64_t)d.npad / 4, (cuuint64_t)d.nslots};
+  const cuuint64_t strides[3] = {(cuuint64_t)d.npad * sizeof(double), 4 * sizeof(double), (cuuint64_t)d.work_stride * sizeof(double)};
+  const cuuint32_t box[4] = {4, TILE, TKC / 4, 1};
+  const cuuint32_t estr[4] = {1, 1, 1, 1};
+  return enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 4, d.work, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+             CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 template <int C>
-static cudaError_t launch_one(const DevBatch& d, int it_begin, int it_end, int nclusters, cudaStream_t st) {
+static cudaError_t launch_one(const DevBatch& d0, int it_begin, int it_end, int nclusters, cudaStream_t st) {
+  DevBatch d = d0;
+  CUtensorMap tm;
+  d.use_tma = make_work_tensor_map(d, &tm) ? 1 : 0;
   if (C == 1) {
-    dense_sampler_kernel<1><<<nclusters, THREADS, dense_smem_bytes(d), st>>>(d, it_begin, it_end);
+    dense_sampler_kernel<1><<<nclusters, THREADS, dense_smem_bytes(d), st>>>(d, it_begin, it_end, tm);
     return cudaGetLastError();
   }
   cudaLaunchConfig_t cfg = {};
@@ -410,7 +457,7 @@ static cudaError_t launch_one(const DevBatch& d, int it_begin, int it_end, int n
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  return cudaLaunchKernelEx(&cfg, dense_sampler_kernel<C>, d, it_begin, it_end);
+  return cudaLaunchKernelEx(&cfg, dense_sampler_kernel<C>, d, it_begin, it_end, tm);
 }
 
 // clusters of C CTAs that the device keeps resident at once (C = 1: one CTA per SM)
