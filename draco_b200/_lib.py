@@ -43,6 +43,7 @@ EXPORTED = [
     "dgibbs_cross_run",
     "dgibbs_cut_data",
     "dgibbs_delay_fft",
+    "dgibbs_delay_fft_noalloc",
     "dgibbs_sample_variance",
 ]
 CROSS_MAX_DATASETS = 4
@@ -200,6 +201,7 @@ def load():
     lib.dgibbs_cut_data.argtypes = [_vp, C.POINTER(Cut)]
     lib.dgibbs_delay_fft.argtypes = [_vp, C.c_int32, C.c_int64, C.c_int32, C.c_int32, C.c_int32, _vp, _vp,
                                      C.POINTER(C.c_double)]
+    lib.dgibbs_delay_fft_noalloc.argtypes = [_vp, C.c_int64, C.c_int32, C.c_int32, C.c_int32, _vp, _vp, C.c_int32]
     lib.dgibbs_sample_variance.argtypes = [_vp, C.c_int32, C.c_int32, C.c_int32, C.c_int32, _vp, _vp, _vp, _vp,
                                            C.POINTER(C.c_double)]
     for name in EXPORTED:

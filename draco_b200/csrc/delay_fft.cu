@@ -8,6 +8,7 @@
 // tables; several CTAs per SM); any other N <= 6400 is a direct O(N^2) DFT against an exact twiddle table in shared
 // memory.
 #include <cstdio>
+#include <mutex>
 #include <string>
 
 #include "dense_core.cuh"
@@ -297,5 +298,94 @@ extern "C" int dgibbs_sample_variance(dgibbs_handle h, int32_t on_device, int32_
   cudaEventDestroy(e0);
   cudaEventDestroy(e1);
   if (ms_kernel) *ms_kernel = (double)ms;
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// dgibbs_delay_fft_noalloc: the same transform for callers that must not allocate (CUDA graph capture, tight serving
+// loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// The scratch of dgibbs_delay_fft -- the window table and the per-stage twiddle tables, which that entry
+// point takes from the handle's grow-only pool (cudaMalloc on first use) -- lives here in a file-scope __device__ array
+// of fixed size, so the transform is limited to N = 2^m, 8 <= N <= DGIBBS_NOALLOC_MAX_N, device-resident rows.
+//
+// The array is part of the library image: every GPU that loads libdgibbs.so holds its 160 KB until the process exits.
+// In HOST code `g_noalloc_scratch` is only a stand-in for the symbol, not a device address; its device address is
+// looked up once per device with cudaGetSymbolAddress (with that device current) and handed to the kernels.
+// Every call on a device shares the one array and finds the previous call's tables in it: both tables are rebuilt in
+// full for (N, window_id) at the head of every call, on the handle's stream, so nothing has to start at zero and
+// nothing stale can be read -- but two calls that overlap on the GPU (different streams / handles on one device)
+// race on it.  Calls on one stream are ordered and safe.
+namespace dg {
+constexpr int NOALLOC_MAX_N = DGIBBS_NOALLOC_MAX_N;
+constexpr int NOALLOC_WINDOW_DOUBLES = NOALLOC_MAX_N;      // window table
+constexpr int NOALLOC_TW_DOUBLES = 4 * NOALLOC_MAX_N;      // 2 N double2 of stage twiddles (as dgibbs_delay_fft sizes them)
+static __device__ __align__(256) double g_noalloc_scratch[NOALLOC_WINDOW_DOUBLES + NOALLOC_TW_DOUBLES];
+static_assert(sizeof(double) * NOALLOC_WINDOW_DOUBLES % 256 == 0, "the twiddle tables start on a 256-byte boundary");
+
+constexpr int NOALLOC_MAX_DEVICES = 64;
+static std::mutex g_noalloc_mu;
+static double* g_noalloc_ptr[NOALLOC_MAX_DEVICES] = {};  // device address of g_noalloc_scratch, per device
+
+// Set-up, once per device, with that device current.
+static cudaError_t noalloc_scratch_address(int device, double** out) {
+  std::lock_guard<std::mutex> lock(g_noalloc_mu);
+  if (!g_noalloc_ptr[device]) {
+    double* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress((void**)&p, g_noalloc_scratch);
+    if (e != cudaSuccess) return e;
+    g_noalloc_ptr[device] = p;
+  }
+  *out = g_noalloc_ptr[device];
+  return cudaSuccess;
+}
+}  // namespace dg
+
+extern "C" int dgibbs_delay_fft_noalloc(dgibbs_handle h, int64_t nrows, int32_t N, int32_t window_id, int32_t shift,
+                                        const void* data, void* out, int32_t sync) {
+  if (!h) return -1;
+  auto bad = [&](const char* what) {
+    dg_set_error(h, (std::string("bad argument: ") + what).c_str());
+    return -2;
+  };
+  if (nrows < 0) return bad("nrows >= 0 is required");
+  if (window_id < -1 || window_id > 7) return bad("window_id");
+  if (N < 8 || (N & (N - 1)) != 0 || N > NOALLOC_MAX_N) {
+    char msg[160];
+    snprintf(msg, sizeof msg, "dgibbs_delay_fft_noalloc serves N = 2^m with 8 <= N <= %d (static scratch); got N = %d: "
+                              "use dgibbs_delay_fft", NOALLOC_MAX_N, (int)N);
+    return bad(msg);
+  }
+  const int dev = dg_device(h);
+  if (dev < 0 || dev >= NOALLOC_MAX_DEVICES) return bad("device index beyond the per-device table of the static scratch");
+  FCU(cudaSetDevice(dev));
+  double* scratch = nullptr;
+  FCU(noalloc_scratch_address(dev, &scratch));
+  if (nrows == 0) return 0;  // set-up only (e.g. before a graph capture)
+  if (!data || !out) return bad("data and out are required (device pointers)");
+  if (data == out) return bad("out may not alias data");
+  cudaStream_t st = dg_stream(h);
+  double* wtab = scratch;
+  double2* tw = reinterpret_cast<double2*>(scratch + NOALLOC_WINDOW_DOUBLES);
+  // both tables are rebuilt in full for this (N, window): the array keeps the last call's contents
+  delay_fft_window_kernel<<<(N + 255) / 256, 256, 0, st>>>(wtab, N, window_id);
+  FCU(build_stage_twiddles(tw, N, st));
+
+  const size_t smem = (size_t)N * 3 * sizeof(double2);
+  void (*kern)(const double2*, double2*, const double*, const double2*, long long, int, int);
+  int nthreads;
+  if (N >= 4096) { kern = delay_fft_pow2_kernel<512>; nthreads = 512; }
+  else if (N >= 2048) { kern = delay_fft_pow2_kernel<256>; nthreads = 256; }
+  else if (N == 1024) { kern = delay_fft_pow2_kernel<128>; nthreads = 128; }
+  else if (N == 512) { kern = delay_fft_pow2_kernel<64>; nthreads = 64; }
+  else { kern = delay_fft_pow2_kernel<32>; nthreads = 32; }
+  FCU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int occ = 0;
+  FCU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, nthreads, smem));
+  if (occ < 1) return bad("the transform does not fit in shared memory");
+  long long grid = (long long)occ * dg_sm_count(h);
+  if (grid > nrows) grid = nrows;
+  kern<<<(unsigned)grid, nthreads, smem, st>>>((const double2*)data, (double2*)out, wtab, tw, (long long)nrows, N, shift ? 1 : 0);
+  FCU(cudaGetLastError());
+  if (sync) FCU(cudaStreamSynchronize(st));
   return 0;
 }

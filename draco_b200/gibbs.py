@@ -501,6 +501,27 @@ def fft_rows(rows, window="nuttall", *, shift=False, handle: Handle | None = Non
     return out
 
 
+def fft_rows_noalloc(rows, out, window="nuttall", *, shift=False, handle: Handle | None = None, sync=True):
+    """:func:`fft_rows` through ``dgibbs_delay_fft_noalloc``: CUDA float64 tensors ``rows`` / ``out`` ``[..., N, 2]`` owned by
+    the caller, N = 2^m in [8, 4096]; the library allocates nothing (its tables live in a static device array).  No
+    counterpart in the reference.  ``sync=False`` only enqueues the
+    kernels on the handle's stream.  Calls that overlap on one GPU race on the shared tables."""
+    import torch
+
+    if window not in WINDOW_IDS:
+        raise ValueError(f"window {window!r} is not one of {sorted(k for k in WINDOW_IDS if k)}")
+    for t in (rows, out):
+        if not _is_device(t) or t.dtype != torch.float64 or t.shape[-1] != 2 or not t.is_contiguous():
+            raise ValueError("rows and out must be contiguous CUDA float64 tensors [..., N, 2]")
+    if rows.shape != out.shape:
+        raise ValueError("rows and out must have the same shape")
+    N = rows.shape[-2]
+    h = handle or get_handle(rows.device.index or 0)
+    h.check(h.lib.dgibbs_delay_fft_noalloc(h._h, rows.numel() // max(2 * N, 1), N, WINDOW_IDS[window], int(bool(shift)),
+                                           _ptr(rows), _ptr(out), int(bool(sync))), "dgibbs_delay_fft_noalloc")
+    return out
+
+
 def delay_spectrum_fft(data, N, window="nuttall", *, device=0):
     """Drop-in for ``delay_spectrum_fft`` (delay.py:2102-2130): ``data[nsample, N]`` -> ``[nsample, N]`` complex128,
     unshifted.  (The reference multiplies ``data`` by the window in place; the input is left untouched here.)"""

@@ -293,6 +293,21 @@ int dgibbs_cut_data(dgibbs_handle h, const dgibbs_cut* c);
 int dgibbs_delay_fft(dgibbs_handle h, int32_t on_device, int64_t nrows, int32_t N, int32_t window_id, int32_t shift,
                      const void* data, void* out, double* ms_kernel);
 
+/* dgibbs_delay_fft for callers that cannot allocate device memory (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  It has NO counterpart in the reference.
+ * Same transform and arguments as dgibbs_delay_fft with on_device = 1 (data / out are DEVICE pointers on the
+ * handle's device; out may not alias data), but the window and twiddle tables live in a static __device__ array of
+ * the library (160 KB held by every GPU that loads it) instead of the handle's pool: the call performs no cudaMalloc /
+ * cudaFree and calls no allocating routine.  Limit: N = 2^m with 8 <= N <= DGIBBS_NOALLOC_MAX_N; anything else is
+ * rejected with -2 and a message (use dgibbs_delay_fft).  nrows = 0 only performs the once-per-device set-up (the
+ * cudaGetSymbolAddress look-up), e.g. ahead of a capture.  sync = 1 synchronises the handle's stream before returning,
+ * sync = 0 only enqueues the kernels on it.  All calls on a device share the one scratch array (rebuilt at the head
+ * of every call): calls that may OVERLAP on the GPU (different streams or handles of one device) race; calls on one
+ * stream are ordered and safe. */
+#define DGIBBS_NOALLOC_MAX_N 4096
+int dgibbs_delay_fft_noalloc(dgibbs_handle h, int64_t nrows, int32_t N, int32_t window_id, int32_t shift,
+                             const void* data, void* out, int32_t sync);
+
 /* DelaySpectrumToPowerSpectrum.process, draco/analysis/delay.py:1061-1106: var[b, n] = variance over the unmasked
  * samples t of spec[b, t, n] (complex128, [B, T, N]); mask [B, T] with 1 = masked sample (the DelayTransform's
  * spectrum_mask) or NULL.  With a mask, NaN results (no unmasked sample) become 0 and bad[b] = 1 (delay.py:1099-1104);
