@@ -197,16 +197,29 @@ extern "C" int dgibbs_delay_fft(dgibbs_handle h, int32_t on_device, int64_t nrow
     FCU(dg_pool_get(h, "dfft_out", bytes, &q));
     y = (double2*)q;
   }
+  // window and twiddle tables: rebuilt only when (N, window) or the pooled buffer changed since the last call
   FCU(dg_pool_get(h, "dfft_window", sizeof(double) * (size_t)N, &q));
   double* wtab = (double*)q;
-  delay_fft_window_kernel<<<(N + 255) / 256, 256, 0, st>>>(wtab, N, window_id);
   FCU(dg_pool_get(h, "dfft_tw", sizeof(double2) * 2 * (size_t)N, &q));  // stage tables: <= 3 (8 + 64 + 512) + 3 N / 4 entries
   double2* tw = (double2*)q;
-  if (pow2)
-    FCU(build_stage_twiddles(tw, N, st));
-  else
-    delay_fft_fulltw_kernel<<<(N + 255) / 256, 256, 0, st>>>(tw, N);
-  FCU(cudaGetLastError());
+  long long *tag_w = dg_tag(h, "dfft_window"), *tag_wp = dg_tag(h, "dfft_window_ptr");
+  long long *tag_t = dg_tag(h, "dfft_tw"), *tag_tp = dg_tag(h, "dfft_tw_ptr");
+  const long long key_w = ((long long)N << 8) | (long long)(window_id + 2), key_t = ((long long)N << 1) | (pow2 ? 1 : 0);
+  if (*tag_w != key_w || *tag_wp != (long long)(uintptr_t)wtab) {
+    delay_fft_window_kernel<<<(N + 255) / 256, 256, 0, st>>>(wtab, N, window_id);
+    FCU(cudaGetLastError());
+    *tag_w = key_w;
+    *tag_wp = (long long)(uintptr_t)wtab;
+  }
+  if (*tag_t != key_t || *tag_tp != (long long)(uintptr_t)tw) {
+    if (pow2)
+      FCU(build_stage_twiddles(tw, N, st));
+    else
+      delay_fft_fulltw_kernel<<<(N + 255) / 256, 256, 0, st>>>(tw, N);
+    FCU(cudaGetLastError());
+    *tag_t = key_t;
+    *tag_tp = (long long)(uintptr_t)tw;
+  }
 
   const size_t smem = (size_t)N * (pow2 ? 3 : 2) * sizeof(double2);
   void (*kern)(const double2*, double2*, const double*, const double2*, long long, int, int) = delay_dft_direct_kernel;
@@ -224,9 +237,7 @@ extern "C" int dgibbs_delay_fft(dgibbs_handle h, int32_t on_device, int64_t nrow
   if (occ < 1) return bad("the transform does not fit in shared memory");
   long long grid = (long long)occ * dg_sm_count(h);
   if (grid > nrows) grid = nrows;
-  cudaEvent_t e0, e1;
-  FCU(cudaEventCreate(&e0));
-  FCU(cudaEventCreate(&e1));
+  const cudaEvent_t e0 = dg_event(h, 0), e1 = dg_event(h, 1);  // the handle's own events: nothing to leak on an early return
   FCU(cudaEventRecord(e0, st));
   kern<<<(unsigned)grid, nthreads, smem, st>>>(x, y, wtab, tw, (long long)nrows, N, shift ? 1 : 0);
   FCU(cudaEventRecord(e1, st));
@@ -235,8 +246,6 @@ extern "C" int dgibbs_delay_fft(dgibbs_handle h, int32_t on_device, int64_t nrow
   FCU(cudaStreamSynchronize(st));
   float ms = 0.f;
   FCU(cudaEventElapsedTime(&ms, e0, e1));
-  cudaEventDestroy(e0);
-  cudaEventDestroy(e1);
   if (ms_kernel) *ms_kernel = (double)ms;
   return 0;
 }
@@ -281,9 +290,7 @@ extern "C" int dgibbs_sample_variance(dgibbs_handle h, int32_t on_device, int32_
     }
   }
   if (bd) FCU(cudaMemsetAsync(bd, 0, (size_t)B, st));
-  cudaEvent_t e0, e1;
-  FCU(cudaEventCreate(&e0));
-  FCU(cudaEventCreate(&e1));
+  const cudaEvent_t e0 = dg_event(h, 0), e1 = dg_event(h, 1);  // the handle's own events: nothing to leak on an early return
   FCU(cudaEventRecord(e0, st));
   sample_variance_kernel<<<dim3((N + 255) / 256, B), 256, 0, st>>>(x, mk, v, bd, T, N);
   FCU(cudaEventRecord(e1, st));
@@ -295,8 +302,6 @@ extern "C" int dgibbs_sample_variance(dgibbs_handle h, int32_t on_device, int32_
   FCU(cudaStreamSynchronize(st));
   float ms = 0.f;
   FCU(cudaEventElapsedTime(&ms, e0, e1));
-  cudaEventDestroy(e0);
-  cudaEventDestroy(e1);
   if (ms_kernel) *ms_kernel = (double)ms;
   return 0;
 }

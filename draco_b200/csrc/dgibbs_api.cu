@@ -28,6 +28,7 @@ struct dgibbs_handle_s {
   std::string err;
   dgibbs_timing timing{};
   std::map<std::string, Buf> pool;  // grow-only device workspace, freed in destroy
+  std::map<std::string, long long> tags;
   cudaEvent_t ev[8]{};
   // pipelined host-pointer path: uploads / downloads on their own streams, two buffer sets
   cudaStream_t up_stream = nullptr, down_stream = nullptr;
@@ -76,6 +77,8 @@ cudaStream_t dg_stream(dgibbs_handle h) { return h->stream; }
 int dg_device(dgibbs_handle h) { return h->device; }
 int dg_sm_count(dgibbs_handle h) { return h->sm_count; }
 void dg_set_error(dgibbs_handle h, const char* msg) { h->err = msg; }
+long long* dg_tag(dgibbs_handle h, const char* name) { return &h->tags[name]; }
+cudaEvent_t dg_event(dgibbs_handle h, int i) { return h->ev[i & 7]; }
 
 extern "C" int dgibbs_version(void) { return DGIBBS_VERSION; }
 
@@ -366,8 +369,18 @@ static int stage_batch(dgibbs_handle h, const dgibbs_problem* p, Staged& s, bool
   // diagonal-branch baselines that will be projected by diag_project_fft_kernel (same conditions as in dgibbs_run)
   d.skip_zT_diag = (d.rng_mode == DGIBBS_RNG_PHILOX && d.nsys <= 4096 && d.niter > 0 && !d.wiener && diag_project_fft_fits(d) &&
                     !getenv("DGIBBS_NO_PROJECT_KERNEL")) ? 1 : 0;
+  CU(pool_get(h, "setup_err", sizeof(int), &q)); d.setup_err = (int*)q;
+  CU(cudaMemsetAsync(d.setup_err, 0, sizeof(int), h->stream));
   CU(launch_setup_baselines(d, s.S0, h->stream));
   h->timing.launches++;
+  {
+    // channel_ind out of range or aliased (the reference would sum the aliased channels; here it is an error, never a race)
+    int err = 0;
+    CU(cudaMemcpyAsync(&err, d.setup_err, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    if (err & 1) return bad_arg(h, 2, d.cplx ? "an fsel entry lies outside [0, N)" : "an fsel entry lies outside [0, N/2]");
+    if (err & 2) return bad_arg(h, 2, "fsel holds the same channel twice for one baseline (check freq_zero / freq_spacing / nfreq)");
+  }
   CU(dense_configure(d));
   return 0;
 }

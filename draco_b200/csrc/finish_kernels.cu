@@ -20,7 +20,9 @@ __global__ void finish_kernel(DevBatch d, const double* __restrict__ S0, int nta
 
   if (k == 0) {
     if (n_done_out) n_done_out[b] = nd;
-    if (success_out) success_out[b] = (nd == niter && !d.failed[b]) ? 1 : 0;
+    // an empty chain is a failure even when nothing failed numerically (nsamp = 0): `if samples: ... else: success = False`,
+    // delay.py:1261-1265
+    if (success_out) success_out[b] = (nd == niter && nd > 0 && !d.failed[b]) ? 1 : 0;
   }
   if (final_S) final_S[idx] = d.S[idx];
 

@@ -50,6 +50,7 @@ struct DevBatch {
   double* h;     // [B][Kpad]  window * sqrt(Ni_r) on the full grid (0 where masked)
   double* zT;    // [B][Tmax][Kpad] whitened data, transposed (sample-major)
   double2* wsre; // [B][Kpad/2] (window, sqrt(Ni_r) of the real part) per channel of the full grid, 0 where masked
+  int* setup_err;         // [1] set by the setup kernel: bit 0 = an fsel entry outside the channel grid, bit 1 = a duplicate
   unsigned char* cident;  // [B] 1: the kept channels are 0 .. M-1 in order (cidx[i] = i for i < M): no index look-up needed
   int skip_zT_diag;  // 1: diagonal-branch baselines get no zT (their projection reads the raw data, project_fft.cu)
   double* ctab;  // [B][nsys]  first column of the circulant FTNiF (cplx: cr[N] then ci[N])
@@ -93,6 +94,9 @@ cudaStream_t dg_stream(dgibbs_handle_s* h);
 int dg_device(dgibbs_handle_s* h);
 int dg_sm_count(dgibbs_handle_s* h);
 void dg_set_error(dgibbs_handle_s* h, const char* msg);
+// per-handle 64-bit tags (0 when new): lets an entry point remember what a pooled table holds between calls
+long long* dg_tag(dgibbs_handle_s* h, const char* name);
+cudaEvent_t dg_event(dgibbs_handle_s* h, int i);  // the handle's pre-created timing events, i in [0, 8)
 namespace dg {
 
 // setup_kernels.cu

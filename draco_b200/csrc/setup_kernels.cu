@@ -82,7 +82,12 @@ __global__ void __launch_bounds__(THREADS) setup_baseline_kernel(DevBatch d, con
   bool inorder = true;
   for (int ci = threadIdx.x; ci < Mb; ci += blockDim.x) {
     long long f = d.fsel[coff + ci];
-    if (f >= 0 && f < nch) cidx[f] = ci;
+    if (f >= 0 && f < nch) {
+      // two entries on one channel (a mis-set freq_zero / freq_spacing / nfreq aliasing channels): reported, not raced
+      if (atomicExch(&cidx[f], ci) != -1) atomicOr(d.setup_err, 2);
+    } else {
+      atomicOr(d.setup_err, 1);
+    }
     inorder = inorder && f == ci;
   }
   const int ident = __syncthreads_and(inorder ? 1 : 0);

@@ -324,8 +324,10 @@ class DelayPowerSpectrumGibbs(DelayPowerSpectrumBase, _RandomTask):
     Extra optional parameter ``rng_mode``: ``"philox"`` (default) draws on the device with
     Philox4x32-10 keyed on (seed, global baseline index, iteration), so results do not depend on
     the number of ranks; ``"injected"`` draws every Gaussian / chi^2 variate from ``self.rng`` on
-    the host in the reference's order and ships them to the device (bit-for-bit comparable with
-    the reference run with the same generator; slow, meant for validation).
+    the host in the reference's order and ships them to the device (slow, meant for validation).  All ``nsamp``
+    iterations of a baseline are drawn up front, so the host generator's stream equals the reference's only while
+    every chain runs to completion: after a chain that stops early (delay.py:1891-1896) the reference has consumed
+    fewer variates than this task, and the baselines that follow see different draws.
     """
 
     initial_amplitude = config.Property(proptype=float, default=10.0)
@@ -580,7 +582,9 @@ class DelayCrossPowerSpectrumEstimator(DelayPowerSpectrumGibbs):
             data = np.stack([j[2] for j in jobs])
             T, M = data.shape[2], data.shape[3]
             draws = None
-            if self.rng_mode == "injected":  # one generator shared by the local baselines in loop order (delay.py:1418)
+            # one generator shared by the local baselines (delay.py:1418); drawn group by group, which is the
+            # reference's loop order only when every local baseline has the same channel selection and sample count
+            if self.rng_mode == "injected":
                 per = [gibbs._host_cross_draws(self.rng, self.nsamp, ndelay, ndata, M, T) for _ in jobs]
                 draws = tuple(np.stack([p[i] for p in per]) for i in range(4))
             samples, n_done, ok = gibbs.cross_batch(

@@ -276,3 +276,27 @@ def test_large_and_odd_sizes(gibbs, N, M, T):
     res = gibbs.run_batch(pb, 2, draws=gibbs.pack_draws(pb, 2, [dr[0]], [dr[1]], [dr[2]]), save_samples=True)
     assert bool(res.success.all())
     np.testing.assert_allclose(res.samples[:, 0], s, rtol=RTOL_SAMPLES)
+
+
+def test_aliased_or_out_of_range_channels_are_an_error(gibbs):
+    """A channel selection that puts two entries on one channel, or one outside the grid (a mis-set freq_zero /
+    freq_spacing / nfreq), is reported -- not dropped silently or resolved by a race (advisor finding r01)."""
+    data, Ni, fsel, S0 = make_case(64, 29, 8, False, False, seed=11)
+    dup = fsel.copy()
+    dup[5] = dup[4]
+    with pytest.raises(gibbs.DGibbsError, match="twice"):
+        gibbs.run_batch(gibbs.pack_batch([data], [Ni], [dup], 64, S0[None]), 2, seed=1)
+    out = fsel.copy()
+    out[-1] = 40  # N/2 = 32 is the last channel of the real-mode grid
+    with pytest.raises(gibbs.DGibbsError, match="outside"):
+        gibbs.run_batch(gibbs.pack_batch([data], [Ni], [out], 64, S0[None]), 2, seed=1)
+    ok = gibbs.run_batch(gibbs.pack_batch([data], [Ni], [fsel], 64, S0[None]), 2, seed=1)  # the handle stays usable
+    assert ok.success.all()
+
+
+def test_empty_chain_is_not_a_success(gibbs):
+    """nsamp = 0: `_estimator` returns the prior with success=False (delay.py:1261-1265)."""
+    data, Ni, fsel, S0 = make_case(64, 29, 8, False, False, seed=11)
+    res = gibbs.run_batch(gibbs.pack_batch([data], [Ni], [fsel], 64, S0[None]), 0, seed=1)
+    assert int(res.n_done[0]) == 0 and not res.success[0]
+    assert np.array_equal(res.spectrum[0], S0)
