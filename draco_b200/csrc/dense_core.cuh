@@ -490,19 +490,22 @@ __device__ __forceinline__ int fft_swz(int p, bool on) { return on ? (p ^ ((p >>
 // Stockham autosort: radix-8 stages (8-point butterflies in registers: 4 passes over shared memory at N = 2048
 // instead of the 6 of a radix-4 chain), then one radix-4 or radix-2 stage; exact twiddles from the table.
 // All NT threads of the CTA must call it; the inputs must be visible (caller synchronises before).
+// Batched form: G independent transforms in lockstep, transform g in x[g N .. (g+1) N) / y[g N ..): for small N one
+// transform keeps only N / 8 threads busy per pass, G of them fill the CTA (per-element arithmetic unchanged).
 template <int NT = THREADS>
-static __device__ double2* fft_inverse_smem(double2* x, double2* y, const double2* tw, int N) {
+static __device__ double2* fft_inverse_smem(double2* x, double2* y, const double2* tw, int N, int G = 1) {
   int Ns = 1;
   bool swz = false;  // is the current input buffer swizzled?
-  const int e8 = N >> 3;
+  const int e8 = N >> 3, l8 = __ffs(e8) - 1;
   while (Ns * 8 <= N) {
     const int s = N / (8 * Ns);
     const bool swz_out = Ns == 1 && N > 8;
-    for (int j = threadIdx.x; j < e8; j += NT) {
+    for (int jj = threadIdx.x; jj < G * e8; jj += NT) {
+      const int j = jj & (e8 - 1), go = (jj >> l8) * N;
       const int k = j & (Ns - 1);
       double2 v[8];
 #pragma unroll
-      for (int r = 0; r < 8; r++) v[r] = x[fft_swz(j + r * e8, swz)];
+      for (int r = 0; r < 8; r++) v[r] = x[go + fft_swz(j + r * e8, swz)];
       if (Ns > 1) {
         const int ks = k * s;  // r k s < N for r < 8
 #pragma unroll
@@ -515,14 +518,15 @@ static __device__ double2* fft_inverse_smem(double2* x, double2* y, const double
       const double2 o2 = make_double2(-v[5].y, v[5].x);                                  // i O_2
       const double2 o3 = make_double2(-(v[7].x + v[7].y) * h, (v[7].x - v[7].y) * h);  // w8^3 O_3
       const int j0 = ((j - k) << 3) + k;
-      y[fft_swz(j0, swz_out)] = cadd(v[0], v[1]);
-      y[fft_swz(j0 + Ns, swz_out)] = cadd(v[2], o1);
-      y[fft_swz(j0 + 2 * Ns, swz_out)] = cadd(v[4], o2);
-      y[fft_swz(j0 + 3 * Ns, swz_out)] = cadd(v[6], o3);
-      y[fft_swz(j0 + 4 * Ns, swz_out)] = csub(v[0], v[1]);
-      y[fft_swz(j0 + 5 * Ns, swz_out)] = csub(v[2], o1);
-      y[fft_swz(j0 + 6 * Ns, swz_out)] = csub(v[4], o2);
-      y[fft_swz(j0 + 7 * Ns, swz_out)] = csub(v[6], o3);
+      double2* yg = y + go;
+      yg[fft_swz(j0, swz_out)] = cadd(v[0], v[1]);
+      yg[fft_swz(j0 + Ns, swz_out)] = cadd(v[2], o1);
+      yg[fft_swz(j0 + 2 * Ns, swz_out)] = cadd(v[4], o2);
+      yg[fft_swz(j0 + 3 * Ns, swz_out)] = cadd(v[6], o3);
+      yg[fft_swz(j0 + 4 * Ns, swz_out)] = csub(v[0], v[1]);
+      yg[fft_swz(j0 + 5 * Ns, swz_out)] = csub(v[2], o1);
+      yg[fft_swz(j0 + 6 * Ns, swz_out)] = csub(v[4], o2);
+      yg[fft_swz(j0 + 7 * Ns, swz_out)] = csub(v[6], o3);
     }
     __syncthreads();
     double2* tmp = x; x = y; y = tmp;
@@ -530,27 +534,30 @@ static __device__ double2* fft_inverse_smem(double2* x, double2* y, const double
     swz = swz_out;
   }
   if (Ns * 4 == N) {  // one radix-4 stage
-    const int quarter = N >> 2, s = 1;
-    for (int j = threadIdx.x; j < quarter; j += NT) {  // k = j (Ns = N / 4)
-      double2 v0 = x[fft_swz(j, swz)], v1 = x[fft_swz(j + quarter, swz)], v2 = x[fft_swz(j + 2 * quarter, swz)],
-              v3 = x[fft_swz(j + 3 * quarter, swz)];
+    const int quarter = N >> 2, s = 1, lq = __ffs(quarter) - 1;
+    for (int jj = threadIdx.x; jj < G * quarter; jj += NT) {  // k = j (Ns = N / 4)
+      const int j = jj & (quarter - 1), go = (jj >> lq) * N;
+      double2 v0 = x[go + fft_swz(j, swz)], v1 = x[go + fft_swz(j + quarter, swz)], v2 = x[go + fft_swz(j + 2 * quarter, swz)],
+              v3 = x[go + fft_swz(j + 3 * quarter, swz)];
       v1 = cmul(v1, tw_get(tw, j * s, N));
       v2 = cmul(v2, tw_get(tw, 2 * j * s, N));
       v3 = cmul(v3, tw_get(tw, 3 * j * s, N));
       dft4_inv(v0, v1, v2, v3);
-      y[j] = v0;
-      y[j + quarter] = v1;
-      y[j + 2 * quarter] = v2;
-      y[j + 3 * quarter] = v3;
+      double2* yg = y + go;
+      yg[j] = v0;
+      yg[j + quarter] = v1;
+      yg[j + 2 * quarter] = v2;
+      yg[j + 3 * quarter] = v3;
     }
     __syncthreads();
     double2* tmp = x; x = y; y = tmp;
   } else if (Ns * 2 == N) {  // one radix-2 stage, twiddle stride 1
-    const int half = N >> 1;
-    for (int j = threadIdx.x; j < half; j += NT) {
-      const double2 v0 = x[fft_swz(j, swz)], v1 = cmul(x[fft_swz(j + half, swz)], tw[j]);
-      y[j] = cadd(v0, v1);
-      y[j + half] = csub(v0, v1);
+    const int half = N >> 1, lh = __ffs(half) - 1;
+    for (int jj = threadIdx.x; jj < G * half; jj += NT) {
+      const int j = jj & (half - 1), go = (jj >> lh) * N;
+      const double2 v0 = x[go + fft_swz(j, swz)], v1 = cmul(x[go + fft_swz(j + half, swz)], tw[j]);
+      y[go + j] = cadd(v0, v1);
+      y[go + j + half] = csub(v0, v1);
     }
     __syncthreads();
     double2* tmp = x; x = y; y = tmp;
@@ -626,11 +633,19 @@ __device__ __forceinline__ void w1_pair2(const DrawCtx& c, int t0, int k, int ns
 //   real mode    : two samples per complex FFT (their spectra are Hermitian-extended and combined as A + iB)
 //   complex mode : one sample per FFT, output interleaved re/im
 // A cluster of `nrank` CTAs shares the rows: CTA `rank` takes every nrank-th sample (pair).
-static __device__ void project_rows_fft(const DevBatch& d, const DrawCtx& c, double* Rh, const double* Si, double2* bufA,
-                                 double2* bufB, double2* tw_s, int rows, int rank = 0, int nrank = 1) {
+// `fbuf` holds PIPE_DOUBLES / 2 complex entries: G = min(THREADS / (N / 8), what fits, 16) transforms run in lockstep
+// (fft_inverse_smem's batched form), i.e. 2 G real samples per pass: at N = 256 the whole prepass of T = 32 samples is
+// 2 passes instead of 16 (cfg1: 29 % of the kernel before).  Per-sample arithmetic does not depend on G.
+static __device__ void project_rows_fft(const DevBatch& d, const DrawCtx& c, double* Rh, const double* Si, double2* fbuf,
+                                 double2* tw_s, int rows, int rank = 0, int nrank = 1) {
   const int N = d.N, nsys = d.nsys, npad = d.npad, nch = d.nch;
   for (int m = threadIdx.x; m < N / 2; m += THREADS) tw_s[m] = d.twtab[m];
   const int step = d.cplx ? 1 : 2;
+  int G = THREADS / max(1, N >> 3);
+  G = max(1, min(min(G, 16), (PIPE_DOUBLES / 2) / (2 * N)));
+  double2* bufA = fbuf;
+  double2* bufB = fbuf + (size_t)G * N;
+  const int hp = npad / 2;
   long long tp = clock64();
 #define PROFX(idx)                                                                       \
   do {                                                                                   \
@@ -640,60 +655,59 @@ static __device__ void project_rows_fft(const DevBatch& d, const DrawCtx& c, dou
       tp = t_;                                                                           \
     }                                                                                    \
   } while (0)
-  for (int t0 = rank * step; t0 < rows; t0 += nrank * step) {
+  for (int tb = rank * step * G; tb < rows; tb += nrank * step * G) {
     __syncthreads();  // previous epilogue finished with the buffers (and tw_s is loaded)
     PROFX(14);
-    if (t0 >= c.Tb) {  // padding rows: zeros (CTA-uniform branch)
-      for (int e = threadIdx.x; e < step * (npad / 2); e += THREADS) {
-        int r = e / (npad / 2), k = (e % (npad / 2)) * 2;
-        if (t0 + r < rows) *reinterpret_cast<double2*>(Rh + (size_t)(t0 + r) * npad + k) = make_double2(0.0, 0.0);
-      }
-      continue;
-    }
+    // ---- stage u of the samples tb + g step (g < G) that exist; rows beyond Tb are zero padding
     if (!d.cplx) {
-      for (int i = threadIdx.x; i < nch; i += THREADS) {
+      for (int e = threadIdx.x; e < G * nch; e += THREADS) {
+        const int g = e / nch, i = e - g * nch, t0 = tb + g * step;
+        if (t0 >= c.Tb || t0 >= rows) continue;
+        double2* bA = bufA + (size_t)g * N;
         double2 U0, U1;
         u_value2(c, t0, i, true, U0, U1);
         if (i == 0 || i == N / 2) {
-          bufA[i] = make_double2(U0.x, U1.x);
+          bA[i] = make_double2(U0.x, U1.x);
         } else {
-          bufA[i] = make_double2(0.5 * (U0.x - U1.y), 0.5 * (U0.y + U1.x));       // (U0 + i U1) / 2
-          bufA[N - i] = make_double2(0.5 * (U0.x + U1.y), 0.5 * (U1.x - U0.y));   // (conj U0 + i conj U1) / 2
+          bA[i] = make_double2(0.5 * (U0.x - U1.y), 0.5 * (U0.y + U1.x));       // (U0 + i U1) / 2
+          bA[N - i] = make_double2(0.5 * (U0.x + U1.y), 0.5 * (U1.x - U0.y));   // (conj U0 + i conj U1) / 2
         }
       }
     } else {
-      for (int i = threadIdx.x; i < N; i += THREADS) {
+      for (int e = threadIdx.x; e < G * N; e += THREADS) {
+        const int g = e / N, i = e - g * N, t0 = tb + g;
+        if (t0 >= c.Tb || t0 >= rows) continue;
         double2 U0, U1;
         u_value2(c, t0, i, false, U0, U1);
-        bufA[i] = U0;
+        bufA[(size_t)g * N + i] = U0;
       }
     }
     __syncthreads();
     PROFX(12);
-    const double2* res = fft_inverse_smem(bufA, bufB, tw_s, N);
+    const double2* res = fft_inverse_smem(bufA, bufB, tw_s, N, G);
     PROFX(13);
-    if (!d.cplx) {
-      const bool two = t0 + 1 < rows;
-      for (int p = threadIdx.x; p < npad / 2; p += THREADS) {
-        const int k = 2 * p;
+    // ---- y = sqrt(Si) w1 + F^T u  (delay.py:1815-1817); zeros in the padding rows / columns
+    for (int e = threadIdx.x; e < G * hp; e += THREADS) {
+      const int g = e / hp, p = e - g * hp, k = 2 * p, t0 = tb + g * step;
+      if (t0 >= rows) continue;
+      const double2* rg = res + (size_t)g * N;
+      if (!d.cplx) {
+        const bool two = t0 + 1 < rows;
         double2 ya = make_double2(0.0, 0.0), yb = make_double2(0.0, 0.0);
-        if (k < nsys) {
-          const double2 r0 = res[k], r1 = res[k + 1];
+        if (k < nsys && t0 < c.Tb) {
+          const double2 r0 = rg[k], r1 = rg[k + 1];
           const double s0 = sqrt(Si[k]), s1 = sqrt(Si[k + 1]);
           double a0, a1, b0, b1;
           w1_pair2(c, t0, k, nsys, true, a0, a1, b0, b1);
-          ya = make_double2(s0 * a0 + r0.x, s1 * a1 + r1.x);   // delay.py:1815-1817
+          ya = make_double2(s0 * a0 + r0.x, s1 * a1 + r1.x);
           if (t0 + 1 < c.Tb) yb = make_double2(s0 * b0 + r0.y, s1 * b1 + r1.y);
         }
         *reinterpret_cast<double2*>(Rh + (size_t)t0 * npad + k) = ya;
         if (two) *reinterpret_cast<double2*>(Rh + (size_t)(t0 + 1) * npad + k) = yb;
-      }
-    } else {
-      for (int p = threadIdx.x; p < npad / 2; p += THREADS) {
-        const int k = 2 * p;
+      } else {
         double2 ya = make_double2(0.0, 0.0);
-        if (k < nsys) {
-          const double2 r0 = res[p];
+        if (k < nsys && t0 < c.Tb) {
+          const double2 r0 = rg[p];
           double n0, n1, b0, b1;
           w1_pair2(c, t0, k, nsys, false, n0, n1, b0, b1);
           ya = make_double2(sqrt(Si[k]) * n0 + r0.x, sqrt(Si[k + 1]) * n1 + r0.y);

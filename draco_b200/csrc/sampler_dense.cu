@@ -122,7 +122,7 @@ __global__ void __launch_bounds__(THREADS, 1) dense_sampler_kernel(DevBatch d, i
         dc.w2 = (d.rng_mode == 0) ? d.w2 + d.w2_off[b] + (long long)it * 2 * Mb * Tb : nullptr;
         dc.Tb = Tb; dc.it = it; dc.half = Kpad >> 1;
         double2* fbuf = reinterpret_cast<double2*>(pipe);
-        project_rows_fft(d, dc, Rh, Si, fbuf, fbuf + N, reinterpret_cast<double2*>(sWp), rhs_frags * 8, rank, C);
+        project_rows_fft(d, dc, Rh, Si, fbuf, reinterpret_cast<double2*>(sWp), rhs_frags * 8, rank, C);
         PROF(0);
       } else {
       {  // Y = sqrt(Si) * w1  (two adjacent delays per thread), zero in the padding
@@ -503,9 +503,10 @@ DensePlan plan_dense(const DevBatch& d, int nchains, int sm_count, int force_clu
       return p;
     }
   }
-  const int S = ncl[1];
-  p.n_main = (nchains / S) * S;
-  p.grid_main = S;
+  // full waves (one chain per SM) on single CTAs; what is left over -- all of a small batch -- on the cluster size that
+  // finishes it soonest
+  p.n_main = (nchains / sm_count) * sm_count;
+  p.grid_main = ncl[1];
   const int rem = nchains - p.n_main;
   if (rem == 0) return p;
   double best = 1e300;
