@@ -299,19 +299,20 @@ def fp64_peak_tflops():
     return 2.0 * n**3 / best / 1e9
 
 
-# dram__bytes_read.sum + dram__bytes_write.sum of dense_sampler_kernel from the committed `ncu --set full`
-# captures profiles/r01e (72.76 GB), r01h (72.89 GB) and r01i_dense_sampler_ncu_raw.csv (66.73 GB read + 6.22 GB written =
-# 72.96 GB) for a launch of 296 baseline-iterations of cfg2
-# geometry = 245.8 MB per baseline-iteration (L panels re-read from DRAM; 14 % of DRAM peak, not the bound).
+# dram__bytes_read.sum + dram__bytes_write.sum of dense_sampler_kernel<1> (TMA operand ring) from the committed
+# `ncu --set full` capture profiles/r02p_dense_sampler_ncu_raw.csv: 66.78 GB read + 6.22 GB written for a launch of 296
+# baseline-iterations of cfg2 geometry = 246.6 MB per baseline-iteration (the r01e / r01h / r01i / r01o captures of the
+# cp.async kernel read the same: 72.8-73.0 GB).  Twice the A-panel model: the B row panel is re-read per row tile and
+# does not stay in L2; 25 % of the DRAM peak, not the bound.
 # Reported per launch of THIS run by scaling with the launch's baseline-iterations (cfg2 geometry only).
-DENSE_TRAFFIC_PER_UNIT = 72.985e9 / 296  # r01o capture: 66.76 GB read + 6.22 GB written
-DENSE_TRAFFIC_SOURCE = "ncu --set full capture of 296 baseline-iterations scaled to this launch (profiles/r01o_dense_sampler_ncu_raw.csv)"
+DENSE_TRAFFIC_PER_UNIT = (66.781169e9 + 6.223135e9) / 296
+DENSE_TRAFFIC_SOURCE = "ncu --set full capture of 296 baseline-iterations scaled to this launch (profiles/r02p_dense_sampler_ncu_raw.csv)"
 
 
-# dram__bytes_read.sum + dram__bytes_write.sum of diag_resident_kernel from the committed `ncu --set full` capture
-# profiles/r01n_diag_path_ncu_raw.csv: 257.65 MB read + 61.77 MB written for a launch of 240 baselines x 20 iterations of
+# dram__bytes_read.sum + dram__bytes_write.sum of diag_resident_kernel<384,0> from the committed `ncu --set full` capture
+# profiles/r02p_diag_path_ncu_raw.csv: 257.75 MB read + 62.32 MB written for a launch of 240 baselines x 20 iterations of
 # cfg3 geometry (the projected data is read once per baseline and then stays in distributed shared memory).
-DIAG_TRAFFIC_PER_UNIT = (257.651712e6 + 61.768704e6) / (240 * 20)
+DIAG_TRAFFIC_PER_UNIT = (257.753088e6 + 62.3232e6) / (240 * 20)
 
 
 def hbm_roofline(nbytes, ms, units=None):
@@ -326,7 +327,7 @@ def hbm_roofline(nbytes, ms, units=None):
     ach = nbytes / (ms / 1e3) / 1e9 if ms > 0 else 0.0
     return {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
             "traffic": DIAG_TRAFFIC_PER_UNIT * units if units else None,
-            "traffic_source": "ncu --set full capture of 4800 baseline-iterations scaled to this launch (profiles/r01n_diag_path_ncu_raw.csv)",
+            "traffic_source": "ncu --set full capture of 4800 baseline-iterations scaled to this launch (profiles/r02p_diag_path_ncu_raw.csv)",
             "peak_source": src, "kernel": "diag_resident_kernel (cluster-resident; diag_sampler_kernel when a slice does not fit)",
             "byte_model": "Q_d = 8 n T + 16 N bytes per baseline-iteration (read projected data once, read+write S)"}
 
