@@ -24,6 +24,7 @@
 #include <vector>
 
 #include "../../include/dgwiener.h"
+#include "wiener_own.h"
 
 namespace {
 
@@ -293,11 +294,19 @@ extern "C" int dgwiener_construct(dgwiener_problem* p) {
 
   const size_t FF = (size_t)F * F, FD = (size_t)F * nd;
   const size_t kbytes = p->filter_is_complex ? 16 : 8, cbytes = p->cov_is_complex ? 16 : 8;
-  const size_t per_pixel = FF * (kbytes + cbytes + 3 * 16) + FD * (16 + 8) + (size_t)F * (8 + 16 + 1) + 64;
+  // solver 3 (and 0 = auto): every contraction, the factorisation and the solves on this repository's own DMMA kernels
+  // (wiener_own.cu); 1 / 2: cuBLAS ZGEMM + cuSOLVER ZPOTRF (batched / per matrix) + cuBLAS ZTRSM
+  const bool own = p->solver == 3 || p->solver == 0;
+  int sm_count = 148;
+  WCU(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, p->device_id));
+  const dgw::OwnGeom og = dgw::own_geom(F, nd, sm_count);
+  const dgw::OwnSizes oz = dgw::own_sizes(og);
+  const size_t per_pixel = own ? FF * (kbytes + cbytes) + 8 * (oz.Pr + oz.Pext + oz.T1r + oz.Ar + oz.Yr) + FD * 8 + (size_t)F * (8 + 16 + 1) + 64
+                               : FF * (kbytes + cbytes + 3 * 16) + FD * (16 + 8) + (size_t)F * (8 + 16 + 1) + 64;
   const size_t budget = p->workspace_bytes > 0 ? (size_t)p->workspace_bytes : ((size_t)8 << 30);
   const int R = (int)std::max<size_t>(1, std::min<size_t>(std::min<size_t>((size_t)nra, 32768), budget / per_pixel));
   // measured (profiles/r01j_perf_wiener_op.json.log): the batched factorisation wins up to F = 512 at least
-  const bool batched = p->solver == 1 || (p->solver == 0 && F <= 512);
+  const bool batched = p->solver == 1;
 
   DevBufs bufs;
   zc *Fp, *FS, *FSFT, *G, *P, *T1, *A, *Y, *rn;
@@ -310,15 +319,30 @@ extern "C" int dgwiener_construct(dgwiener_problem* p) {
   WCU(bufs.alloc(&Fp, FD * 16)); WCU(bufs.alloc(&FS, FD * 16)); WCU(bufs.alloc(&FSFT, FF * 16)); WCU(bufs.alloc(&G, FF * 16));
   WCU(bufs.alloc(&prior, (size_t)nd * 8)); WCU(bufs.alloc(&window, (size_t)F * 8)); WCU(bufs.alloc(&bp, (size_t)nel * F * 8));
   WCU(bufs.alloc(&K, (size_t)R * FF * kbytes)); WCU(bufs.alloc(&C, (size_t)R * FF * cbytes));
-  WCU(bufs.alloc(&P, (size_t)R * FF * 16)); WCU(bufs.alloc(&T1, (size_t)R * FF * 16)); WCU(bufs.alloc(&A, (size_t)R * FF * 16));
-  WCU(bufs.alloc(&Y, (size_t)R * FD * 16)); WCU(bufs.alloc(&outd, (size_t)R * FD * 8));
+  dgw::OwnBufs ob{};
+  if (own) {
+    // T1 only carries the host Fourier operator to the device; P / A / Y are replaced by the interleaved-real buffers
+    WCU(bufs.alloc(&T1, std::max(FD, FF) * 16));
+    P = A = Y = nullptr;
+    struct { double** p; size_t n; } own_list[] = {{&ob.Pr, R * oz.Pr}, {&ob.Pext, R * oz.Pext}, {&ob.T1r, R * oz.T1r}, {&ob.Ar, R * oz.Ar},
+                                                   {&ob.Yr, R * oz.Yr}, {&ob.Gext, oz.Gext}, {&ob.Fpr, oz.Fpr}, {&ob.work, oz.work}, {&ob.Wp, oz.Wp}};
+    for (auto& it : own_list) {
+      WCU(bufs.alloc(it.p, it.n * 8));
+      WCU(cudaMemsetAsync(*it.p, 0, it.n * 8, L.stream));  // the padding of every matrix stays zero from here on
+    }
+    WCU(dgw::own_configure());
+  } else {
+    WCU(bufs.alloc(&P, (size_t)R * FF * 16)); WCU(bufs.alloc(&T1, (size_t)R * FF * 16)); WCU(bufs.alloc(&A, (size_t)R * FF * 16));
+    WCU(bufs.alloc(&Y, (size_t)R * FD * 16));
+  }
+  WCU(bufs.alloc(&outd, (size_t)R * FD * 8));
   WCU(bufs.alloc(&w, (size_t)R * F * 8)); WCU(bufs.alloc(&rn, (size_t)R * F * 16)); WCU(bufs.alloc(&M, (size_t)R * F));
   WCU(bufs.alloc(&info, (size_t)R * sizeof(int)));
   WCU(bufs.alloc(&Aptr, (size_t)R * sizeof(zc*))); WCU(bufs.alloc(&Yptr, (size_t)R * sizeof(zc*)));
   // per-stream cuSOLVER workspaces (per-matrix mode)
   zc* swork[NSTREAM] = {};
   int lwork = 0;
-  if (!batched) {
+  if (!batched && !own) {
     WBL(cusolverDnZpotrf_bufferSize(L.ssolver[0], CUBLAS_FILL_MODE_LOWER, F, A, F, &lwork));
     for (int i = 0; i < NSTREAM; i++) WCU(bufs.alloc(&swork[i], (size_t)std::max(lwork, 1) * 16));
   }
@@ -339,6 +363,10 @@ extern "C" int dgwiener_construct(dgwiener_problem* p) {
   WBL(cublasZgemm(L.blas, CUBLAS_OP_N, CUBLAS_OP_C, F, F, nd, &one, FS, F, Fp, F, &zero, FSFT, F));
   launches += 2;
   flop += 8.0 * F * (double)F * nd;
+  if (own) {
+    WCU(dgw::own_prepare_fourier(st, og, Fp, ob));
+    launches += 1;
+  }
 
   for (int r0 = 0; r0 < nra; r0 += R) {
     const int Rc = std::min(R, nra - r0);
@@ -349,6 +377,13 @@ extern "C" int dgwiener_construct(dgwiener_problem* p) {
       WCU(cudaMemcpyAsync(w, p->weight + ((size_t)ee * nra + r0) * F, (size_t)Rc * F * 8, cudaMemcpyHostToDevice, st));
       WCU(cudaEventRecord(L.evA, st));
       const int gridE = (int)std::min<size_t>((nFF + 255) / 256, 148 * 16);
+      if (own) {
+        mask_noise_kernel<<<(unsigned)(((size_t)Rc * F + 255) / 256), 256, 0, st>>>(w, C, p->cov_is_complex, window, M, rn, Rc, F);
+        launches += 1;
+        WCU(cudaMemsetAsync(info, 0, (size_t)Rc * sizeof(int), st));
+        WCU(dgw::own_chunk(st, og, ob, Rc, sm_count, FSFT, bp + (size_t)ee * F, K, p->filter_is_complex, C, p->cov_is_complex, M, rn,
+                           prior, window, outd, info, &launches));
+      } else {
       beam_scale_kernel<<<dim3((F + 127) / 128, F), 128, 0, st>>>(FSFT, bp + (size_t)ee * F, G, F);
       mask_noise_kernel<<<(unsigned)(((size_t)Rc * F + 255) / 256), 256, 0, st>>>(w, C, p->cov_is_complex, window, M, rn, Rc, F);
       mask_filter_kernel<<<gridE, 256, 0, st>>>(K, p->filter_is_complex, M, P, nFF, F);
@@ -391,6 +426,7 @@ extern "C" int dgwiener_construct(dgwiener_problem* p) {
       const size_t nFD = (size_t)Rc * FD;
       epilogue_kernel<<<(int)std::min<size_t>((nFD + 255) / 256, 148 * 16), 256, 0, st>>>(Y, prior, window, M, outd, nFD, F, nd);
       launches += 1;
+      }  // library path
       WCU(cudaEventRecord(L.ev1, st));
       WCU(cudaMemcpyAsync(hinfo.data(), info, (size_t)Rc * sizeof(int), cudaMemcpyDeviceToHost, st));
       char* dst = (char*)p->out + 8 * ((size_t)r0 * p->out_stride_ra + (size_t)ee * p->out_stride_el);
@@ -407,7 +443,7 @@ extern "C" int dgwiener_construct(dgwiener_problem* p) {
           p->bad_el = ee;
           p->bad_ra = r0 + r;
           g_err = "covariance of pixel (ra " + std::to_string(r0 + r) + ", el " + std::to_string(ee) +
-                  ") is not positive definite (leading minor " + std::to_string(hinfo[r]) + ")";
+                  ") is not positive definite" + (own ? std::string() : " (leading minor " + std::to_string(hinfo[r]) + ")");
           return 1;
         }
     }

@@ -34,7 +34,9 @@ typedef struct {
   int32_t nra, nel;         /* pixels: right ascension, local elevations                     */
   int32_t filter_is_complex; /* 0: filter is float64, 1: complex128 (RingMap "complex_filter") */
   int32_t cov_is_complex;    /* 0: freq_cov is float64, 1: complex128                          */
-  int32_t solver;           /* 0 auto, 1 batched factorisation, 2 per-matrix on several streams */
+  int32_t solver;           /* 0 auto (= 3), 3 this library's own DMMA kernels for every contraction,
+                               the factorisation and the solves; 1 / 2 cuBLAS + cuSOLVER (batched factorisation /
+                               per matrix on several streams) */
   const void* fourier;      /* [F, ndelay] complex128: exp(2 pi i freq tau) / sqrt(ntau), powerspec.py:229 */
   const double* prior;      /* [ndelay] diagonal signal prior, powerspec.py:233              */
   const double* window;     /* [F] spectral window (zero = channel not used), powerspec.py:207 */

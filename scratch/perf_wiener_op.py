@@ -34,7 +34,7 @@ def run(F, nra, nel, cplx, cpu_pixels):
     freq, weight, beam, filt, cov, win, S, tau, ntau = problem(F, nra, nel, cplx)
     Fm = wo.fourier_operator(freq, tau, ntau)
     res = {"F": F, "ndelay": int(tau.size), "nra": nra, "nel": nel, "complex_inputs": cplx}
-    for solver, label in ((1, "batched"), (2, "streams")):
+    for solver, label in ((1, "batched"), (2, "streams"), (3, "own_kernels")):
         best = None
         for rep in range(3):
             t = {}
@@ -56,7 +56,7 @@ def run(F, nra, nel, cplx, cpu_pixels):
     err = np.abs(got[:nr, 0] - ref[:, 0]).max() / np.abs(ref).max()
     res["max_rel_err_vs_oracle"] = float(err)
     k = "streams" if "streams" in res else "batched"
-    res["speedup_compute"] = round(res["oracle_cpu"]["ms_per_pixel"] * 1e3 / min(res[x]["us_per_pixel"] for x in ("batched", "streams") if x in res), 1)
+    res["speedup_compute"] = round(res["oracle_cpu"]["ms_per_pixel"] * 1e3 / min(res[x]["us_per_pixel"] for x in ("batched", "streams", "own_kernels") if x in res), 1)
     print(json.dumps(res), flush=True)
 
 

@@ -65,7 +65,7 @@ def random_problem(F, nra, nel, cplx_filter, cplx_cov, seed, window="blackman"):
     return freq, weight, beam, filt, cov, win, S, tau, ntau
 
 
-@pytest.mark.parametrize("solver", [1, 2])
+@pytest.mark.parametrize("solver", [1, 2, 3])
 @pytest.mark.parametrize("cplx_filter,cplx_cov", [(False, False), (True, True), (True, False), (False, True)])
 def test_operator_matches_oracle(solver, cplx_filter, cplx_cov):
     """Both factorisation paths (batched / per-matrix on several streams), every dtype combination, F not a
