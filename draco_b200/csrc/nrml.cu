@@ -12,11 +12,13 @@
 
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
 
 #include "../../include/dgnrml.h"
+#include "nrml_own.h"
 
 namespace {
 
@@ -117,7 +119,7 @@ __global__ void col_dot_kernel(const zc* __restrict__ Ut, const zc* __restrict__
 
 // H[a, b] = nsamp (Re(G_ab conj(G_ba)) [+ 2 Re(K_ab G_ba) + delta_ab t_a])  (delayopt.py:221-236), row-major out
 __global__ void hessian_kernel(const zc* __restrict__ G, const zc* __restrict__ K, const double* __restrict__ t,
-                               double* __restrict__ H, int N, int exact, double nsamp) {
+                               double* __restrict__ H, int N, int exact, double nsamp, int ld) {
   constexpr int TS = 16;  // blockDim = (TS, TS)
   __shared__ zc gab[TS][TS + 1], kab[TS][TS + 1], gba[TS][TS + 1];
   const int A0 = blockIdx.y * TS, B0 = blockIdx.x * TS, tx = threadIdx.x;
@@ -125,11 +127,11 @@ __global__ void hessian_kernel(const zc* __restrict__ G, const zc* __restrict__ 
     const int ty = threadIdx.y;
     const int a = A0 + tx, b = B0 + ty;  // a fast: column-major reads of G[a, b], K[a, b]
     if (a < N && b < N) {
-      gab[ty][tx] = G[(size_t)b * N + a];
-      if (exact) kab[ty][tx] = K[(size_t)b * N + a];
+      gab[ty][tx] = G[(size_t)b * ld + a];
+      if (exact) kab[ty][tx] = K[(size_t)b * ld + a];
     }
     const int bb = B0 + tx, aa = A0 + ty;  // b fast: G[b, a]
-    if (aa < N && bb < N) gba[ty][tx] = G[(size_t)aa * N + bb];
+    if (aa < N && bb < N) gba[ty][tx] = G[(size_t)aa * ld + bb];
   }
   __syncthreads();
   {
@@ -189,7 +191,10 @@ struct dgnrml_s {
   int lwork = 0;
   std::vector<double> x_at;
   bool factored = false, have_hess_terms = false;
+  bool own = true;   // every contraction / factorisation / solve on this repository's kernels (nrml_own.cu)
+  dgn::Own o;
   double last_ms = 0, last_flop = 0;
+  long long last_launches = 0;
   std::string err;
 };
 
@@ -212,6 +217,7 @@ struct dgnrml_s {
 
 static int nrml_free(dgnrml s) {
   cudaSetDevice(s->device);
+  dgn::own_free(s->o);
   for (void* p : {(void*)s->X, (void*)s->MF, (void*)s->U, (void*)s->Ut, (void*)s->W, (void*)s->C, (void*)s->XC,
                   (void*)s->CiX, (void*)s->G, (void*)s->K, (void*)s->work, (void*)s->noise, (void*)s->x, (void*)s->sq,
                   (void*)s->t, (void*)s->H, (void*)s->scal, (void*)s->info})
@@ -259,6 +265,13 @@ extern "C" int dgnrml_create(int32_t device_id, int32_t M, int32_t N, int32_t ns
   conj_copy_kernel<<<1024, 256, 0, s->stream>>>(s->CiX, s->X, MM);
   NCU(cudaMemcpyAsync(s->W, MF, MN * 16, cudaMemcpyHostToDevice, s->stream));
   transpose_kernel<<<dim3((N + 31) / 32, (M + 31) / 32), dim3(32, 8), 0, s->stream>>>(s->W, s->MF, M, N);
+  s->own = getenv("DGNRML_LIBRARY") == nullptr;  // DGNRML_LIBRARY=1: cuBLAS / cuSOLVER path (A/B)
+  if (s->own) {
+    int sm_count = 148;
+    NCU(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, device_id));
+    NCU(dgn::own_alloc(s->o, M, N, sm_count, s->stream));
+    NCU(dgn::own_set_mf(s->o, s->W, s->stream));  // W still holds the row-major MF
+  }
   NCU(cudaMemcpyAsync(s->noise, noise, (size_t)M * 8, cudaMemcpyHostToDevice, s->stream));
   NCU(cudaGetLastError());
   NCU(cudaStreamSynchronize(s->stream));
@@ -287,6 +300,19 @@ extern "C" int dgnrml_eval(dgnrml s, const double* x, int32_t what, double* valu
     NCU(cudaMemcpyAsync(s->x, x, (size_t)N * 8, cudaMemcpyHostToDevice, s->stream));
     prep_kernel<<<(N + 255) / 256, 256, 0, s->stream>>>(s->x, s->sq, N, s->lo, s->hi);
     scale_cols_kernel<<<2048, 256, 0, s->stream>>>(s->MF, s->sq, s->U, M, N);
+    if (s->own) {
+      int info = 0;
+      long long nl = 0;
+      NCU(dgn::own_precompute(s->o, s->stream, s->sq, s->U, s->X, s->noise, s->t, s->scal, &info, (int64_t*)&nl));
+      s->last_launches = nl + 3;
+      if (info != 0) {
+        s->err = "covariance not positive definite (block column " + std::to_string(info - 1) + ")";
+        return 1;
+      }
+      s->x_at.assign(x, x + N);
+      s->factored = true;
+      flop += 4.0 * M * (double)M * N + 4.0 / 3.0 * M * (double)M * M + 16.0 * M * (double)M * N + 8.0 * M * (double)M * M;
+    } else {
     NBL(cublasZherk(L.blas, CUBLAS_FILL_MODE_LOWER, CUBLAS_OP_N, M, N, &done, s->U, M, &dzero, s->C, M));
     finish_cov_kernel<<<dim3((M + 127) / 128, M), 128, 0, s->stream>>>(s->C, s->X, s->noise, s->XC, M);
     NBL(cusolverDnZpotrf(L.solver, CUBLAS_FILL_MODE_LOWER, M, s->C, M, s->work, s->lwork, s->info));
@@ -304,9 +330,12 @@ extern "C" int dgnrml_eval(dgnrml s, const double* x, int32_t what, double* valu
     s->x_at.assign(x, x + N);
     s->factored = true;
     flop += 4.0 * M * (double)M * N + 4.0 / 3.0 * M * (double)M * M + 16.0 * M * (double)M * N;
+    }  // library path
   }
   double scal[2] = {0.0, 0.0};
-  if (what & DGNRML_VALUE) {  // delayopt.py:166-189
+  if ((what & DGNRML_VALUE) && s->own) {  // log det C and trace(C^-1 X) came out of the factorisation (X rode along)
+    NCU(cudaMemcpyAsync(scal, s->scal, 16, cudaMemcpyDeviceToHost, s->stream));
+  } else if (what & DGNRML_VALUE) {  // delayopt.py:166-189
     diag_reduce_kernel<<<1, 256, 0, s->stream>>>(s->C, M, 1, s->scal);
     NCU(cudaMemcpyAsync(s->CiX, s->X, MM * 16, cudaMemcpyDeviceToDevice, s->stream));
     NBL(cusolverDnZpotrs(L.solver, CUBLAS_FILL_MODE_LOWER, M, M, s->C, M, s->CiX, M, s->info));
@@ -317,14 +346,22 @@ extern "C" int dgnrml_eval(dgnrml s, const double* x, int32_t what, double* valu
   if (what & DGNRML_GRADIENT) NCU(cudaMemcpyAsync(gradient, s->t, (size_t)N * 8, cudaMemcpyDeviceToHost, s->stream));
   if (what & DGNRML_HESSIAN) {  // delayopt.py:209-236
     if (!s->have_hess_terms) {
-      NBL(cublasZgemm(L.blas, CUBLAS_OP_C, CUBLAS_OP_N, N, N, M, &one, s->U, M, s->Ut, M, &zero, s->G, N));
-      flop += 8.0 * M * (double)N * N;
-      if (s->exact) {
-        NBL(cublasZgemm(L.blas, CUBLAS_OP_C, CUBLAS_OP_N, N, N, M, &one, s->Ut, M, s->W, M, &zero, s->K, N));
-        flop += 8.0 * M * (double)N * N;
+      const zc *Gp = s->G, *Kp = s->K;
+      int ldg = N;
+      if (s->own) {
+        long long nl = 0;
+        NCU(dgn::own_hessian_terms(s->o, s->stream, s->exact, (int64_t*)&nl));
+        s->last_launches += nl;
+        Gp = reinterpret_cast<const zc*>(s->o.G);
+        Kp = reinterpret_cast<const zc*>(s->o.K);
+        ldg = s->o.ldG();
+      } else {
+        NBL(cublasZgemm(L.blas, CUBLAS_OP_C, CUBLAS_OP_N, N, N, M, &one, s->U, M, s->Ut, M, &zero, s->G, N));
+        if (s->exact) NBL(cublasZgemm(L.blas, CUBLAS_OP_C, CUBLAS_OP_N, N, N, M, &one, s->Ut, M, s->W, M, &zero, s->K, N));
       }
-      hessian_kernel<<<dim3((N + 15) / 16, (N + 15) / 16), dim3(16, 16), 0, s->stream>>>(s->G, s->K, s->t, s->H, N, s->exact,
-                                                                                        (double)s->nsamp);
+      flop += 8.0 * M * (double)N * N * (s->exact ? 2.0 : 1.0);
+      hessian_kernel<<<dim3((N + 15) / 16, (N + 15) / 16), dim3(16, 16), 0, s->stream>>>(Gp, Kp, s->t, s->H, N, s->exact,
+                                                                                        (double)s->nsamp, ldg);
       s->have_hess_terms = true;
     }
     NCU(cudaEventRecord(s->ev1, s->stream));

@@ -276,6 +276,14 @@ static cudaError_t launch_gemm(cudaStream_t st, int sm_count, const TileGemm& t)
   return cudaGetLastError();
 }
 
+cudaError_t own_gemm(cudaStream_t st, int sm_count, const double* A, long long sA, int lda, const double* B, long long sB, int ldb,
+                     double* C, long long sC, int ldc, int mt, int nt, int kchunks, int nn, int lower_only, int batch) {
+  cudaError_t e = own_configure();
+  if (e != cudaSuccess) return e;
+  TileGemm t{A, sA, lda, B, sB, ldb, C, sC, ldc, mt, nt, kchunks, nn, lower_only, batch};
+  return launch_gemm(st, sm_count, t);
+}
+
 cudaError_t own_chunk(cudaStream_t st, const OwnGeom& g, const OwnBufs& b, int Rc, int sm_count, const cuDoubleComplex* FSFT,
                       const double* beam_power_el, const void* K, int k_cplx, const void* C, int c_cplx, const unsigned char* M,
                       const cuDoubleComplex* rn, const double* prior, const double* window, float2* outd, int* info,

@@ -43,4 +43,11 @@ cudaError_t own_chunk(cudaStream_t st, const OwnGeom& g, const OwnBufs& b, int R
                       const cuDoubleComplex* rn, const double* prior, const double* window, float2* outd, int* info,
                       int64_t* launches);
 
+// The tile GEMM by itself (used by the NRML objective, nrml_own.cu): C[b] = A[b] B[b] (nn = 1; A [M][K] pitch lda,
+// B [K][N] pitch ldb) or A[b] B[b]^T (nn = 0; B [N][K], both with pitch lda) over mt x nt output tiles of 128 x 128, K =
+// 32 kchunks; every dimension a multiple of 128 / 32 (zero-padded buffers).  lower_only: C holds complex entries
+// interleaved along its rows and only the tiles that touch its lower triangle are formed.
+cudaError_t own_gemm(cudaStream_t st, int sm_count, const double* A, long long sA, int lda, const double* B, long long sB, int ldb,
+                     double* C, long long sC, int ldc, int mt, int nt, int kchunks, int nn, int lower_only, int batch);
+
 }  // namespace dgw
