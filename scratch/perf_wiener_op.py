@@ -34,7 +34,10 @@ def run(F, nra, nel, cplx, cpu_pixels):
     freq, weight, beam, filt, cov, win, S, tau, ntau = problem(F, nra, nel, cplx)
     Fm = wo.fourier_operator(freq, tau, ntau)
     res = {"F": F, "ndelay": int(tau.size), "nra": nra, "nel": nel, "complex_inputs": cplx}
-    for solver, label in ((1, "batched"), (2, "streams"), (3, "own_kernels")):
+    solvers = ((1, "batched"), (2, "streams"), (3, "own_kernels"))
+    if os.environ.get("PERF_WIENER_ONLY"):  # e.g. PERF_WIENER_ONLY=3 for a launch list of the own-kernel path alone
+        solvers = tuple(x for x in solvers if str(x[0]) == os.environ["PERF_WIENER_ONLY"])
+    for solver, label in solvers:
         best = None
         for rep in range(3):
             t = {}
@@ -47,6 +50,9 @@ def run(F, nra, nel, cplx, cpu_pixels):
                       "wall_ms": round(best["wall_ms"], 2),
                       "us_per_pixel": round(best["ms_compute"] * 1e3 / (nra * nel), 2),
                       "tflops": round(best["flop"] / best["ms_compute"] / 1e9, 2), "launches": best["launches"]}
+    if os.environ.get("PERF_WIENER_ONLY"):
+        print(json.dumps(res), flush=True)
+        return
     # oracle on the host (numpy + LAPACK, all BLAS threads), a bounded number of pixels
     nr = max(1, min(nra, cpu_pixels))
     t0 = time.perf_counter()
