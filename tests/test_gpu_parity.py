@@ -143,8 +143,8 @@ def test_cfg1_geometry_full_chain(gibbs):
 
 
 def test_cfg2_geometry_short_chain(gibbs):
-    """BASELINE config 2/4 geometry (N=2048, M=1024, T=64, non-uniform weights): 2 baselines x 3
-    iterations against the oracle with injected draws."""
+    """BASELINE config 2/4 geometry (N=2048, M=1024, T=64, non-uniform weights): 4 baselines x 6
+    iterations against the oracle with injected draws, on single CTAs and on clusters of 2."""
     from draco_b200 import synth
 
     cfg = synth.CONFIGS["cfg2"]
@@ -152,25 +152,30 @@ def test_cfg2_geometry_short_chain(gibbs):
     delays, chan = oracle.calculate_delays(freq)
     N = len(delays)
     assert N == 2048
-    niter = 3
+    niter, nb = 6, 4
+    freq, vis, wgt = synth.make_stack(cfg, nbase=nb)
     datas, Nis, fsels, refs, draws = [], [], [], [], []
-    for b in range(2):
+    for b in range(nb):
         d, w, nzf, _ = oracle.cut_data(vis[b], wgt[b])
         s, ok, dr = recorded_chain(d, N, w, np.full(N, 10.0), cfg.window, chan[nzf], niter, False, seed=400 + b)
+        assert ok
         datas.append(d); Nis.append(w); fsels.append(chan[nzf]); refs.append(s); draws.append(dr)
-    pb = gibbs.pack_batch(datas, Nis, fsels, N, np.full((2, N), 10.0), window=cfg.window)
-    res = gibbs.run_batch(pb, niter, draws=gibbs.pack_draws(pb, niter, *zip(*draws)), save_samples=True)
-    for b in range(2):
+    pb = gibbs.pack_batch(datas, Nis, fsels, N, np.full((nb, N), 10.0), window=cfg.window)
+    packed = gibbs.pack_draws(pb, niter, *zip(*draws))
+    res = gibbs.run_batch(pb, niter, draws=packed, save_samples=True, cluster_size=1)
+    for b in range(nb):
         np.testing.assert_allclose(res.samples[:, b], refs[b], rtol=RTOL_SAMPLES)
+    res2 = gibbs.run_batch(pb, niter, draws=packed, save_samples=True, cluster_size=2)
+    assert np.array_equal(res2.samples, res.samples)
 
 
 def test_cfg5_geometry_short_chain(gibbs):
     """BASELINE config 5 geometry (N=4096, M~1229, T=16, 40 % of the channels flagged in contiguous RFI-like bands,
-    non-uniform weights): 2 baselines from different mask blocks x 2 iterations against the oracle with injected draws."""
+    non-uniform weights): 2 baselines from different mask blocks x 3 iterations against the oracle with injected draws."""
     from draco_b200 import synth
 
     cfg = synth.CONFIGS["cfg5"]
-    niter = 2
+    niter = 3
     datas, Nis, fsels, refs, draws = [], [], [], [], []
     for b, off in enumerate((0, 500)):  # the masks are redrawn per block of 500 baselines
         freq, vis, wgt = synth.make_stack(cfg, nbase=1, base_offset=off)
@@ -208,6 +213,29 @@ def test_device_resident_equals_host_path(gibbs):
     sub = gibbs.pack_batch(datas[2:4], Nis[2:4], fsels[2:4], 128, np.full((2, 128), 10.0), global_id=np.array([19, 20]))
     c = gibbs.run_batch(sub, 4, seed=3, save_samples=True)
     assert np.array_equal(c.samples, a.samples[:, 2:4])
+
+
+@pytest.mark.parametrize("ways", [2, 4, 8])
+def test_results_do_not_depend_on_the_number_of_shards(gibbs, ways):
+    """One batch of 24 ragged baselines run whole and as 2 / 4 / 8 contiguous shards (`dist.split_range`, the layout
+    of 1 / 2 / 4 / 8 ranks): bit-identical samples and spectra -- the Philox key is the global baseline id."""
+    from draco_b200 import dist as ddist
+
+    nb, N, niter = 24, 128, 5
+    datas, Nis, fsels = [], [], []
+    for i in range(nb):
+        data, Ni, fsel, _ = make_case(N, 38 + (i % 7), 5 + (i % 3), False, False, seed=50 + i)
+        datas.append(data); Nis.append(Ni); fsels.append(fsel)
+    gid = np.arange(nb) + 1000
+    whole = gibbs.run_batch(gibbs.pack_batch(datas, Nis, fsels, N, np.full((nb, N), 10.0), global_id=gid), niter, seed=8,
+                            save_samples=True)
+    assert whole.success.all()
+    for r in range(ways):
+        lo, hi = ddist.split_range(nb, ways, r)
+        part = gibbs.run_batch(gibbs.pack_batch(datas[lo:hi], Nis[lo:hi], fsels[lo:hi], N, np.full((hi - lo, N), 10.0),
+                                                global_id=gid[lo:hi]).to_device(0), niter, seed=8, save_samples=True)
+        assert np.array_equal(part.samples.cpu().numpy(), whole.samples[:, lo:hi])
+        assert np.array_equal(part.spectrum.cpu().numpy(), whole.spectrum[lo:hi])
 
 
 def test_philox_posterior_statistics(gibbs):
