@@ -871,17 +871,29 @@ struct CholWS {
   int npad, nblk, RT, rhs_frags;
 };
 
+// The NT update of one tile, acc -= W[rowA : rowA+128, 0 : kcols] W[rowB : rowB+128, 0 : kcols]^T with W = the slot's
+// workspace (the RHS rows follow the npad rows of L), is a policy: per-thread cp.async staging here, the TMA + mbarrier
+// ring in tma_pipe.cuh (NtTma).
+struct NtCpAsync {
+  const double* Wk;
+  double* pipe;
+  int npad;
+  __device__ __forceinline__ void operator()(Acc& acc, const Lane& ln, int rowA, int rowB, int kcols, int variant) {
+    gemm_nt(pipe, acc, ln, Wk + (size_t)rowA * npad, Wk + (size_t)rowB * npad, npad, kcols / KC, variant);
+  }
+};
+
 // Left-looking blocked Cholesky of the matrix whose 128x128 tiles `gen(sT, ti, tj, lower_only)` ADDS
 // into a staged tile, with the RHS rows riding along as extra row tiles (forward solve).  Returns false
-// on a non-positive pivot (LAPACK dpotrf semantics).  Every thread of the CTA must call it.
-template <class Gen>
-__device__ __forceinline__ bool chol_factor_forward(const CholWS& w, const Lane& ln, const Gen& gen) {
+// on a non-positive pivot (LAPACK dpotrf semantics).  Every thread of the CTA must call it.  w.Rh must be
+// w.Wk + npad * npad (one contiguous workspace).
+template <class Gen, class NT>
+__device__ __forceinline__ bool chol_factor_forward(const CholWS& w, const Lane& ln, const Gen& gen, NT& nt) {
   Acc acc;
   const int npad = w.npad, nblk = w.nblk;
   for (int j = 0; j < nblk; j++) {
-    const double* Bp = w.Wk + (size_t)j * TILE * npad;
     acc_zero(acc);
-    gemm_nt(w.pipe, acc, ln, Bp, Bp, npad, j * (TILE / KC), ln.warp < 4 ? V_DIAG_LO : V_DIAG_HI);
+    nt(acc, ln, j * TILE, j * TILE, j * TILE, ln.warp < 4 ? V_DIAG_LO : V_DIAG_HI);
     stage_acc(acc, w.pipe, ln, true, true);
     __syncthreads();
     gen(w.pipe, j, j, true);
@@ -905,8 +917,7 @@ __device__ __forceinline__ bool chol_factor_forward(const CholWS& w, const Lane&
       }
       const int var = rhs_variant(do0, do1);
       acc_zero(acc);
-      gemm_nt(w.pipe, acc, ln, i < nblk ? w.Wk + (size_t)i * TILE * npad : w.Rh + (size_t)(i - nblk) * TILE * npad, Bp, npad,
-              j * (TILE / KC), var);
+      nt(acc, ln, i * TILE, j * TILE, j * TILE, var);
       stage_acc(acc, w.pipe, ln, do0, do1);
       __syncthreads();
       if (i < nblk) gen(w.pipe, i, j, false);
@@ -919,6 +930,11 @@ __device__ __forceinline__ bool chol_factor_forward(const CholWS& w, const Lane&
     }
   }
   return true;
+}
+template <class Gen>
+__device__ __forceinline__ bool chol_factor_forward(const CholWS& w, const Lane& ln, const Gen& gen) {
+  NtCpAsync nt{w.Wk, w.pipe, w.npad};
+  return chol_factor_forward(w, ln, gen, nt);
 }
 
 // Backward solve  x^T = z^T L^-1  on the RHS rows, in place.

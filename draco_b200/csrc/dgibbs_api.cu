@@ -557,7 +557,14 @@ static int run_core(dgibbs_handle h, const dgibbs_problem* p, dgibbs_result* r, 
     DevBatch df = d;
     df.blist = d_freq;
     df.nlist = (int)freq_list.size();
-    CU(launch_freq_sampler(df, 0, d.niter, h->stream));
+    // one tensor map serves the list when every chain pads its 2M system to the same size
+    int npt = 0;
+    for (int b : freq_list) {
+      const int n = (2 * s.M[b] + TILE - 1) / TILE * TILE;
+      npt = (npt == 0 || npt == n) ? n : -1;
+      if (npt < 0) break;
+    }
+    CU(launch_freq_sampler(df, 0, d.niter, h->stream, npt > 0 ? npt : 0));
     h->timing.launches++;
     h->timing.sampler_launches++;
   }

@@ -132,7 +132,8 @@ cudaError_t launch_diag_sampler(const DevBatch& d, int it_begin, int it_end, int
 bool diag_project_fft_fits(const DevBatch& d);
 cudaError_t launch_diag_project_fft(const DevBatch& d, int sm_count, cudaStream_t st);
 bool freq_branch_fits(const DevBatch& d, int M, int T);
-cudaError_t launch_freq_sampler(const DevBatch& d, int it_begin, int it_end, cudaStream_t st);
+// uniform_npt: the padded 2M system size shared by every chain of d.blist (feeds the TMA operand ring), or 0
+cudaError_t launch_freq_sampler(const DevBatch& d, int it_begin, int it_end, cudaStream_t st, int uniform_npt);
 
 // finish_kernels.cu
 cudaError_t launch_finish(const DevBatch& d, const double* S0, double median_frac, double* spectrum,

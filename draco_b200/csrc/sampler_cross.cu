@@ -21,6 +21,8 @@
 
 #include "../../include/dgibbs.h"
 #include "dense_core.cuh"
+#include "tma_host.h"
+#include "tma_pipe.cuh"
 
 namespace dg {
 
@@ -234,7 +236,8 @@ struct CrossGen {
 
 // ----------------------------------------------------------------------------- the sampler
 // Shared memory: [sWp: WP_DOUBLES][pipe: PIPE_DOUBLES][misc]
-__global__ void __launch_bounds__(THREADS, 1) cross_sampler_kernel(CrossBatch d) {
+__global__ void __launch_bounds__(THREADS, 1)
+    cross_sampler_kernel(CrossBatch d, int use_tma, const __grid_constant__ CUtensorMap tmap) {
   extern __shared__ __align__(16) double smem[];
   const Lane ln;
   const int slot = blockIdx.x;
@@ -243,6 +246,10 @@ __global__ void __launch_bounds__(THREADS, 1) cross_sampler_kernel(CrossBatch d)
   double* pipe = sWp + WP_DOUBLES;
   double* misc = pipe + PIPE_DOUBLES;
   int* flag = reinterpret_cast<int*>(misc + 8);
+  // operand ring of the factorisation's NT updates (tma_pipe.cuh); cp.async loaders when the host found no tensor map
+  TmaRing ring;
+  if (use_tma) tma_ring_init(ring, reinterpret_cast<unsigned long long*>(misc + MISC_DOUBLES));
+  NtTma nt_tma{&tmap, &ring, pipe, slot};
 
   CholWS ws;
   const size_t wrows = (size_t)npad + (size_t)d.RT * TILE;
@@ -363,7 +370,7 @@ __global__ void __launch_bounds__(THREADS, 1) cross_sampler_kernel(CrossBatch d)
         }
       __syncthreads();
       // ---- 3. Cholesky solve of the real embedding (delay.py:2047-2058)
-      bool alive = chol_factor_forward(ws, ln, gen);
+      const bool alive = use_tma ? chol_factor_forward(ws, ln, gen, nt_tma) : chol_factor_forward(ws, ln, gen);
       if (!alive) {
         __syncthreads();
         if (threadIdx.x == 0) *flag = 1;
@@ -538,9 +545,11 @@ extern "C" int dgibbs_cross_run(dgibbs_handle h, const dgibbs_cross_problem* p, 
   cross_setup_kernel<<<d.B, 256, 0, st>>>(d);
   XCU(cudaGetLastError());
   if (d.niter > 0) {
-    const size_t smem = sizeof(double) * (WP_DOUBLES + PIPE_DOUBLES + MISC_DOUBLES);
+    const size_t smem = sizeof(double) * (WP_DOUBLES + PIPE_DOUBLES + MISC_DOUBLES + 2 * TNST);
     XCU(cudaFuncSetAttribute(cross_sampler_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    cross_sampler_kernel<<<d.nslots, THREADS, smem, st>>>(d);
+    CUtensorMap tm;
+    const int use_tma = tma_work_map(&tm, d.work, wrows, d.npad, wrows * d.npad, d.nslots, sizeof(double) * WP_DOUBLES, TILE, TKC);
+    cross_sampler_kernel<<<d.nslots, THREADS, smem, st>>>(d, use_tma, tm);
     XCU(cudaGetLastError());
   }
   std::vector<int> failed(B);

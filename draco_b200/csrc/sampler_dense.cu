@@ -31,6 +31,7 @@
 #include <cstring>
 
 #include "dense_core.cuh"
+#include "tma_host.h"
 #include "tma_pipe.cuh"
 
 #ifndef DGIBBS_COST_C2
@@ -400,40 +401,15 @@ cudaError_t dense_configure(const DevBatch& d) {
   return cudaFuncSetAttribute(dense_sampler_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
 }
 
-// ---- tensor map of the chain workspaces (tma_pipe.cuh): (k mod 4, row, k div 4, slot)
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
-                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
-                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-static EncodeTiledFn encode_fn() {
-  static EncodeTiledFn fn = []() -> EncodeTiledFn {
-    void* p = nullptr;
-    cudaDriverEntryPointQueryResult qr;
-    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qr) != cudaSuccess ||
-        qr != cudaDriverEntryPointSuccess) {
-      cudaGetLastError();
-      return nullptr;
-    }
-    return (EncodeTiledFn)p;
-  }();
-  return fn;
-}
-
+// ---- tensor map of the chain workspaces (tma_pipe.cuh / tma_host.h): (k mod 4, row, k div 4, slot)
 // true: `tm` describes d.work for the TMA ring; false: this geometry keeps the cp.async loaders
 static bool make_work_tensor_map(const DevBatch& d, CUtensorMap* tm) {
-  memset(tm, 0, sizeof *tm);
-  static const bool off = getenv("DGIBBS_NO_TMA") != nullptr;
-  if (off || d.project_only) return false;
+  if (d.project_only) {
+    memset(tm, 0, sizeof *tm);
+    return false;
+  }
   const size_t ring_off = sizeof(double) * ((d.ctab_smem ? (size_t)d.nsys : 0) + WP_DOUBLES);
-  if (ring_off % 128 != 0 || (d.work_stride * sizeof(double)) % 16 != 0 || ((uintptr_t)d.work) % 16 != 0) return false;
-  EncodeTiledFn enc = encode_fn();
-  if (!enc) return false;
-  const cuuint64_t wrows = (cuuint64_t)d.npad + (cuuint64_t)d.RT * TILE;
-  const cuuint64_t dims[4] = {4, wrows, (cuuint64_t)d.npad / 4, (cuuint64_t)d.nslots};
-  const cuuint64_t strides[3] = {(cuuint64_t)d.npad * sizeof(double), 4 * sizeof(double), (cuuint64_t)d.work_stride * sizeof(double)};
-  const cuuint32_t box[4] = {4, TILE, TKC / 4, 1};
-  const cuuint32_t estr[4] = {1, 1, 1, 1};
-  return enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 4, d.work, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-             CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+  return tma_work_map(tm, d.work, (size_t)d.npad + (size_t)d.RT * TILE, d.npad, d.work_stride, d.nslots, ring_off, TILE, TKC);
 }
 
 template <int C>

@@ -14,6 +14,8 @@
 //   S' = var_s(d) T / chi2                     moments accumulated on the fly: d is never stored
 // Only the 2M-sized system touches HBM: (2M)^3 / 3 flop instead of N^3 / 3 (>= 8x fewer).
 #include "dense_core.cuh"
+#include "tma_host.h"
+#include "tma_pipe.cuh"
 
 namespace dg {
 
@@ -55,7 +57,8 @@ struct FreqGen {
 };
 
 // Shared memory: [sWp: WP_DOUBLES][pipe: PIPE_DOUBLES][misc]
-__global__ void __launch_bounds__(THREADS, 1) freq_sampler_kernel(DevBatch d, int it_begin, int it_end) {
+__global__ void __launch_bounds__(THREADS, 1)
+    freq_sampler_kernel(DevBatch d, int it_begin, int it_end, int use_tma, const __grid_constant__ CUtensorMap tmap) {
   extern __shared__ __align__(16) double smem[];
   const Lane ln;
   const int slot = blockIdx.x;
@@ -66,6 +69,11 @@ __global__ void __launch_bounds__(THREADS, 1) freq_sampler_kernel(DevBatch d, in
   double2* bufA = reinterpret_cast<double2*>(pipe);
   double2* bufB = bufA + N;
   double2* tw_s = reinterpret_cast<double2*>(sWp);
+  // operand ring of the factorisation's NT updates (tma_pipe.cuh); the host passes a tensor map only when every chain
+  // of the list has the same padded system size (the map's row pitch)
+  TmaRing ring;
+  if (use_tma) tma_ring_init(ring, reinterpret_cast<unsigned long long*>(misc + MISC_DOUBLES));
+  NtTma nt_tma{&tmap, &ring, pipe, slot};
 
   const size_t wrows_full = (size_t)d.npad + (size_t)d.RT * TILE;
   double* Wk = d.work + (size_t)slot * d.work_stride;  // the slot's delay-space workspace is large enough
@@ -184,7 +192,7 @@ __global__ void __launch_bounds__(THREADS, 1) freq_sampler_kernel(DevBatch d, in
         __syncthreads();
       }
       // ---- x = Ci^-1 y   (delay.py:1851-1858)
-      alive = chol_factor_forward(ws, ln, gen);
+      alive = use_tma ? chol_factor_forward(ws, ln, gen, nt_tma) : chol_factor_forward(ws, ln, gen);
       if (!alive) {
         __syncthreads();
         if (threadIdx.x == 0) {
@@ -285,13 +293,20 @@ bool freq_branch_fits(const DevBatch& d, int M, int T) {
   return npt <= (size_t)d.npad;  // L and the RHS of the 2M system fit the slot; Sh w1 has its own tail
 }
 
-cudaError_t launch_freq_sampler(const DevBatch& d, int it_begin, int it_end, cudaStream_t st) {
+cudaError_t launch_freq_sampler(const DevBatch& d, int it_begin, int it_end, cudaStream_t st, int uniform_npt) {
   if (d.nlist <= 0) return cudaSuccess;
-  const size_t smem = sizeof(double) * (WP_DOUBLES + PIPE_DOUBLES + MISC_DOUBLES);
+  const size_t smem = sizeof(double) * (WP_DOUBLES + PIPE_DOUBLES + MISC_DOUBLES + 2 * TNST);
   cudaError_t e = cudaFuncSetAttribute(freq_sampler_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   const int grid = d.nlist < d.nslots ? d.nlist : d.nslots;
-  freq_sampler_kernel<<<grid, THREADS, smem, st>>>(d, it_begin, it_end);
+  CUtensorMap tm;
+  int use_tma = 0;
+  if (uniform_npt > 0)
+    use_tma = tma_work_map(&tm, d.work, (size_t)uniform_npt + (size_t)d.RT * TILE, uniform_npt, d.work_stride, d.nslots,
+                           sizeof(double) * WP_DOUBLES, TILE, TKC);
+  else
+    memset(&tm, 0, sizeof tm);
+  freq_sampler_kernel<<<grid, THREADS, smem, st>>>(d, it_begin, it_end, use_tma, tm);
   return cudaGetLastError();
 }
 

@@ -160,4 +160,15 @@ __device__ __forceinline__ void gemm_nt_tma(const CUtensorMap* tm, TmaRing& R, d
   __syncthreads();
 }
 
+// NT-update policy of chol_factor_forward (dense_core.cuh) on the ring
+struct NtTma {
+  const CUtensorMap* tm;
+  TmaRing* R;
+  double* ring;
+  int slot;
+  __device__ __forceinline__ void operator()(Acc& acc, const Lane& ln, int rowA, int rowB, int kcols, int variant) {
+    gemm_nt_tma(tm, *R, ring, acc, ln, slot, rowA, rowB, kcols / TKC, variant);
+  }
+};
+
 }  // namespace dg

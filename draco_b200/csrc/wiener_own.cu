@@ -24,6 +24,8 @@
 #include <cstdlib>
 
 #include "dense_core.cuh"
+#include "tma_host.h"
+#include "tma_pipe.cuh"
 
 namespace dgw {
 using namespace dg;
@@ -202,7 +204,8 @@ struct EmbedGen {
   }
 };
 
-__global__ void __launch_bounds__(THREADS, 1) own_solve_kernel(SolveArgs a) {
+__global__ void __launch_bounds__(THREADS, 1)
+    own_solve_kernel(SolveArgs a, int use_tma, const __grid_constant__ CUtensorMap tmap) {
   extern __shared__ __align__(16) double smem[];
   const Lane ln;
   CholWS w;
@@ -216,6 +219,10 @@ __global__ void __launch_bounds__(THREADS, 1) own_solve_kernel(SolveArgs a) {
   w.Wk = a.work + (size_t)blockIdx.x * a.work_stride;
   w.Rh = w.Wk + (size_t)a.LD * a.LD;
   w.Wpg = a.Wp + (size_t)blockIdx.x * a.nblk * WP_DOUBLES;
+  // operand ring of the factorisation's NT updates (tma_pipe.cuh)
+  TmaRing ring;
+  if (use_tma) tma_ring_init(ring, reinterpret_cast<unsigned long long*>(w.misc + MISC_DOUBLES));
+  NtTma nt_tma{&tmap, &ring, w.pipe, (int)blockIdx.x};
   const int half = a.LD / 2;
   // rows of the right-hand-side tiles that no pixel ever writes: keep them finite (they are staged, never used)
   for (long long e = threadIdx.x; e < (long long)a.RT * TILE * half; e += THREADS)
@@ -233,7 +240,7 @@ __global__ void __launch_bounds__(THREADS, 1) own_solve_kernel(SolveArgs a) {
     }
     __syncthreads();
     EmbedGen gen{a.Ar + (size_t)r * a.sAr, a.F, a.LD};
-    const bool ok = chol_factor_forward(w, ln, gen);  // CTA-uniform
+    const bool ok = use_tma ? chol_factor_forward(w, ln, gen, nt_tma) : chol_factor_forward(w, ln, gen);  // CTA-uniform
     if (!ok) {
       if (threadIdx.x == 0) a.info[r] = 1;
       continue;
@@ -255,7 +262,7 @@ __global__ void __launch_bounds__(THREADS, 1) own_solve_kernel(SolveArgs a) {
 
 // ------------------------------------------------------------------------------------------------ host
 static size_t gemm_smem() { return sizeof(double) * PIPE_DOUBLES; }
-static size_t solve_smem() { return sizeof(double) * (WP_DOUBLES + PIPE_DOUBLES + MISC_DOUBLES); }
+static size_t solve_smem() { return sizeof(double) * (WP_DOUBLES + PIPE_DOUBLES + MISC_DOUBLES + 2 * TNST); }
 
 cudaError_t own_configure() {
   cudaError_t e = cudaFuncSetAttribute(own_tile_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gemm_smem());
@@ -326,7 +333,10 @@ cudaError_t own_chunk(cudaStream_t st, const OwnGeom& g, const OwnBufs& b, int R
   mark();
   SolveArgs a{b.Ar, z.Ar, b.Yr, z.Yr, b.work, g.work_stride, b.Wp, prior, window, M, outd, info, Rc, g.F, g.nd, g.LD, g.nblk, g.RT};
   const int grid = Rc < g.nslots ? Rc : g.nslots;
-  own_solve_kernel<<<grid, THREADS, solve_smem(), st>>>(a);
+  CUtensorMap tm;
+  const int use_tma = tma_work_map(&tm, b.work, (size_t)g.LD + (size_t)g.RT * TILE, g.LD, g.work_stride, g.nslots,
+                                   sizeof(double) * WP_DOUBLES, TILE, TKC);
+  own_solve_kernel<<<grid, THREADS, solve_smem(), st>>>(a, use_tma, tm);
   if ((e = cudaGetLastError()) != cudaSuccess) return e;
   mark();
   if (prof) {
