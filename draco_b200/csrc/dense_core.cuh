@@ -447,6 +447,116 @@ __device__ __forceinline__ void trisolve(double* sT, const double* sWp, const La
     default: break;
   }
 }
+// ----------------------------------------------------------------------------- triangular solve in registers
+// The same solves on the ACCUMULATOR registers (the tile as the GEMM left it: lane (g, q) holds columns 2q, 2q+1 of row g
+// of every 8x8 block), right-looking: once block column p is solved it is applied to the blocks behind it, which are
+// independent of each other -- the tile makes no round trip through shared memory, there is no __syncwarp, and the only
+// dependent chain is  quad shuffle -> 2 DMMA (W8_p) -> quad shuffle -> 2 DMMA  per block column.  The staged form above
+// ran at ~10 cycles per DMMA (shared-memory read-modify-write of the tile, 30-cycle load latency in front of every
+// k-step) against 4.3 in the GEMM loops (profiles/r02x_upd_probe.log).
+#ifndef DGIBBS_TRISOLVE_REG
+#define DGIBBS_TRISOLVE_REG 1
+#endif
+// accumulator layout -> A-operand layout of one 8x8 block: lane (g, q) gets entries (g, q) and (g, q + 4)
+struct QuadXpose {
+  int s0, s1;
+  bool odd;
+  __device__ QuadXpose() {
+    const int lane = threadIdx.x & 31, q = lane & 3;
+    s0 = (lane & ~3) | (q >> 1);
+    s1 = s0 + 2;
+    odd = q & 1;
+  }
+  __device__ __forceinline__ void operator()(double c0, double c1, double& a0, double& a1) const {
+    const double u0 = __shfl_sync(0xffffffffu, c0, s0), u1 = __shfl_sync(0xffffffffu, c1, s0);
+    const double v0 = __shfl_sync(0xffffffffu, c0, s1), v1 = __shfl_sync(0xffffffffu, c1, s1);
+    a0 = odd ? u1 : u0;
+    a1 = odd ? v1 : v0;
+  }
+};
+// acc <- acc * inv(L_jj)^T   (forward; NN = false)    or    acc <- acc * inv(L_jj)   (backward; NN = true)
+template <bool NN, bool D0, bool D1>
+__device__ __forceinline__ void trisolve_reg_body(Acc& acc, const double* sWp, const Lane& ln) {
+  const int g = ln.g, q = ln.q;
+  const int bo0 = NN ? q * 8 + (g ^ wp_swz(q)) : g * 8 + (q ^ wp_swz(g));
+  const int bo1 = NN ? (4 + q) * 8 + (g ^ wp_swz(4 + q)) : g * 8 + ((4 + q) ^ wp_swz(g));
+  const QuadXpose xp;
+#pragma unroll
+  for (int pp = 0; pp < 16; pp++) {
+    const int p = NN ? 15 - pp : pp;
+    const double* w8 = sWp + wp_block(p, p);
+    const double wb0 = w8[bo0], wb1 = w8[bo1];
+    double a[2][2];
+#pragma unroll
+    for (int f = 0; f < 2; f++) {
+      if (f == 0 ? !D0 : !D1) continue;
+      double x0, x1;
+      xp(acc[f][p][0], acc[f][p][1], x0, x1);
+      double o0 = 0.0, o1 = 0.0, e0 = 0.0, e1 = 0.0;
+      dmma(o0, o1, x0, wb0);
+      dmma(e0, e1, x1, wb1);
+      o0 += e0;
+      o1 += e1;
+      acc[f][p][0] = o0;
+      acc[f][p][1] = o1;
+      xp(o0, o1, a[f][0], a[f][1]);
+      a[f][0] = -a[f][0];
+      a[f][1] = -a[f][1];
+    }
+#pragma unroll
+    for (int nn = 1; nn < 16; nn++) {
+      if (nn > 15 - pp) continue;  // blocks behind column p: p+1 .. 15 (forward), p-1 .. 0 (backward)
+      const int nb = NN ? p - nn : p + nn;
+      const double* lb = sWp + (NN ? wp_block(p, nb) : wp_block(nb, p));
+      const double b0 = lb[bo0], b1 = lb[bo1];
+      if (D0) {
+        dmma(acc[0][nb][0], acc[0][nb][1], a[0][0], b0);
+        dmma(acc[0][nb][0], acc[0][nb][1], a[0][1], b1);
+      }
+      if (D1) {
+        dmma(acc[1][nb][0], acc[1][nb][1], a[1][0], b0);
+        dmma(acc[1][nb][0], acc[1][nb][1], a[1][1], b1);
+      }
+    }
+  }
+}
+template <bool NN>
+__device__ __forceinline__ void trisolve_reg(Acc& acc, const double* sWp, const Lane& ln, int variant) {
+  switch (variant) {  // warp-uniform
+    case V_FULL: trisolve_reg_body<NN, true, true>(acc, sWp, ln); break;
+    case V_ROW0: trisolve_reg_body<NN, true, false>(acc, sWp, ln); break;
+    case V_ROW1: trisolve_reg_body<NN, false, true>(acc, sWp, ln); break;
+    default: break;
+  }
+}
+// acc += the circulant entries of an interior tile strictly below the diagonal (stage_acc_circ without the staging)
+__device__ __forceinline__ void acc_add_circ(Acc& acc, const Lane& ln, const double* cwin) {
+#pragma unroll
+  for (int f = 0; f < 2; f++) {
+    const int r = ln.rf[f] * 8 + ln.g;
+    const double* cp = cwin + TILE + r - 2 * ln.q;
+#pragma unroll
+    for (int nb = 0; nb < 16; nb++) {
+      acc[f][nb][0] += cp[-nb * 8];
+      acc[f][nb][1] += cp[-nb * 8 - 1];
+    }
+  }
+}
+// acc += tile at `base` (row pitch ld) for the fragments that are in use
+__device__ __forceinline__ void acc_add_global(Acc& acc, const double* base, int ld, const Lane& ln, bool do0, bool do1) {
+#pragma unroll
+  for (int f = 0; f < 2; f++) {
+    if (f == 0 ? !do0 : !do1) continue;
+    const double* row = base + (size_t)(ln.rf[f] * 8 + ln.g) * ld + 2 * ln.q;
+#pragma unroll
+    for (int nb = 0; nb < 16; nb++) {
+      const double2 v = *reinterpret_cast<const double2*>(row + nb * 8);
+      acc[f][nb][0] += v.x;
+      acc[f][nb][1] += v.y;
+    }
+  }
+}
+
 // staged tile rows [r0, r1) -> global (row pitch ld), coalesced
 __device__ __forceinline__ void copy_tile_out(const double* sT, double* dst, int ld, int r1, int r0 = 0) {
   for (int e = r0 * (TILE / 2) + threadIdx.x; e < r1 * (TILE / 2); e += THREADS) {
@@ -720,7 +830,168 @@ static __device__ void project_rows_fft(const DevBatch& d, const DrawCtx& c, dou
 }
 
 // ----------------------------------------------------------------------------- diagonal tile
-// In-place blocked Cholesky of the staged 128x128 tile (lower) by 8-column panels.  Per panel p:
+#ifndef DGIBBS_FACTOR_LOOKAHEAD
+#define DGIBBS_FACTOR_LOOKAHEAD 1
+#endif
+// 8x8 Cholesky of block (p, p) of the staged tile and its inverse W8_p, in registers: every lane of the calling warp
+// computes the same values (identical-value stores).  W8_p goes to the diagonal slot p of sWp (bank-swizzled).
+// Returns false on a non-positive pivot (same test as LAPACK dpotrf: ajj <= 0 or NaN).
+__device__ __forceinline__ bool pivot_block(const double* sT, double* sWp, int p) {
+  double a[8][8], w[8][8], rinv[8];
+  bool ok = true;
+#pragma unroll
+  for (int i = 0; i < 8; i++)
+#pragma unroll
+    for (int c = 0; c <= i; c++) a[i][c] = sT[(8 * p + i) * LDW + 8 * p + c];
+#pragma unroll
+  for (int k = 0; k < 8; k++) {
+    double dk = a[k][k];
+    if (!(dk > 0.0)) ok = false;
+    const double r = rsqrt(dk);  // one reciprocal square root instead of sqrt + division on the serial chain
+    const double piv = dk * r;
+    rinv[k] = r;
+    a[k][k] = piv;
+#pragma unroll
+    for (int i = k + 1; i < 8; i++) a[i][k] *= r;
+#pragma unroll
+    for (int c = k + 1; c < 8; c++)
+#pragma unroll
+      for (int i = c; i < 8; i++) a[i][c] -= a[i][k] * a[c][k];
+  }
+#pragma unroll
+  for (int c = 0; c < 8; c++) {
+    w[c][c] = rinv[c];
+#pragma unroll
+    for (int i = c + 1; i < 8; i++) {
+      double s = 0.0;
+#pragma unroll
+      for (int k = c; k < i; k++) s += a[i][k] * w[k][c];
+      w[i][c] = -s * rinv[i];
+    }
+  }
+  double* wpp = sWp + wp_block(p, p);
+#pragma unroll
+  for (int i = 0; i < 8; i++)
+#pragma unroll
+    for (int c = 0; c < 8; c++) wpp[i * 8 + (c ^ wp_swz(i))] = (c <= i) ? w[i][c] : 0.0;
+  return ok;
+}
+
+// named barrier 1 of the CTA (barrier 0 is __syncthreads): warp 0 arrives, warps 1.. wait
+__device__ __forceinline__ void bar1_arrive() { asm volatile("bar.arrive 1, %0;" ::"n"(THREADS) : "memory"); }
+__device__ __forceinline__ void bar1_sync() { asm volatile("bar.sync 1, %0;" ::"n"(THREADS) : "memory"); }
+
+#ifndef FD_T  // timing hooks of scratch/factor_probe.cu
+#define FD_T(k)
+#define FD_DECL
+#endif
+#if DGIBBS_FACTOR_LOOKAHEAD
+// In-place blocked Cholesky of the staged 128x128 tile (lower) by 8-column panels, right-looking with a look-ahead of one
+// panel: the 8x8 pivot factorisation is a serial chain of 8 reciprocal square roots that one warp computes, so warp 0
+// runs AHEAD -- as soon as panel p's pivot block is inverted it solves block (p+1, p), updates block (p+1, p+1) and
+// factors it, while warps 1..7 solve the rest of panel p and apply it to the trailing blocks.  Per panel p:
+//   warp 0      : L(p+1,p) = C(p+1,p) W8_p^T;  [arrive]  C(p+1,p+1) -= L(p+1,p) L(p+1,p)^T;  W8_{p+1} = inv(chol(C(p+1,p+1)))
+//   warps 1..7  : L(rb,p) = C(rb,p) W8_p^T (rb > p+1);  [wait]  C(rb,cb) -= L(rb,p) L(cb,p)^T  (rb >= cb > p, not (p+1,p+1))
+// The left-looking form (DGIBBS_FACTOR_LOOKAHEAD=0) put three CTA barriers and the idle time of seven warps on every
+// pivot block: 31 us per tile, a third of the kernel at N = 256 (profiles/r02m_phase_cycles_cfg1.log).
+// On exit sWp holds L_jj packed by 8x8 blocks (bank-swizzled; written as the blocks are solved) with W8_p in the
+// diagonal slots.
+// Returns false on a non-positive pivot.
+static __device__ bool factor_diag(double* sT, double* sWp, double* misc, const Lane& ln) {
+  (void)misc;
+  const int g = ln.g, q = ln.q;
+  const int bo0 = g * 8 + (q ^ wp_swz(g)), bo1 = g * 8 + ((4 + q) ^ wp_swz(g));
+  // block (rb, p) <- block (rb, p) W8_p^T
+  // (and its packed copy in sWp: entry (n, k) of the block at n * 8 + (k ^ swz(n)))
+  const int po = g * 8 + ((2 * q) ^ wp_swz(g));
+  auto solve_block = [&](int rb, int p, double b0, double b1) {
+    double* cp = sT + (rb * 8 + g) * LDW + 8 * p;
+    const double a0 = cp[q], a1 = cp[4 + q];
+    double o0 = 0.0, o1 = 0.0;
+    dmma(o0, o1, a0, b0);
+    dmma(o0, o1, a1, b1);
+    __syncwarp();
+    *reinterpret_cast<double2*>(cp + 2 * q) = make_double2(o0, o1);
+    *reinterpret_cast<double2*>(sWp + wp_block(rb, p) + po) = make_double2(o0, o1);
+  };
+  // blocks (rb, cb0 .. cb0+3) that lie in [cb0, rb] -= L(rb, p) L(cb, p)^T: four independent chains
+  auto update_row4 = [&](int rb, int cb0, int p) {
+    const double* ap = sT + (rb * 8 + g) * LDW + 8 * p + q;
+    const double a0 = -ap[0], a1 = -ap[4];
+    double2 c[4];
+    double bb0[4], bb1[4];
+#pragma unroll
+    for (int u = 0; u < 4; u++)
+      if (cb0 + u <= rb) {
+        c[u] = *reinterpret_cast<const double2*>(sT + (rb * 8 + g) * LDW + 8 * (cb0 + u) + 2 * q);
+        const double* bp = sT + ((cb0 + u) * 8 + g) * LDW + 8 * p + q;
+        bb0[u] = bp[0];
+        bb1[u] = bp[4];
+      }
+#pragma unroll
+    for (int u = 0; u < 4; u++)
+      if (cb0 + u <= rb) dmma(c[u].x, c[u].y, a0, bb0[u]);
+#pragma unroll
+    for (int u = 0; u < 4; u++)
+      if (cb0 + u <= rb) dmma(c[u].x, c[u].y, a1, bb1[u]);
+#pragma unroll
+    for (int u = 0; u < 4; u++)
+      if (cb0 + u <= rb) *reinterpret_cast<double2*>(sT + (rb * 8 + g) * LDW + 8 * (cb0 + u) + 2 * q) = c[u];
+  };
+  // block (rb, cb) -= L(rb, p) L(cb, p)^T
+  auto update_block = [&](int rb, int cb, int p) {
+    double2* cp = reinterpret_cast<double2*>(sT + (rb * 8 + g) * LDW + 8 * cb + 2 * q);
+    const double* ap = sT + (rb * 8 + g) * LDW + 8 * p + q;
+    const double* bp = sT + (cb * 8 + g) * LDW + 8 * p + q;
+    double2 c = *cp;
+    dmma(c.x, c.y, -ap[0], bp[0]);
+    dmma(c.x, c.y, -ap[4], bp[4]);
+    *cp = c;
+  };
+  // the verdict on a pivot block travels through the panel's closing barrier (warp 0 runs ahead of the others: a flag
+  // in shared memory could be read on both sides of its next store)
+  int bad = 0;
+  FD_DECL;
+  FD_T(0);
+  if (ln.warp == 0) bad = pivot_block(sT, sWp, 0) ? 0 : 1;
+  if (__syncthreads_or(bad)) return false;
+  FD_T(1);
+  for (int p = 0; p < 15; p++) {
+    const double* w8 = sWp + wp_block(p, p);
+    const double b0 = w8[bo0], b1 = w8[bo1];
+    if (ln.warp == 0) {
+      solve_block(p + 1, p, b0, b1);
+      __threadfence_block();
+      __syncwarp();
+      bar1_arrive();  // L(p+1, p) is in place
+      FD_T(2);
+      update_block(p + 1, p + 1, p);
+      __syncwarp();
+      FD_T(3);
+      bad = pivot_block(sT, sWp, p + 1) ? 0 : 1;
+      FD_T(4);
+    } else {
+      for (int rb = p + 1 + ln.warp; rb < 16; rb += NWARP - 1) solve_block(rb, p, b0, b1);
+      FD_T(2);
+      bar1_sync();
+      FD_T(3);
+      // trailing blocks of rows p+2 .. 15 in groups of four along the row, dealt round-robin to the seven warps
+      int turn = ln.warp - 1;
+      for (int rb = 15; rb > p + 1; rb--)
+        for (int cb0 = p + 1; cb0 <= rb; cb0 += 4) {
+          if (turn == 0) update_row4(rb, cb0, p);
+          turn = turn == 0 ? NWARP - 2 : turn - 1;
+        }
+      FD_T(4);
+    }
+    if (__syncthreads_or(bad)) return false;
+    FD_T(5);
+  }
+  FD_T(6);
+  return true;
+}
+#else
+// In-place blocked Cholesky of the staged 128x128 tile (lower) by 8-column panels, left-looking.  Per panel p:
 //   S1  all warps : panel blocks  C(rb,p) -= L(rb,0:p) L(p,0:p)^T                      (DMMA)
 //   S2  warp 0    : 8x8 Cholesky of C(p,p) and its inverse W8_p, in registers
 //   S3  all warps : L(rb,p) = C(rb,p) W8_p^T  (rb > p)                                 (DMMA)
@@ -749,44 +1020,7 @@ static __device__ bool factor_diag(double* sT, double* sWp, double* misc, const 
     __syncthreads();
     // ---- S2 (every lane of warp 0 computes the same 8x8 factor; identical-value stores)
     if (ln.warp == 0) {
-      double a[8][8], w[8][8], rinv[8];
-      bool ok = true;
-#pragma unroll
-      for (int i = 0; i < 8; i++)
-#pragma unroll
-        for (int c = 0; c <= i; c++) a[i][c] = sT[(8 * p + i) * LDW + 8 * p + c];
-#pragma unroll
-      for (int k = 0; k < 8; k++) {
-        double dk = a[k][k];
-        if (!(dk > 0.0)) ok = false;
-        const double r = rsqrt(dk);  // one reciprocal square root instead of sqrt + division on the serial chain
-        const double piv = dk * r;
-        rinv[k] = r;
-        a[k][k] = piv;
-#pragma unroll
-        for (int i = k + 1; i < 8; i++) a[i][k] *= r;
-#pragma unroll
-        for (int c = k + 1; c < 8; c++)
-#pragma unroll
-          for (int i = c; i < 8; i++) a[i][c] -= a[i][k] * a[c][k];
-      }
-#pragma unroll
-      for (int c = 0; c < 8; c++) {
-        w[c][c] = rinv[c];
-#pragma unroll
-        for (int i = c + 1; i < 8; i++) {
-          double s = 0.0;
-#pragma unroll
-          for (int k = c; k < i; k++) s += a[i][k] * w[k][c];
-          w[i][c] = -s * rinv[i];
-        }
-      }
-      double* wpp = sWp + wp_block(p, p);
-#pragma unroll
-      for (int i = 0; i < 8; i++)
-#pragma unroll
-        for (int c = 0; c < 8; c++) wpp[i * 8 + (c ^ wp_swz(i))] = (c <= i) ? w[i][c] : 0.0;
-      if (!ok) *flag = 1;
+      if (!pivot_block(sT, sWp, p)) *flag = 1;
     }
     __syncthreads();
     if (*flag) return false;
@@ -816,6 +1050,7 @@ static __device__ bool factor_diag(double* sT, double* sWp, double* misc, const 
   __syncthreads();
   return true;
 }
+#endif
 
 // ----------------------------------------------------------------------------- diagonal branch
 // Ci = D + b u u^T with D = diag(a + Si), u_k = (-1)^k: solve every RHS row in place by

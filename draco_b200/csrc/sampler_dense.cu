@@ -263,6 +263,24 @@ __global__ void __launch_bounds__(THREADS, 1) dense_sampler_kernel(DevBatch d, i
           if (use_tma) gemm_nt_tma(&tmap, ring, pipe, acc, ln, slot, i * TILE, j * TILE, j * (TILE / TKC), var);
           else gemm_nt(pipe, acc, ln, Wk + (size_t)i * TILE * npad, Bp, npad, j * (TILE / KC), var);
           PROF(6);
+#if DGIBBS_TRISOLVE_REG
+          if (interior || i >= nblk) {
+            // the tile stays in the accumulator registers: generated part (or the right-hand side) added in place,
+            // solved by quad shuffles + DMMA, stored straight to the workspace
+            if (interior) acc_add_circ(acc, ln, cwin);  // (gemm_nt ends with a barrier: the window is visible)
+            else acc_add_global(acc, out, npad, ln, do0, do1);
+            PROF(5);
+            trisolve_reg<false>(acc, sWp, ln, var);
+            tile_store_global(acc, out, npad, ln, do0, do1);
+            __syncthreads();  // the circulant window is rewritten for the next tile
+            PROF(8);
+            if (C > 1 && i == j + 1) {
+              cluster_arrive();
+              pending = true;
+            }
+            continue;
+          }
+#endif
           if (interior) {  // interior tile below the diagonal: generated in registers (gemm_nt ends with a barrier)
             stage_acc_circ(acc, pipe, ln, cwin);
           } else {
@@ -315,6 +333,12 @@ __global__ void __launch_bounds__(THREADS, 1) dense_sampler_kernel(DevBatch d, i
           acc_zero(acc);
           gemm_nn<true>(pipe, acc, ln, rrow, npad, Wk + j * TILE, npad, (j + 1) * TILE, (nblk - 1 - j) * (TILE / KC), var);
           PROF(9);
+#if DGIBBS_TRISOLVE_REG
+          acc_add_global(acc, xt, npad, ln, do0, do1);
+          trisolve_reg<true>(acc, sWp, ln, var);
+          tile_store_global(acc, xt, npad, ln, do0, do1);
+          __syncthreads();  // x_j is read by the next update; sWp is reloaded
+#else
           stage_acc(acc, pipe, ln, do0, do1);
           __syncthreads();
           add_global(pipe, xt, npad, nrows, row_lo);
@@ -323,6 +347,7 @@ __global__ void __launch_bounds__(THREADS, 1) dense_sampler_kernel(DevBatch d, i
           __syncthreads();
           copy_tile_out(pipe, xt, npad, nrows, row_lo);
           __syncthreads();
+#endif
           PROF(10);
         }
       }
