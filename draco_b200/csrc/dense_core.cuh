@@ -881,10 +881,6 @@ __device__ __forceinline__ bool pivot_block(const double* sT, double* sWp, int p
 __device__ __forceinline__ void bar1_arrive() { asm volatile("bar.arrive 1, %0;" ::"n"(THREADS) : "memory"); }
 __device__ __forceinline__ void bar1_sync() { asm volatile("bar.sync 1, %0;" ::"n"(THREADS) : "memory"); }
 
-#ifndef FD_T  // timing hooks of scratch/factor_probe.cu
-#define FD_T(k)
-#define FD_DECL
-#endif
 #if DGIBBS_FACTOR_LOOKAHEAD
 // In-place blocked Cholesky of the staged 128x128 tile (lower) by 8-column panels, right-looking with a look-ahead of one
 // panel: the 8x8 pivot factorisation is a serial chain of 8 reciprocal square roots that one warp computes, so warp 0
@@ -951,11 +947,8 @@ static __device__ bool factor_diag(double* sT, double* sWp, double* misc, const 
   // the verdict on a pivot block travels through the panel's closing barrier (warp 0 runs ahead of the others: a flag
   // in shared memory could be read on both sides of its next store)
   int bad = 0;
-  FD_DECL;
-  FD_T(0);
   if (ln.warp == 0) bad = pivot_block(sT, sWp, 0) ? 0 : 1;
   if (__syncthreads_or(bad)) return false;
-  FD_T(1);
   for (int p = 0; p < 15; p++) {
     const double* w8 = sWp + wp_block(p, p);
     const double b0 = w8[bo0], b1 = w8[bo1];
@@ -964,17 +957,12 @@ static __device__ bool factor_diag(double* sT, double* sWp, double* misc, const 
       __threadfence_block();
       __syncwarp();
       bar1_arrive();  // L(p+1, p) is in place
-      FD_T(2);
       update_block(p + 1, p + 1, p);
       __syncwarp();
-      FD_T(3);
       bad = pivot_block(sT, sWp, p + 1) ? 0 : 1;
-      FD_T(4);
     } else {
       for (int rb = p + 1 + ln.warp; rb < 16; rb += NWARP - 1) solve_block(rb, p, b0, b1);
-      FD_T(2);
       bar1_sync();
-      FD_T(3);
       // trailing blocks of rows p+2 .. 15 in groups of four along the row, dealt round-robin to the seven warps
       int turn = ln.warp - 1;
       for (int rb = 15; rb > p + 1; rb--)
@@ -982,12 +970,9 @@ static __device__ bool factor_diag(double* sT, double* sWp, double* misc, const 
           if (turn == 0) update_row4(rb, cb0, p);
           turn = turn == 0 ? NWARP - 2 : turn - 1;
         }
-      FD_T(4);
     }
     if (__syncthreads_or(bad)) return false;
-    FD_T(5);
   }
-  FD_T(6);
   return true;
 }
 #else
@@ -1153,6 +1138,15 @@ __device__ __forceinline__ bool chol_factor_forward(const CholWS& w, const Lane&
       const int var = rhs_variant(do0, do1);
       acc_zero(acc);
       nt(acc, ln, i * TILE, j * TILE, j * TILE, var);
+#if DGIBBS_TRISOLVE_REG
+      if (i >= nblk) {  // right-hand-side tile: solved on the accumulator registers
+        acc_add_global(acc, out, npad, ln, do0, do1);
+        trisolve_reg<false>(acc, w.sWp, ln, var);
+        tile_store_global(acc, out, npad, ln, do0, do1);
+        __syncthreads();
+        continue;
+      }
+#endif
       stage_acc(acc, w.pipe, ln, do0, do1);
       __syncthreads();
       if (i < nblk) gen(w.pipe, i, j, false);
@@ -1188,6 +1182,13 @@ __device__ __forceinline__ void chol_backward(const CholWS& w, const Lane& ln) {
       cp_async_commit();
       acc_zero(acc);
       gemm_nn<true>(w.pipe, acc, ln, rrow, npad, w.Wk + j * TILE, npad, (j + 1) * TILE, (nblk - 1 - j) * (TILE / KC), var);
+#if DGIBBS_TRISOLVE_REG
+      acc_add_global(acc, xt, npad, ln, do0, do1);
+      trisolve_reg<true>(acc, w.sWp, ln, var);
+      tile_store_global(acc, xt, npad, ln, do0, do1);
+      __syncthreads();  // x_j is read by the next update; sWp is reloaded
+      (void)nrows;
+#else
       stage_acc(acc, w.pipe, ln, do0, do1);
       __syncthreads();
       add_global(w.pipe, xt, npad, nrows);
@@ -1196,6 +1197,7 @@ __device__ __forceinline__ void chol_backward(const CholWS& w, const Lane& ln) {
       __syncthreads();
       copy_tile_out(w.pipe, xt, npad, nrows);
       __syncthreads();
+#endif
     }
   }
 }
