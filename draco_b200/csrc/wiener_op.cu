@@ -73,6 +73,30 @@ __global__ void fourier_prep_kernel(const zc* __restrict__ fourier, const double
   FS[(size_t)d * F + k] = make_cuDoubleComplex(v.x * prior[d], -v.y * prior[d]);
 }
 
+// FSFT'(i, j) = sum_d FS(i, d) conj(F'(j, d))  (powerspec.py:234; column-major [F, F], once per call): 16 x 16 output
+// tile per block, the two operand slabs of 16 delays staged through shared memory (own-kernel path; the library paths
+// call ZGEMM)
+__global__ void fsft_kernel(const zc* __restrict__ FS, const zc* __restrict__ Fp, zc* __restrict__ FSFT, int F, int nd) {
+  __shared__ double2 sa[16][17], sb[16][17];
+  const int tx = threadIdx.x, ty = threadIdx.y;
+  const int i = blockIdx.x * 16 + tx, j = blockIdx.y * 16 + ty;
+  double re = 0.0, im = 0.0;
+  for (int d0 = 0; d0 < nd; d0 += 16) {
+    const int d = d0 + ty, ia = blockIdx.x * 16 + tx, jb = blockIdx.y * 16 + tx;
+    sa[ty][tx] = (d < nd && ia < F) ? FS[(size_t)d * F + ia] : make_double2(0.0, 0.0);
+    sb[ty][tx] = (d < nd && jb < F) ? Fp[(size_t)d * F + jb] : make_double2(0.0, 0.0);
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < 16; k++) {
+      const double2 a = sa[k][tx], b = sb[k][ty];  // a conj(b)
+      re += a.x * b.x + a.y * b.y;
+      im += a.y * b.x - a.x * b.y;
+    }
+    __syncthreads();
+  }
+  if (i < F && j < F) FSFT[(size_t)j * F + i] = make_cuDoubleComplex(re, im);
+}
+
 // G'(i, j) = FSFT'(i, j) b_i b_j, b = sqrt(beam power)  (powerspec.py:266, 288)
 __global__ void beam_scale_kernel(const zc* __restrict__ FSFT, const double* __restrict__ bp, zc* __restrict__ G, int F) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y;
@@ -360,7 +384,12 @@ extern "C" int dgwiener_construct(dgwiener_problem* p) {
   WCU(cudaMemcpyAsync(T1, p->fourier, FD * 16, cudaMemcpyHostToDevice, st));
   fourier_prep_kernel<<<dim3((F + 127) / 128, nd), 128, 0, st>>>(T1, prior, Fp, FS, F, nd);
   // FSFT' = (F' S) F'^H  (powerspec.py:234)
-  WBL(cublasZgemm(L.blas, CUBLAS_OP_N, CUBLAS_OP_C, F, F, nd, &one, FS, F, Fp, F, &zero, FSFT, F));
+  if (own) {
+    fsft_kernel<<<dim3((F + 15) / 16, (F + 15) / 16), dim3(16, 16), 0, st>>>(FS, Fp, FSFT, F, nd);
+    WCU(cudaGetLastError());
+  } else {
+    WBL(cublasZgemm(L.blas, CUBLAS_OP_N, CUBLAS_OP_C, F, F, nd, &one, FS, F, Fp, F, &zero, FSFT, F));
+  }
   launches += 2;
   flop += 8.0 * F * (double)F * nd;
   if (own) {
