@@ -13,7 +13,38 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 # DGIBBS_LIB_PATH: load another build of the library (A/B timing of kernel variants, scratch/build_variant.sh)
 LIB_PATH = os.environ.get("DGIBBS_LIB_PATH") or os.path.join(HERE, "libdgibbs.so")
 
-WINDOW_IDS = {
+WINDOW_TUKEY_BASE = 1 << 20
+
+
+class _WindowIds(dict):
+    """Window name -> ``window_id`` of include/dgibbs.h; ``"tukey-0.X"`` (draco/util/tools.py:569-581) maps to
+    ``DGIBBS_WINDOW_TUKEY(X * 1e6)``."""
+
+    @staticmethod
+    def _tukey(name):
+        if not (isinstance(name, str) and name.startswith("tukey")):
+            return None
+        try:
+            r = float(name.split("-")[1])
+        except (IndexError, ValueError):
+            return None
+        m = round(r * 1e6)
+        # the device rebuilds r as m / 1e6: only fractions with at most six decimals map onto themselves
+        if not (0 < m <= 1000000) or m / 1e6 != r:
+            return None
+        return WINDOW_TUKEY_BASE + m
+
+    def __contains__(self, name):
+        return dict.__contains__(self, name) or self._tukey(name) is not None
+
+    def __missing__(self, name):
+        wid = self._tukey(name)
+        if wid is None:
+            raise KeyError(name)
+        return wid
+
+
+WINDOW_IDS = _WindowIds({
     None: -1,
     "uniform": 0,
     "hann": 1,
@@ -23,7 +54,8 @@ WINDOW_IDS = {
     "nuttall": 5,
     "blackman_nuttall": 6,
     "blackman_harris": 7,
-}
+    "triangular": 8,
+})
 RNG_INJECTED, RNG_PHILOX, RNG_ZERO = 0, 1, 2
 BRANCH_SKIPPED, BRANCH_DELAY_SPACE, BRANCH_FREQ_SPACE, BRANCH_DIAGONAL = 0, 1, 2, 3
 

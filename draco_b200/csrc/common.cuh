@@ -9,6 +9,12 @@ constexpr int TILE = 128;     // block-column width and row-tile height of the f
 constexpr int KC = 32;        // K chunk staged per pipeline stage (one CTA barrier per chunk: 256 DMMAs per warp between barriers)
 constexpr int THREADS = 256;  // 8 warps per CTA, one CTA per SM
 constexpr int NWARP = THREADS / 32;
+// window ids beyond the cosine-sum table (window.cuh, include/dgibbs.h): "triangular", "tukey-r" with r in 1e-6 units
+constexpr int DG_WINDOW_TRIANGULAR = 8;
+constexpr int DG_WINDOW_TUKEY_BASE = 1 << 20;
+__host__ __device__ __forceinline__ bool window_id_valid(int id) {
+  return (id >= -1 && id <= DG_WINDOW_TRIANGULAR) || (id >= DG_WINDOW_TUKEY_BASE && id <= DG_WINDOW_TUKEY_BASE + 1000000);
+}
 constexpr int LDA_NT = KC + 4;    // smem row pitch (doubles) of a [rows][KC] tile: conflict-free fragments
 constexpr int LDB_NN = TILE + 4;  // smem row pitch of a [KC][TILE] tile
 constexpr int LDW = TILE + 4;     // smem row pitch of a full 128x128 tile

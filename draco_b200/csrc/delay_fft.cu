@@ -178,7 +178,7 @@ extern "C" int dgibbs_delay_fft(dgibbs_handle h, int32_t on_device, int64_t nrow
     return -2;
   };
   if (nrows < 0 || N <= 0) return bad("nrows >= 0 and N > 0 are required");
-  if (window_id < -1 || window_id > 7) return bad("window_id");
+  if (!window_id_valid(window_id)) return bad("window_id");
   if (ms_kernel) *ms_kernel = 0.0;
   if (nrows == 0) return 0;
   if (!data || !out) return bad("data and out are required");
@@ -204,7 +204,7 @@ extern "C" int dgibbs_delay_fft(dgibbs_handle h, int32_t on_device, int64_t nrow
   double2* tw = (double2*)q;
   long long *tag_w = dg_tag(h, "dfft_window"), *tag_wp = dg_tag(h, "dfft_window_ptr");
   long long *tag_t = dg_tag(h, "dfft_tw"), *tag_tp = dg_tag(h, "dfft_tw_ptr");
-  const long long key_w = ((long long)N << 8) | (long long)(window_id + 2), key_t = ((long long)N << 1) | (pow2 ? 1 : 0);
+  const long long key_w = ((long long)N << 24) | (long long)(window_id + 2), key_t = ((long long)N << 1) | (pow2 ? 1 : 0);
   if (*tag_w != key_w || *tag_wp != (long long)(uintptr_t)wtab) {
     delay_fft_window_kernel<<<(N + 255) / 256, 256, 0, st>>>(wtab, N, window_id);
     FCU(cudaGetLastError());
@@ -353,7 +353,7 @@ extern "C" int dgibbs_delay_fft_noalloc(dgibbs_handle h, int64_t nrows, int32_t 
     return -2;
   };
   if (nrows < 0) return bad("nrows >= 0 is required");
-  if (window_id < -1 || window_id > 7) return bad("window_id");
+  if (!window_id_valid(window_id)) return bad("window_id");
   if (N < 8 || (N & (N - 1)) != 0 || N > NOALLOC_MAX_N) {
     char msg[160];
     snprintf(msg, sizeof msg, "dgibbs_delay_fft_noalloc serves N = 2^m with 8 <= N <= %d (static scratch); got N = %d: "

@@ -221,7 +221,7 @@ static int check_problem(dgibbs_handle h, const dgibbs_problem* p) {
   if (p->B <= 0) return bad_arg(h, 2, "B must be positive");
   if (p->N < 2 || (!p->complex_timedomain && (p->N & 1))) return bad_arg(h, 2, "N must be even and >= 2");
   if (p->niter < 0) return bad_arg(h, 2, "niter must be >= 0");
-  if (p->window_id < -1 || p->window_id > 7) return bad_arg(h, 2, "unknown window_id");
+  if (!window_id_valid(p->window_id)) return bad_arg(h, 2, "unknown window_id");
   if (p->rng_mode < 0 || p->rng_mode > 2) return bad_arg(h, 2, "unknown rng_mode");
   if (p->cluster_size != 0 && p->cluster_size != 1 && p->cluster_size != 2 && p->cluster_size != 4)
     return bad_arg(h, 2, "cluster_size must be 0 (auto), 1, 2 or 4");

@@ -23,6 +23,7 @@
 #include "dense_core.cuh"
 #include "tma_host.h"
 #include "tma_pipe.cuh"
+#include "window.cuh"
 
 namespace dg {
 
@@ -136,24 +137,6 @@ __device__ __forceinline__ double2 cnormal(const Philox& ph, unsigned it, unsign
   return make_double2(n0 * 0.70710678118654752440, n1 * 0.70710678118654752440);
 }
 
-// cosine-sum window coefficients, draco/util/tools.py:584-595 (same table as setup_kernels.cu)
-static __constant__ double c_xwindow[8][4] = {
-    {1, 0, 0, 0},
-    {0.5, -0.5, 0, 0},
-    {0.5, -0.5, 0, 0},
-    {0.53836, -0.46164, 0, 0},
-    {0.42, -0.5, 0.08, 0},
-    {0.355768, -0.487396, 0.144232, -0.012604},
-    {0.3635819, -0.4891775, 0.1365995, -0.0106411},
-    {0.35875, -0.48829, 0.14128, -0.01168},
-};
-__device__ __forceinline__ double window_value_x(int window_id, double x) {
-  double w = 0.0;
-#pragma unroll
-  for (int j = 0; j < 4; j++) w += c_xwindow[window_id][j] * cos(2.0 * 3.141592653589793 * (double)j * x);
-  return (x >= 0.0 && x <= 1.0) ? w : 0.0;
-}
-
 // ----------------------------------------------------------------------------- per-problem setup
 // window (x = fsel / N, delay.py:1982), whitening, first columns of the circulant blocks, initial state
 __global__ void cross_setup_kernel(CrossBatch d) {
@@ -164,7 +147,7 @@ __global__ void cross_setup_kernel(CrossBatch d) {
     double w = 1.0;
     if (d.window_id >= 0) {
       const double x = (double)d.fsel[f] * 1.0 / (double)N;
-      w = window_value_x(d.window_id, x);
+      w = window_value(d.window_id, x);
     }
     d.h[(size_t)b * nd * M + e] = w * sqrt(d.Ni[(size_t)b * nd * M + e]);
   }
@@ -173,7 +156,7 @@ __global__ void cross_setup_kernel(CrossBatch d) {
     const int f = (int)(e % M);
     const int dd = (int)(e / ((long long)T * M));
     double w = 1.0;
-    if (d.window_id >= 0) w = window_value_x(d.window_id, (double)d.fsel[f] * 1.0 / (double)N);
+    if (d.window_id >= 0) w = window_value(d.window_id, (double)d.fsel[f] * 1.0 / (double)N);
     const double sq = sqrt(d.Ni[((size_t)b * nd + dd) * M + f]);
     const double2 v = d.data[(size_t)b * nd * T * M + e];
     d.z[(size_t)b * nd * T * M + e] = make_double2((v.x * w) * sq, (v.y * w) * sq);
@@ -489,7 +472,7 @@ extern "C" int dgibbs_cross_run(dgibbs_handle h, const dgibbs_cross_problem* p, 
   if (!p || p->struct_size != (int32_t)sizeof(dgibbs_cross_problem)) return bad(2, "problem struct");
   if (p->B <= 0 || p->N < 1 || p->T < 1 || p->M < 1 || p->niter < 0) return bad(2, "B, N, T, M must be positive");
   if (p->nd < 1 || p->nd > DGIBBS_CROSS_MAX_DATASETS) return bad(2, "nd must be in [1, DGIBBS_CROSS_MAX_DATASETS]");
-  if (p->window_id < -1 || p->window_id > 7) return bad(2, "unknown window_id");
+  if (!window_id_valid(p->window_id)) return bad(2, "unknown window_id");
   if (p->rng_mode < 0 || p->rng_mode > 2) return bad(2, "unknown rng_mode");
   if (!p->data || !p->Ni || !p->fsel || !p->S0) return bad(2, "a required input pointer is NULL");
   if (p->rng_mode == DGIBBS_RNG_INJECTED && p->niter > 0 && (!p->w1 || !p->w2 || !p->wg || (p->nd > 1 && !p->wn)))

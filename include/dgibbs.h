@@ -35,7 +35,11 @@ extern "C" {
 
 #define DGIBBS_VERSION 100 /* 0.1.0 */
 
-/* window_id: index into the cosine-sum table of draco/util/tools.py:584-595 */
+/* window_id: index into the cosine-sum table of draco/util/tools.py:584-595, DGIBBS_WINDOW_TRIANGULAR
+ * (tools.py:566-567) or DGIBBS_WINDOW_TUKEY(r) for "tukey-r" (tools.py:569-581; r = the tapered fraction in units of
+ * 1e-6, 0 .. 1000000: "tukey-0.5" is DGIBBS_WINDOW_TUKEY(500000)) */
+#define DGIBBS_WINDOW_TUKEY_BASE (1 << 20)
+#define DGIBBS_WINDOW_TUKEY(r_millionths) (DGIBBS_WINDOW_TUKEY_BASE + (r_millionths))
 enum {
   DGIBBS_WINDOW_NONE = -1,
   DGIBBS_WINDOW_UNIFORM = 0,
@@ -45,7 +49,8 @@ enum {
   DGIBBS_WINDOW_BLACKMAN = 4,
   DGIBBS_WINDOW_NUTTALL = 5,
   DGIBBS_WINDOW_BLACKMAN_NUTTALL = 6,
-  DGIBBS_WINDOW_BLACKMAN_HARRIS = 7
+  DGIBBS_WINDOW_BLACKMAN_HARRIS = 7,
+  DGIBBS_WINDOW_TRIANGULAR = 8
 };
 
 /* rng_mode */

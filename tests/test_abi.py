@@ -107,3 +107,21 @@ def test_wiener_operator_entry_points():
         with pytest.raises(_lib.DGibbsError):
             powerspec.wiener_delay_operator(F, np.ones(2), np.ones(4), np.eye(4)[None], np.eye(4)[None],
                                             np.ones((1, 1, 4)), np.ones((1, 4)))
+
+
+def test_window_ids_follow_the_header():
+    """Window names of draco/util/tools.py:547-601 -> window_id of include/dgibbs.h, 'tukey-0.X' included."""
+    from draco_b200 import _lib
+
+    hdr = open(os.path.join(ROOT, "include", "dgibbs.h")).read()
+    enum = dict(re.findall(r"DGIBBS_WINDOW_([A-Z_]+)\s*=\s*(-?\d+)", hdr))
+    for name, wid in _lib.WINDOW_IDS.items():
+        assert int(enum["NONE" if name is None else name.upper()]) == wid
+    assert "#define DGIBBS_WINDOW_TUKEY_BASE (1 << 20)" in hdr
+    assert _lib.WINDOW_IDS["tukey-0.5"] == (1 << 20) + 500000
+    assert _lib.WINDOW_IDS["tukey-0.25"] == (1 << 20) + 250000
+    assert "tukey-0.3" in _lib.WINDOW_IDS and "tukey-1.0" in _lib.WINDOW_IDS
+    for bad in ("tukey", "tukey-", "tukey-0", "tukey-1.5", "tukey-0.1234567", "kaiser", "tukey-x"):
+        assert bad not in _lib.WINDOW_IDS
+        with pytest.raises(KeyError):
+            _lib.WINDOW_IDS[bad]

@@ -61,6 +61,37 @@ def test_golden_setup_wiener_chain(gibbs, golden, name):
     np.testing.assert_allclose(np.array(samples), ref, rtol=RTOL_SAMPLES)
 
 
+ALL_WINDOWS = ["uniform", "hann", "hanning", "hamming", "blackman", "nuttall", "blackman_nuttall", "blackman_harris",
+               "triangular", "tukey-0.5", "tukey-0.3", None]
+
+
+@pytest.mark.parametrize("window", ALL_WINDOWS)
+def test_every_window_of_window_generalised(gibbs, window):
+    """draco/util/tools.py:547-601 offers eight cosine-sum windows, 'triangular' and 'tukey-0.X'; the oracle's restatement
+    is pinned on reference-generated values of all of them (tests/test_oracle.py::test_windows).  Here: the whitened data
+    z, F^T N^-1 h and F^T N^-1 F of the device set-up, and the plain FFT delay transform, against the oracle for each."""
+    N, M, T = 64, 20, 6
+    data, Ni, fsel, S0 = make_case(N, M, T, False, False, seed=21)
+    z, fh, ff = gibbs.compute_delay_spectrum_inputs(data, N, Ni, fsel, window, False)
+    zo, fho, ffo = oracle.whiten_inputs(data, N, Ni, fsel, window, False)
+    np.testing.assert_allclose(z, zo, rtol=RTOL_SETUP, atol=1e-12)
+    assert relmax(fh, fho) < RTOL_SETUP
+    assert relmax(ff, ffo) < RTOL_SETUP
+    rng = np.random.default_rng(5)
+    rows = rng.standard_normal((3, 48)) + 1j * rng.standard_normal((3, 48))
+    from oracle import transform_oracle
+
+    np.testing.assert_allclose(gibbs.fft_rows(rows, window), transform_oracle.delay_spectrum_fft(rows, 48, window), rtol=1e-12,
+                               atol=1e-13)
+
+
+def test_unknown_windows_are_refused(gibbs):
+    data, Ni, fsel, S0 = make_case(32, 10, 4, False, False, seed=3)
+    for bad in ("tukey", "tukey-1.5", "tukey-0.1234567", "kaiser"):
+        with pytest.raises(ValueError):
+            gibbs.compute_delay_spectrum_inputs(data, 32, Ni, fsel, bad, False)
+
+
 @pytest.mark.parametrize("name", ["f_real_cfg1", "f_cplx_n64", "t_real_n64"])
 def test_dense_projection_fallback_matches_golden(gibbs, golden, name, monkeypatch):
     """The masked inverse DFT has two implementations: an in-smem FFT (N a power of two) and the
