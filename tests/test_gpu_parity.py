@@ -367,3 +367,25 @@ def test_empty_chain_is_not_a_success(gibbs):
     res = gibbs.run_batch(gibbs.pack_batch([data], [Ni], [fsel], 64, S0[None]), 0, seed=1)
     assert int(res.n_done[0]) == 0 and not res.success[0]
     assert np.array_equal(res.spectrum[0], S0)
+
+
+@pytest.mark.parametrize("geom", [(256, 102, 32, 6, 1), (512, 200, 40, 3, 1), (1024, 410, 16, 2, 1), (512, 60, 24, 3, 2)])
+def test_copies_of_one_chain_agree_bit_for_bit(gibbs, geom):
+    """Race detector (compute-sanitizer is not available on the GPU pool): several waves of chains with the SAME data, weights
+    and Philox key (global_id) must produce the same bits on every SM, every wave and every cluster size -- the kernels
+    exchange data between warps through shared memory behind named barriers, mbarriers and TMA, and a missed ordering
+    shows up as a chain that differs from its copies."""
+    N, M, T, niter, branch = geom  # branch 1: delay-space (dense) kernel, 2: few-channel kernel
+    data, Ni, fsel, S0 = make_case(N, M, T, False, False, seed=31)
+    nb = 2 * 148 + 37
+    pb = gibbs.pack_batch([data] * nb, [Ni] * nb, [fsel] * nb, N, np.full((nb, N), 10.0), window="nuttall",
+                          global_id=np.zeros(nb, dtype=np.int64))
+    first = None
+    for cs in (1, 2, 0):
+        res = gibbs.run_batch(pb, niter, seed=9, save_samples=True, cluster_size=cs, force_branch=branch)
+        assert res.success.all() and (np.asarray(res.branch) == branch).all()
+        smp = np.asarray(res.samples)
+        assert np.array_equal(smp, np.broadcast_to(smp[:, :1], smp.shape)), f"cluster_size={cs}: copies differ"
+        if first is None:
+            first = smp[:, 0].copy()
+        assert np.array_equal(smp[:, 0], first)
