@@ -294,6 +294,26 @@ __device__ __forceinline__ void stage_acc_circ(const Acc& acc, double* sT, const
       *reinterpret_cast<double2*>(row + nb * 8) = make_double2(acc[f][nb][0] + cp[-nb * 8], acc[f][nb][1] + cp[-nb * 8 - 1]);
   }
 }
+// the same on the accumulator registers, before the tile is staged (lower-triangle blocks of this warp's two row
+// fragments; one pass over shared memory less than add_generated_diag_win on the staged tile)
+__device__ __forceinline__ void acc_add_diag_win(Acc& acc, const Lane& ln, const double* cwin, const double* Si, int R0) {
+#pragma unroll
+  for (int f = 0; f < 2; f++) {
+    const int rb = ln.rf[f], r = rb * 8 + ln.g;
+    const double* cp = cwin + TILE + r - 2 * ln.q;
+#pragma unroll
+    for (int nb = 0; nb < (f == 0 ? 8 : 16); nb++) {
+      if (nb > rb) continue;
+      double v0 = cp[-nb * 8], v1 = cp[-nb * 8 - 1];
+      if (nb == rb) {
+        if (2 * ln.q == ln.g) v0 += Si[R0 + r];
+        if (2 * ln.q + 1 == ln.g) v1 += Si[R0 + r];
+      }
+      acc[f][nb][0] += v0;
+      acc[f][nb][1] += v1;
+    }
+  }
+}
 // lower triangle of an interior diagonal tile: sT += circ window + diag(Si)
 __device__ __forceinline__ void add_generated_diag_win(double* sT, const double* cwin, const double* Si, int R0) {
 #pragma unroll 2
@@ -882,17 +902,19 @@ __device__ __forceinline__ void bar1_arrive() { asm volatile("bar.arrive 1, %0;"
 __device__ __forceinline__ void bar1_sync() { asm volatile("bar.sync 1, %0;" ::"n"(THREADS) : "memory"); }
 
 #if DGIBBS_FACTOR_LOOKAHEAD
-// In-place blocked Cholesky of the staged 128x128 tile (lower) by 8-column panels, right-looking with a look-ahead of one
-// panel: the 8x8 pivot factorisation is a serial chain of 8 reciprocal square roots that one warp computes, so warp 0
-// runs AHEAD -- as soon as panel p's pivot block is inverted it solves block (p+1, p), updates block (p+1, p+1) and
-// factors it, while warps 1..7 solve the rest of panel p and apply it to the trailing blocks.  Per panel p:
-//   warp 0      : L(p+1,p) = C(p+1,p) W8_p^T;  [arrive]  C(p+1,p+1) -= L(p+1,p) L(p+1,p)^T;  W8_{p+1} = inv(chol(C(p+1,p+1)))
-//   warps 1..7  : L(rb,p) = C(rb,p) W8_p^T (rb > p+1);  [wait]  C(rb,cb) -= L(rb,p) L(cb,p)^T  (rb >= cb > p, not (p+1,p+1))
-// The left-looking form (DGIBBS_FACTOR_LOOKAHEAD=0) put three CTA barriers and the idle time of seven warps on every
-// pivot block: 31 us per tile, a third of the kernel at N = 256 (profiles/r02m_phase_cycles_cfg1.log).
+// In-place blocked Cholesky of the staged 128x128 tile (lower) by 8-column panels: LEFT-looking updates (a block is
+// read and written once, its sum runs in registers) with a LOOK-AHEAD of one panel.  The 8x8 pivot factorisation is a
+// serial chain of 8 reciprocal square roots that one warp computes (~1.2 k cycles), so warp 0 runs ahead on the pivot
+// path while warps 1..7 prepare the next panel column.  Per panel p (W8_p known, column p updated but not solved):
+//   warp 0      : L(p+1,p) = C(p+1,p) W8_p^T;  [arrive]  C(p+1,p+1) -= L(p+1,0:p+1) L(p+1,0:p+1)^T;
+//                 W8_{p+1} = inv(chol(C(p+1,p+1)))
+//   warps 1..7  : L(rb,p) = C(rb,p) W8_p^T (rb > p+1);  [wait]  C(rb,p+1) -= L(rb,0:p+1) L(p+1,0:p+1)^T  (rb > p+1)
+// Earlier forms, cycles per tile in isolation (scratch/factor_probe.cu, profiles/r02x_upd_probe.log, r03i): left-looking
+// without look-ahead (three CTA barriers and seven idle warps per pivot block; DGIBBS_FACTOR_LOOKAHEAD=0) 50.5 k;
+// right-looking with look-ahead 49.5 k (every trailing block read-modify-written in shared memory per panel: ~10 cycles
+// per DMMA).
 // On exit sWp holds L_jj packed by 8x8 blocks (bank-swizzled; written as the blocks are solved) with W8_p in the
-// diagonal slots.
-// Returns false on a non-positive pivot.
+// diagonal slots.  Returns false on a non-positive pivot.
 static __device__ bool factor_diag(double* sT, double* sWp, double* misc, const Lane& ln) {
   (void)misc;
   const int g = ln.g, q = ln.q;
@@ -910,39 +932,34 @@ static __device__ bool factor_diag(double* sT, double* sWp, double* misc, const 
     *reinterpret_cast<double2*>(cp + 2 * q) = make_double2(o0, o1);
     *reinterpret_cast<double2*>(sWp + wp_block(rb, p) + po) = make_double2(o0, o1);
   };
-  // blocks (rb, cb0 .. cb0+3) that lie in [cb0, rb] -= L(rb, p) L(cb, p)^T: four independent chains
-  auto update_row4 = [&](int rb, int cb0, int p) {
-    const double* ap = sT + (rb * 8 + g) * LDW + 8 * p + q;
-    const double a0 = -ap[0], a1 = -ap[4];
-    double2 c[4];
-    double bb0[4], bb1[4];
-#pragma unroll
-    for (int u = 0; u < 4; u++)
-      if (cb0 + u <= rb) {
-        c[u] = *reinterpret_cast<const double2*>(sT + (rb * 8 + g) * LDW + 8 * (cb0 + u) + 2 * q);
-        const double* bp = sT + ((cb0 + u) * 8 + g) * LDW + 8 * p + q;
-        bb0[u] = bp[0];
-        bb1[u] = bp[4];
+  // blocks (rbA, cb) and, if rbB < 16, (rbB, cb) -= L(rb, 0:nk) L(cb, 0:nk)^T; two accumulators per block (k4 halves)
+  auto update_pair = [&](int rbA, int rbB, int cb, int nk) {
+    const bool two = rbB < 16;
+    double2* cpA = reinterpret_cast<double2*>(sT + (rbA * 8 + g) * LDW + 8 * cb + 2 * q);
+    double2* cpB = reinterpret_cast<double2*>(sT + ((two ? rbB : rbA) * 8 + g) * LDW + 8 * cb + 2 * q);
+    const double* apA = sT + (rbA * 8 + g) * LDW + q;
+    const double* apB = sT + ((two ? rbB : rbA) * 8 + g) * LDW + q;
+    const double* bp = sT + (cb * 8 + g) * LDW + q;
+    double2 cA = *cpA, cB = *cpB;
+    double eA0 = 0.0, eA1 = 0.0, eB0 = 0.0, eB1 = 0.0;
+    if (two) {
+#pragma unroll 2
+      for (int k = 0; k < nk; k++) {
+        const double b0 = bp[8 * k], b1 = bp[8 * k + 4];
+        dmma(cA.x, cA.y, -apA[8 * k], b0);
+        dmma(eA0, eA1, -apA[8 * k + 4], b1);
+        dmma(cB.x, cB.y, -apB[8 * k], b0);
+        dmma(eB0, eB1, -apB[8 * k + 4], b1);
       }
-#pragma unroll
-    for (int u = 0; u < 4; u++)
-      if (cb0 + u <= rb) dmma(c[u].x, c[u].y, a0, bb0[u]);
-#pragma unroll
-    for (int u = 0; u < 4; u++)
-      if (cb0 + u <= rb) dmma(c[u].x, c[u].y, a1, bb1[u]);
-#pragma unroll
-    for (int u = 0; u < 4; u++)
-      if (cb0 + u <= rb) *reinterpret_cast<double2*>(sT + (rb * 8 + g) * LDW + 8 * (cb0 + u) + 2 * q) = c[u];
-  };
-  // block (rb, cb) -= L(rb, p) L(cb, p)^T
-  auto update_block = [&](int rb, int cb, int p) {
-    double2* cp = reinterpret_cast<double2*>(sT + (rb * 8 + g) * LDW + 8 * cb + 2 * q);
-    const double* ap = sT + (rb * 8 + g) * LDW + 8 * p + q;
-    const double* bp = sT + (cb * 8 + g) * LDW + 8 * p + q;
-    double2 c = *cp;
-    dmma(c.x, c.y, -ap[0], bp[0]);
-    dmma(c.x, c.y, -ap[4], bp[4]);
-    *cp = c;
+      *cpB = make_double2(cB.x + eB0, cB.y + eB1);
+    } else {
+#pragma unroll 2
+      for (int k = 0; k < nk; k++) {
+        dmma(cA.x, cA.y, -apA[8 * k], bp[8 * k]);
+        dmma(eA0, eA1, -apA[8 * k + 4], bp[8 * k + 4]);
+      }
+    }
+    *cpA = make_double2(cA.x + eA0, cA.y + eA1);
   };
   // the verdict on a pivot block travels through the panel's closing barrier (warp 0 runs ahead of the others: a flag
   // in shared memory could be read on both sides of its next store)
@@ -957,19 +974,15 @@ static __device__ bool factor_diag(double* sT, double* sWp, double* misc, const 
       __threadfence_block();
       __syncwarp();
       bar1_arrive();  // L(p+1, p) is in place
-      update_block(p + 1, p + 1, p);
+      update_pair(p + 1, 16, p + 1, p + 1);
       __syncwarp();
       bad = pivot_block(sT, sWp, p + 1) ? 0 : 1;
     } else {
-      for (int rb = p + 1 + ln.warp; rb < 16; rb += NWARP - 1) solve_block(rb, p, b0, b1);
+      const int rbA = p + 1 + ln.warp, rbB = rbA + NWARP - 1;  // at most 14 blocks below (p+1, p+1) for 7 warps
+      if (rbA < 16) solve_block(rbA, p, b0, b1);
+      if (rbB < 16) solve_block(rbB, p, b0, b1);
       bar1_sync();
-      // trailing blocks of rows p+2 .. 15 in groups of four along the row, dealt round-robin to the seven warps
-      int turn = ln.warp - 1;
-      for (int rb = 15; rb > p + 1; rb--)
-        for (int cb0 = p + 1; cb0 <= rb; cb0 += 4) {
-          if (turn == 0) update_row4(rb, cb0, p);
-          turn = turn == 0 ? NWARP - 2 : turn - 1;
-        }
+      if (rbA < 16) update_pair(rbA, rbB, p + 1, p + 1);
     }
     if (__syncthreads_or(bad)) return false;
   }

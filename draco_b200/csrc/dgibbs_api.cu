@@ -592,7 +592,7 @@ static int run_core(dgibbs_handle h, const dgibbs_problem* p, dgibbs_result* r, 
       for (int i = 0; i < 16; i++) pc[i] = 0;
     }
     static const char* names[12] = {"prepass", "phase0_gemm", "diag_gemm", "diag_stage_factor", "diag_storeW", "row_stage_addG",
-                                    "row_gemm", "(unused)", "row_trimul_store", "back_gemm", "back_trimul", "draw"};
+                                    "row_gemm", "diag_stage_gen", "row_trimul_store", "back_gemm", "back_trimul", "draw"};
     double tot = 0;
     for (int i = 0; i < 12; i++) tot += (double)pc[i];
     for (int i = 0; i < 12; i++)

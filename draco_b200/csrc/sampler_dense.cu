@@ -223,11 +223,16 @@ __global__ void __launch_bounds__(THREADS, 1) dense_sampler_kernel(DevBatch d, i
         if (use_tma) gemm_nt_tma(&tmap, ring, pipe, acc, ln, slot, j * TILE, j * TILE, j * (TILE / TKC), ln.warp < 4 ? V_DIAG_LO : V_DIAG_HI);
         else gemm_nt(pipe, acc, ln, Bp, Bp, npad, j * (TILE / KC), ln.warp < 4 ? V_DIAG_LO : V_DIAG_HI);
         PROF(2);
-        stage_acc(acc, pipe, ln, true, true);
+        if (interior_j) {  // generated part added in registers on the way to the staged tile
+          acc_add_diag_win(acc, ln, cwin, Si, j * TILE);
+          stage_acc(acc, pipe, ln, true, true);
+        } else {
+          stage_acc(acc, pipe, ln, true, true);
+          __syncthreads();
+          add_generated(pipe, ct, Si, N, nsys, d.cplx, j, j, true);
+        }
         __syncthreads();
-        if (interior_j) add_generated_diag_win(pipe, cwin, Si, j * TILE);
-        else add_generated(pipe, ct, Si, N, nsys, d.cplx, j, j, true);
-        __syncthreads();
+        PROF(7);
         alive = factor_diag(pipe, sWp, misc, ln);
         if (!alive) break;
         PROF(3);
