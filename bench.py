@@ -300,13 +300,13 @@ def fp64_peak_tflops():
 
 
 # dram__bytes_read.sum + dram__bytes_write.sum of dense_sampler_kernel<1> (TMA operand ring, register tri-solves) from the
-# committed `ncu --set full` capture profiles/r03c_dense_sampler_ncu_raw.csv: 66.74 GB read + 6.23 GB written for a launch
-# of 296 baseline-iterations of cfg2 geometry = 246.5 MB per baseline-iteration (r02p, before the register tri-solves:
-# 66.78 + 6.22; the r01 captures of the cp.async kernel: 72.8-73.0 GB).  Twice the A-panel model: the B row panel is re-read per row tile and
+# committed `ncu --set full` capture profiles/r03n_dense_sampler_ncu_raw.csv: 66.73 GB read + 6.22 GB written for a launch
+# of 296 baseline-iterations of cfg2 geometry = 246.5 MB per baseline-iteration (r03c / r02p, earlier kernels of the
+# round: 66.74 + 6.23 / 66.78 + 6.22; the r01 captures of the cp.async kernel: 72.8-73.0 GB).  Twice the A-panel model: the B row panel is re-read per row tile and
 # does not stay in L2; 25 % of the DRAM peak, not the bound.
 # Reported per launch of THIS run by scaling with the launch's baseline-iterations (cfg2 geometry only).
-DENSE_TRAFFIC_PER_UNIT = (66.740086e9 + 6.226206e9) / 296
-DENSE_TRAFFIC_SOURCE = "ncu --set full capture of 296 baseline-iterations scaled to this launch (profiles/r03c_dense_sampler_ncu_raw.csv)"
+DENSE_TRAFFIC_PER_UNIT = (66.727257e9 + 6.224364e9) / 296
+DENSE_TRAFFIC_SOURCE = "ncu --set full capture of 296 baseline-iterations scaled to this launch (profiles/r03n_dense_sampler_ncu_raw.csv)"
 
 
 # dram__bytes_read.sum + dram__bytes_write.sum of diag_resident_kernel<384,0> from the committed `ncu --set full` capture
