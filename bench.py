@@ -34,6 +34,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
+T_START = time.perf_counter()
 METRIC = "baseline-Gibbs-iterations/sec @nfreq=1024"
 UNIT = "baseline-iterations/s"
 
@@ -55,7 +56,15 @@ def parse():
     ap.add_argument("--strong-nsamp", type=int, default=None)
     ap.add_argument("--diag-nbase", type=int, default=None, help="override the TOTAL pixels of the diag record (debug)")
     ap.add_argument("--e2e-steps", type=int, default=5, help="e2e is timed on min(steps, this) steps")
+    ap.add_argument("--budget-s", type=float, default=780.0,
+                    help="wall-clock budget of the whole run: an optional record (e2e_task / strong / diag) whose estimated "
+                         "cost would go past it is skipped and says so in the line")
     return ap.parse_args()
+
+
+def budget_allows(elapsed_s, estimate_s, budget_s):
+    """An optional record runs only if its estimated cost keeps the whole run inside the wall-clock budget."""
+    return budget_s <= 0 or elapsed_s + estimate_s <= budget_s
 
 
 def workload_label(cfg, nbase, nsamp):
@@ -570,14 +579,30 @@ def main():
     del pb_pin
 
     extra = {}
-    if not args.no_task:
+    skipped = {}
+    rate = value / world  # baseline-iterations/s of one GPU, for the cost estimates
+
+    def fits(name, est_s):
+        """True if the optional record `name` (estimated `est_s` seconds) still fits the run's wall-clock budget;
+        decided on the slowest rank's clock so that every rank takes the same branch (the records hold collectives)."""
+        el = torch.tensor([time.perf_counter() - T_START], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(el, op=dist.ReduceOp.MAX)
+        ok = budget_allows(float(el.item()), est_s, args.budget_s)
+        if not ok:
+            skipped[name] = f"skipped: {float(el.item()):.0f} s elapsed + ~{est_s:.0f} s estimated > --budget-s {args.budget_s:.0f}"
+        return ok
+
+    if not args.no_task and fits("e2e_task", 25.0 + 2.2 * nbase * nsamp / rate):
         extra["e2e_task"] = task_record(args, cfg, nsamp, nbase, rank, world, local, sync, handle)
     del pb_dev
     torch.cuda.empty_cache()
-    if not args.no_strong:
+    c4 = synth.CONFIGS["cfg4"]
+    strong_units = (args.strong_nbase or c4.nbase) * (args.strong_nsamp or c4.nsamp) / world
+    if not args.no_strong and fits("strong", 20.0 + 0.004 * (args.strong_nbase or c4.nbase) / world + 1.08 * strong_units / rate):
         extra["strong"] = strong_record(args, handle, rank, world, local, sync)
         torch.cuda.empty_cache()
-    if not args.no_diag:
+    if not args.no_diag and fits("diag", 15.0 + 45.0 * (args.diag_nbase or synth.CONFIGS["cfg3"].nbase) / 16384 / world):
         import bench_diag
 
         extra["diag"] = bench_diag.diag_record(args, handle, rank, world, local, sync)
@@ -620,6 +645,8 @@ def main():
         if extra.get("strong"):
             out["strong"] = extra.pop("strong")
         out["extra"] = {k: v for k, v in extra.items() if v is not None}
+        if skipped:
+            out["extra"]["skipped_for_time"] = skipped
         if not args.no_cpu_baseline and world == 1:
             out["cpu_baseline"] = cpu_baseline(cfg, nsamp)
         print(json.dumps(out))
