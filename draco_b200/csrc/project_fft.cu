@@ -13,9 +13,21 @@
 
 namespace dg {
 
-constexpr int PTHREADS = 256;  // 3 CTAs of 8 warps per SM at N = 2048 (512 threads measured slower: 3.3 vs 2.6 ms)
+constexpr int PTHREADS = 256;  // 8 warps per CTA (512 threads measured slower: 3.3 vs 2.6 ms)
+// Resident CTAs per SM the register allocation must allow.  Without a bound ptxas takes 98 registers: TWO CTAs per SM
+// at N = 2048 (ncu r02p: occupancy limited by registers and shared memory alike, 16 warps, long-scoreboard stalls
+// 4.8 per issue) although three 64 KB buffers fit; bounded to 3 it takes 79, no spills: 1.83 -> 1.47 ms for 2048
+// cfg3 baselines (profiles/r04c_proj_variants.log).  0 = no bound.
+#ifndef DGIBBS_PROJ_MINB
+#define DGIBBS_PROJ_MINB 3
+#endif
+#if DGIBBS_PROJ_MINB > 0
+#define DGIBBS_PROJ_BOUNDS __launch_bounds__(PTHREADS, DGIBBS_PROJ_MINB)
+#else
+#define DGIBBS_PROJ_BOUNDS __launch_bounds__(PTHREADS)
+#endif
 
-__global__ void __launch_bounds__(PTHREADS) diag_project_fft_kernel(DevBatch d, int ppb, long long nwork) {
+__global__ void DGIBBS_PROJ_BOUNDS diag_project_fft_kernel(DevBatch d, int ppb, long long nwork) {
   extern __shared__ __align__(16) double2 fsm[];
   double2* bufA = fsm;
   double2* bufB = fsm + d.N;
