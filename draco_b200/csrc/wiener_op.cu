@@ -320,15 +320,32 @@ extern "C" int dgwiener_construct(dgwiener_problem* p) {
   const size_t kbytes = p->filter_is_complex ? 16 : 8, cbytes = p->cov_is_complex ? 16 : 8;
   // solver 3 (and 0 = auto): every contraction, the factorisation and the solves on this repository's own DMMA kernels
   // (wiener_own.cu); 1 / 2: cuBLAS ZGEMM + cuSOLVER ZPOTRF (batched / per matrix) + cuBLAS ZTRSM
-  const bool own = p->solver == 3 || p->solver == 0;
+  // 4: as 3 with the three contractions on the INT8 tensor cores (Ozaki split, ozaki_gemm.cuh: tcgen05.mma kind::i8 + TMEM)
+  const bool own = p->solver == 3 || p->solver == 0 || p->solver == 4;
   int sm_count = 148;
   WCU(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, p->device_id));
   const dgw::OwnGeom og = dgw::own_geom(F, nd, sm_count);
   const dgw::OwnSizes oz = dgw::own_sizes(og);
-  const size_t per_pixel = own ? FF * (kbytes + cbytes) + 8 * (oz.Pr + oz.Pext + oz.T1r + oz.Ar + oz.Yr) + FD * 8 + (size_t)F * (8 + 16 + 1) + 64
+  const size_t pp_own = FF * (kbytes + cbytes) + 8 * (oz.Pr + oz.Pext + oz.T1r + oz.Ar + oz.Yr) + FD * 8 + (size_t)F * (8 + 16 + 1) + 64;
+  const size_t pp_int8 = pp_own + oz.qP + oz.qPe + 4 * (oz.eP + oz.ePe);
+  // default budget of a chunk: 32 GiB of the 180 GB, at most half of what is free (a full wave of F = 1024 pixels needs 15 / 23 GB)
+  size_t budget = (size_t)32 << 30;
+  if (p->workspace_bytes > 0) {
+    budget = (size_t)p->workspace_bytes;
+  } else {
+    size_t free_b = 0, total_b = 0;
+    if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) budget = std::max<size_t>((size_t)1 << 30, std::min(budget, free_b / 2));
+  }
+  // 0 (auto): the int8 contractions from F = 256 (measured faster there: profiles/r04i_perf_wiener_op.json.log) provided the
+  // budget still holds a full wave of pixels with their slices; the DMMA contractions otherwise
+  const size_t wave = std::min<size_t>((size_t)nra, (size_t)og.nslots);
+  const int ozaki = (p->solver == 4 || (p->solver == 0 && F >= 256 && budget / pp_int8 >= wave)) ? 1 : 0;
+  const size_t per_pixel = own ? (ozaki ? pp_int8 : pp_own)
                                : FF * (kbytes + cbytes + 3 * 16) + FD * (16 + 8) + (size_t)F * (8 + 16 + 1) + 64;
-  const size_t budget = p->workspace_bytes > 0 ? (size_t)p->workspace_bytes : ((size_t)8 << 30);
-  const int R = (int)std::max<size_t>(1, std::min<size_t>(std::min<size_t>((size_t)nra, 32768), budget / per_pixel));
+  int R = (int)std::max<size_t>(1, std::min<size_t>(std::min<size_t>((size_t)nra, 32768), budget / per_pixel));
+  // the factorisation runs one pixel per SM at a time: a chunk that is not the last one should fill whole waves
+  // (r04g: 296 pixels in chunks of 209 + 87 ran the solve kernel for 3 waves instead of 2)
+  if (own && R < nra && R > og.nslots) R -= R % og.nslots;
   // measured (profiles/r01j_perf_wiener_op.json.log): the batched factorisation wins up to F = 512 at least
   const bool batched = p->solver == 1;
 
@@ -353,6 +370,11 @@ extern "C" int dgwiener_construct(dgwiener_problem* p) {
     for (auto& it : own_list) {
       WCU(bufs.alloc(it.p, it.n * 8));
       WCU(cudaMemsetAsync(*it.p, 0, it.n * 8, L.stream));  // the padding of every matrix stays zero from here on
+    }
+    if (ozaki) {
+      WCU(bufs.alloc(&ob.qP, R * oz.qP)); WCU(bufs.alloc(&ob.qPe, R * oz.qPe)); WCU(bufs.alloc(&ob.qG, oz.qG)); WCU(bufs.alloc(&ob.qF, oz.qF));
+      WCU(bufs.alloc(&ob.eP, R * oz.eP * 4)); WCU(bufs.alloc(&ob.ePe, R * oz.ePe * 4)); WCU(bufs.alloc(&ob.eG, oz.eG * 4));
+      WCU(bufs.alloc(&ob.eF, oz.eF * 4));
     }
     WCU(dgw::own_configure());
   } else {
@@ -393,8 +415,8 @@ extern "C" int dgwiener_construct(dgwiener_problem* p) {
   launches += 2;
   flop += 8.0 * F * (double)F * nd;
   if (own) {
-    WCU(dgw::own_prepare_fourier(st, og, Fp, ob));
-    launches += 1;
+    WCU(dgw::own_prepare_fourier(st, og, Fp, ob, ozaki));
+    launches += 1 + ozaki;
   }
 
   for (int r0 = 0; r0 < nra; r0 += R) {
@@ -411,7 +433,7 @@ extern "C" int dgwiener_construct(dgwiener_problem* p) {
         launches += 1;
         WCU(cudaMemsetAsync(info, 0, (size_t)Rc * sizeof(int), st));
         WCU(dgw::own_chunk(st, og, ob, Rc, sm_count, FSFT, bp + (size_t)ee * F, K, p->filter_is_complex, C, p->cov_is_complex, M, rn,
-                           prior, window, outd, info, &launches));
+                           prior, window, outd, info, &launches, ozaki));
       } else {
       beam_scale_kernel<<<dim3((F + 127) / 128, F), 128, 0, st>>>(FSFT, bp + (size_t)ee * F, G, F);
       mask_noise_kernel<<<(unsigned)(((size_t)Rc * F + 255) / 256), 256, 0, st>>>(w, C, p->cov_is_complex, window, M, rn, Rc, F);

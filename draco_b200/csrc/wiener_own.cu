@@ -24,6 +24,7 @@
 #include <cstdlib>
 
 #include "dense_core.cuh"
+#include "ozaki_gemm.cuh"
 #include "tma_host.h"
 #include "tma_pipe.cuh"
 
@@ -57,6 +58,14 @@ OwnSizes own_sizes(const OwnGeom& g) {
   s.Fpr = (size_t)g.NDR * g.LD;
   s.work = (size_t)g.nslots * g.work_stride;
   s.Wp = (size_t)g.nslots * g.nblk * WP_DOUBLES;
+  s.qP = oz::slice_bytes(g.FR, g.LD);
+  s.qPe = oz::slice_bytes(g.LD, g.LD);
+  s.eP = oz::exp_ints(g.FR, g.LD);
+  s.ePe = oz::exp_ints(g.LD, g.LD);
+  s.qG = oz::slice_bytes(g.LD, g.LD);
+  s.qF = oz::slice_bytes(g.NDR, g.LD);
+  s.eG = oz::exp_ints(g.LD, g.LD);
+  s.eF = oz::exp_ints(g.NDR, g.LD);
   return s;
 }
 
@@ -75,6 +84,20 @@ __global__ void own_embed_g_kernel(const double2* __restrict__ FSFT, const doubl
   const double re = v.x * s, im = v.y * s;
   *reinterpret_cast<double2*>(Gext + (size_t)(2 * k) * LD + 2 * i) = make_double2(re, im);
   *reinterpret_cast<double2*>(Gext + (size_t)(2 * k + 1) * LD + 2 * i) = make_double2(-im, re);
+}
+
+// The transpose of Gext, written directly (solver 4: the int8 GEMM takes both operands with K contiguous, T1r = Pr (Gext^T)^T):
+// GextT[c][r] = Gext[r][c]
+__global__ void own_embed_gT_kernel(const double2* __restrict__ FSFT, const double* __restrict__ bp, double* __restrict__ GextT, int F,
+                                    int LD) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x, i = blockIdx.y;
+  if (k >= F) return;
+  const double s = sqrt(bp[i]) * sqrt(bp[k]);
+  const double2 v = FSFT[(size_t)k * F + i];
+  const double re = v.x * s, im = v.y * s;
+  // Gext[2k][2i] = re, Gext[2k][2i+1] = im, Gext[2k+1][2i] = -im, Gext[2k+1][2i+1] = re
+  *reinterpret_cast<double2*>(GextT + (size_t)(2 * i) * LD + 2 * k) = make_double2(re, -im);
+  *reinterpret_cast<double2*>(GextT + (size_t)(2 * i + 1) * LD + 2 * k) = make_double2(im, re);
 }
 
 // Pr (interleaved) and Pext from the filter K of the chunk: P = memory of H = diag(M) K (powerspec.py:281-283)
@@ -270,9 +293,11 @@ cudaError_t own_configure() {
   return cudaFuncSetAttribute(own_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)solve_smem());
 }
 
-cudaError_t own_prepare_fourier(cudaStream_t st, const OwnGeom& g, const cuDoubleComplex* Fp, const OwnBufs& b) {
+cudaError_t own_prepare_fourier(cudaStream_t st, const OwnGeom& g, const cuDoubleComplex* Fp, const OwnBufs& b, int ozaki) {
   own_pad_fourier_kernel<<<dim3((g.F + 127) / 128, g.nd), 128, 0, st>>>(reinterpret_cast<const double2*>(Fp), b.Fpr, g.F, g.nd, g.LD);
-  return cudaGetLastError();
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess || !ozaki) return e;
+  return oz::split(st, b.Fpr, 0, g.LD, g.NDR, g.LD, oz::TM, b.qF, 0, b.eF, 0, 1);
 }
 
 static cudaError_t launch_gemm(cudaStream_t st, int sm_count, const TileGemm& t) {
@@ -291,10 +316,81 @@ cudaError_t own_gemm(cudaStream_t st, int sm_count, const double* A, long long s
   return launch_gemm(st, sm_count, t);
 }
 
+// Solver 4: the three contractions on the INT8 tensor cores (ozaki_gemm.cuh: tcgen05.mma kind::i8, accumulators in TMEM)
+// instead of the DMMA tile GEMM; everything else (masks, noise, factorisation, solves, epilogue) as solver 3.
+//   T1r = Pr (Gext^T)^T      A operand: slices of Pr,  B operand: slices of Gext^T (once per elevation)
+//   Ar  = T1r Pext^T         A operand: slices of T1r (in the buffer Pr's slices leave), B operand: slices of Pext; lower tiles
+//   Yr  = Fpr Pext^T         A operand: slices of Fpr (once per call), B operand: the same slices of Pext
+static cudaError_t own_chunk_ozaki(cudaStream_t st, const OwnGeom& g, const OwnBufs& b, const OwnSizes& z, int Rc, int sm_count,
+                                   const cuDoubleComplex* FSFT, const double* beam_power_el, const void* K, int k_cplx, const void* C,
+                                   int c_cplx, const unsigned char* M, const cuDoubleComplex* rn, const double* prior, const double* window,
+                                   float2* outd, int* info, int64_t* launches) {
+  const size_t nFF = (size_t)Rc * g.F * g.F;
+  const int gridE = (int)std::min<size_t>((nFF + 255) / 256, (size_t)sm_count * 16);
+  cudaError_t e;
+  static const bool prof = getenv("DGWIENER_PROFILE") != nullptr;
+  cudaEvent_t ev[12] = {};
+  int nev = 0;
+  auto mark = [&]() {
+    if (prof && nev < 12) {
+      cudaEventCreate(&ev[nev]);
+      cudaEventRecord(ev[nev++], st);
+    }
+  };
+  mark();
+  // Gext is scratch here: it receives the transpose (its own layout is only needed by the DMMA NN GEMM)
+  own_embed_gT_kernel<<<dim3((g.F + 127) / 128, g.F), 128, 0, st>>>(reinterpret_cast<const double2*>(FSFT), beam_power_el, b.Gext, g.F,
+                                                                  g.LD);
+  own_prep_p_kernel<<<gridE, 256, 0, st>>>(K, k_cplx, M, b.Pr, b.Pext, g.F, g.LD, z.Pr, z.Pext, nFF);
+  if ((e = cudaGetLastError()) != cudaSuccess) return e;
+  mark();
+  if ((e = oz::split(st, b.Gext, 0, g.LD, g.LD, g.LD, oz::TN, b.qG, 0, b.eG, 0, 1)) != cudaSuccess) return e;
+  if ((e = oz::split(st, b.Pr, (long long)z.Pr, g.LD, g.FR, g.LD, oz::TM, b.qP, (long long)z.qP, b.eP, (long long)z.eP, Rc)) != cudaSuccess) return e;
+  if ((e = oz::split(st, b.Pext, (long long)z.Pext, g.LD, g.LD, g.LD, oz::TN, b.qPe, (long long)z.qPe, b.ePe, (long long)z.ePe, Rc)) != cudaSuccess)
+    return e;
+  mark();
+  oz::GemmParams t1{b.qP, (long long)z.qP, b.qG, 0, b.eP, (long long)z.eP, b.eG, 0, b.T1r, (long long)z.T1r, g.LD, g.FR, g.LD, g.LD, Rc, 0};
+  if ((e = oz::gemm_nt(st, sm_count, t1)) != cudaSuccess) return e;
+  mark();
+  if ((e = oz::split(st, b.T1r, (long long)z.T1r, g.LD, g.FR, g.LD, oz::TM, b.qP, (long long)z.qP, b.eP, (long long)z.eP, Rc)) != cudaSuccess) return e;
+  mark();
+  oz::GemmParams t2{b.qP, (long long)z.qP, b.qPe, (long long)z.qPe, b.eP, (long long)z.eP, b.ePe, (long long)z.ePe, b.Ar, (long long)z.Ar,
+                    g.LD, g.FR, g.LD, g.LD, Rc, 1};
+  if ((e = oz::gemm_nt(st, sm_count, t2)) != cudaSuccess) return e;
+  mark();
+  own_add_noise_kernel<<<gridE, 256, 0, st>>>(b.Ar, C, c_cplx, reinterpret_cast<const double2*>(rn), M, g.F, g.LD, z.Ar, nFF);
+  if ((e = cudaGetLastError()) != cudaSuccess) return e;
+  mark();
+  oz::GemmParams t3{b.qF, 0, b.qPe, (long long)z.qPe, b.eF, 0, b.ePe, (long long)z.ePe, b.Yr, (long long)z.Yr, g.LD, g.NDR, g.LD, g.LD, Rc, 0};
+  if ((e = oz::gemm_nt(st, sm_count, t3)) != cudaSuccess) return e;
+  mark();
+  SolveArgs a{b.Ar, z.Ar, b.Yr, z.Yr, b.work, g.work_stride, b.Wp, prior, window, M, outd, info, Rc, g.F, g.nd, g.LD, g.nblk, g.RT};
+  const int grid = Rc < g.nslots ? Rc : g.nslots;
+  CUtensorMap tm;
+  const int use_tma = tma_work_map(&tm, b.work, (size_t)g.LD + (size_t)g.RT * TILE, g.LD, g.work_stride, g.nslots,
+                                   sizeof(double) * WP_DOUBLES, TILE, TKC);
+  own_solve_kernel<<<grid, THREADS, solve_smem(), st>>>(a, use_tma, tm);
+  if ((e = cudaGetLastError()) != cudaSuccess) return e;
+  mark();
+  if (prof) {
+    cudaStreamSynchronize(st);
+    static const char* names[9] = {"embed^T + prep", "split G^T, P, Pext", "int8 gemm T1 = P G", "split T1", "int8 gemm A = T1 P^H (lower)",
+                                   "add noise", "int8 gemm Y = F' P^H", "factor + solve + epilogue", ""};
+    for (int i = 0; i + 1 < nev; i++) {
+      float ms = 0.f;
+      cudaEventElapsedTime(&ms, ev[i], ev[i + 1]);
+      fprintf(stderr, "[dgwiener ozaki] F=%d Rc=%d %-30s %9.3f ms\n", g.F, Rc, names[i], ms);
+    }
+    for (int i = 0; i < nev; i++) cudaEventDestroy(ev[i]);
+  }
+  if (launches) *launches += 12;
+  return cudaSuccess;
+}
+
 cudaError_t own_chunk(cudaStream_t st, const OwnGeom& g, const OwnBufs& b, int Rc, int sm_count, const cuDoubleComplex* FSFT,
                       const double* beam_power_el, const void* K, int k_cplx, const void* C, int c_cplx, const unsigned char* M,
                       const cuDoubleComplex* rn, const double* prior, const double* window, float2* outd, int* info,
-                      int64_t* launches) {
+                      int64_t* launches, int ozaki) {
   const OwnSizes z = own_sizes(g);
   const size_t nFF = (size_t)Rc * g.F * g.F;
   const int gridE = (int)std::min<size_t>((nFF + 255) / 256, (size_t)sm_count * 16);
@@ -303,6 +399,7 @@ cudaError_t own_chunk(cudaStream_t st, const OwnGeom& g, const OwnBufs& b, int R
   static const bool prof = getenv("DGWIENER_PROFILE") != nullptr;
   cudaEvent_t ev[8] = {};
   int nev = 0;
+  if (ozaki) return own_chunk_ozaki(st, g, b, z, Rc, sm_count, FSFT, beam_power_el, K, k_cplx, C, c_cplx, M, rn, prior, window, outd, info, launches);
   auto mark = [&]() {
     if (prof && nev < 8) {
       cudaEventCreate(&ev[nev]);

@@ -25,23 +25,30 @@ OwnGeom own_geom(int F, int nd, int sm_count);
 struct OwnSizes {
   size_t Pr, Pext, T1r, Ar, Yr;      // per pixel
   size_t Gext, Fpr, work, Wp;        // once
+  // int8 contractions (ozaki_gemm.cuh; solver 4): slice bytes / exponent ints of the operands
+  size_t qP, qPe, eP, ePe;           // per pixel: Pr (then T1r) as A operand, Pext as B operand
+  size_t qG, qF, eG, eF;             // once: Gext^T as B operand, Fpr as A operand
 };
 OwnSizes own_sizes(const OwnGeom& g);
 
 struct OwnBufs {
   double *Pr, *Pext, *T1r, *Ar, *Yr;  // [R][...]; must be zero-filled once after allocation (the padding stays zero)
   double *Gext, *Fpr, *work, *Wp;
+  // solver 4 only (null otherwise)
+  int8_t *qP, *qPe, *qG, *qF;
+  int *eP, *ePe, *eG, *eF;
 };
 
 cudaError_t own_configure();
 // Fpr (zero-padded row-major copy of F'^T: [nd][F] complex) from the column-major F' [F, nd]
-cudaError_t own_prepare_fourier(cudaStream_t st, const OwnGeom& g, const cuDoubleComplex* Fp, const OwnBufs& b);
+// (ozaki: also its int8 slices, for the contraction Y = F' P^H on the int8 tensor cores)
+cudaError_t own_prepare_fourier(cudaStream_t st, const OwnGeom& g, const cuDoubleComplex* Fp, const OwnBufs& b, int ozaki);
 // One chunk of Rc pixels of one elevation: out[r][d][f] = complex64(prior_d window_f (A_r^-1 R_r^T)[d][f]) with
 // A_r = H_r G H_r^H + N_r (powerspec.py:288-316); info[r] = 1 where A_r is not positive definite.
 cudaError_t own_chunk(cudaStream_t st, const OwnGeom& g, const OwnBufs& b, int Rc, int sm_count, const cuDoubleComplex* FSFT,
                       const double* beam_power_el, const void* K, int k_cplx, const void* C, int c_cplx, const unsigned char* M,
                       const cuDoubleComplex* rn, const double* prior, const double* window, float2* outd, int* info,
-                      int64_t* launches);
+                      int64_t* launches, int ozaki);
 
 // The tile GEMM by itself (used by the NRML objective, nrml_own.cu): C[b] = A[b] B[b] (nn = 1; A [M][K] pitch lda,
 // B [K][N] pitch ldb) or A[b] B[b]^T (nn = 0; B [N][K], both with pitch lda) over mt x nt output tiles of 128 x 128, K =

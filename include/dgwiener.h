@@ -34,9 +34,12 @@ typedef struct {
   int32_t nra, nel;         /* pixels: right ascension, local elevations                     */
   int32_t filter_is_complex; /* 0: filter is float64, 1: complex128 (RingMap "complex_filter") */
   int32_t cov_is_complex;    /* 0: freq_cov is float64, 1: complex128                          */
-  int32_t solver;           /* 0 auto (= 3), 3 this library's own DMMA kernels for every contraction,
-                               the factorisation and the solves; 1 / 2 cuBLAS + cuSOLVER (batched factorisation /
-                               per matrix on several streams) */
+  int32_t solver;           /* 0 auto (= 4 from F = 256 when the budget holds a full wave of pixels, else 3), 3 this
+                               library's own DMMA kernels for every contraction,
+                               the factorisation and the solves; 4 as 3 with the three contractions on the INT8
+                               tensor cores (Ozaki split of the fp64 operands into 8 signed 7-bit slices,
+                               tcgen05.mma kind::i8 with int32 accumulators in TMEM: fp64-equivalent results);
+                               1 / 2 cuBLAS + cuSOLVER (batched factorisation / per matrix on several streams) */
   const void* fourier;      /* [F, ndelay] complex128: exp(2 pi i freq tau) / sqrt(ntau), powerspec.py:229 */
   const double* prior;      /* [ndelay] diagonal signal prior, powerspec.py:233              */
   const double* window;     /* [F] spectral window (zero = channel not used), powerspec.py:207 */
@@ -46,7 +49,7 @@ typedef struct {
   const double* beam_power; /* [nel, F] dirty-beam power (its square root scales the prior), powerspec.py:266 */
   void* out;                /* complex64; operator of pixel (ra, el) = [ndelay, F] block at out + 8 * (ra * out_stride_ra + el * out_stride_el) */
   int64_t out_stride_ra, out_stride_el; /* in complex64 elements                               */
-  int64_t workspace_bytes;  /* device memory budget for one chunk of pixels (0: 8 GiB)       */
+  int64_t workspace_bytes;  /* device memory budget for one chunk of pixels (0: 32 GiB, at most half of the free memory) */
   int32_t out_on_device;    /* 1: out is a device pointer (same strides): the operator never visits the host */
   int32_t reserved;
   /* results */

@@ -34,7 +34,7 @@ def run(F, nra, nel, cplx, cpu_pixels):
     freq, weight, beam, filt, cov, win, S, tau, ntau = problem(F, nra, nel, cplx)
     Fm = wo.fourier_operator(freq, tau, ntau)
     res = {"F": F, "ndelay": int(tau.size), "nra": nra, "nel": nel, "complex_inputs": cplx}
-    solvers = ((1, "batched"), (2, "streams"), (3, "own_kernels"))
+    solvers = ((1, "batched"), (2, "streams"), (3, "own_kernels"), (4, "own_kernels_int8"))
     if os.environ.get("PERF_WIENER_ONLY"):  # e.g. PERF_WIENER_ONLY=3 for a launch list of the own-kernel path alone
         solvers = tuple(x for x in solvers if str(x[0]) == os.environ["PERF_WIENER_ONLY"])
     for solver, label in solvers:
@@ -62,7 +62,7 @@ def run(F, nra, nel, cplx, cpu_pixels):
     err = np.abs(got[:nr, 0] - ref[:, 0]).max() / np.abs(ref).max()
     res["max_rel_err_vs_oracle"] = float(err)
     k = "streams" if "streams" in res else "batched"
-    res["speedup_compute"] = round(res["oracle_cpu"]["ms_per_pixel"] * 1e3 / min(res[x]["us_per_pixel"] for x in ("batched", "streams", "own_kernels") if x in res), 1)
+    res["speedup_compute"] = round(res["oracle_cpu"]["ms_per_pixel"] * 1e3 / min(res[x]["us_per_pixel"] for x in ("batched", "streams", "own_kernels", "own_kernels_int8") if x in res), 1)
     print(json.dumps(res), flush=True)
 
 

@@ -65,11 +65,12 @@ def random_problem(F, nra, nel, cplx_filter, cplx_cov, seed, window="blackman"):
     return freq, weight, beam, filt, cov, win, S, tau, ntau
 
 
-@pytest.mark.parametrize("solver", [1, 2, 3])
+@pytest.mark.parametrize("solver", [1, 2, 3, 4])
 @pytest.mark.parametrize("cplx_filter,cplx_cov", [(False, False), (True, True), (True, False), (False, True)])
 def test_operator_matches_oracle(solver, cplx_filter, cplx_cov):
-    """Both factorisation paths (batched / per-matrix on several streams), every dtype combination, F not a
-    multiple of anything, several chunks of pixels (tiny workspace budget)."""
+    """Both library factorisation paths (batched / per-matrix on several streams), the own DMMA kernels (3) and the own
+    kernels with the contractions on the int8 tensor cores (4: Ozaki split, tcgen05 + TMEM); every dtype combination, F
+    not a multiple of anything, several chunks of pixels (tiny workspace budget)."""
     freq, weight, beam, filt, cov, win, S, tau, ntau = random_problem(52, 7, 3, cplx_filter, cplx_cov, 77)
     ref = wo.construct_operator(freq, weight, beam, filt, cov, win, S, tau, ntau)
     t = {}
@@ -77,6 +78,29 @@ def test_operator_matches_oracle(solver, cplx_filter, cplx_cov):
                                           solver=solver, workspace_bytes=3 * 52 * 52 * 100, timing=t)
     close_c64(got, ref)
     assert t["launches"] > 0 and t["flop"] > 0
+
+
+def test_auto_solver_takes_the_int8_contractions_from_256_channels():
+    """solver = 0 picks the int8 tensor-core contractions (solver 4) from F = 256 and the DMMA ones (3) below; both agree
+    with the oracle at complex64 resolution."""
+    freq, weight, beam, filt, cov, win, S, tau, ntau = random_problem(256, 3, 1, True, False, 79)
+    ref = wo.construct_operator(freq, weight, beam, filt, cov, win, S, tau, ntau)
+    Fm = wo.fourier_operator(freq, tau, ntau)
+    t0, t3, t4 = {}, {}, {}
+    got0 = powerspec.wiener_delay_operator(Fm, S, win, filt, cov, weight, beam, timing=t0)
+    got3 = powerspec.wiener_delay_operator(Fm, S, win, filt, cov, weight, beam, solver=3, timing=t3)
+    got4 = powerspec.wiener_delay_operator(Fm, S, win, filt, cov, weight, beam, solver=4, timing=t4)
+    for got in (got0, got3, got4):
+        close_c64(got, ref)
+    assert t0["launches"] == t4["launches"] > t3["launches"]  # the split kernels of the int8 path
+    np.testing.assert_array_equal(got0, got4)
+    small = random_problem(52, 2, 1, False, False, 80)
+    ts0, ts3 = {}, {}
+    args = (wo.fourier_operator(small[0], small[7], small[8]), small[6], small[5], small[3], small[4], small[1], small[2])
+    a = powerspec.wiener_delay_operator(*args, timing=ts0)
+    b = powerspec.wiener_delay_operator(*args, solver=3, timing=ts3)
+    assert ts0["launches"] == ts3["launches"]
+    np.testing.assert_array_equal(a, b)
 
 
 def test_strided_output_and_larger_band():
