@@ -16,7 +16,7 @@ LIB = os.path.join(HERE, "libdgibbs.so")
 # NRML likelihood object: separate library because it links cuBLAS / cuSOLVER
 NRML_LIB = os.path.join(HERE, "libdgnrml.so")
 NRML_SOURCES = ["nrml.cu", "wiener_op.cu", "wiener_own.cu", "nrml_own.cu"]
-NRML_HEADERS = [os.path.join("..", "..", "include", "dgnrml.h"), os.path.join("..", "..", "include", "dgwiener.h"), "wiener_own.h", "nrml_own.h",
+NRML_HEADERS = [os.path.join("..", "..", "include", "dgnrml.h"), os.path.join("..", "..", "include", "dgwiener.h"), "wiener_own.h", "nrml_own.h", "ozaki_gemm.cuh",
                 "dense_core.cuh", "tma_pipe.cuh", "tma_host.h", "common.cuh", "internal.h"]
 SOURCES = ["dgibbs_api.cu", "setup_kernels.cu", "sampler_dense.cu", "sampler_diag.cu", "sampler_cross.cu", "sampler_freq.cu", "project_fft.cu", "cut_kernels.cu", "finish_kernels.cu", "delay_fft.cu"]
 HEADERS = ["common.cuh", "internal.h", "dense_core.cuh", "tma_pipe.cuh", "tma_host.h", "window.cuh", "fft_fused.cuh", os.path.join("..", "..", "include", "dgibbs.h")]

@@ -1,7 +1,7 @@
 // fp64 GEMM on the INT8 tensor cores (Ozaki split):  C[b] = A[b] B[b]^T  for fp64 A [M][K], B [N][K] (K contiguous).
 //
 // tcgen05.mma has no f64 kind, so fp64 contractions otherwise run on the DMMA pipe (37 TFLOP/s).  Here every operand row
-// is split, per block of 128 columns, into S signed 7-bit slices under one exponent,
+// is split, per block of 256 columns, into S signed 7-bit slices under one exponent,
 //     x = 2^e (q_0 2^-6 + q_1 2^-13 + ... + q_{S-1} 2^-(6 + 7 (S - 1))),   q_s in [-64, 64]   (oz_split_kernel)
 // and     A B^T = sum_kb 2^(e_i + f_j) sum_{d < S} 2^-(12 + 7 d) D_d,   D_d = sum_{s + t = d} Q_s R_t^T
 // with the D_d exact in int32: S (S + 1) / 2 int8 GEMMs on tcgen05.mma.cta_group::1.kind::i8 (M = 128, N = 64, K = 32),
@@ -9,13 +9,14 @@
 // error against the exact product is BELOW that of an fp64 FMA chain (1.2e-15 vs 2.2e-15 of |A||B|^T on rows spanning 12
 // decades, profiles/r04f_ozaki_gemm.log; the accuracy study of the split: scratch/ozaki_study.py).
 //
-// Kernel (oz_gemm_kernel, 9 warps, one 128 x 64 output tile per CTA at a time, persistent grid):
+// Kernel (oz_gemm_kernel, 10 warps, one 128 x 64 output tile per CTA at a time, persistent grid):
 //   * the split kernel writes the slices of a (tile, 64-column K stage) as ONE contiguous block in the canonical
 //     no-swizzle K-major core-matrix order (8 rows x 16 bytes), so a stage arrives as flat cp.async.bulk copies completing
 //     on an mbarrier; descriptors: LBO = K-direction stride of the core matrices, SBO = 8-row-group stride (= 128 B);
-//   * warp 8: one elected thread is TMA producer AND MMA issuer: two stages in flight, a stage is refilled as soon as the
-//     tcgen05.commit behind its MMAs arrives; descriptors are base + constant (one uniform add per operand per MMA);
-//   * warps 0-7: epilogue per 128-column block: tcgen05.ld 32x32b, int64 combination of the diagonals, x 2^(e_i + f_j),
+//   * warp 9: one elected thread is the TMA producer: two stages in flight, a stage buffer is refilled as soon as the
+//     tcgen05.commit behind its MMAs arrives;  warp 8: one elected thread issues the MMAs (72 per stage; descriptors are
+//     base + constant: one uniform add per operand per MMA);
+//   * warps 0-7: epilogue per 256-column block: tcgen05.ld 32x32b, int64 combination of the diagonals, x 2^(e_i + f_j),
 //     fp64 accumulation in registers (two warps per TMEM lane quarter).  TMEM is full, so the epilogue of a block and the
 //     MMAs of the next do not overlap; the operands of the next block stream in underneath.
 // Measured on B200 (296 x [512 x 1024 x 1024], S = 8): 53.2 TFLOP/s-equivalent against 35.7 for cuBLAS
@@ -27,31 +28,34 @@
 namespace dgw {
 namespace oz {
 
-constexpr int TM = 128, TN = 64, KB = 128, KS = 64;  // output tile, exponent block, K stage
-constexpr int NTHREADS = 288;                       // 8 epilogue warps + 1 producer / issuer warp
+constexpr int TM = 128, TN = 64, KS = 64;  // output tile, K stage (columns per TMA stage)
+constexpr int BST = 4, KB = BST * KS;      // exponent block: 4 stages = 256 columns (the last block of a row may hold 2)
+constexpr int NTHREADS = 320;              // 8 epilogue warps + MMA issuer warp + TMA producer warp
 constexpr int S = 8;                                // slices: fp64-equivalent
 
 // ------------------------------------------------------------------------------------------------ split
-// One warp per (8 rows, 128 columns): lane = (row % 8) + 8 * (16-column chunk of a stage).  A thread holds its row's 16
-// columns of both stages, so every slice leaves as one 16-byte store and a warp's stores are 4 x 128 contiguous bytes.
-//   q: [b][tile = row / TR][stage = k / 64][s][k16 (4)][row group (TR / 8)][row % 8][k % 16],  ex: [b][k / 128][rows]
+// One warp per (8 rows, exponent block): lane = (row % 8) + 8 * (16-column chunk of a stage).  A thread takes its row's 16
+// columns of a stage at a time, so every slice leaves as one 16-byte store and a warp's stores are 4 x 128 contiguous
+// bytes.  K % 128 == 0: a block holds 4 stages, the last one of a row possibly 2.
+//   q: [b][tile = row / TR][stage = k / 64][s][k16 (4)][row group (TR / 8)][row % 8][k % 16],  ex: [b][block][rows]
 template <int NS>
 __global__ void __launch_bounds__(256) oz_split_kernel(const double* __restrict__ X, long long sX, int ld, int rows, int K, int TR,
                                                        int8_t* __restrict__ q, long long sQ, int* __restrict__ ex, long long sE, int batch) {
   const long long warp = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const int lane = threadIdx.x & 31, nkb = K / KB, ng = rows >> 3;
+  const int lane = threadIdx.x & 31, nks = K / KS, nkb = (nks + BST - 1) / BST, ng = rows >> 3;
   if (warp >= (long long)batch * ng * nkb) return;
   const int g8 = (int)(warp % ng), kb = (int)((warp / ng) % nkb), b = (int)(warp / ((long long)ng * nkb));
   const int r = g8 * 8 + (lane & 7), kc = lane >> 3;
-  double m[2][16];
+  const int nst = min(BST, nks - kb * BST);
+  const double* xrow = X + (size_t)b * sX + (size_t)r * ld + (size_t)kb * BST * KS + kc * 16;
+  // pass 1: the block's row maximum (the values are read again from L1 / L2 below: keeping 4 x 16 doubles per thread
+  // costs 176 registers and leaves one CTA per SM on a bandwidth-bound kernel)
   double amax = 0.0;
-#pragma unroll
-  for (int st = 0; st < 2; st++) {
-    const double4* src = reinterpret_cast<const double4*>(X + (size_t)b * sX + (size_t)r * ld + kb * KB + st * KS + kc * 16);
+  for (int st = 0; st < nst; st++) {
+    const double4* src = reinterpret_cast<const double4*>(xrow + st * KS);
 #pragma unroll
     for (int v = 0; v < 4; v++) {
       const double4 t = src[v];
-      m[st][4 * v] = t.x; m[st][4 * v + 1] = t.y; m[st][4 * v + 2] = t.z; m[st][4 * v + 3] = t.w;
       amax = fmax(amax, fmax(fmax(fabs(t.x), fabs(t.y)), fmax(fabs(t.z), fabs(t.w))));
     }
   }
@@ -63,14 +67,19 @@ __global__ void __launch_bounds__(256) oz_split_kernel(const double* __restrict_
     if (f == 0.5) e -= 1;              // exact power of two: |x 2^-e| <= 1 still holds
   }
   if (kc == 0) ex[(size_t)b * sE + (size_t)kb * rows + r] = e;
-  const int tile = r / TR, rr = r % TR, nks = K / KS, ntile = rows / TR;
+  const int tile = r / TR, rr = r % TR;
   const double sc = __longlong_as_double((long long)(6 - e + 1023) << 52);  // 2^(6 - e); |e| is far inside the normal range
+  // pass 2: stage by stage, 16 columns per thread, S slices of 16 bytes each
+  for (int st = 0; st < nst; st++) {
+    const double4* src = reinterpret_cast<const double4*>(xrow + st * KS);
+    double m[16];
 #pragma unroll
-  for (int st = 0; st < 2; st++) {
-    int8_t* dst = q + (size_t)b * sQ + (((size_t)tile * nks + (kb * 2 + st)) * NS) * TR * KS + (size_t)kc * TR * 16 + (size_t)(rr >> 3) * 128 +
-                  (rr & 7) * 16;
-#pragma unroll
-    for (int c = 0; c < 16; c++) m[st][c] *= sc;
+    for (int v = 0; v < 4; v++) {
+      const double4 t = src[v];
+      m[4 * v] = t.x * sc; m[4 * v + 1] = t.y * sc; m[4 * v + 2] = t.z * sc; m[4 * v + 3] = t.w * sc;
+    }
+    int8_t* dst = q + (size_t)b * sQ + (((size_t)tile * nks + (kb * BST + st)) * NS) * TR * KS + (size_t)kc * TR * 16 +
+                  (size_t)(rr >> 3) * 128 + (rr & 7) * 16;
 #pragma unroll
     for (int s = 0; s < NS; s++) {
       uint32_t w[4];
@@ -79,8 +88,8 @@ __global__ void __launch_bounds__(256) oz_split_kernel(const double* __restrict_
         w[v] = 0;
 #pragma unroll
         for (int c = 0; c < 4; c++) {
-          const double qv = rint(m[st][4 * v + c]);
-          m[st][4 * v + c] = (m[st][4 * v + c] - qv) * 128.0;  // exact
+          const double qv = rint(m[4 * v + c]);
+          m[4 * v + c] = (m[4 * v + c] - qv) * 128.0;  // exact
           w[v] |= ((uint32_t)(uint8_t)(int8_t)(int)qv) << (8 * c);
         }
       }
@@ -200,7 +209,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) oz_gemm_kernel(GemmParams p) {
   __shared__ __align__(8) uint64_t bar_full[2], bar_free[2], bar_acc, bar_empty;
   __shared__ uint32_t tmem_base_s;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int mt = p.M / TM, nt = p.N / TN, nkb = p.K / KB, nks = p.K / KS;
+  const int mt = p.M / TM, nt = p.N / TN, nks = p.K / KS, nkb = (nks + BST - 1) / BST;
   const long long per = (long long)mt * nt, ntiles = (long long)p.batch * per;
   // this CTA's tiles: blockIdx.x, + gridDim.x, ... without the ones a lower-only result does not need (complex column
   // 32 in of tile column `in` against complex row 128 im + 127 of tile row `im`)
@@ -230,8 +239,27 @@ __global__ void __launch_bounds__(NTHREADS, 1) oz_gemm_kernel(GemmParams p) {
   tc_fence_after();
   const uint32_t tmem = tmem_base_s;
 
-  if (warp == 8) {
-    // ------------------------------------------------------------ producer + MMA issuer
+  if (warp == 9) {
+    // ------------------------------------------------------------ TMA producer: the CTA's stream of stages, two in flight
+    if (elect_one()) {
+      unsigned g = 0;  // stages loaded so far; stage g lives in buffer g & 1, its k-th use being k = g >> 1
+      for (long long tile = next_tile(blockIdx.x); tile < ntiles; tile = next_tile(tile + gridDim.x)) {
+        const int b = (int)(tile / per), rem = (int)(tile % per), im = rem / nt, in = rem % nt;
+        const int8_t* ga = p.qa + (size_t)b * p.sQA + (size_t)im * nks * A_ST;
+        const int8_t* gb = p.qb + (size_t)b * p.sQB + (size_t)in * nks * B_ST;
+        for (int ks = 0; ks < nks; ks++, g++) {
+          const int buf = g & 1;
+          if (g >= 2) mbar_wait(&bar_free[buf], ((g >> 1) - 1) & 1);  // the MMAs of the buffer's previous stage have read it
+          uint8_t* sa = oz_smem + buf * STAGE;
+          mbar_expect_tx(&bar_full[buf], STAGE);
+          for (int c = 0; c < A_ST; c += 8192) bulk_g2s(sa + c, ga + (size_t)ks * A_ST + c, 8192, &bar_full[buf]);
+          for (int c = 0; c < B_ST; c += 4096) bulk_g2s(sa + A_ST + c, gb + (size_t)ks * B_ST + c, 4096, &bar_full[buf]);
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 8) {
+    // ------------------------------------------------------------ MMA issuer
     if (elect_one()) {
       const uint32_t idesc = umma_idesc_i8(TM, TN);
       uint64_t da0[2], db0[2];
@@ -239,55 +267,33 @@ __global__ void __launch_bounds__(NTHREADS, 1) oz_gemm_kernel(GemmParams p) {
         da0[st] = umma_desc(smem_u32(oz_smem + st * STAGE), TM * 16, 128);
         db0[st] = umma_desc(smem_u32(oz_smem + st * STAGE + A_ST), TN * 16, 128);
       }
-      auto load_stage = [&](long long tile, int kb, int st) {
-        const int b = (int)(tile / per), rem = (int)(tile % per), im = rem / nt, in = rem % nt;
-        const int ks = kb * 2 + st;
-        const int8_t* ga = p.qa + (size_t)b * p.sQA + ((size_t)im * nks + ks) * A_ST;
-        const int8_t* gb = p.qb + (size_t)b * p.sQB + ((size_t)in * nks + ks) * B_ST;
-        uint8_t* sa = oz_smem + st * STAGE;
-        mbar_expect_tx(&bar_full[st], STAGE);
-        for (int c = 0; c < A_ST; c += 8192) bulk_g2s(sa + c, ga + c, 8192, &bar_full[st]);
-        for (int c = 0; c < B_ST; c += 4096) bulk_g2s(sa + A_ST + c, gb + c, 4096, &bar_full[st]);
-      };
-      long long tile = next_tile(blockIdx.x);
-      if (tile < ntiles) {
-        load_stage(tile, 0, 0);
-        load_stage(tile, 0, 1);
-      }
-      unsigned n = 0;  // K blocks issued so far by this CTA
-      while (tile < ntiles) {
-        const long long after = next_tile(tile + gridDim.x);
+      unsigned g = 0, n = 0;  // stages / exponent blocks issued so far by this CTA
+      for (long long tile = next_tile(blockIdx.x); tile < ntiles; tile = next_tile(tile + gridDim.x)) {
         for (int kb = 0; kb < nkb; kb++, n++) {
+          const int nst = min(BST, nks - kb * BST);
           if (n > 0) mbar_wait(&bar_empty, (n - 1) & 1);  // the epilogue has drained the accumulators of the previous block
           tc_fence_after();
-#pragma unroll
-          for (int st = 0; st < 2; st++) {
-            mbar_wait(&bar_full[st], n & 1);
+          for (int q = 0; q < nst; q++, g++) {
+            const int buf = g & 1;
+            mbar_wait(&bar_full[buf], (g >> 1) & 1);
             tc_fence_after();
+            const uint64_t dab = da0[buf], dbb = db0[buf];
 #pragma unroll
             for (int j = 0; j < KS / 32; j++)
 #pragma unroll
               for (int s = 0; s < NS; s++) {
-                const uint64_t da = da0[st] + (uint64_t)((s * TM * KS + j * 2 * TM * 16) >> 4);
+                const uint64_t da = dab + (uint64_t)((s * TM * KS + j * 2 * TM * 16) >> 4);
 #pragma unroll
                 for (int t = 0; t < NS - s; t++) {
-                  const uint64_t db = db0[st] + (uint64_t)((t * TN * KS + j * 2 * TN * 16) >> 4);
-                  umma_i8(tmem + (uint32_t)(s + t) * TN, da, db, idesc, (st > 0 || j > 0 || s > 0) ? 1u : 0u);
+                  const uint64_t db = dbb + (uint64_t)((t * TN * KS + j * 2 * TN * 16) >> 4);
+                  // every diagonal d is first touched by (stage 0, j = 0, s = 0, t = d) of its block: that MMA overwrites
+                  umma_i8(tmem + (uint32_t)(s + t) * TN, da, db, idesc, (j > 0 || s > 0) ? 1u : (q > 0 ? 1u : 0u));
                 }
               }
-            umma_commit(&bar_free[st]);  // arrives when the MMAs issued so far have read their operands
+            umma_commit(&bar_free[buf]);  // arrives when the MMAs issued so far have read their operands
           }
           umma_commit(&bar_acc);
-          // refill both stages with the next K block of this CTA's work (possibly the next tile's first block)
-          const bool last = kb + 1 == nkb;
-          const long long ntile = last ? after : tile;
-          if (ntile < ntiles)
-            for (int st = 0; st < 2; st++) {
-              mbar_wait(&bar_free[st], n & 1);
-              load_stage(ntile, last ? 0 : kb + 1, st);
-            }
         }
-        tile = after;
       }
     }
     __syncwarp();
@@ -336,13 +342,13 @@ __global__ void __launch_bounds__(NTHREADS, 1) oz_gemm_kernel(GemmParams p) {
 
 // ------------------------------------------------------------------------------------------------ host
 inline size_t slice_bytes(size_t rows, size_t K) { return rows * K * S; }     // per matrix
-inline size_t exp_ints(size_t rows, size_t K) { return rows * (K / KB); }     // per matrix
+inline size_t exp_ints(size_t rows, size_t K) { return rows * ((K / KS + BST - 1) / BST); }  // per matrix
 constexpr int gemm_smem() { return 2 * S * (TM + TN) * KS; }
 
 // rows % TR == 0 (TR = 128 for an A operand, 64 for a B operand), K % 128 == 0, 16-byte aligned rows (ld % 2 == 0)
 inline cudaError_t split(cudaStream_t st, const double* X, long long sX, int ld, int rows, int K, int TR, int8_t* q, long long sQ, int* ex,
                          long long sE, int batch) {
-  const long long warps = (long long)batch * (rows / 8) * (K / KB);
+  const long long warps = (long long)batch * (rows / 8) * ((K / KS + BST - 1) / BST);
   if (warps <= 0) return cudaSuccess;
   oz_split_kernel<S><<<(unsigned)((warps * 32 + 255) / 256), 256, 0, st>>>(X, sX, ld, rows, K, TR, q, sQ, ex, sE, batch);
   return cudaGetLastError();
