@@ -28,5 +28,6 @@ print(f"# ncu --metrics gpu__time_duration.sum --clock-control none -c 400: {wha
 for n, (c, ms) in sorted(agg.items(), key=lambda kv: -kv[1][1]):
     print(f"{n:60s} {c:6d} launches {ms:12.3f} ms {100 * ms / tot:6.2f} %")
 own = sum(ms for n, (c, ms) in agg.items()
-          if "dg::" in n or "dgw::" in n or "dgn::" in n or n.startswith("<unnamed>::") or n.startswith("void <unnamed>::"))  # (anonymous namespaces of csrc/)
+          if "dg::" in n or "dgw::" in n or "dgn::" in n or "oz::oz_" in n  # oz:: = dgw::oz (csrc/ozaki_gemm.cuh; ncu prints the inner namespace)
+          or n.startswith("<unnamed>::") or n.startswith("void <unnamed>::"))  # (anonymous namespaces of csrc/)
 print(f"# kernels of this repository: {100 * own / tot:.2f} % of the device time")

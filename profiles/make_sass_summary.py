@@ -2,7 +2,8 @@
     python profiles/make_sass_summary.py > profiles/sass_summary.txt
 DMMA = fp64 tensor pipe (mma.sync m8n8k4.f64), LDGSTS = cp.async, UBLKCP = cp.async.bulk (1-D TMA), UTMALDG =
 cp.async.bulk.tensor (tiled TMA through a tensor map), SYNCS = mbarrier operations, UCGABAR = cluster barrier,
-UTCMMA / LDTM = tcgen05 (none: tcgen05 has no f64 kind)."""
+UTCIMMA / LDTM = tcgen05 (tcgen05.mma kind::i8 / tcgen05.ld: the Ozaki-split int8 GEMM of csrc/ozaki_gemm.cuh; tcgen05 has no
+f64 kind, so the fp64 kernels carry none)."""
 import collections
 import os
 import re
@@ -10,7 +11,7 @@ import subprocess
 import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-KEYS = ["DMMA", "DFMA", "LDGSTS", "UBLKCP", "UTMALDG", "UTMASTG", "SYNCS", "UCGABAR", "BAR.SYNC", "UTCMMA", "LDTM", "LDS", "STS"]
+KEYS = ["DMMA", "DFMA", "LDGSTS", "UBLKCP", "UTMALDG", "UTMASTG", "SYNCS", "UCGABAR", "BAR.SYNC", "UTCIMMA", "LDTM", "LDS", "STS"]
 
 
 def demangle(names):

@@ -103,6 +103,20 @@ def test_auto_solver_takes_the_int8_contractions_from_256_channels():
     np.testing.assert_array_equal(a, b)
 
 
+def test_int8_contractions_with_a_short_last_exponent_block():
+    """F = 160: the padded real width is 384 = one exponent block of four 64-column stages and one of two; two row tiles,
+    six column tiles, lower-only tiles of A (csrc/ozaki_gemm.cuh)."""
+    freq, weight, beam, filt, cov, win, S, tau, ntau = random_problem(160, 4, 2, True, True, 81, window="uniform")
+    ref = wo.construct_operator(freq, weight, beam, filt, cov, win, S, tau, ntau)
+    Fm = wo.fourier_operator(freq, tau, ntau)
+    got4 = powerspec.wiener_delay_operator(Fm, S, win, filt, cov, weight, beam, solver=4)
+    got3 = powerspec.wiener_delay_operator(Fm, S, win, filt, cov, weight, beam, solver=3)
+    close_c64(got4, ref)
+    close_c64(got3, ref)
+    # both paths compute in (at least) fp64: they differ from each other far less than either differs from complex64 rounding
+    assert np.abs(got4.astype(np.complex128) - got3).max() <= 4e-7 * np.abs(ref).max()
+
+
 def test_strided_output_and_larger_band():
     """F = 160 (per-matrix path by default), the output written into a [pol, ra, el, delay, freq] slab."""
     freq, weight, beam, filt, cov, win, S, tau, ntau = random_problem(160, 5, 2, False, False, 78, window="uniform")
