@@ -510,6 +510,60 @@ extern "C" int dgwiener_construct(dgwiener_problem* p) {
   return 0;
 }
 
+extern "C" int dgwiener_gemm_ozaki(int32_t device_id, const double* A, const double* B, double* C, int32_t M, int32_t N, int32_t K,
+                                   int32_t batch, double* ms_device) {
+  g_err.clear();
+  if (device_id < 0 || device_id >= 64) return -1;
+  if (M < 0 || N < 0 || K < 0 || batch < 0 || M % 128 || N % 64 || K % 128) {
+    g_err = "dgwiener_gemm_ozaki: M % 128, N % 64 and K % 128 must be 0";
+    return -5;
+  }
+  if (ms_device) *ms_device = 0.0;
+  if ((size_t)M * N * batch == 0) return 0;
+  if (!A || !B || !C) return -2;
+  {
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || device_id >= count) {
+      g_err = "no CUDA device " + std::to_string(device_id) + " (there is no CPU fallback)";
+      cudaGetLastError();
+      return 100;
+    }
+  }
+  WCU(cudaSetDevice(device_id));
+  if (int rc = init_libs(device_id)) return rc;
+  WLibs& L = g_wlibs[device_id];
+  cudaStream_t st = L.stream;
+  int sm_count = 148;
+  WCU(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, device_id));
+  const dgw::OzakiScratch z = dgw::own_gemm_ozaki_sizes(M, N, K, batch);
+  DevBufs bufs;
+  double *dA, *dB, *dC;
+  int8_t *qa, *qb;
+  int *ea, *eb;
+  const size_t nA = (size_t)batch * M * K, nB = (size_t)batch * N * K, nC = (size_t)batch * M * N;
+  WCU(bufs.alloc(&dA, nA * 8)); WCU(bufs.alloc(&dB, nB * 8)); WCU(bufs.alloc(&dC, nC * 8));
+  WCU(bufs.alloc(&qa, z.qa)); WCU(bufs.alloc(&qb, z.qb)); WCU(bufs.alloc(&ea, z.ea * 4)); WCU(bufs.alloc(&eb, z.eb * 4));
+  if (K > 0) {
+    WCU(cudaMemcpyAsync(dA, A, nA * 8, cudaMemcpyHostToDevice, st));
+    WCU(cudaMemcpyAsync(dB, B, nB * 8, cudaMemcpyHostToDevice, st));
+  }
+  WCU(cudaEventRecord(L.evA, st));
+  if (K > 0) {
+    WCU(dgw::own_gemm_ozaki(st, sm_count, dA, dB, dC, M, N, K, batch, qa, qb, ea, eb));
+  } else {
+    WCU(cudaMemsetAsync(dC, 0, nC * 8, st));
+  }
+  WCU(cudaEventRecord(L.ev1, st));
+  WCU(cudaMemcpyAsync(C, dC, nC * 8, cudaMemcpyDeviceToHost, st));
+  WCU(cudaStreamSynchronize(st));
+  if (ms_device) {
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, L.evA, L.ev1);
+    *ms_device = ms;
+  }
+  return 0;
+}
+
 extern "C" int dgwiener_apply(dgwiener_apply_problem* p) {
   g_err.clear();
   if (!p) return -1;

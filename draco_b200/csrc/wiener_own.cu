@@ -450,4 +450,24 @@ cudaError_t own_chunk(cudaStream_t st, const OwnGeom& g, const OwnBufs& b, int R
   return cudaSuccess;
 }
 
+OzakiScratch own_gemm_ozaki_sizes(int M, int N, int K, int batch) {
+  OzakiScratch z{};
+  z.qa = (size_t)batch * oz::slice_bytes(M, K);
+  z.qb = (size_t)batch * oz::slice_bytes(N, K);
+  z.ea = (size_t)batch * oz::exp_ints(M, K);
+  z.eb = (size_t)batch * oz::exp_ints(N, K);
+  return z;
+}
+
+cudaError_t own_gemm_ozaki(cudaStream_t st, int sm_count, const double* A, const double* B, double* C, int M, int N, int K, int batch,
+                           int8_t* qa, int8_t* qb, int* ea, int* eb) {
+  const long long sQA = (long long)oz::slice_bytes(M, K), sQB = (long long)oz::slice_bytes(N, K);
+  const long long sEA = (long long)oz::exp_ints(M, K), sEB = (long long)oz::exp_ints(N, K);
+  cudaError_t e;
+  if ((e = oz::split(st, A, (long long)M * K, K, M, K, oz::TM, qa, sQA, ea, sEA, batch)) != cudaSuccess) return e;
+  if ((e = oz::split(st, B, (long long)N * K, K, N, K, oz::TN, qb, sQB, eb, sEB, batch)) != cudaSuccess) return e;
+  oz::GemmParams p{qa, sQA, qb, sQB, ea, sEA, eb, sEB, C, (long long)M * N, N, M, N, K, batch, 0};
+  return oz::gemm_nt(st, sm_count, p);
+}
+
 }  // namespace dgw

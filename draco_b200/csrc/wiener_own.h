@@ -57,4 +57,15 @@ cudaError_t own_chunk(cudaStream_t st, const OwnGeom& g, const OwnBufs& b, int R
 cudaError_t own_gemm(cudaStream_t st, int sm_count, const double* A, long long sA, int lda, const double* B, long long sB, int ldb,
                      double* C, long long sC, int ldc, int mt, int nt, int kchunks, int nn, int lower_only, int batch);
 
+// The int8 tensor-core GEMM by itself (ozaki_gemm.cuh) on device-resident fp64 operands: C[b] = A[b] B[b]^T, A [M][K],
+// B [N][K], C [M][N] row-major and dense; M % 128 == N % 64 == K % 128 == 0.  Scratch: slice bytes / exponent ints from
+// own_gemm_ozaki_sizes.
+struct OzakiScratch {
+  size_t qa, qb;  // bytes
+  size_t ea, eb;  // ints
+};
+OzakiScratch own_gemm_ozaki_sizes(int M, int N, int K, int batch);
+cudaError_t own_gemm_ozaki(cudaStream_t st, int sm_count, const double* A, const double* B, double* C, int M, int N, int K, int batch,
+                           int8_t* qa, int8_t* qb, int* ea, int* eb);
+
 }  // namespace dgw

@@ -34,7 +34,8 @@ else:
     _ContainerTask = _compat.ContainerTask
     containers = _compat
 
-WIENER_EXPORTED = ["dgwiener_construct", "dgwiener_apply", "dgwiener_sizeof", "dgwiener_apply_sizeof", "dgwiener_last_error"]
+WIENER_EXPORTED = ["dgwiener_construct", "dgwiener_apply", "dgwiener_sizeof", "dgwiener_apply_sizeof", "dgwiener_last_error",
+                   "dgwiener_gemm_ozaki"]
 _vp = C.c_void_p
 
 
@@ -79,6 +80,9 @@ def load_wiener():
         lib.dgwiener_apply.argtypes = [C.POINTER(WienerApplyProblem)]
         lib.dgwiener_apply.restype = C.c_int
         lib.dgwiener_apply_sizeof.restype = C.c_int
+        lib.dgwiener_gemm_ozaki.argtypes = [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32,
+                                            C.POINTER(C.c_double)]
+        lib.dgwiener_gemm_ozaki.restype = C.c_int
         for st, fn in ((WienerProblem, lib.dgwiener_sizeof), (WienerApplyProblem, lib.dgwiener_apply_sizeof)):
             if fn() != C.sizeof(st):
                 raise RuntimeError(f"ABI mismatch: {st.__name__} is {C.sizeof(st)} bytes here, {fn()} in libdgnrml.so; "
@@ -169,6 +173,30 @@ def wiener_delay_operator(fourier, prior, window, filt, freq_cov, weight, beam_p
         raise _glib.DGibbsError(f"dgwiener_construct failed ({rc}): {lib.dgwiener_last_error().decode()}")
     if timing is not None:
         timing.update(ms_device=p.ms_device, ms_compute=p.ms_compute, flop=p.flop, launches=p.launches)
+    return out
+
+
+def gemm_nt_int8(A, B, device=0, timing=None):
+    """``A @ B.T`` (last two axes; a leading batch axis is allowed) for float64 operands on the INT8 tensor cores: the
+    contraction kernel of ``solver=4`` by itself (``dgwiener_gemm_ozaki``, ``csrc/ozaki_gemm.cuh``): 8 signed 7-bit slices per
+    row and 256 columns, ``tcgen05.mma kind::i8``, int32 accumulators in TMEM -- results of fp64 quality (error ~1e-15 of the
+    product of the row maxima).  Shapes: ``A [.., M, K]``, ``B [.., N, K]`` with ``M % 128 == N % 64 == K % 128 == 0``."""
+    A = np.ascontiguousarray(A, dtype=np.float64)
+    B = np.ascontiguousarray(B, dtype=np.float64)
+    if A.ndim not in (2, 3) or B.ndim != A.ndim or A.shape[-1] != B.shape[-1] or (A.ndim == 3 and A.shape[0] != B.shape[0]):
+        raise ValueError(f"gemm_nt_int8: incompatible shapes {A.shape} and {B.shape}")
+    batch = A.shape[0] if A.ndim == 3 else 1
+    M, K, N = A.shape[-2], A.shape[-1], B.shape[-2]
+    if M % 128 or N % 64 or K % 128:
+        raise ValueError("gemm_nt_int8: M % 128, N % 64 and K % 128 must be 0")
+    out = np.empty(A.shape[:-1] + (N,), dtype=np.float64)
+    ms = C.c_double(0.0)
+    lib = load_wiener()
+    rc = lib.dgwiener_gemm_ozaki(int(device), A.ctypes.data, B.ctypes.data, out.ctypes.data, M, N, K, batch, C.byref(ms))
+    if rc != 0:
+        raise _glib.DGibbsError(f"dgwiener_gemm_ozaki failed ({rc}): {lib.dgwiener_last_error().decode()}")
+    if timing is not None:
+        timing["ms_device"] = ms.value
     return out
 
 

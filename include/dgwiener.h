@@ -87,6 +87,16 @@ typedef struct {
 } dgwiener_apply_problem;
 
 int dgwiener_apply(dgwiener_apply_problem* p);
+
+/* The contraction kernel of solver 4 by itself:  C[b] = A[b] B[b]^T  on the INT8 tensor cores (fp64 operands split into 8
+ * signed 7-bit slices per row and block of 256 columns, tcgen05.mma kind::i8, int32 accumulators in TMEM; fp64-equivalent
+ * results: csrc/ozaki_gemm.cuh).  It stands where the reference calls numpy's matmul on complex128 operands
+ * (draco/analysis/powerspec.py:288-304: H (FSF^H o bb^T) H^H and F^H H^H); exported so that tests hold the kernel BIT FOR BIT to
+ * the host emulation of its integer arithmetic (oracle/ozaki_emulation.py, tests/test_gpu_ozaki_gemm.py).
+ * A [batch][M][K], B [batch][N][K], C [batch][M][N]: float64, C-contiguous HOST pointers; M % 128 == N % 64 == K % 128 == 0
+ * (-5 otherwise).  ms_device (may be NULL): device time of split + GEMM. */
+int dgwiener_gemm_ozaki(int32_t device_id, const double* A, const double* B, double* C, int32_t M, int32_t N, int32_t K, int32_t batch,
+                        double* ms_device);
 int dgwiener_sizeof(void);
 int dgwiener_apply_sizeof(void);
 const char* dgwiener_last_error(void);
