@@ -5,8 +5,10 @@
 // factorisation is spread over the whole grid:
 //
 //   * every complex matrix is row-major with interleaved (re, im) doubles and a 128-padded real pitch (a column-major
-//     complex [M, N] array IS the row-major [N][M] one); products are REAL tile GEMMs of exactly the complex flop count
-//     through dgw::own_gemm (wiener_own.cu): C = Um Um_ext^T (lower tiles), W = Ut XC_emb, G = Ut U_ext^T, K = W Ut_ext^T;
+//     complex [M, N] array IS the row-major [N][M] one); products are REAL GEMMs of exactly the complex flop count:
+//     C = Um Um_ext^T (lower tiles), W = Ut XC_emb, G = Ut U_ext^T, K = W Ut_ext^T -- since r04 on the INT8 tensor cores
+//     (Ozaki split, tcgen05.mma kind::i8, fp64-equivalent: ozaki_gemm.cuh through dgw::own_gemm_ozaki_pitched); DGNRML_NO_INT8=1
+//     keeps the DMMA tile GEMM dgw::own_gemm (wiener_own.cu);
 //   * the Hermitian system runs in its real embedding E (2M x 2M, identity in the padding) through a RIGHT-LOOKING
 //     blocked Cholesky over 128-wide block columns: per block column one CTA factors the diagonal tile (factor_diag
 //     of dense_core.cuh: 8-column panels, 8 x 8 inverses only), one CTA per tile below it applies inv(L_jj)^T, and a
@@ -16,7 +18,9 @@
 //     5 launches per block column; every tile operation is a DMMA GEMM on 128 x 128 x 128.
 #include "nrml_own.h"
 
+#include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 
 #include "dense_core.cuh"
 #include "wiener_own.h"
@@ -265,6 +269,14 @@ cudaError_t own_alloc(Own& o, int M, int N, int sm_count, cudaStream_t st) {
   }
   cudaError_t e = cudaMalloc((void**)&o.flag, sizeof(int));
   if (e != cudaSuccess) return e;
+  o.int8 = getenv("DGNRML_NO_INT8") == nullptr;
+  if (o.int8) {  // scratch of the int8 contractions: the largest A operand (Um or Ut / W rows) and B operand (an extension)
+    const dgw::OzakiScratch z1 = dgw::own_gemm_ozaki_sizes(o.MR, o.LDM, o.LDN, 1), z2 = dgw::own_gemm_ozaki_sizes(o.NR, o.LDN, o.LDM, 1);
+    if ((e = cudaMalloc((void**)&o.qa, std::max(z1.qa, z2.qa))) != cudaSuccess) return e;
+    if ((e = cudaMalloc((void**)&o.qb, std::max(z1.qb, z2.qb))) != cudaSuccess) return e;
+    if ((e = cudaMalloc((void**)&o.ea, std::max(z1.ea, z2.ea) * sizeof(int))) != cudaSuccess) return e;
+    if ((e = cudaMalloc((void**)&o.eb, std::max(z1.eb, z2.eb) * sizeof(int))) != cudaSuccess) return e;
+  }
   if (o.LDM > 2 * M) own_pad_diag_kernel<<<(o.LDM - 2 * M + 127) / 128, 128, 0, st>>>(o.T, 2 * M, o.LDM);  // identity in the padding
   for (auto kern : {(const void*)rl_diag_kernel}) {
     e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_factor());
@@ -285,6 +297,8 @@ void own_free(Own& o) {
   for (double* p : {o.MFm, o.Um, o.UmExt, o.Q, o.T, o.XCemb, o.UrowExt, o.UtrowExt, o.Wrow, o.G, o.K, o.Wpg, o.logl})
     if (p) cudaFree(p);
   if (o.flag) cudaFree(o.flag);
+  for (void* p : {(void*)o.qa, (void*)o.qb, (void*)o.ea, (void*)o.eb})
+    if (p) cudaFree(p);
   o = Own{};
 }
 
@@ -301,6 +315,14 @@ cudaError_t own_set_mf(Own& o, const cuDoubleComplex* MF_rowmajor, cudaStream_t 
   return cudaGetLastError();
 }
 
+// C = A B^T (both operands with K contiguous): the INT8 tensor-core GEMM (fp64-equivalent, ozaki_gemm.cuh) or the DMMA tile GEMM
+static cudaError_t gemm_nt(Own& o, cudaStream_t st, const double* A, int lda, const double* B, int ldb, double* C, int ldc, int Mr, int Nc,
+                           int K, int lower_only) {
+  if (o.int8) return dgw::own_gemm_ozaki_pitched(st, o.sm_count, A, lda, B, ldb, C, ldc, Mr, Nc, K, lower_only, o.qa, o.qb, o.ea, o.eb);
+  if (lda != ldb) return cudaErrorInvalidValue;  // the DMMA NT form shares one pitch
+  return dgw::own_gemm(st, o.sm_count, A, 0, lda, B, 0, ldb, C, 0, ldc, Mr / TILE, Nc / TILE, K / KC, 0, lower_only, 1);
+}
+
 cudaError_t own_precompute(Own& o, cudaStream_t st, const double* sq, const cuDoubleComplex* U_colmajor,
                            const cuDoubleComplex* X_colmajor, const double* noise, double* t_dev, double* scal_dev,
                            int* info_host, int64_t* launches) {
@@ -314,9 +336,7 @@ cudaError_t own_precompute(Own& o, cudaStream_t st, const double* sq, const cuDo
   own_rows_kernel<<<2048, 256, 0, st>>>(reinterpret_cast<const double2*>(X_colmajor), M, M, o.CiX(), LDM, nullptr);
   nl += 3;
   // Q = Um Um^H on and below the diagonal: Q[i][j] = C(i, j) - noise
-  if ((e = dgw::own_gemm(st, o.sm_count, o.Um, 0, LDN, o.UmExt, 0, LDN, o.Q, 0, LDM, o.MR / TILE, LDM / TILE, LDN / KC, 0, 1, 1)) !=
-      cudaSuccess)
-    return e;
+  if ((e = gemm_nt(o, st, o.Um, LDN, o.UmExt, LDN, o.Q, LDM, o.MR, LDM, LDN, 1)) != cudaSuccess) return e;
   own_finish_kernel<<<dim3((M + 127) / 128, M), 128, 0, st>>>(o.Q, noise, reinterpret_cast<const double2*>(X_colmajor), o.T, o.XCemb, M,
                                                             LDM);
   nl += 2;
@@ -350,9 +370,14 @@ cudaError_t own_precompute(Own& o, cudaStream_t st, const double* sq, const cuDo
   }
   if ((e = cudaGetLastError()) != cudaSuccess) return e;
   // W = (X - C) Ut :  Wrow = Utrow XCemb ;  t ;  log det, trace
-  if ((e = dgw::own_gemm(st, o.sm_count, o.Ut(), 0, LDM, o.XCemb, 0, LDM, o.Wrow, 0, LDM, o.NR / TILE, LDM / TILE, LDM / KC, 1, 0, 1)) !=
-      cudaSuccess)
+  // (the real embedding of the Hermitian X - C is symmetric, so the int8 path takes it as the [N][K] operand of an NT product;
+  // the two readings differ by the rounding asymmetry of the caller's X(i, j) against conj X(j, i))
+  if (o.int8) {
+    if ((e = gemm_nt(o, st, o.Ut(), LDM, o.XCemb, LDM, o.Wrow, LDM, o.NR, LDM, LDM, 0)) != cudaSuccess) return e;
+  } else if ((e = dgw::own_gemm(st, o.sm_count, o.Ut(), 0, LDM, o.XCemb, 0, LDM, o.Wrow, 0, LDM, o.NR / TILE, LDM / TILE, LDM / KC, 1, 0,
+                                1)) != cudaSuccess) {
     return e;
+  }
   own_row_dot_kernel<<<(N + 7) / 8, 256, 0, st>>>(o.Ut(), o.Wrow, t_dev, M, N, LDM);
   own_scalars_kernel<<<1, 256, 0, st>>>(o.logl, nblk, o.CiX(), M, LDM, scal_dev);
   nl += 3;
@@ -363,15 +388,11 @@ cudaError_t own_precompute(Own& o, cudaStream_t st, const double* sq, const cuDo
 cudaError_t own_hessian_terms(Own& o, cudaStream_t st, int exact, int64_t* launches) {
   cudaError_t e;
   // G[b][a] = sum_i Utrow[b][i] conj(Urow[a][i]) = (U^H Ut)(a, b)
-  if ((e = dgw::own_gemm(st, o.sm_count, o.Ut(), 0, o.LDM, o.UrowExt, 0, o.LDM, o.G, 0, o.LDN, o.NR / TILE, o.LDN / TILE, o.LDM / KC, 0, 0,
-                         1)) != cudaSuccess)
-    return e;
+  if ((e = gemm_nt(o, st, o.Ut(), o.LDM, o.UrowExt, o.LDM, o.G, o.LDN, o.NR, o.LDN, o.LDM, 0)) != cudaSuccess) return e;
   if (launches) *launches += 1;
   if (exact) {  // K[b][a] = sum_i Wrow[b][i] conj(Utrow[a][i]) = (Ut^H W)(a, b)
     own_ext_rows_kernel<<<2048, 256, 0, st>>>(o.Ut(), o.N, o.M, o.LDM, o.UtrowExt);
-    if ((e = dgw::own_gemm(st, o.sm_count, o.Wrow, 0, o.LDM, o.UtrowExt, 0, o.LDM, o.K, 0, o.LDN, o.NR / TILE, o.LDN / TILE, o.LDM / KC, 0,
-                           0, 1)) != cudaSuccess)
-      return e;
+    if ((e = gemm_nt(o, st, o.Wrow, o.LDM, o.UtrowExt, o.LDM, o.K, o.LDN, o.NR, o.LDN, o.LDM, 0)) != cudaSuccess) return e;
     if (launches) *launches += 2;
   }
   return cudaGetLastError();

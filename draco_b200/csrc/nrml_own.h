@@ -16,6 +16,11 @@ struct Own {
   double *MFm = nullptr, *Um = nullptr, *UmExt = nullptr, *Q = nullptr, *T = nullptr, *XCemb = nullptr, *UrowExt = nullptr,
          *UtrowExt = nullptr, *Wrow = nullptr, *G = nullptr, *K = nullptr, *Wpg = nullptr, *logl = nullptr;
   int* flag = nullptr;
+  // the products C = U U^H, W = (X - C) Ut, G = U^H Ut, K = Ut^H W on the INT8 tensor cores (ozaki_gemm.cuh) unless
+  // DGNRML_NO_INT8 is set when the objective is created: slices / exponents of one A and one B operand
+  int int8 = 0;
+  int8_t *qa = nullptr, *qb = nullptr;
+  int *ea = nullptr, *eb = nullptr;
   // views into T
   double* Ut() const { return T + (size_t)nblk * 128 * LDM; }                 // [NR][LDM] rows = columns of C^-1 U
   double* CiX() const { return T + (size_t)(nblk + rtU) * 128 * LDM; }        // [MR][LDM] rows = columns of C^-1 X

@@ -470,4 +470,13 @@ cudaError_t own_gemm_ozaki(cudaStream_t st, int sm_count, const double* A, const
   return oz::gemm_nt(st, sm_count, p);
 }
 
+cudaError_t own_gemm_ozaki_pitched(cudaStream_t st, int sm_count, const double* A, int lda, const double* B, int ldb, double* C, int ldc,
+                                   int M, int N, int K, int lower_only, int8_t* qa, int8_t* qb, int* ea, int* eb) {
+  cudaError_t e;
+  if ((e = oz::split(st, A, 0, lda, M, K, oz::TM, qa, 0, ea, 0, 1)) != cudaSuccess) return e;
+  if ((e = oz::split(st, B, 0, ldb, N, K, oz::TN, qb, 0, eb, 0, 1)) != cudaSuccess) return e;
+  oz::GemmParams p{qa, 0, qb, 0, ea, 0, eb, 0, C, 0, ldc, M, N, K, 1, lower_only};
+  return oz::gemm_nt(st, sm_count, p);
+}
+
 }  // namespace dgw

@@ -67,5 +67,9 @@ struct OzakiScratch {
 OzakiScratch own_gemm_ozaki_sizes(int M, int N, int K, int batch);
 cudaError_t own_gemm_ozaki(cudaStream_t st, int sm_count, const double* A, const double* B, double* C, int M, int N, int K, int batch,
                            int8_t* qa, int8_t* qb, int* ea, int* eb);
+// One product with row pitches (the drop-in for own_gemm(..., nn = 0, ..., batch = 1) of the NRML objective): C = A B^T, A [M][K]
+// pitch lda, B [N][K] pitch ldb, C [M][N] pitch ldc; lower_only as in own_gemm.  Scratch sized by own_gemm_ozaki_sizes(M, N, K, 1).
+cudaError_t own_gemm_ozaki_pitched(cudaStream_t st, int sm_count, const double* A, int lda, const double* B, int ldb, double* C, int ldc,
+                                   int M, int N, int K, int lower_only, int8_t* qa, int8_t* qb, int* ea, int* eb);
 
 }  // namespace dgw
