@@ -32,6 +32,10 @@ constexpr int TM = 128, TN = 64, KS = 64;  // output tile, K stage (columns per 
 constexpr int BST = 4, KB = BST * KS;      // exponent block: 4 stages = 256 columns (the last block of a row may hold 2)
 constexpr int NTHREADS = 320;              // 8 epilogue warps + MMA issuer warp + TMA producer warp
 constexpr int S = 8;                                // slices: fp64-equivalent
+// Exponent written for a row block that holds a NaN, an infinity or a magnitude >= 2^960 (whose products overflow fp64
+// anyway): every output that touches the block is NaN -- a non-finite operand must stay loud (fmax() skips NaNs and the
+// conversion of a NaN to int8 gives 0: without this a NaN would silently count as zero).  Row blocks below 2^-960 count as zero.
+constexpr int E_NONFINITE = 1 << 20, E_LIMIT = 960;
 
 // ------------------------------------------------------------------------------------------------ split
 // One warp per (8 rows, exponent block): lane = (row % 8) + 8 * (16-column chunk of a stage).  A thread takes its row's 16
@@ -39,7 +43,7 @@ constexpr int S = 8;                                // slices: fp64-equivalent
 // bytes.  K % 128 == 0: a block holds 4 stages, the last one of a row possibly 2.
 //   q: [b][tile = row / TR][stage = k / 64][s][k16 (4)][row group (TR / 8)][row % 8][k % 16],  ex: [b][block][rows]
 template <int NS>
-__global__ void __launch_bounds__(256) oz_split_kernel(const double* __restrict__ X, long long sX, int ld, int rows, int K, int TR,
+__global__ void __launch_bounds__(256, 3) oz_split_kernel(const double* __restrict__ X, long long sX, int ld, int rows, int K, int TR,
                                                        int8_t* __restrict__ q, long long sQ, int* __restrict__ ex, long long sE, int batch) {
   const long long warp = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31, nks = K / KS, nkb = (nks + BST - 1) / BST, ng = rows >> 3;
@@ -51,24 +55,32 @@ __global__ void __launch_bounds__(256) oz_split_kernel(const double* __restrict_
   // pass 1: the block's row maximum (the values are read again from L1 / L2 below: keeping 4 x 16 doubles per thread
   // costs 176 registers and leaves one CTA per SM on a bandwidth-bound kernel)
   double amax = 0.0;
+  int bad = 0;  // a NaN or an infinity in the block (x - x is 0 for every finite x)
   for (int st = 0; st < nst; st++) {
     const double4* src = reinterpret_cast<const double4*>(xrow + st * KS);
 #pragma unroll
     for (int v = 0; v < 4; v++) {
       const double4 t = src[v];
       amax = fmax(amax, fmax(fmax(fabs(t.x), fabs(t.y)), fmax(fabs(t.z), fabs(t.w))));
+      bad |= !((t.x - t.x) + (t.y - t.y) + (t.z - t.z) + (t.w - t.w) == 0.0);
     }
   }
   amax = fmax(amax, __shfl_xor_sync(0xffffffffu, amax, 8));
   amax = fmax(amax, __shfl_xor_sync(0xffffffffu, amax, 16));
+  bad |= __shfl_xor_sync(0xffffffffu, bad, 8);
+  bad |= __shfl_xor_sync(0xffffffffu, bad, 16);
   int e = 0;
   if (amax > 0.0) {
     const double f = frexp(amax, &e);  // amax = f 2^e, f in [0.5, 1)
     if (f == 0.5) e -= 1;              // exact power of two: |x 2^-e| <= 1 still holds
   }
+  const bool zero = bad || e < -E_LIMIT;  // no slices: a non-finite block is carried by its exponent, a tiny one is 0
+  if (bad || e > E_LIMIT) e = E_NONFINITE;
+  else if (zero) e = 0;
   if (kc == 0) ex[(size_t)b * sE + (size_t)kb * rows + r] = e;
   const int tile = r / TR, rr = r % TR;
-  const double sc = __longlong_as_double((long long)(6 - e + 1023) << 52);  // 2^(6 - e); |e| is far inside the normal range
+  const bool noslice = zero || e == E_NONFINITE;
+  const double sc = noslice ? 0.0 : __longlong_as_double((long long)(6 - e + 1023) << 52);  // 2^(6 - e), |e| <= 960
   // pass 2: stage by stage, 16 columns per thread, S slices of 16 bytes each
   for (int st = 0; st < nst; st++) {
     const double4* src = reinterpret_cast<const double4*>(xrow + st * KS);
@@ -76,7 +88,8 @@ __global__ void __launch_bounds__(256) oz_split_kernel(const double* __restrict_
 #pragma unroll
     for (int v = 0; v < 4; v++) {
       const double4 t = src[v];
-      m[4 * v] = t.x * sc; m[4 * v + 1] = t.y * sc; m[4 * v + 2] = t.z * sc; m[4 * v + 3] = t.w * sc;
+      m[4 * v] = noslice ? 0.0 : t.x * sc; m[4 * v + 1] = noslice ? 0.0 : t.y * sc;
+      m[4 * v + 2] = noslice ? 0.0 : t.z * sc; m[4 * v + 3] = noslice ? 0.0 : t.w * sc;
     }
     int8_t* dst = q + (size_t)b * sQ + (((size_t)tile * nks + (kb * BST + st)) * NS) * TR * KS + (size_t)kc * TR * 16 +
                   (size_t)(rr >> 3) * 128 + (rr & 7) * 16;
@@ -323,7 +336,9 @@ __global__ void __launch_bounds__(NTHREADS, 1) oz_gemm_kernel(GemmParams p) {
             int Dd[NS];
 #pragma unroll
             for (int d = 0; d < NS; d++) Dd[d] = (int)D[d][c];
-            acc[c0 + c] += combine<NS>(Dd) * pow2i(ea_row + __ldg(ebp + c0 + c));
+            const int es = ea_row + __ldg(ebp + c0 + c);
+            // (a non-finite row block on either side: NaN, and it stays NaN through the remaining blocks)
+            acc[c0 + c] += es >= E_NONFINITE / 2 ? __longlong_as_double(0x7ff8000000000000ll) : combine<NS>(Dd) * pow2i(es);
           }
         }
         tc_fence_before();

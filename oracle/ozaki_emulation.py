@@ -19,14 +19,24 @@ import numpy as np
 
 STAGE = 64
 BLOCK_STAGES = 4
+# a row block with a NaN, an infinity or a magnitude >= 2^960 carries this exponent and no slices: every output that touches it
+# is NaN (a non-finite operand stays loud); a block below 2^-960 counts as zero
+E_NONFINITE = 1 << 20
+E_LIMIT = 960
 
 
 def split_block(X, nslice=8):
     """(e, q): ``X[i, k] ~ 2^e[i] sum_s q[s, i, k] 2^-(6 + 7 s)``; q integer-valued float64 in [-64, 64]."""
-    amax = np.abs(X).max(axis=1) if X.shape[1] else np.zeros(X.shape[0])
-    f, x = np.frexp(amax)  # amax = f 2^x, f in [0.5, 1)
+    bad = ~np.isfinite(X).all(axis=1)
+    with np.errstate(invalid="ignore"):
+        amax = np.fmax.reduce(np.abs(X), axis=1, initial=0.0)  # fmax: NaNs are skipped, as on the device
+    f, x = np.frexp(np.where(np.isfinite(amax), amax, 0.0))  # amax = f 2^x, f in [0.5, 1)
     e = np.where(amax > 0, np.where(f == 0.5, x - 1, x), 0).astype(np.int64)
-    r = X * np.exp2(6.0 - e)[:, None]  # exact
+    bad |= e > E_LIMIT
+    zero = bad | (e < -E_LIMIT)
+    e = np.where(bad, E_NONFINITE, np.where(zero, 0, e))
+    with np.errstate(invalid="ignore", over="ignore"):
+        r = np.where(zero[:, None], 0.0, X * np.exp2(6.0 - np.where(zero, 0, e))[:, None])  # exact
     q = np.empty((nslice,) + X.shape)
     for s in range(nslice):
         q[s] = np.rint(r)
@@ -68,7 +78,9 @@ def gemm_nt(A, B, nslice=8, block_columns=STAGE * BLOCK_STAGES, return_accumulat
         for d in range(4, nslice):
             lo = lo * 128 + D[d]
         comb = hi.astype(np.float64) * 2.0**-33 + lo.astype(np.float64) * lo_scale
-        out += comb * np.exp2((ea[:, None] + eb[None, :]).astype(np.float64))
+        es = ea[:, None] + eb[None, :]
+        nonfinite = es >= E_NONFINITE // 2
+        out += np.where(nonfinite, np.nan, comb * np.exp2(np.where(nonfinite, 0, es).astype(np.float64)))
         accs.append(D)
     return (out, accs) if return_accumulators else out
 

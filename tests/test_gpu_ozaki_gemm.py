@@ -35,6 +35,20 @@ def test_device_product_is_of_fp64_quality():
     np.testing.assert_array_equal(got, powerspec.gemm_nt_int8(A[None], B[None])[0])
 
 
+def test_non_finite_operands_give_nan_not_zero():
+    """A NaN / infinity in an operand must not be swallowed by the split (fmax skips NaNs, NaN -> int8 is 0): every output
+    that touches the row block is NaN; everything else is bit for bit the emulation's."""
+    rng = np.random.default_rng(12)
+    A, B = rng.standard_normal((128, 512)), rng.standard_normal((64, 512))
+    A[5, 300] = np.nan
+    B[7, 10] = np.inf
+    A[9, 0] = 2.0**990
+    A[11] = 2.0**-1000 * rng.standard_normal(512)
+    got = powerspec.gemm_nt_int8(A, B)
+    assert np.isnan(got[5]).all() and np.isnan(got[:, 7]).all() and np.isnan(got[9]).all()
+    np.testing.assert_array_equal(got, oe.gemm_nt(A, B))  # NaNs in the same places, the rest equal
+
+
 def test_bad_shapes_are_refused():
     with pytest.raises(ValueError):
         powerspec.gemm_nt_int8(np.zeros((100, 128)), np.zeros((64, 128)))

@@ -54,3 +54,26 @@ def test_exponent_blocks_follow_the_device_layout():
     assert oe.block_edges(128) == [(0, 128)]
     assert oe.block_edges(384) == [(0, 256), (256, 384)]
     assert oe.block_edges(1024) == [(0, 256), (256, 512), (512, 768), (768, 1024)]
+
+
+def test_non_finite_operands_stay_loud_and_tiny_blocks_count_as_zero():
+    """fmax() skips NaNs and a NaN converts to the int8 value 0: without the sentinel exponent a NaN would silently count as
+    zero.  A row block with a NaN / infinity / magnitude >= 2^960 makes every output that touches it NaN."""
+    rng = np.random.default_rng(11)
+    A, B = rng.standard_normal((128, 512)), rng.standard_normal((64, 512))
+    A[5, 300] = np.nan
+    B[7, 10] = np.inf
+    A[9, 0] = 2.0**990
+    A[11] = 2.0**-1000 * rng.standard_normal(512)
+    out = oe.gemm_nt(A, B)
+    assert np.isnan(out[5]).all() and np.isnan(out[:, 7]).all() and np.isnan(out[9]).all()
+    rest = np.ones(out.shape, dtype=bool)
+    rest[[5, 9]] = False
+    rest[:, 7] = False
+    assert np.isfinite(out[rest]).all() and not out[11][rest[11]].any()
+    clean = oe.gemm_nt(np.delete(A, [5, 9, 11], axis=0)[:128 - 3], np.delete(B, 7, axis=0))
+    np.testing.assert_array_equal(np.delete(np.delete(out, [5, 9, 11], axis=0), 7, axis=1), clean)
+    e, q = oe.split_block(A[:, :256], 8)
+    assert e[9] == oe.E_NONFINITE and not q[:, 9].any() and e[11] == 0 and not q[:, 11].any() and e[5] < 8
+    e, q = oe.split_block(A[:, 256:], 8)  # the NaN of row 5 sits in the second exponent block
+    assert e[5] == oe.E_NONFINITE and not q[:, 5].any() and e[9] < 8
