@@ -9,7 +9,8 @@ shard of the baseline axis (weak scaling; per-rank work fixed), followed by the 
 the baseline-group averages.  `value` has the inputs resident in HBM; `e2e` goes through the
 host-pointer C-ABI call (H2D + D2H inside the timed region).  Rank 0 prints ONE JSON line.
 
-The same line carries three more records (each skippable with --no-strong / --no-diag / --no-task):
+The same line carries three more records (each skippable with --no-strong / --no-diag / --no-task) and, at one GPU, the
+side record `extra.int8_gemm` of the int8 tensor-core GEMM behind the Wiener operator / NRML objective (--no-int8):
   strong    ONE step of BASELINE config 4 at FIXED total size: 4096 baselines x nsamp 200 divided over the ranks in
             contiguous blocks (dist.split_range, the reference's MPI layout delay.py:2297-2298), 64 groups of 64
             averaged with an NCCL all-reduce, spectra all-gathered; `result_checksum` must be identical at 1/2/4/8 GPUs.
@@ -52,6 +53,7 @@ def parse():
     ap.add_argument("--no-strong", action="store_true", help="skip the fixed-size cfg4 record")
     ap.add_argument("--no-diag", action="store_true", help="skip the cfg3 (diagonal branch) record")
     ap.add_argument("--no-task", action="store_true", help="skip the task-level end-to-end record")
+    ap.add_argument("--no-int8", action="store_true", help="skip the side record of the int8 tensor-core GEMM (1 GPU only)")
     ap.add_argument("--strong-nbase", type=int, default=None, help="override the TOTAL baselines of the strong record (debug)")
     ap.add_argument("--strong-nsamp", type=int, default=None)
     ap.add_argument("--diag-nbase", type=int, default=None, help="override the TOTAL pixels of the diag record (debug)")
@@ -443,6 +445,37 @@ def strong_record(args, handle, rank, world, local, sync):
     return out
 
 
+def int8_gemm_record(device=0, batch=37):
+    """The fp64-quality GEMM on the INT8 tensor cores (draco_b200/csrc/ozaki_gemm.cuh: Ozaki split, tcgen05.mma kind::i8, TMEM
+    accumulators) that the Wiener delay-transform operator and the NRML objective use for their contractions, through its C-ABI
+    entry point with HOST operands: `batch` x [512 x 1024 x 1024], the operator's A = T1 P^H shape at 512 channels.  The timed
+    region is the device time of split + GEMM reported by the library (CUDA events around its kernels); the copies are outside.
+    A side record: it never raises (an error is returned as text) and never touches the headline numbers."""
+    try:
+        from draco_b200 import powerspec
+
+        rng = np.random.default_rng(0)
+        M, N, K = 512, 1024, 1024
+        A, B = rng.standard_normal((batch, M, K)), rng.standard_normal((batch, N, K))
+        powerspec.gemm_nt_int8(A[:1], B[:1], device=device)  # library load, kernel attributes
+        best = None
+        for _ in range(2):
+            t = {}
+            C = powerspec.gemm_nt_int8(A, B, device=device, timing=t)
+            best = t["ms_device"] if best is None else min(best, t["ms_device"])
+        ref = A[0, :128] @ B[0, :64].T
+        bound = np.abs(A[0, :128]) @ np.abs(B[0, :64]).T
+        flop = 2.0 * M * N * K * batch
+        return {"what": "C[b] = A[b] B[b]^T, fp64 in / fp64 out, 8 signed 7-bit slices per row x 256 columns on tcgen05.mma kind::i8 "
+                        "(36 int8 GEMMs, int32 accumulators in TMEM); dgwiener_gemm_ozaki, split + GEMM device time",
+                "shape": [batch, M, N, K], "ms_device": best, "tflops_equivalent_incl_split": flop / best / 1e9,
+                "max_diff_vs_numpy_dgemm_over_absA_absB": float((np.abs(C[0, :128, :64] - ref) / bound).max()),
+                "reference_points": "GEMM alone 61.3 TFLOP/s-equivalent, cuBLAS DgemmStridedBatched 35.7, fp64 DMMA pipe 37.0 "
+                                    "(profiles/r04j_ozaki_gemm.log)"}
+    except Exception as exc:  # noqa: BLE001 -- a side record must not cost the bench line
+        return {"error": f"{type(exc).__name__}: {exc}"[:300]}
+
+
 def task_record(args, cfg, nsamp, nbase, rank, world, local, sync, handle):
     """Wall time of DelayPowerSpectrumGibbs.process() on a complex64 / float32 SiderealStream holding this rank's shard:
     device cut + pack + H2D + all chains + D2H ('wall time of _evaluate')."""
@@ -607,6 +640,9 @@ def main():
 
         extra["diag"] = bench_diag.diag_record(args, handle, rank, world, local, sync)
         torch.cuda.empty_cache()
+
+    if world == 1 and not args.no_int8 and fits("int8_gemm", 15.0):
+        extra["int8_gemm"] = int8_gemm_record(local)
 
     if rank == 0:
         ach = flop / (max(ms_sampler, 1e-9) / 1e3) / 1e12

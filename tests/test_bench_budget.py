@@ -27,3 +27,14 @@ def test_budget_flag_has_a_default_below_the_drivers_limit(monkeypatch):
     args = b.parse()
     assert 0 < args.budget_s <= 800.0
     assert args.steps >= 1 and args.warmup >= 3
+
+
+def test_int8_side_record_never_raises():
+    """Without a GPU the C-ABI call fails loudly; the side record must turn that into text, not into a lost bench line."""
+    import torch
+
+    b = _bench()
+    rec = b.int8_gemm_record(batch=1)
+    assert isinstance(rec, dict)
+    if not torch.cuda.is_available():
+        assert "error" in rec and "CUDA" in rec["error"]
