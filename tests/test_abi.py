@@ -109,6 +109,26 @@ def test_wiener_operator_entry_points():
                                             np.ones((1, 1, 4)), np.ones((1, 4)))
 
 
+def test_int8_gemm_wrapper_validates_shapes_before_the_device():
+    """powerspec.gemm_nt_int8 (dgwiener_gemm_ozaki): shape errors are Python errors; without a GPU the call itself fails loudly."""
+    import numpy as np
+    import torch
+
+    from draco_b200 import _lib, powerspec
+
+    with pytest.raises(ValueError):
+        powerspec.gemm_nt_int8(np.zeros((100, 128)), np.zeros((64, 128)))  # M % 128
+    with pytest.raises(ValueError):
+        powerspec.gemm_nt_int8(np.zeros((128, 128)), np.zeros((60, 128)))  # N % 64
+    with pytest.raises(ValueError):
+        powerspec.gemm_nt_int8(np.zeros((128, 192)), np.zeros((64, 192)))  # K % 128
+    with pytest.raises(ValueError):
+        powerspec.gemm_nt_int8(np.zeros((2, 128, 128)), np.zeros((3, 64, 128)))  # batch mismatch
+    if not torch.cuda.is_available():
+        with pytest.raises(_lib.DGibbsError):
+            powerspec.gemm_nt_int8(np.zeros((128, 128)), np.zeros((64, 128)))
+
+
 def test_window_ids_follow_the_header():
     """Window names of draco/util/tools.py:547-601 -> window_id of include/dgibbs.h, 'tukey-0.X' included."""
     from draco_b200 import _lib
