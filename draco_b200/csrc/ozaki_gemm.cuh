@@ -7,7 +7,7 @@
 // with the D_d exact in int32: S (S + 1) / 2 int8 GEMMs on tcgen05.mma.cta_group::1.kind::i8 (M = 128, N = 64, K = 32),
 // the S accumulators side by side in TMEM.  With S = 8 the result carries 55 bits below each block's row maximum: the
 // error against the exact product is BELOW that of an fp64 FMA chain (1.2e-15 vs 2.2e-15 of |A||B|^T on rows spanning 12
-// decades, profiles/r04f_ozaki_gemm.log; the accuracy study of the split: scratch/ozaki_study.py).
+// decades, profiles/r04j_ozaki_gemm.log; the accuracy study of the split: scratch/ozaki_study.py).
 //
 // Kernel (oz_gemm_kernel, 10 warps, one 128 x 64 output tile per CTA at a time, persistent grid):
 //   * the split kernel writes the slices of a (tile, 64-column K stage) as ONE contiguous block in the canonical
@@ -19,8 +19,10 @@
 //   * warps 0-7: epilogue per 256-column block: tcgen05.ld 32x32b, int64 combination of the diagonals, x 2^(e_i + f_j),
 //     fp64 accumulation in registers (two warps per TMEM lane quarter).  TMEM is full, so the epilogue of a block and the
 //     MMAs of the next do not overlap; the operands of the next block stream in underneath.
-// Measured on B200 (296 x [512 x 1024 x 1024], S = 8): 53.2 TFLOP/s-equivalent against 35.7 for cuBLAS
-// DgemmStridedBatched on the same operands and 32.7 for this repository's DMMA tile GEMM.
+// Measured on B200 (296 x [512 x 1024 x 1024], S = 8): 61.3 TFLOP/s-equivalent against 35.7 for cuBLAS
+// DgemmStridedBatched on the same operands and 32.7 for this repository's DMMA tile GEMM (profiles/r04j_ozaki_gemm.log;
+// ncu: IMMA sub-pipe 48.7 % active, profiles/r04m_oz_gemm_ncu_raw.csv).  Held bit for bit to oracle/ozaki_emulation.py
+// through dgwiener_gemm_ozaki (tests/test_gpu_ozaki_gemm.py).
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
